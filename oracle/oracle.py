@@ -1,0 +1,277 @@
+"""ctypes binding of the CPU ORACLE (oracle/libvolrt_oracle.so) and, when built,
+of the reference's own FastNoise2 (oracle/_ref/libvolrt_ref.so).
+
+TEST INFRASTRUCTURE ONLY — imported by tests/, __graft_entry__.smoke() and the
+cpu_baseline / --impl reference legs of bench.py; never by volumetricrenderer_b200.
+See oracle/volrt_oracle.h for what each function restates (reference file:line).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_ORACLE_SO = os.path.join(HERE, "libvolrt_oracle.so")
+_REF_SO = os.path.join(HERE, "_ref", "libvolrt_ref.so")
+
+VOL_RGBA8, VOL_R16F, VOL_R8, VOL_R32F = 0, 1, 2, 3
+DENSITY_RGBA_PRODUCT, DENSITY_SINGLE, DENSITY_FBM = 0, 1, 2
+OUT_RGBA8_UNORM, OUT_RGBA8_SRGB, OUT_RGBA16F = 0, 1, 2
+NOISE_CELLULAR, NOISE_PERLIN, NOISE_SIMPLEX = 0, 1, 2
+LEVEL_AUTO, LEVEL_SSE2, LEVEL_SSE41, LEVEL_AVX2, LEVEL_AVX512 = 0, 1, 2, 3, 4
+
+
+class VoVolume(C.Structure):
+    _fields_ = [("texels", C.c_void_p), ("w", C.c_int32), ("h", C.c_int32), ("d", C.c_int32),
+                ("format", C.c_int32)]
+
+
+class VoParams(C.Structure):
+    _fields_ = [
+        ("ubo0", C.c_float * 48), ("ubo1", C.c_float * 36),
+        ("max_steps", C.c_int32), ("step_scale", C.c_float), ("density", C.c_float),
+        ("sample_scale", C.c_float), ("coord_scale", C.c_float * 4), ("scroll_weight", C.c_float * 4),
+        ("density_mode", C.c_int32), ("light_steps", C.c_int32), ("light_step_len", C.c_float),
+        ("sun_dir", C.c_float * 3), ("sun_color", C.c_float * 3), ("ambient", C.c_float),
+        ("sigma_t", C.c_float), ("early_term_eps", C.c_float),
+        ("fbm_octaves", C.c_int32), ("fbm_seed", C.c_int32), ("fbm_frequency", C.c_float),
+        ("fbm_gain", C.c_float), ("fbm_lacunarity", C.c_float), ("fbm_coverage", C.c_float),
+        ("fbm_falloff0", C.c_float), ("fbm_falloff1", C.c_float),
+    ]
+
+
+def build(ref=True):
+    """Compile the oracle (always) and oracle/_ref (only where /root/reference exists)."""
+    subprocess.check_call(["make", "-s", "-C", HERE, "all"])
+    if ref and os.path.isdir("/root/reference/vendor/noise"):
+        subprocess.check_call(["make", "-s", "-C", HERE, "-j8", "ref"])
+
+
+_lib = None
+_ref = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_ORACLE_SO):
+            build(ref=False)
+        L = C.CDLL(_ORACLE_SO)
+        fp, ip, u8p = C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_uint8)
+        L.vo_scene_default.argtypes = [C.c_float, C.c_float, C.c_float, fp, fp]
+        L.vo_decode_ubo1.argtypes = [C.c_void_p, C.c_uint32, fp]
+        L.vo_params_default.argtypes = [C.POINTER(VoParams)]
+        L.vo_mat4_inverse.argtypes = [fp, fp]
+        L.vo_sample.argtypes = [C.POINTER(VoVolume), C.c_float, C.c_float, C.c_float, fp]
+        L.vo_render.argtypes = [C.POINTER(VoVolume), C.POINTER(VoParams), C.c_int, C.c_int, C.c_int, C.c_int,
+                                fp, ip, C.POINTER(C.c_uint64), C.c_int]
+        L.vo_render.restype = C.c_int
+        L.vo_encode.argtypes = [fp, C.c_int64, C.c_int, C.c_void_p]
+        L.vo_noise.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
+        L.vo_noise.restype = C.c_float
+        L.vo_fbm_perlin.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float]
+        L.vo_fbm_perlin.restype = C.c_float
+        L.vo_noise_grid.argtypes = [C.c_int, fp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, fp, C.c_int]
+        L.vo_pack_rgba8.argtypes = [fp, fp, fp, fp, fp, C.c_int64, u8p]
+        L.vo_bake_default.argtypes = [u8p, C.c_int, C.c_int]
+        L.vo_bake_smoke_r16f.argtypes = [C.POINTER(C.c_uint16), C.c_int, C.POINTER(VoParams), C.c_float, C.c_int]
+        L.vo_float_to_half.argtypes = [C.c_float]
+        L.vo_float_to_half.restype = C.c_uint16
+        L.vo_half_to_float.argtypes = [C.c_uint16]
+        L.vo_half_to_float.restype = C.c_float
+        L.vo_hw_threads.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def have_ref():
+    return os.path.exists(_REF_SO)
+
+
+def ref():
+    """The reference's FastNoise2 (oracle/_ref). Raises if it was never built."""
+    global _ref
+    if _ref is None:
+        if not have_ref():
+            raise RuntimeError("oracle/_ref/libvolrt_ref.so missing: run `make -C oracle ref` where /root/reference exists")
+        R = C.CDLL(_REF_SO)
+        fp = C.POINTER(C.c_float)
+        R.vref_max_level.restype = C.c_int
+        R.vref_grid.argtypes = [C.c_int, C.c_int, fp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, fp]
+        R.vref_points.argtypes = [C.c_int, C.c_int, fp, C.c_int, fp, fp, fp, C.c_int]
+        R.vref_fbm_points.argtypes = [C.c_int, fp, C.c_int, fp, fp, fp, C.c_int, C.c_int, C.c_float, C.c_float]
+        R.vref_bake_default.argtypes = [C.POINTER(C.c_uint8), C.c_int, C.c_int, fp]
+        _ref = R
+    return _ref
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+# ------------------------------------------------------------------ scene / params
+def scene_default(phi_deg=0.0, theta_deg=0.0, frame_time=0.0):
+    """-> (ubo0: 192 bytes, ubo1: the 140-byte C++ struct image) as numpy float32 arrays."""
+    u0 = np.zeros(48, np.float32)
+    u1 = np.zeros(35, np.float32)
+    lib().vo_scene_default(phi_deg, theta_deg, frame_time, _fp(u0), _fp(u1))
+    return u0, u1
+
+
+def decode_ubo1(raw_bytes):
+    out = np.zeros(36, np.float32)
+    buf = (C.c_char * len(raw_bytes)).from_buffer_copy(raw_bytes)
+    lib().vo_decode_ubo1(C.cast(buf, C.c_void_p), len(raw_bytes), _fp(out))
+    return out
+
+
+def params_default(**kw):
+    p = VoParams()
+    lib().vo_params_default(C.byref(p))
+    set_params(p, **kw)
+    return p
+
+
+def set_params(p, **kw):
+    for k, v in kw.items():
+        cur = getattr(p, k)
+        if hasattr(cur, "__len__"):
+            v = list(np.asarray(v, np.float32).ravel())
+            assert len(v) == len(cur), k
+            for i, x in enumerate(v):
+                cur[i] = float(x)
+        else:
+            setattr(p, k, v)
+    return p
+
+
+def set_scene(p, ubo0, ubo1_raw):
+    """ubo0: 48 floats; ubo1_raw: bytes/array as the host writes them (140 or 144 B)."""
+    u0 = np.asarray(ubo0, np.float32).ravel()
+    for i in range(48):
+        p.ubo0[i] = float(u0[i])
+    dec = decode_ubo1(np.asarray(ubo1_raw, np.float32).tobytes())
+    for i in range(36):
+        p.ubo1[i] = float(dec[i])
+    return p
+
+
+def mat4_inverse(m):
+    m = np.ascontiguousarray(m, np.float32).ravel()
+    out = np.zeros(16, np.float32)
+    lib().vo_mat4_inverse(_fp(m), _fp(out))
+    return out
+
+
+# ------------------------------------------------------------------ volume / render
+_FMT_DTYPE = {VOL_RGBA8: np.uint8, VOL_R16F: np.uint16, VOL_R8: np.uint8, VOL_R32F: np.float32}
+
+
+def make_volume(texels, fmt):
+    """texels: numpy array shaped (d,h,w[,4]); returns (VoVolume, keepalive)."""
+    t = np.ascontiguousarray(texels)
+    if fmt == VOL_R16F and t.dtype == np.float16:
+        t = t.view(np.uint16)
+    assert t.dtype == _FMT_DTYPE[fmt], (t.dtype, fmt)
+    d, h, w = t.shape[:3]
+    v = VoVolume(t.ctypes.data, w, h, d, fmt)
+    return v, t
+
+
+def sample(vol, u, v, w):
+    out = np.zeros(4, np.float32)
+    lib().vo_sample(C.byref(vol), u, v, w, _fp(out))
+    return out
+
+
+def render(vol, p, W, H, rows=None, threads=0, want_steps=False):
+    """-> (rgba float32 (rows,W,4), stats dict[, steps int32 (rows,W)])"""
+    r0, r1 = rows if rows is not None else (0, H)
+    out = np.zeros((r1 - r0, W, 4), np.float32)
+    steps = np.zeros((r1 - r0, W), np.int32) if want_steps else None
+    st = (C.c_uint64 * 4)()
+    rc = lib().vo_render(C.byref(vol) if vol is not None else None, C.byref(p), W, H, r0, r1, _fp(out),
+                         steps.ctypes.data_as(C.POINTER(C.c_int32)) if want_steps else None, st, threads)
+    if rc != 0:
+        raise ValueError("vo_render rc=%d" % rc)
+    stats = {"covered": int(st[0]), "steps": int(st[1]), "early": int(st[2]), "light_samples": int(st[3])}
+    return (out, stats, steps) if want_steps else (out, stats)
+
+
+def encode(rgba, fmt):
+    rgba = np.ascontiguousarray(rgba, np.float32)
+    n = rgba.size // 4
+    out = np.zeros(rgba.shape, np.uint16 if fmt == OUT_RGBA16F else np.uint8)
+    lib().vo_encode(_fp(rgba), n, fmt, out.ctypes.data)
+    return out
+
+
+# ------------------------------------------------------------------ noise
+def noise(gen, seed, x, y, z):
+    return float(lib().vo_noise(gen, seed, x, y, z))
+
+
+def noise_points(gen, seed, xs, ys, zs):
+    L = lib()
+    return np.array([L.vo_noise(gen, seed, float(a), float(b), float(c)) for a, b, c in zip(xs, ys, zs)], np.float32)
+
+
+def fbm_points(seed, xs, ys, zs, octaves=5, gain=0.5, lacunarity=2.0):
+    L = lib()
+    return np.array([L.vo_fbm_perlin(seed, float(a), float(b), float(c), octaves, gain, lacunarity)
+                     for a, b, c in zip(xs, ys, zs)], np.float32)
+
+
+def noise_grid(gen, n, freq, seed, threads=0):
+    nx, ny, nz = (n, n, n) if np.isscalar(n) else n
+    out = np.zeros((nz, ny, nx), np.float32)
+    mm = np.zeros(2, np.float32)
+    lib().vo_noise_grid(gen, _fp(out), nx, ny, nz, freq, seed, _fp(mm), threads)
+    return out, mm
+
+
+def bake_default(size=128, threads=0):
+    out = np.zeros((size, size, size, 4), np.uint8)
+    lib().vo_bake_default(out.ctypes.data_as(C.POINTER(C.c_uint8)), size, threads)
+    return out
+
+
+def bake_smoke_r16f(n, p, threshold=0.0, threads=0):
+    out = np.zeros((n, n, n), np.uint16)
+    lib().vo_bake_smoke_r16f(out.ctypes.data_as(C.POINTER(C.c_uint16)), n, C.byref(p), threshold, threads)
+    return out
+
+
+# ------------------------------------------------------------------ reference FastNoise2
+def ref_grid(gen, n, freq, seed, level=LEVEL_AUTO):
+    nx, ny, nz = (n, n, n) if np.isscalar(n) else n
+    out = np.zeros((nz, ny, nx), np.float32)
+    mm = np.zeros(2, np.float32)
+    if ref().vref_grid(gen, level, _fp(out), nx, ny, nz, freq, seed, _fp(mm)) != 0:
+        raise RuntimeError("FastNoise2 level %d unavailable on this CPU" % level)
+    return out, mm
+
+
+def ref_points(gen, seed, xs, ys, zs, level=LEVEL_AUTO):
+    xs, ys, zs = (np.ascontiguousarray(a, np.float32) for a in (xs, ys, zs))
+    out = np.zeros(len(xs), np.float32)
+    if ref().vref_points(gen, level, _fp(out), len(xs), _fp(xs), _fp(ys), _fp(zs), seed) != 0:
+        raise RuntimeError("FastNoise2 level %d unavailable on this CPU" % level)
+    return out
+
+
+def ref_fbm_points(seed, xs, ys, zs, octaves=5, gain=0.5, lacunarity=2.0, level=LEVEL_AUTO):
+    xs, ys, zs = (np.ascontiguousarray(a, np.float32) for a in (xs, ys, zs))
+    out = np.zeros(len(xs), np.float32)
+    if ref().vref_fbm_points(level, _fp(out), len(xs), _fp(xs), _fp(ys), _fp(zs), seed, octaves, gain, lacunarity) != 0:
+        raise RuntimeError("FastNoise2 level %d unavailable on this CPU" % level)
+    return out
+
+
+def ref_bake_default(size=128, level=LEVEL_AUTO):
+    out = np.zeros((size, size, size, 4), np.uint8)
+    mm = np.zeros(8, np.float32)
+    if ref().vref_bake_default(out.ctypes.data_as(C.POINTER(C.c_uint8)), size, level, _fp(mm)) != 0:
+        raise RuntimeError("FastNoise2 level %d unavailable on this CPU" % level)
+    return out, mm
