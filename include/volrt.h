@@ -1,0 +1,244 @@
+/*
+ * volrt.h — C ABI of libvolrt: the B200-native (sm_100a CUDA) drop-in for the one
+ * data-parallel hot path of Raspy-Py/VolumetricRenderer — the per-pixel volumetric
+ * ray-march of shaders/frag.glsl and the noise-volume bake that feeds it.
+ *
+ * The reference has no plugin / FFI layer: its hot path is reached through Vulkan
+ * object construction and three call sites in one main().  Every export below names
+ * the reference call site it replaces (paths relative to the reference root).
+ *
+ * Conventions
+ *   - extern "C", fixed-width types, plain pointers + sizes; no C++/torch types, no exceptions.
+ *   - every call returns vr_status; the message of the last failure is kept per context
+ *     (vr_last_error).  The reference's Error(...) macro throws and terminates
+ *     (source/Etna/Core/Utils.h:22-29) — that is deliberately not carried over.
+ *   - the library owns all device memory; the caller owns every pointer it passes and may free
+ *     it on return; out-handles are written only on VR_OK.
+ *   - no global state; a context is not internally locked (one thread at a time per context).
+ *   - every struct starts with struct_size (= sizeof the struct the caller compiled against).
+ *   - there is NO CPU fallback: without a CUDA device vr_create fails with VR_ERR_CUDA.
+ */
+#ifndef VOLRT_H
+#define VOLRT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VR_VERSION_MAJOR 0
+#define VR_VERSION_MINOR 1
+#define VR_MAX_DEVICES 8
+
+typedef struct vr_context vr_context;
+typedef int32_t vr_status;
+
+enum {
+    VR_OK = 0,
+    VR_ERR_INVALID_ARGUMENT = 1,
+    VR_ERR_CUDA = 2,
+    VR_ERR_OUT_OF_MEMORY = 3,
+    VR_ERR_UNSUPPORTED = 4,
+    VR_ERR_BAD_STATE = 5
+};
+
+/* colour-target encodings.  The reference renders into the swapchain format, which prefers
+ * R8G8B8A8_SRGB and otherwise takes the platform's first format
+ * (source/Etna/Core/Vulkan/VulkanSwapchain.cpp:181-191; target: VulkanRenderer.cpp:75-80). */
+typedef enum vr_output_format {
+    VR_OUT_RGBA8_UNORM = 0,
+    VR_OUT_RGBA8_SRGB = 1,
+    VR_OUT_RGBA16F = 2,
+    VR_OUT_RGBA32F = 3          /* raw shader output, for parity work */
+} vr_output_format;
+
+/* volume texel formats.  Reference: VK_FORMAT_R8G8B8A8_UNORM (VulkanTexture.cpp:116). */
+typedef enum vr_volume_format {
+    VR_VOL_RGBA8_UNORM = 0,
+    VR_VOL_R16F = 1,
+    VR_VOL_R8_UNORM = 2
+} vr_volume_format;
+
+/* sampler addressing.  Reference: MIRRORED_REPEAT on U,V,W (VulkanCore.cpp:683-685). */
+typedef enum vr_address_mode {
+    VR_ADDRESS_MIRRORED_REPEAT = 0,
+    VR_ADDRESS_CLAMP_TO_EDGE = 1
+} vr_address_mode;
+
+/* where the volume lives and who filters it */
+typedef enum vr_layout {
+    VR_LAYOUT_AUTO = 0,      /* TEXTURE */
+    VR_LAYOUT_TEXTURE = 1,   /* cudaArray + texture unit: hardware trilinear (fixed-point weights) */
+    VR_LAYOUT_LINEAR = 2,    /* x-fastest global memory, trilinear in FP32 in the kernel (bit-exact
+                                against the CPU oracle) */
+    VR_LAYOUT_BRICK = 3      /* R16F only: bricked global layout, bricks staged to shared memory by
+                                TMA (cp.async.bulk.tensor.3d), trilinear in FP32 */
+} vr_layout;
+
+typedef enum vr_density_mode {
+    VR_DENSITY_RGBA_PRODUCT = 0,   /* frag.glsl:66-71: (s1*s2)*(s3+s4)*scale, four fetches  */
+    VR_DENSITY_SINGLE = 1,         /* T(P).r * sample_scale, one fetch (smoke grids)        */
+    VR_DENSITY_FBM = 2             /* in-kernel FastNoise2-semantics fBm over Perlin        */
+} vr_density_mode;
+
+typedef enum vr_memory_kind {
+    VR_MEM_NONE = 0,     /* render into the context's own device frame only */
+    VR_MEM_HOST = 1,
+    VR_MEM_DEVICE = 2    /* device pointer on the context's device, or peer-mapped */
+} vr_memory_kind;
+
+enum {
+    VR_RENDER_ASYNC = 1u << 0,     /* return after enqueueing; complete with vr_wait            */
+    VR_RENDER_DIRECT = 1u << 1,    /* VR_MEM_DEVICE only: the march kernel stores its pixels straight
+                                      into dst (which may be another GPU's memory mapped through
+                                      NVLink peer access / CUDA IPC) instead of the context frame */
+    VR_RENDER_STATS = 1u << 2      /* count covered rays / steps on the device (slower variant) */
+};
+
+/* replaces renderer.Init() + AddRenderPass("BasePass", ...) + render-target creation:
+ * source/Etna/TestMain.cpp:121-122,156-166; Core/Vulkan/VulkanRenderer.cpp:17-118,232-256 */
+typedef struct vr_create_info {
+    uint32_t struct_size;
+    int32_t device;              /* CUDA ordinal of this context's GPU                       */
+    uint32_t width, height;      /* reference: 1280 x 720 (VulkanContext.cpp:24)             */
+    uint32_t format;             /* vr_output_format                                         */
+    uint32_t max_views;          /* frames held by the context (0 -> 1)                      */
+    uint32_t flags;
+} vr_create_info;
+
+/* replaces vkc::Texture3D texture(pixelData.data(), VkExtent3D(size,size,size)):
+ * TestMain.cpp:128; VulkanTexture.cpp:111-156; sampler VulkanCore.cpp:676-710 */
+typedef struct vr_volume_desc {
+    uint32_t struct_size;
+    uint32_t width, height, depth;
+    uint32_t format;             /* vr_volume_format  */
+    uint32_t address_mode;       /* vr_address_mode   */
+    uint32_t layout;             /* vr_layout         */
+} vr_volume_desc;
+
+/* one channel recipe of the bake, TestMain.cpp:59-62,75-80:
+ *   s = 1 - (field - min) / (max - min);  s <- s^power;  byte = (uint8)(s * 255)   (truncation)
+ * where {min,max} are those of the `norm_*` field — which in the reference is NOT always the
+ * stored field: the second cellular call overwrites buffer 1 and buffer 2 stays zero (quirk Q1). */
+#define VR_NOISE_CELLULAR_DISTANCE 0u
+#define VR_NOISE_PERLIN 1u
+#define VR_NOISE_SIMPLEX 2u
+#define VR_NOISE_ZERO 3u
+#define VR_NOISE_SAME 0xffffffffu
+typedef struct vr_noise_channel {
+    uint32_t generator;          /* VR_NOISE_*: the field whose values are packed             */
+    float frequency;
+    int32_t seed;
+    uint32_t norm_generator;     /* field whose min/max normalises; VR_NOISE_SAME = the above */
+    float norm_frequency;
+    int32_t norm_seed;
+    uint32_t power;              /* 1 or 4 in the reference                                   */
+} vr_noise_channel;
+
+/* replaces the start-up bake, TestMain.cpp:43-92 (FastNoise2 GenUniformGrid3D x4 + pack) */
+typedef struct vr_noise_desc {
+    uint32_t struct_size;
+    uint32_t size;               /* cube edge; reference 128                                  */
+    uint32_t format;             /* VR_VOL_RGBA8_UNORM: the 4 channel recipes below;
+                                    VR_VOL_R16F: the fBm smoke field rho(P) of vr_params.fbm_*
+                                    at voxel centres, minus `threshold`, clamped at 0          */
+    uint32_t layout;             /* vr_layout                                                 */
+    uint32_t address_mode;       /* vr_address_mode                                           */
+    float threshold;
+    vr_noise_channel channel[4];
+} vr_noise_desc;
+
+/* replaces objectUniformBuffer.Update(&osd, frame) / globalUniformBuffer.Update(&gsd, frame):
+ * TestMain.cpp:248-249; Core/Vulkan/VulkanUniformBuffer.h:58-61.  The UBO bytes are copied at
+ * call time and decoded with the std140 offsets the SHADER uses (frag.glsl:9-14, vert.glsl:4-9);
+ * bytes past *_size read as zero.  Handing over the reference's C++ structs verbatim (192 B and
+ * 140 B, TestMain.cpp:27-39) therefore reproduces its MediaScroll misalignment exactly. */
+typedef struct vr_params {
+    uint32_t struct_size;
+    uint32_t ubo0_size;          /* 192                                                        */
+    const void* ubo0;            /* ObjectShaderData: Model, View, Projection                  */
+    const void* ubo1;            /* GlobalShaderData: WorldToLocal, CameraPosition, MediaScroll */
+    uint32_t ubo1_size;          /* 140 (C++ sizeof) or 144 (std140)                           */
+    uint32_t max_steps;          /* frag.glsl:30   128                                         */
+    float step_scale;            /* frag.glsl:42   4                                           */
+    float density;               /* frag.glsl:29   1                                           */
+    float sample_scale;          /* frag.glsl:63   0.2                                         */
+    float coord_scale[4];        /* frag.glsl:66-69  1, .8, .75, .7                            */
+    float scroll_weight[4];      /* frag.glsl:66-69  0, .2, .25, .3                            */
+    /* ---- extensions beyond the reference; all zero = frag.glsl ---- */
+    uint32_t density_mode;       /* vr_density_mode                                            */
+    uint32_t light_steps;        /* sun light-march samples per primary step                   */
+    float light_step_len;        /* box units                                                  */
+    float sun_dir[3];            /* box space, unit length                                     */
+    float sun_color[3];
+    float ambient;
+    float sigma_t;               /* > 0: front-to-back compositing instead of optical depth    */
+    float early_term_eps;        /* > 0: stop a ray once transmittance < eps                   */
+    uint32_t skip_empty;         /* use the min-max brick grid to jump over empty space        */
+    int32_t fbm_octaves;         /* VR_DENSITY_FBM: FastNoise2 FractalFBm over Perlin          */
+    int32_t fbm_seed;
+    float fbm_frequency;
+    float fbm_gain;
+    float fbm_lacunarity;
+    float fbm_coverage;
+    float fbm_falloff0, fbm_falloff1;
+    /* multi-view batch: view k uses view_ubos + k*336 bytes = {ubo0[192], ubo1 std140[144]};
+     * view_count 0/1 with view_ubos NULL = the single view above */
+    uint32_t view_count;
+    const void* view_ubos;
+} vr_params;
+
+/* replaces EnqueueRenderPass + BeginFrame/EndFrame -> vkCmdDrawIndexed + submit:
+ * TestMain.cpp:194-217,251,255; VulkanRenderer.cpp:174-230 */
+typedef struct vr_target {
+    uint32_t struct_size;
+    uint32_t memory_kind;        /* vr_memory_kind                                             */
+    void* dst;                   /* view-major, row-major from row 0 of the FULL frame         */
+    size_t row_pitch;            /* bytes; 0 = tightly packed                                  */
+    uint32_t row_begin, row_end; /* band of rows to render (0,0 = all rows)                    */
+    uint32_t view_begin, view_end; /* views to render (0,0 = all)                              */
+    uint32_t flags;              /* VR_RENDER_*                                                */
+    void* stream;                /* cudaStream_t; NULL = the context's own stream              */
+} vr_target;
+
+typedef struct vr_stats {
+    uint32_t struct_size;
+    float gpu_ms;                /* device time of the last vr_render's kernels (CUDA events)  */
+    uint64_t rays;               /* pixels shaded or cleared                                   */
+    uint64_t covered;            /* VR_RENDER_STATS only from here on                          */
+    uint64_t steps;
+    uint64_t early_terminated;
+    uint64_t light_samples;
+    uint64_t skipped_steps;
+    uint32_t kernel_launches;    /* kernels launched by the last vr_render                     */
+} vr_stats;
+
+uint32_t vr_version(void);
+vr_status vr_params_default(vr_params* p);           /* reference literals, extensions off */
+vr_status vr_create(const vr_create_info* info, vr_context** out);
+void vr_destroy(vr_context* ctx);                    /* replaces renderer.Shutdown(), TestMain.cpp:260 */
+const char* vr_last_error(const vr_context* ctx);    /* ctx may be NULL: last vr_create failure */
+vr_status vr_upload_volume(vr_context* ctx, const vr_volume_desc* desc, const void* texels);
+vr_status vr_generate_volume(vr_context* ctx, const vr_noise_desc* desc, const vr_params* fbm);
+vr_status vr_download_volume(vr_context* ctx, void* texels, size_t bytes);  /* x-fastest copy back */
+vr_status vr_noise_desc_default(vr_noise_desc* d);   /* the reference's bake incl. quirk Q1 */
+vr_status vr_set_params(vr_context* ctx, const vr_params* p);
+vr_status vr_render(vr_context* ctx, const vr_target* target);
+vr_status vr_wait(vr_context* ctx);
+vr_status vr_get_stats(vr_context* ctx, vr_stats* out);
+/* the context's device frame (view 0, row 0) and its layout, for zero-copy consumers */
+vr_status vr_frame_info(vr_context* ctx, void** dev_ptr, size_t* row_pitch, size_t* view_stride);
+/* row bands of equal estimated cost for `parts` GPUs: bounds[parts+1] */
+vr_status vr_row_bands(vr_context* ctx, uint32_t parts, uint32_t* bounds);
+/* NVLink peer gather across processes: rank 0 exports its frame, the others map it and render
+ * their band with VR_RENDER_DIRECT into the mapped pointer. handle = 64 bytes (cudaIpcMemHandle_t) */
+vr_status vr_frame_export(vr_context* ctx, void* handle64);
+vr_status vr_frame_import(vr_context* ctx, const void* handle64, void** mapped);
+vr_status vr_frame_unmap(vr_context* ctx, void* mapped);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,448 @@
+// libvolrt march kernels for sm_100a.
+//
+// One thread per pixel; a warp owns an 8x4-pixel tile (rays of a warp stay within ~2 voxels of
+// each other, so their fetches share L1/TEX lines), a CTA of 4 warps owns 16x8 pixels.
+// What each piece computes, with the reference line it replaces:
+//   setup_ray      shaders/vert.glsl:17-22 + rasteriser coverage and
+//                  shaders/frag.glsl:36-54 (camera/fragment to box space, IntersectAABB :18-27,
+//                  step count :46, map to [0,1]^3 :49-54)
+//   density_*      frag.glsl:66-71 (four fetches, (s1*s2)*(s3+s4)*scale) and the extension modes
+//   march_kernel   frag.glsl:57-80 (step loop, Beer-Lambert) + A.6 compositing integrator
+//   store_pixel    colour-target conversion (VulkanRenderer.cpp:75-80, VulkanSwapchain.cpp:181-191)
+//
+// Numerics: the per-ray set-up is written with explicitly rounded intrinsics (__fmul_rn ...)
+// in the same operation order as the CPU oracle, because the step count n = int(|Pin-Pout|/step)
+// is discontinuous: one ulp in the set-up can add or drop a whole sample.  The LINEAR variants keep
+// that discipline through the whole loop and reproduce the oracle's binary32 values bit for bit;
+// the TEX variants use the texture unit's fixed-point trilinear weights and FMA contraction.
+#include "volrt_internal.h"
+#include <math_constants.h>
+
+namespace volrt {
+
+struct f3 { float x, y, z; };
+
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float dvd(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ f3 add3(f3 a, f3 b) { return {add(a.x, b.x), add(a.y, b.y), add(a.z, b.z)}; }
+__device__ __forceinline__ f3 sub3(f3 a, f3 b) { return {sub(a.x, b.x), sub(a.y, b.y), sub(a.z, b.z)}; }
+__device__ __forceinline__ f3 mul3(f3 a, float s) { return {mul(a.x, s), mul(a.y, s), mul(a.z, s)}; }
+__device__ __forceinline__ f3 div3(f3 a, float s) { return {dvd(a.x, s), dvd(a.y, s), dvd(a.z, s)}; }
+__device__ __forceinline__ f3 div33(f3 a, f3 b) { return {dvd(a.x, b.x), dvd(a.y, b.y), dvd(a.z, b.z)}; }
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return add(add(mul(a.x, b.x), mul(a.y, b.y)), mul(a.z, b.z)); }
+
+// column-major mat4 * (x,y,z,w): r_i = ((m0i*x + m1i*y) + m2i*z) + m3i*w, each op rounded
+__device__ __forceinline__ void mat_mul4(const float* __restrict__ m, float x, float y, float z, float w, float out[4]) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        out[i] = add(add(add(mul(m[i], x), mul(m[4 + i], y)), mul(m[8 + i], z)), mul(m[12 + i], w));
+}
+__device__ __forceinline__ f3 xform_point(const float* __restrict__ m, f3 p) {
+    float r[4]; mat_mul4(m, p.x, p.y, p.z, 1.0f, r); return {r[0], r[1], r[2]};
+}
+__device__ __forceinline__ f3 xform_dir(const float* __restrict__ m, f3 p) {
+    float r[4]; mat_mul4(m, p.x, p.y, p.z, 0.0f, r); return {r[0], r[1], r[2]};
+}
+
+// frag.glsl:18-27
+__device__ __forceinline__ void intersect_aabb(f3 o, f3 d, float& tNear, float& tFar) {
+    const f3 lo = {-1.0f, -1.0f, -1.0f}, hi = {1.0f, 1.0f, 1.0f};
+    f3 tMin = div33(sub3(lo, o), d), tMax = div33(sub3(hi, o), d);
+    f3 t1 = {fminf(tMin.x, tMax.x), fminf(tMin.y, tMax.y), fminf(tMin.z, tMax.z)};
+    f3 t2 = {fmaxf(tMin.x, tMax.x), fmaxf(tMin.y, tMax.y), fmaxf(tMin.z, tMax.z)};
+    tNear = fmaxf(fmaxf(t1.x, t1.y), t1.z);
+    tFar = fminf(fminf(t2.x, t2.y), t2.z);
+}
+
+struct Ray {
+    f3 pin;        // first sample, texture space [0,1]^3 (exactly on the entry face)
+    f3 step;       // stepVec / boxRange
+    int n;         // actualSteps
+};
+
+// returns false for pixels the rasteriser would not shade (they keep the clear colour)
+__device__ __forceinline__ bool setup_ray(const MarchParams& P, const ViewConst* __restrict__ V, int px, int py,
+                                          float step_size, Ray& r) {
+    // pixel centre -> NDC (viewport (0,0,W,H), TestMain.cpp:198-205)
+    float x = sub(mul(add((float)px, 0.5f), dvd(2.0f, (float)P.width)), 1.0f);
+    float y = sub(mul(add((float)py, 0.5f), dvd(2.0f, (float)P.height)), 1.0f);
+    float pn[4], pf[4];
+    mat_mul4(V->inv_pv, x, y, 0.0f, 1.0f, pn);      // near-plane point (depth 0..1 clip space)
+    mat_mul4(V->inv_pv, x, y, 1.0f, 1.0f, pf);
+    f3 o_w = div3({pn[0], pn[1], pn[2]}, pn[3]);
+    f3 f_w = div3({pf[0], pf[1], pf[2]}, pf[3]);
+    f3 d_w = sub3(f_w, o_w);
+    f3 o_c = xform_point(V->inv_model, o_w);
+    f3 d_c = xform_dir(V->inv_model, d_w);
+    float t0, tF;
+    intersect_aabb(o_c, d_c, t0, tF);
+    // front face visible, in front of the near plane and before the far plane
+    // (cull back, depth LESS: VulkanPipeline.cpp:107-108,130-132)
+    if (!(t0 <= tF && t0 >= 0.0f && t0 <= 1.0f)) return false;
+    f3 entry = add3(o_c, mul3(d_c, t0));
+    f3 fragPosition = xform_point(V->model, entry);                                   // vert.glsl:20
+    f3 cam = {V->cam[0], V->cam[1], V->cam[2]};
+    f3 camL = xform_point(V->w2l, cam);                                               // frag.glsl:36
+    f3 fragL = xform_point(V->w2l, fragPosition);                                     // :37
+    f3 v = sub3(fragL, camL);
+    float inv = dvd(1.0f, __fsqrt_rn(dot3(v, v)));
+    f3 dir = mul3(v, inv);                                                            // :38
+    float tNear, tFar;
+    intersect_aabb(camL, dir, tNear, tFar);                                           // :39
+    f3 Pin = add3(camL, mul3(dir, tNear));                                            // :43
+    f3 Pout = add3(camL, mul3(dir, tFar));                                            // :44
+    f3 stepVec = {mul(step_size, dir.x), mul(step_size, dir.y), mul(step_size, dir.z)};  // :45
+    f3 dd = sub3(Pin, Pout);
+    float q = dvd(__fsqrt_rn(dot3(dd, dd)), step_size);
+    int n = (q >= 0.0f) ? __float2int_rz(q) : 0;                                      // :46 int() truncates
+    r.n = min(P.max_steps, n);
+    r.pin = {mul(add(Pin.x, 1.0f), 0.5f), mul(add(Pin.y, 1.0f), 0.5f), mul(add(Pin.z, 1.0f), 0.5f)};  // :49-53
+    r.step = {mul(stepVec.x, 0.5f), mul(stepVec.y, 0.5f), mul(stepVec.z, 0.5f)};      // :54
+    return true;
+}
+
+// ------------------------------------------------------------------ colour target
+__device__ __forceinline__ float srgb_encode(float c) {
+    return c <= 0.0031308f ? 12.92f * c : 1.055f * powf(c, 1.0f / 2.4f) - 0.055f;
+}
+__device__ __forceinline__ void store_pixel(const MarchParams& P, int view, int px, int py, float r, float g, float b, float a) {
+    char* row = (char*)P.out + (size_t)view * P.view_stride + (size_t)py * P.row_pitch;
+    switch (P.out_format) {
+        case VR_OUT_RGBA8_UNORM:
+        case VR_OUT_RGBA8_SRGB: {
+            r = __saturatef(r); g = __saturatef(g); b = __saturatef(b); a = __saturatef(a);
+            if (P.out_format == VR_OUT_RGBA8_SRGB) { r = srgb_encode(r); g = srgb_encode(g); b = srgb_encode(b); }
+            uchar4 o;
+            o.x = (unsigned char)__float2int_rn(r * 255.0f); o.y = (unsigned char)__float2int_rn(g * 255.0f);
+            o.z = (unsigned char)__float2int_rn(b * 255.0f); o.w = (unsigned char)__float2int_rn(a * 255.0f);
+            ((uchar4*)row)[px] = o;
+            break;
+        }
+        case VR_OUT_RGBA16F: {
+            __half2 lo = __floats2half2_rn(r, g), hi = __floats2half2_rn(b, a);
+            uint2 o; o.x = *(unsigned int*)&lo; o.y = *(unsigned int*)&hi;
+            ((uint2*)row)[px] = o;
+            break;
+        }
+        default:
+            ((float4*)row)[px] = make_float4(r, g, b, a);
+    }
+}
+
+// ------------------------------------------------------------------ software sampler (LINEAR layout)
+// SURVEY.md A.4 / VulkanCore.cpp:676-710: texel centre convention u*N - 0.5, linear filter,
+// mirrored repeat.  Same operation order as the oracle => identical binary32 results.
+__device__ __forceinline__ int wrap_index(int i, int n, int address_mode) {
+    if ((unsigned)i < (unsigned)n) return i;
+    if (address_mode == VR_ADDRESS_CLAMP_TO_EDGE) return i < 0 ? 0 : n - 1;
+    int m = i % (2 * n);
+    if (m < 0) m += 2 * n;
+    return m < n ? m : 2 * n - 1 - m;
+}
+
+struct Taps {            // the 8 corner offsets and 3 fractions of one trilinear fetch
+    int i0, i1, j0, j1, k0, k1;
+    float fx, fy, fz;
+};
+__device__ __forceinline__ Taps make_taps(const MarchParams& P, f3 u) {
+    float x = sub(mul(u.x, (float)P.vw), 0.5f), y = sub(mul(u.y, (float)P.vh), 0.5f), z = sub(mul(u.z, (float)P.vd), 0.5f);
+    float x0 = floorf(x), y0 = floorf(y), z0 = floorf(z);
+    Taps t;
+    t.fx = sub(x, x0); t.fy = sub(y, y0); t.fz = sub(z, z0);
+    int i = (int)x0, j = (int)y0, k = (int)z0;
+    t.i0 = wrap_index(i, P.vw, P.address_mode); t.i1 = wrap_index(i + 1, P.vw, P.address_mode);
+    t.j0 = wrap_index(j, P.vh, P.address_mode); t.j1 = wrap_index(j + 1, P.vh, P.address_mode);
+    t.k0 = wrap_index(k, P.vd, P.address_mode); t.k1 = wrap_index(k + 1, P.vd, P.address_mode);
+    return t;
+}
+__device__ __forceinline__ float trilerp(const Taps& t, const float c[8]) {
+    float wx0 = sub(1.0f, t.fx), wy0 = sub(1.0f, t.fy), wz0 = sub(1.0f, t.fz);
+    float a = add(mul(add(mul(c[0], wx0), mul(c[1], t.fx)), wy0), mul(add(mul(c[2], wx0), mul(c[3], t.fx)), t.fy));
+    float b = add(mul(add(mul(c[4], wx0), mul(c[5], t.fx)), wy0), mul(add(mul(c[6], wx0), mul(c[7], t.fx)), t.fy));
+    return add(mul(a, wz0), mul(b, t.fz));
+}
+// channel CH of an RGBA8 volume; unorm[] = { i / 255.0f } staged in shared memory
+template <int CH>
+__device__ __forceinline__ float sample_rgba8_linear(const MarchParams& P, const float* __restrict__ unorm, f3 u) {
+    Taps t = make_taps(P, u);
+    const unsigned char* __restrict__ base = (const unsigned char*)P.lin + CH;
+    size_t r00 = ((size_t)t.k0 * P.vh + t.j0) * P.vw, r10 = ((size_t)t.k0 * P.vh + t.j1) * P.vw;
+    size_t r01 = ((size_t)t.k1 * P.vh + t.j0) * P.vw, r11 = ((size_t)t.k1 * P.vh + t.j1) * P.vw;
+    float c[8];
+    c[0] = unorm[__ldg(base + 4 * (r00 + t.i0))]; c[1] = unorm[__ldg(base + 4 * (r00 + t.i1))];
+    c[2] = unorm[__ldg(base + 4 * (r10 + t.i0))]; c[3] = unorm[__ldg(base + 4 * (r10 + t.i1))];
+    c[4] = unorm[__ldg(base + 4 * (r01 + t.i0))]; c[5] = unorm[__ldg(base + 4 * (r01 + t.i1))];
+    c[6] = unorm[__ldg(base + 4 * (r11 + t.i0))]; c[7] = unorm[__ldg(base + 4 * (r11 + t.i1))];
+    return trilerp(t, c);
+}
+__device__ __forceinline__ float sample_single_linear(const MarchParams& P, const float* __restrict__ unorm, f3 u) {
+    Taps t = make_taps(P, u);
+    size_t r00 = ((size_t)t.k0 * P.vh + t.j0) * P.vw, r10 = ((size_t)t.k0 * P.vh + t.j1) * P.vw;
+    size_t r01 = ((size_t)t.k1 * P.vh + t.j0) * P.vw, r11 = ((size_t)t.k1 * P.vh + t.j1) * P.vw;
+    size_t idx[8] = {r00 + t.i0, r00 + t.i1, r10 + t.i0, r10 + t.i1, r01 + t.i0, r01 + t.i1, r11 + t.i0, r11 + t.i1};
+    float c[8];
+    if (P.vol_format == VR_VOL_R16F) {
+        const __half* __restrict__ h = (const __half*)P.lin;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) c[q] = __half2float(__ldg(h + idx[q]));
+    } else {
+        const unsigned char* __restrict__ b = (const unsigned char*)P.lin;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) c[q] = unorm[__ldg(b + idx[q])];
+    }
+    return trilerp(t, c);
+}
+
+// ------------------------------------------------------------------ procedural density
+// FastNoise2 0.10.0 Perlin 3-D (vendor/noise/include/FastNoise/Generators/Perlin.inl:34-64) with
+// HashPrimes / GetGradientDot / InterpQuintic / Lerp of Utils.inl:229-247,294-340, and
+// FractalFBm (Fractal.inl:17-39).  FMAs are contracted here (FastNoise2's AVX2/AVX-512 levels do
+// the same); the oracle evaluates unfused like its SSE2 level — they agree to ~1e-6.
+__device__ __forceinline__ float grad_dot(int hash, float fx, float fy, float fz) {
+    int h13 = hash & 13;
+    float u = h13 < 8 ? fx : fy;
+    float v = h13 == 12 ? fx : fz;
+    v = h13 < 2 ? fy : v;
+    return __int_as_float(__float_as_int(u) ^ (hash << 31)) + __int_as_float(__float_as_int(v) ^ ((hash & 2) << 30));
+}
+__device__ __forceinline__ int hash3(int seed_xz, int xy) {   // (seed ^ x ^ y ^ z) * C; (h >> 15) ^ h
+    int h = (seed_xz ^ xy) * 0x27d4eb2d;
+    return (h >> 15) ^ h;
+}
+__device__ __forceinline__ float quintic(float t) { return t * t * t * fmaf(t, fmaf(t, 6.0f, -15.0f), 10.0f); }
+__device__ __forceinline__ float lerpf(float a, float b, float t) { return fmaf(t, b - a, a); }
+
+__device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
+    float xs = floorf(x), ys = floorf(y), zs = floorf(z);
+    int x0 = __float2int_rn(xs) * 501125321, y0 = __float2int_rn(ys) * 1136930381, z0 = __float2int_rn(zs) * 1720413743;
+    int x1 = x0 + 501125321, y1 = y0 + 1136930381, z1 = z0 + 1720413743;
+    float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
+    float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
+    xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
+    int sz0 = seed ^ z0, sz1 = seed ^ z1;
+    int xy00 = x0 ^ y0, xy10 = x1 ^ y0, xy01 = x0 ^ y1, xy11 = x1 ^ y1;
+    float a = lerpf(lerpf(grad_dot(hash3(sz0, xy00), xf0, yf0, zf0), grad_dot(hash3(sz0, xy10), xf1, yf0, zf0), xs),
+                    lerpf(grad_dot(hash3(sz0, xy01), xf0, yf1, zf0), grad_dot(hash3(sz0, xy11), xf1, yf1, zf0), xs), ys);
+    float b = lerpf(lerpf(grad_dot(hash3(sz1, xy00), xf0, yf0, zf1), grad_dot(hash3(sz1, xy10), xf1, yf0, zf1), xs),
+                    lerpf(grad_dot(hash3(sz1, xy01), xf0, yf1, zf1), grad_dot(hash3(sz1, xy11), xf1, yf1, zf1), xs), ys);
+    return 0.964921414852142333984375f * lerpf(a, b, zs);
+}
+
+__device__ __forceinline__ float fbm_perlin(const MarchParams& P, float x, float y, float z) {
+    int seed = P.fbm_seed;
+    float amp = P.fbm_bounding;
+    float sum = perlin3(seed, x, y, z) * amp;
+    for (int i = 1; i < P.fbm_octaves; ++i) {
+        seed += 1;
+        amp *= P.fbm_gain;
+        x *= P.fbm_lacunarity; y *= P.fbm_lacunarity; z *= P.fbm_lacunarity;
+        sum = fmaf(perlin3(seed, x, y, z), amp, sum);
+    }
+    return sum;
+}
+
+// rho = max(0, .5 fbm + .5 - coverage) * (1 - smoothstep(f0, f1, maxabs(P - 1/2)))
+__device__ __forceinline__ float density_fbm(const MarchParams& P, f3 u) {
+    float m = fmaxf(fmaxf(fabsf(u.x - 0.5f), fabsf(u.y - 0.5f)), fabsf(u.z - 0.5f));
+    float t = __saturatef((m - P.fbm_falloff0) / (P.fbm_falloff1 - P.fbm_falloff0));
+    float edge = 1.0f - t * t * (3.0f - 2.0f * t);
+    if (edge <= 0.0f) return 0.0f;
+    float f = fbm_perlin(P, u.x * P.fbm_frequency, u.y * P.fbm_frequency, u.z * P.fbm_frequency);
+    return fmaxf(0.0f, (0.5f * f + 0.5f) - P.fbm_coverage) * edge;
+}
+
+// ------------------------------------------------------------------ density functors
+struct RayConst {           // per-ray constants of frag.glsl:67-69: cX * scroll_weight, rounded once
+    f3 off1, off2, off3;
+};
+
+template <int VARIANT>
+__device__ __forceinline__ float density_at(const MarchParams& P, const RayConst& rc, const float* __restrict__ unorm, f3 p) {
+    if (VARIANT == MARCH_RGBA_TEX) {
+        // frag.glsl:66-71.  coord = Pin*scale_k + cK*weight_k
+        float s1 = tex3D<float4>(P.tex, p.x * P.coord_scale[0], p.y * P.coord_scale[0], p.z * P.coord_scale[0]).x;
+        float s2 = tex3D<float4>(P.tex, fmaf(p.x, P.coord_scale[1], rc.off1.x), fmaf(p.y, P.coord_scale[1], rc.off1.y), fmaf(p.z, P.coord_scale[1], rc.off1.z)).y;
+        float s3 = tex3D<float4>(P.tex, fmaf(p.x, P.coord_scale[2], rc.off2.x), fmaf(p.y, P.coord_scale[2], rc.off2.y), fmaf(p.z, P.coord_scale[2], rc.off2.z)).z;
+        float s4 = tex3D<float4>(P.tex, fmaf(p.x, P.coord_scale[3], rc.off3.x), fmaf(p.y, P.coord_scale[3], rc.off3.y), fmaf(p.z, P.coord_scale[3], rc.off3.z)).w;
+        return (s1 * s2) * (s3 + s4) * P.sample_scale;
+    } else if (VARIANT == MARCH_RGBA_LINEAR) {
+        f3 u1 = mul3(p, P.coord_scale[0]);
+        f3 u2 = add3(mul3(p, P.coord_scale[1]), rc.off1);
+        f3 u3 = add3(mul3(p, P.coord_scale[2]), rc.off2);
+        f3 u4 = add3(mul3(p, P.coord_scale[3]), rc.off3);
+        float s1 = sample_rgba8_linear<0>(P, unorm, u1);
+        float s2 = sample_rgba8_linear<1>(P, unorm, u2);
+        float s3 = sample_rgba8_linear<2>(P, unorm, u3);
+        float s4 = sample_rgba8_linear<3>(P, unorm, u4);
+        return mul(mul(mul(s1, s2), add(s3, s4)), P.sample_scale);
+    } else if (VARIANT == MARCH_SINGLE_TEX) {
+        return tex3D<float>(P.tex, p.x, p.y, p.z) * P.sample_scale;
+    } else if (VARIANT == MARCH_SINGLE_LINEAR) {
+        return mul(sample_single_linear(P, unorm, p), P.sample_scale);
+    } else {
+        return density_fbm(P, p);
+    }
+}
+
+__device__ __forceinline__ bool brick_occupied(const MarchParams& P, f3 p) {
+    const BrickInfo& B = P.bricks;
+    int bx = min(max((int)(p.x * B.inv_brick[0]), 0), B.bx - 1);
+    int by = min(max((int)(p.y * B.inv_brick[1]), 0), B.by - 1);
+    int bz = min(max((int)(p.z * B.inv_brick[2]), 0), B.bz - 1);
+    return __ldg(B.occupied + ((size_t)bz * B.by + by) * B.bx + bx) != 0;
+}
+__device__ __forceinline__ bool inside01(f3 p) {
+    return p.x >= 0.0f && p.x <= 1.0f && p.y >= 0.0f && p.y <= 1.0f && p.z >= 0.0f && p.z <= 1.0f;
+}
+
+// ------------------------------------------------------------------ the march
+template <int VARIANT, bool COMPOSITE, bool STATS>
+__global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ MarchParams P) {
+    constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
+    constexpr bool STRICT = LINEAR;                       // bit-for-bit with the oracle
+    constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
+    __shared__ float unorm[LINEAR ? 256 : 1];
+    if (LINEAR) {
+        for (int i = threadIdx.x; i < 256; i += 128) unorm[i] = dvd((float)i, 255.0f);
+        __syncthreads();
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int px = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int py = P.row_begin + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const int view = P.view_begin + blockIdx.z;
+    if (px >= P.width || py >= P.row_end) return;
+    const ViewConst* __restrict__ V = P.views + view;
+
+    const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);          // frag.glsl:42
+    Ray ray;
+    if (!setup_ray(P, V, px, py, step_size, ray)) {
+        store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);                          // VulkanRenderPass.cpp:17-19
+        return;
+    }
+    RayConst rc;
+    rc.off1 = {mul(V->scroll_y[0], P.scroll_weight[1]), mul(V->scroll_y[1], P.scroll_weight[1]), mul(V->scroll_y[2], P.scroll_weight[1])};
+    rc.off2 = {mul(V->scroll_z[0], P.scroll_weight[2]), mul(V->scroll_z[1], P.scroll_weight[2]), mul(V->scroll_z[2], P.scroll_weight[2])};
+    rc.off3 = {mul(V->scroll_w[0], P.scroll_weight[3]), mul(V->scroll_w[1], P.scroll_weight[3]), mul(V->scroll_w[2], P.scroll_weight[3])};
+
+    f3 p = ray.pin;
+    const int n = ray.n;
+    const bool skip = CAN_SKIP && P.skip_empty;
+    unsigned long long n_light = 0, n_skipped = 0;
+    bool early = false;
+    float cr, cg, cb;
+
+    if (!COMPOSITE) {
+        // reference integrator, frag.glsl:55-80
+        float acc = 0.0f;
+        const bool et = P.early_term_eps > 0.0f;
+        const float stop = et ? -logf(P.early_term_eps) : CUDART_INF_F;
+        for (int i = 0; i < n; ++i) {
+            if (skip && !brick_occupied(P, p)) { if (STATS) ++n_skipped; p = add3(p, ray.step); continue; }
+            float d = density_at<VARIANT>(P, rc, unorm, p);
+            acc = STRICT ? add(acc, d) : acc + d;
+            p = add3(p, ray.step);                                                     // running add, :74
+            if (et && mul(mul(acc, step_size), P.density) > stop) { early = true; break; }
+        }
+        acc = mul(acc, step_size);                                                     // :76
+        float c = sub(1.0f, expf(mul(P.density, fminf(-acc, 0.0f))));                  // :79
+        cr = cg = cb = c;
+    } else {
+        // front-to-back compositing with a sun light-march
+        float T = 1.0f;
+        cr = cg = cb = 0.0f;
+        const f3 lv = {P.sun_dir[0] * P.light_step_len * 0.5f, P.sun_dir[1] * P.light_step_len * 0.5f, P.sun_dir[2] * P.light_step_len * 0.5f};
+        for (int i = 0; i < n; ++i) {
+            float rho = 0.0f;
+            if (skip && !brick_occupied(P, p)) { if (STATS) ++n_skipped; }
+            else rho = density_at<VARIANT>(P, rc, unorm, p);
+            if (rho > 0.0f) {                       // rho == 0 contributes exactly nothing
+                float a = 1.0f - expf(-P.sigma_t * rho * step_size);
+                float S = 1.0f;
+                if (P.light_steps > 0) {
+                    float sumL = 0.0f;
+                    f3 pl = p;
+                    for (int j = 1; j <= P.light_steps; ++j) {
+                        pl = {pl.x + lv.x, pl.y + lv.y, pl.z + lv.z};
+                        if (!inside01(pl)) break;   // the march leaves the box for good (box is convex)
+                        if (skip && !brick_occupied(P, pl)) continue;
+                        sumL += density_at<VARIANT>(P, rc, unorm, pl);
+                        if (STATS) ++n_light;
+                    }
+                    S = expf(-P.sigma_t * sumL * P.light_step_len);
+                }
+                float w = T * a;
+                cr = fmaf(w, fmaf(P.sun_color[0], S, P.ambient), cr);
+                cg = fmaf(w, fmaf(P.sun_color[1], S, P.ambient), cg);
+                cb = fmaf(w, fmaf(P.sun_color[2], S, P.ambient), cb);
+                T *= 1.0f - a;
+            }
+            p = add3(p, ray.step);
+            if (P.early_term_eps > 0.0f && T < P.early_term_eps) { early = true; break; }
+        }
+    }
+    store_pixel(P, view, px, py, cr, cg, cb, 1.0f);                                    // :80
+    if (STATS) {
+        atomicAdd(&P.counters[0], 1ull);
+        atomicAdd(&P.counters[1], (unsigned long long)n);
+        if (early) atomicAdd(&P.counters[2], 1ull);
+        if (n_light) atomicAdd(&P.counters[3], n_light);
+        if (n_skipped) atomicAdd(&P.counters[4], n_skipped);
+    }
+}
+
+// per-row sum of step counts (the cost model for row bands)
+__global__ void __launch_bounds__(256) row_cost_kernel(const __grid_constant__ MarchParams P, int view, float* __restrict__ row_cost) {
+    const int py = blockIdx.x;
+    const ViewConst* __restrict__ V = P.views + view;
+    const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);
+    float s = 0.0f;
+    for (int px = threadIdx.x; px < P.width; px += blockDim.x) {
+        Ray r;
+        if (setup_ray(P, V, px, py, step_size, r)) s += (float)r.n + 2.0f;   // +2: set-up and store
+    }
+    __shared__ float red[8];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        row_cost[py] = t + 0.05f * (float)P.width;     // uncovered pixels are cheap, not free
+    }
+}
+
+template <int VARIANT>
+static cudaError_t launch_v(const MarchParams& p, dim3 grid, bool composite, bool stats, cudaStream_t s) {
+    if (composite) {
+        if (stats) march_kernel<VARIANT, true, true><<<grid, 128, 0, s>>>(p);
+        else march_kernel<VARIANT, true, false><<<grid, 128, 0, s>>>(p);
+    } else {
+        if (stats) march_kernel<VARIANT, false, true><<<grid, 128, 0, s>>>(p);
+        else march_kernel<VARIANT, false, false><<<grid, 128, 0, s>>>(p);
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_march(const MarchParams& p, int variant, int n_views, bool stats, cudaStream_t stream) {
+    int rows = p.row_end - p.row_begin;
+    if (rows <= 0 || n_views <= 0) return cudaSuccess;
+    dim3 grid((p.width + 15) / 16, (rows + 7) / 8, n_views);
+    bool composite = p.sigma_t > 0.0f;
+    switch (variant) {
+        case MARCH_RGBA_TEX: return launch_v<MARCH_RGBA_TEX>(p, grid, composite, stats, stream);
+        case MARCH_RGBA_LINEAR: return launch_v<MARCH_RGBA_LINEAR>(p, grid, composite, stats, stream);
+        case MARCH_SINGLE_TEX: return launch_v<MARCH_SINGLE_TEX>(p, grid, composite, stats, stream);
+        case MARCH_SINGLE_LINEAR: return launch_v<MARCH_SINGLE_LINEAR>(p, grid, composite, stats, stream);
+        case MARCH_FBM: return launch_v<MARCH_FBM>(p, grid, composite, stats, stream);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_row_cost(const MarchParams& p, int view, float* row_cost, cudaStream_t stream) {
+    row_cost_kernel<<<p.height, 256, 0, stream>>>(p, view, row_cost);
+    return cudaGetLastError();
+}
+
+}  // namespace volrt

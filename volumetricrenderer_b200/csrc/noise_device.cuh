@@ -1,0 +1,138 @@
+// Device-side coherent noise with FastNoise2 0.10.0 semantics (the library the reference bakes
+// its volume with, vendor/noise @ 787b8c8a).  Paths: vendor/noise/include/FastNoise/Generators/.
+//   perlin3    Perlin.inl:34-64
+//   simplex3   Simplex.inl:56-125
+//   cellular3  Cellular.inl:307-366 with the CellularDistance defaults (Cellular.h:16-17,88-90:
+//              jitter 1, EuclideanSquared, Index0)
+//   hash / gradient / fade / lerp   Utils.inl:229-247,294-340
+//   fbm        Fractal.inl:17-39, bounding Fractal.h:27-38
+// FMAs are contracted and 1/sqrt is rsqrtf (FastNoise2's own levels use rsqrtps / rsqrt14ps / a
+// bit hack and are compiled -ffast-math), so like FastNoise2's ISA levels among themselves the
+// results agree to ~1e-5, i.e. <= 1 LSB of the packed texel.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace volrt {
+
+constexpr int kPrimeX = 501125321, kPrimeY = 1136930381, kPrimeZ = 1720413743;   // Utils.inl:9-11
+
+struct FbmField {
+    int octaves, seed;
+    float frequency, gain, lacunarity, coverage, falloff0, falloff1, bounding, threshold;
+};
+
+__device__ __forceinline__ float grad_dot(int hash, float fx, float fy, float fz) {
+    int h13 = hash & 13;
+    float u = h13 < 8 ? fx : fy;
+    float v = h13 == 12 ? fx : fz;
+    v = h13 < 2 ? fy : v;
+    return __int_as_float(__float_as_int(u) ^ (hash << 31)) + __int_as_float(__float_as_int(v) ^ ((hash & 2) << 30));
+}
+__device__ __forceinline__ int hash3(int seed_xz, int xy) {   // (seed ^ x ^ y ^ z) * C; (h >> 15) ^ h
+    int h = (seed_xz ^ xy) * 0x27d4eb2d;
+    return (h >> 15) ^ h;
+}
+__device__ __forceinline__ float quintic(float t) { return t * t * t * fmaf(t, fmaf(t, 6.0f, -15.0f), 10.0f); }
+__device__ __forceinline__ float lerpf(float a, float b, float t) { return fmaf(t, b - a, a); }
+
+__device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
+    float xs = floorf(x), ys = floorf(y), zs = floorf(z);
+    int x0 = __float2int_rn(xs) * kPrimeX, y0 = __float2int_rn(ys) * kPrimeY, z0 = __float2int_rn(zs) * kPrimeZ;
+    int x1 = x0 + kPrimeX, y1 = y0 + kPrimeY, z1 = z0 + kPrimeZ;
+    float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
+    float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
+    xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
+    int sz0 = seed ^ z0, sz1 = seed ^ z1;
+    int xy00 = x0 ^ y0, xy10 = x1 ^ y0, xy01 = x0 ^ y1, xy11 = x1 ^ y1;
+    float a = lerpf(lerpf(grad_dot(hash3(sz0, xy00), xf0, yf0, zf0), grad_dot(hash3(sz0, xy10), xf1, yf0, zf0), xs),
+                    lerpf(grad_dot(hash3(sz0, xy01), xf0, yf1, zf0), grad_dot(hash3(sz0, xy11), xf1, yf1, zf0), xs), ys);
+    float b = lerpf(lerpf(grad_dot(hash3(sz1, xy00), xf0, yf0, zf1), grad_dot(hash3(sz1, xy10), xf1, yf0, zf1), xs),
+                    lerpf(grad_dot(hash3(sz1, xy01), xf0, yf1, zf1), grad_dot(hash3(sz1, xy11), xf1, yf1, zf1), xs), ys);
+    return 0.964921414852142333984375f * lerpf(a, b, zs);
+}
+
+__device__ __forceinline__ float simplex3(int seed, float x, float y, float z) {
+    const float F3 = 1.0f / 3.0f, G3 = 1.0f / 2.0f;
+    float s = F3 * (x + y + z);
+    x += s; y += s; z += s;
+    float x0 = floorf(x), y0 = floorf(y), z0 = floorf(z);
+    float xi = x - x0, yi = y - y0, zi = z - z0;
+    int i = __float2int_rn(x0) * kPrimeX, j = __float2int_rn(y0) * kPrimeY, k = __float2int_rn(z0) * kPrimeZ;
+    bool x_ge_y = xi >= yi, y_ge_z = yi >= zi, x_ge_z = xi >= zi;
+    float g = G3 * (xi + yi + zi);
+    x0 = xi - g; y0 = yi - g; z0 = zi - g;
+    bool i1 = x_ge_y && x_ge_z, j1 = y_ge_z && !x_ge_y, k1 = !x_ge_z && !y_ge_z;
+    bool i2 = x_ge_y || x_ge_z, j2 = !x_ge_y || y_ge_z, k2 = x_ge_z && y_ge_z;   // k2 is used N-masked
+    float x1 = (i1 ? x0 - 1.0f : x0) + G3, y1 = (j1 ? y0 - 1.0f : y0) + G3, z1 = (k1 ? z0 - 1.0f : z0) + G3;
+    float x2 = (i2 ? x0 - 1.0f : x0) + G3 * 2, y2 = (j2 ? y0 - 1.0f : y0) + G3 * 2, z2 = (k2 ? z0 : z0 - 1.0f) + G3 * 2;
+    float x3 = x0 + (G3 * 3 - 1), y3 = y0 + (G3 * 3 - 1), z3 = z0 + (G3 * 3 - 1);
+    auto falloff = [](float a, float b, float c) {
+        float t = fmaf(-a, a, fmaf(-b, b, fmaf(-c, c, 0.6f)));
+        t = fmaxf(t, 0.0f);
+        t *= t;
+        return t * t;
+    };
+    float t0 = falloff(x0, y0, z0), t1 = falloff(x1, y1, z1), t2 = falloff(x2, y2, z2), t3 = falloff(x3, y3, z3);
+    float n0 = grad_dot(hash3(seed ^ k, i ^ j), x0, y0, z0);
+    float n1 = grad_dot(hash3(seed ^ (k1 ? k + kPrimeZ : k), (i1 ? i + kPrimeX : i) ^ (j1 ? j + kPrimeY : j)), x1, y1, z1);
+    float n2 = grad_dot(hash3(seed ^ (k2 ? k : k + kPrimeZ), (i2 ? i + kPrimeX : i) ^ (j2 ? j + kPrimeY : j)), x2, y2, z2);
+    float n3 = grad_dot(hash3(seed ^ (k + kPrimeZ), (i + kPrimeX) ^ (j + kPrimeY)), x3, y3, z3);
+    return 32.69428253173828125f * fmaf(n0, t0, fmaf(n1, t1, fmaf(n2, t2, n3 * t3)));
+}
+
+__device__ __forceinline__ float cellular3(int seed, float x, float y, float z) {
+    const float jitter = 0.396144f;                   // kJitter3D * jitter modifier 1
+    float best = CUDART_INF_F;                        // Index0 of the sorted distances = the minimum
+    int xc = __float2int_rn(x) - 1, ycBase = __float2int_rn(y) - 1, zcBase = __float2int_rn(z) - 1;
+    float xcf = (float)xc - x, ycfBase = (float)ycBase - y, zcfBase = (float)zcBase - z;
+    xc *= kPrimeX; ycBase *= kPrimeY; zcBase *= kPrimeZ;
+#pragma unroll
+    for (int xi = 0; xi < 3; ++xi) {
+        float ycf = ycfBase; int yc = ycBase;
+#pragma unroll
+        for (int yi = 0; yi < 3; ++yi) {
+            float zcf = zcfBase; int zc = zcBase;
+            int sxy = seed ^ xc ^ yc;
+#pragma unroll
+            for (int zi = 0; zi < 3; ++zi) {
+                int hash = (sxy ^ zc) * 0x27d4eb2d;   // HashPrimesHB, Utils.inl:304-312
+                float xd = (float)(hash & 0x3ff) - 511.5f;
+                float yd = (float)((hash >> 10) & 0x3ff) - 511.5f;
+                float zd = (float)((hash >> 20) & 0x3ff) - 511.5f;
+                float invMag = jitter * rsqrtf(fmaf(xd, xd, fmaf(yd, yd, zd * zd)));
+                xd = fmaf(xd, invMag, xcf); yd = fmaf(yd, invMag, ycf); zd = fmaf(zd, invMag, zcf);
+                float nd = fmaf(zd, zd, fmaf(yd, yd, xd * xd));
+                best = fminf(best, nd);
+                zcf += 1.0f; zc += kPrimeZ;
+            }
+            ycf += 1.0f; yc += kPrimeY;
+        }
+        xcf += 1.0f; xc += kPrimeX;
+    }
+    return best;
+}
+
+__device__ __forceinline__ float fbm_perlin(const FbmField& F, float x, float y, float z) {
+    int seed = F.seed;
+    float amp = F.bounding;
+    float sum = perlin3(seed, x, y, z) * amp;
+    for (int i = 1; i < F.octaves; ++i) {
+        seed += 1;
+        amp *= F.gain;
+        x *= F.lacunarity; y *= F.lacunarity; z *= F.lacunarity;
+        sum = fmaf(perlin3(seed, x, y, z), amp, sum);
+    }
+    return sum;
+}
+
+// rho = max(0, .5 fbm + .5 - coverage) * (1 - smoothstep(f0, f1, maxabs(P - 1/2)))
+__device__ __forceinline__ float density_fbm(const FbmField& F, float ux, float uy, float uz) {
+    float m = fmaxf(fmaxf(fabsf(ux - 0.5f), fabsf(uy - 0.5f)), fabsf(uz - 0.5f));
+    float t = __saturatef((m - F.falloff0) / (F.falloff1 - F.falloff0));
+    float edge = 1.0f - t * t * (3.0f - 2.0f * t);
+    if (edge <= 0.0f) return 0.0f;
+    float f = fbm_perlin(F, ux * F.frequency, uy * F.frequency, uz * F.frequency);
+    return fmaxf(0.0f, (0.5f * f + 0.5f) - F.coverage) * edge;
+}
+
+}  // namespace volrt

@@ -1,0 +1,646 @@
+// libvolrt: the C ABI of include/volrt.h over the sm_100a kernels.  Host-side only logic here:
+// context + resource ownership, UBO decoding (std140), volume upload into a cudaArray / linear
+// buffer, launch configuration, row-band cost model, CUDA-IPC export of the frame for the
+// NVLink peer gather.  There is no CPU rendering path in this library.
+#include "volrt_internal.h"
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace volrt;
+
+struct vr_context {
+    int device = 0;
+    uint32_t width = 0, height = 0, format = 0, max_views = 1;
+    size_t px_bytes = 4, row_pitch = 0, view_stride = 0;
+    void* frame = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    // volume
+    bool has_volume = false;
+    vr_volume_desc vdesc{};
+    void* lin = nullptr;            // x-fastest copy (all layouts: source of the array, occupancy, download)
+    size_t lin_bytes = 0;
+    cudaArray_t array = nullptr;
+    cudaTextureObject_t tex = 0;
+    uint8_t* occupied = nullptr;
+    BrickInfo bricks{};
+    // params
+    bool has_params = false;
+    vr_params params{};
+    ViewConst* d_views = nullptr;
+    ViewConst* h_views = nullptr;   // pinned staging
+    uint32_t view_count = 1, view_capacity = 0;
+    unsigned long long* d_counters = nullptr;
+    unsigned long long* h_counters = nullptr;   // pinned
+    float* d_row_cost = nullptr;
+    vr_stats stats{};
+    std::string err;
+};
+
+static thread_local std::string g_create_error;
+
+static vr_status fail(vr_context* ctx, vr_status st, const char* what, cudaError_t e = cudaSuccess) {
+    std::string m = what;
+    if (e != cudaSuccess) { m += ": "; m += cudaGetErrorName(e); m += " — "; m += cudaGetErrorString(e); }
+    if (ctx) ctx->err = m; else g_create_error = m;
+    return st;
+}
+#define VR_CUDA(ctx, call)                                                                        \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, #call, e_); \
+    } while (0)
+
+static size_t out_px_bytes(uint32_t fmt) {
+    switch (fmt) {
+        case VR_OUT_RGBA8_UNORM: case VR_OUT_RGBA8_SRGB: return 4;
+        case VR_OUT_RGBA16F: return 8;
+        case VR_OUT_RGBA32F: return 16;
+    }
+    return 0;
+}
+static size_t texel_bytes(uint32_t fmt) {
+    switch (fmt) {
+        case VR_VOL_RGBA8_UNORM: return 4;
+        case VR_VOL_R16F: return 2;
+        case VR_VOL_R8_UNORM: return 1;
+    }
+    return 0;
+}
+
+extern "C" uint32_t vr_version(void) { return (VR_VERSION_MAJOR << 16) | VR_VERSION_MINOR; }
+
+extern "C" const char* vr_last_error(const vr_context* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+extern "C" vr_status vr_params_default(vr_params* p) {
+    if (!p) return VR_ERR_INVALID_ARGUMENT;
+    std::memset(p, 0, sizeof *p);
+    p->struct_size = sizeof *p;
+    p->ubo0_size = 192;
+    p->ubo1_size = 140;
+    p->max_steps = 128;            // frag.glsl:30
+    p->step_scale = 4.0f;          // frag.glsl:42
+    p->density = 1.0f;             // frag.glsl:29
+    p->sample_scale = 0.2f;        // frag.glsl:63
+    const float cs[4] = {1.0f, 0.8f, 0.75f, 0.7f}, sw[4] = {0.0f, 0.2f, 0.25f, 0.3f};   // frag.glsl:66-69
+    for (int i = 0; i < 4; ++i) { p->coord_scale[i] = cs[i]; p->scroll_weight[i] = sw[i]; }
+    p->sun_dir[2] = 1.0f;
+    p->sun_color[0] = p->sun_color[1] = p->sun_color[2] = 1.0f;
+    p->fbm_octaves = 5; p->fbm_seed = 1337; p->fbm_frequency = 128.0f * 0.03f;
+    p->fbm_gain = 0.5f; p->fbm_lacunarity = 2.0f; p->fbm_coverage = 0.45f;
+    p->fbm_falloff0 = 0.35f; p->fbm_falloff1 = 0.5f;
+    p->view_count = 1;
+    return VR_OK;
+}
+
+extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
+    if (!info || !out || info->struct_size < sizeof(vr_create_info))
+        return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: null argument or struct_size too small");
+    if (info->width == 0 || info->height == 0 || info->width > 32768 || info->height > 32768)
+        return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: width/height out of range");
+    if (out_px_bytes(info->format) == 0) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: unknown output format");
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, VR_ERR_CUDA, "vr_create: no CUDA device (libvolrt has no CPU path)", e);
+    if (info->device < 0 || info->device >= ndev) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: device ordinal out of range");
+    VR_CUDA(nullptr, cudaSetDevice(info->device));
+    vr_context* c = new (std::nothrow) vr_context();
+    if (!c) return fail(nullptr, VR_ERR_OUT_OF_MEMORY, "vr_create: host allocation failed");
+    c->device = info->device;
+    c->width = info->width; c->height = info->height; c->format = info->format;
+    c->max_views = info->max_views ? info->max_views : 1;
+    c->px_bytes = out_px_bytes(info->format);
+    c->row_pitch = c->px_bytes * c->width;
+    c->view_stride = c->row_pitch * c->height;
+    c->stats.struct_size = sizeof(vr_stats);
+    auto bail = [&](const char* what, cudaError_t ce) {
+        vr_status st = fail(nullptr, ce == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, what, ce);
+        vr_destroy(c);
+        return st;
+    };
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
+    if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaMalloc(&c->frame, c->view_stride * c->max_views)) != cudaSuccess) return bail("cudaMalloc(frame)", e);
+    c->view_capacity = c->max_views;
+    if ((e = cudaMalloc(&c->d_views, sizeof(ViewConst) * c->view_capacity)) != cudaSuccess) return bail("cudaMalloc(views)", e);
+    if ((e = cudaMallocHost(&c->h_views, sizeof(ViewConst) * c->view_capacity)) != cudaSuccess) return bail("cudaMallocHost(views)", e);
+    if ((e = cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc(counters)", e);
+    if ((e = cudaMallocHost(&c->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMallocHost(counters)", e);
+    if ((e = cudaMalloc(&c->d_row_cost, sizeof(float) * c->height)) != cudaSuccess) return bail("cudaMalloc(row_cost)", e);
+    *out = c;
+    return VR_OK;
+}
+
+static void release_volume(vr_context* c) {
+    if (c->tex) { cudaDestroyTextureObject(c->tex); c->tex = 0; }
+    if (c->array) { cudaFreeArray(c->array); c->array = nullptr; }
+    if (c->lin) { cudaFree(c->lin); c->lin = nullptr; }
+    if (c->occupied) { cudaFree(c->occupied); c->occupied = nullptr; }
+    c->lin_bytes = 0;
+    c->has_volume = false;
+}
+
+extern "C" void vr_destroy(vr_context* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    release_volume(c);
+    if (c->frame) cudaFree(c->frame);
+    if (c->d_views) cudaFree(c->d_views);
+    if (c->h_views) cudaFreeHost(c->h_views);
+    if (c->d_counters) cudaFree(c->d_counters);
+    if (c->h_counters) cudaFreeHost(c->h_counters);
+    if (c->d_row_cost) cudaFree(c->d_row_cost);
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+// build the texture object (TEXTURE layout) and the occupancy grid from c->lin
+static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
+    const uint32_t layout = d.layout == VR_LAYOUT_AUTO ? (uint32_t)VR_LAYOUT_TEXTURE : d.layout;
+    if (layout == VR_LAYOUT_TEXTURE) {
+        cudaChannelFormatDesc cd;
+        switch (d.format) {
+            case VR_VOL_RGBA8_UNORM: cd = cudaCreateChannelDesc<uchar4>(); break;
+            case VR_VOL_R16F: cd = cudaCreateChannelDescHalf(); break;
+            default: cd = cudaCreateChannelDesc<unsigned char>(); break;
+        }
+        cudaExtent ext = make_cudaExtent(d.width, d.height, d.depth);
+        VR_CUDA(c, cudaMalloc3DArray(&c->array, &cd, ext));
+        cudaMemcpy3DParms cp = {};
+        cp.srcPtr = make_cudaPitchedPtr(c->lin, d.width * texel_bytes(d.format), d.width, d.height);
+        cp.dstArray = c->array;
+        cp.extent = ext;
+        cp.kind = cudaMemcpyDeviceToDevice;
+        VR_CUDA(c, cudaMemcpy3DAsync(&cp, c->stream));
+        cudaResourceDesc rd = {};
+        rd.resType = cudaResourceTypeArray;
+        rd.res.array.array = c->array;
+        cudaTextureDesc td = {};
+        // VulkanCore.cpp:680-694: LINEAR mag/min, MIRRORED_REPEAT x3, normalised coordinates, one mip
+        cudaTextureAddressMode am = d.address_mode == VR_ADDRESS_CLAMP_TO_EDGE ? cudaAddressModeClamp : cudaAddressModeMirror;
+        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = am;
+        td.filterMode = cudaFilterModeLinear;
+        td.readMode = d.format == VR_VOL_R16F ? cudaReadModeElementType : cudaReadModeNormalizedFloat;
+        td.normalizedCoords = 1;
+        VR_CUDA(c, cudaCreateTextureObject(&c->tex, &rd, &td, nullptr));
+    }
+    // min-max bricks (8^3 voxels + 1-texel apron) for empty-space skipping
+    BrickInfo& B = c->bricks;
+    B.bx = (d.width + 7) / 8; B.by = (d.height + 7) / 8; B.bz = (d.depth + 7) / 8;
+    B.inv_brick[0] = (float)d.width / 8.0f; B.inv_brick[1] = (float)d.height / 8.0f; B.inv_brick[2] = (float)d.depth / 8.0f;
+    VR_CUDA(c, cudaMalloc(&c->occupied, (size_t)B.bx * B.by * B.bz));
+    B.occupied = c->occupied;
+    VR_CUDA(c, launch_occupancy(c->lin, d.format, d.width, d.height, d.depth, d.address_mode, c->occupied, B.bx, B.by, B.bz, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->vdesc = d;
+    c->vdesc.layout = layout;
+    c->has_volume = true;
+    return VR_OK;
+}
+
+static vr_status check_volume_desc(vr_context* c, const vr_volume_desc* d) {
+    if (!d || d->struct_size < sizeof(vr_volume_desc)) return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: null or struct_size too small");
+    if (d->width == 0 || d->height == 0 || d->depth == 0 || d->width > 4096 || d->height > 4096 || d->depth > 4096)
+        return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: dimensions must be in 1..4096");
+    if (texel_bytes(d->format) == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: unknown format");
+    if (d->address_mode > VR_ADDRESS_CLAMP_TO_EDGE) return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: unknown address mode");
+    if (d->layout > VR_LAYOUT_BRICK) return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: unknown layout");
+    if (d->layout == VR_LAYOUT_BRICK) return fail(c, VR_ERR_UNSUPPORTED, "volume desc: VR_LAYOUT_BRICK (TMA brick path) is not built yet");
+    return VR_OK;
+}
+
+extern "C" vr_status vr_upload_volume(vr_context* c, const vr_volume_desc* d, const void* texels) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!texels) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_upload_volume: texels is null");
+    vr_status st = check_volume_desc(c, d);
+    if (st != VR_OK) return st;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    release_volume(c);
+    c->lin_bytes = (size_t)d->width * d->height * d->depth * texel_bytes(d->format);
+    VR_CUDA(c, cudaMalloc(&c->lin, c->lin_bytes));
+    // synchronous like the reference's staging copy + vkQueueWaitIdle (VulkanCore.cpp:529-541)
+    VR_CUDA(c, cudaMemcpyAsync(c->lin, texels, c->lin_bytes, cudaMemcpyHostToDevice, c->stream));
+    st = finish_volume(c, *d);
+    if (st != VR_OK) release_volume(c);
+    return st;
+}
+
+extern "C" vr_status vr_download_volume(vr_context* c, void* texels, size_t bytes) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_download_volume: no volume");
+    if (!texels || bytes < c->lin_bytes) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_download_volume: buffer too small");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaMemcpyAsync(texels, c->lin, c->lin_bytes, cudaMemcpyDeviceToHost, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VR_OK;
+}
+
+// ------------------------------------------------------------------ volume bake on the device
+extern "C" vr_status vr_noise_desc_default(vr_noise_desc* d) {
+    if (!d) return VR_ERR_INVALID_ARGUMENT;
+    std::memset(d, 0, sizeof *d);
+    d->struct_size = sizeof *d;
+    d->size = 128;                                   // TestMain.cpp:51
+    d->format = VR_VOL_RGBA8_UNORM;
+    d->layout = VR_LAYOUT_TEXTURE;
+    d->address_mode = VR_ADDRESS_MIRRORED_REPEAT;
+    // TestMain.cpp:59-62 with quirk Q1: buffer 1 ends up holding the (0.03, seed 2) cellular field
+    // but is normalised with the (0.01, seed 1) field's range; buffer 2 is never written (zeros)
+    // and is normalised with the (0.03, seed 2) range.
+    d->channel[0] = {VR_NOISE_CELLULAR_DISTANCE, 0.03f, 2, VR_NOISE_CELLULAR_DISTANCE, 0.01f, 1, 4};   // :80 s1^4
+    d->channel[1] = {VR_NOISE_ZERO, 0.0f, 0, VR_NOISE_CELLULAR_DISTANCE, 0.03f, 2, 1};
+    d->channel[2] = {VR_NOISE_PERLIN, 0.19f, 3, VR_NOISE_SAME, 0.0f, 0, 1};
+    d->channel[3] = {VR_NOISE_SIMPLEX, 0.15f, 4, VR_NOISE_SAME, 0.0f, 0, 1};
+    return VR_OK;
+}
+
+static float fbm_bounding(int octaves, float gain) {    // Fractal.h:27-38
+    float g = std::fabs(gain), amp = g, sum = 1.0f;
+    for (int i = 1; i < octaves; ++i) { sum += amp; amp *= g; }
+    return 1.0f / sum;
+}
+
+extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, const vr_params* fbm) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!d || d->struct_size < sizeof(vr_noise_desc)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: null desc or struct_size too small");
+    vr_volume_desc vd = {sizeof(vr_volume_desc), d->size, d->size, d->size, d->format, d->address_mode, d->layout};
+    vr_status st = check_volume_desc(c, &vd);
+    if (st != VR_OK) return st;
+    if (d->format == VR_VOL_R8_UNORM) return fail(c, VR_ERR_UNSUPPORTED, "vr_generate_volume: RGBA8 (channel recipes) or R16F (fBm smoke) only");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    release_volume(c);
+    const int n = (int)d->size;
+    const size_t vox = (size_t)n * n * n;
+    c->lin_bytes = vox * texel_bytes(d->format);
+    VR_CUDA(c, cudaMalloc(&c->lin, c->lin_bytes));
+    if (d->format == VR_VOL_R16F) {
+        vr_params def;
+        vr_params_default(&def);
+        const vr_params* f = fbm ? fbm : &def;
+        if (f->fbm_octaves < 1 || f->fbm_octaves > 16) { release_volume(c); return fail(c, VR_ERR_INVALID_ARGUMENT, "fbm_octaves must be in 1..16"); }
+        FbmField ff = {f->fbm_octaves, f->fbm_seed, f->fbm_frequency, f->fbm_gain, f->fbm_lacunarity, f->fbm_coverage,
+                       f->fbm_falloff0, f->fbm_falloff1, fbm_bounding(f->fbm_octaves, f->fbm_gain), d->threshold};
+        VR_CUDA(c, launch_smoke_fill(ff, n, (__half*)c->lin, c->stream));
+    } else {
+        // each distinct field is generated once; min/max folded on the device
+        struct Gen { NoiseField f; float* buf; unsigned int* mm; bool keep; };
+        std::vector<Gen> gens;
+        auto find = [&](uint32_t g, float fr, int32_t s) -> int {
+            for (size_t i = 0; i < gens.size(); ++i)
+                if (gens[i].f.generator == g && gens[i].f.frequency == fr && gens[i].f.seed == s) return (int)i;
+            return -1;
+        };
+        int field_of[4], norm_of[4];
+        for (int k = 0; k < 4; ++k) {
+            const vr_noise_channel& ch = d->channel[k];
+            if (ch.generator > VR_NOISE_ZERO || (ch.norm_generator > VR_NOISE_ZERO && ch.norm_generator != VR_NOISE_SAME) || ch.power < 1 || ch.power > 8) {
+                release_volume(c);
+                return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: bad channel recipe");
+            }
+            field_of[k] = -1;
+            if (ch.generator != VR_NOISE_ZERO) {
+                field_of[k] = find(ch.generator, ch.frequency, ch.seed);
+                if (field_of[k] < 0) { gens.push_back({{ch.generator, ch.frequency, ch.seed}, nullptr, nullptr, true}); field_of[k] = (int)gens.size() - 1; }
+                gens[field_of[k]].keep = true;
+            }
+            if (ch.norm_generator == VR_NOISE_SAME) norm_of[k] = field_of[k];
+            else if (ch.norm_generator == VR_NOISE_ZERO) norm_of[k] = -1;
+            else {
+                norm_of[k] = find(ch.norm_generator, ch.norm_frequency, ch.norm_seed);
+                if (norm_of[k] < 0) { gens.push_back({{ch.norm_generator, ch.norm_frequency, ch.norm_seed}, nullptr, nullptr, false}); norm_of[k] = (int)gens.size() - 1; }
+            }
+            if (norm_of[k] < 0) { release_volume(c); return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: a channel needs a non-zero field to normalise with"); }
+        }
+        unsigned int* d_mm = nullptr;
+        std::vector<unsigned int> h_mm(gens.size() * 2);
+        for (size_t i = 0; i < gens.size(); ++i) minmax_init(&h_mm[i * 2]);
+        auto cleanup = [&]() { for (auto& g : gens) if (g.buf) cudaFree(g.buf); if (d_mm) cudaFree(d_mm); };
+        cudaError_t e = cudaMalloc(&d_mm, h_mm.size() * sizeof(unsigned int));
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_mm, h_mm.data(), h_mm.size() * sizeof(unsigned int), cudaMemcpyHostToDevice, c->stream);
+        for (size_t i = 0; i < gens.size() && e == cudaSuccess; ++i) {
+            gens[i].mm = d_mm + i * 2;
+            if (gens[i].keep) {
+                e = cudaMalloc(&gens[i].buf, vox * sizeof(float));
+                if (e == cudaSuccess) e = launch_noise_fill(gens[i].f, n, gens[i].buf, gens[i].mm, c->stream);
+            } else {
+                e = launch_noise_minmax_only(gens[i].f, n, gens[i].mm, c->stream);
+            }
+        }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h_mm.data(), d_mm, h_mm.size() * sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e == cudaSuccess) {
+            PackChannel pc[4];
+            for (int k = 0; k < 4; ++k) {
+                pc[k].field = field_of[k] >= 0 ? gens[field_of[k]].buf : nullptr;
+                pc[k].mn = minmax_decode(h_mm[norm_of[k] * 2]);
+                pc[k].mx = minmax_decode(h_mm[norm_of[k] * 2 + 1]);
+                pc[k].power = d->channel[k].power;
+            }
+            e = launch_noise_pack(pc, (int64_t)vox, (uint8_t*)c->lin, c->stream);
+        }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        cleanup();
+        if (e != cudaSuccess) { release_volume(c); return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, "vr_generate_volume", e); }
+    }
+    st = finish_volume(c, vd);
+    if (st != VR_OK) release_volume(c);
+    return st;
+}
+
+// ------------------------------------------------------------------ params
+static void mat_mul_d(const float* a, const float* b, double* out) {      // out = a*b, column-major
+    for (int col = 0; col < 4; ++col)
+        for (int r = 0; r < 4; ++r) {
+            double s = 0.0;
+            for (int k = 0; k < 4; ++k) s += (double)a[k * 4 + r] * (double)b[col * 4 + k];
+            out[col * 4 + r] = s;
+        }
+}
+static bool inverse_d(const double* m, double* inv) {                      // cofactor expansion in double
+    double c[16];
+    c[0] = m[5] * (m[10] * m[15] - m[11] * m[14]) - m[9] * (m[6] * m[15] - m[7] * m[14]) + m[13] * (m[6] * m[11] - m[7] * m[10]);
+    c[1] = -(m[1] * (m[10] * m[15] - m[11] * m[14]) - m[9] * (m[2] * m[15] - m[3] * m[14]) + m[13] * (m[2] * m[11] - m[3] * m[10]));
+    c[2] = m[1] * (m[6] * m[15] - m[7] * m[14]) - m[5] * (m[2] * m[15] - m[3] * m[14]) + m[13] * (m[2] * m[7] - m[3] * m[6]);
+    c[3] = -(m[1] * (m[6] * m[11] - m[7] * m[10]) - m[5] * (m[2] * m[11] - m[3] * m[10]) + m[9] * (m[2] * m[7] - m[3] * m[6]));
+    c[4] = -(m[4] * (m[10] * m[15] - m[11] * m[14]) - m[8] * (m[6] * m[15] - m[7] * m[14]) + m[12] * (m[6] * m[11] - m[7] * m[10]));
+    c[5] = m[0] * (m[10] * m[15] - m[11] * m[14]) - m[8] * (m[2] * m[15] - m[3] * m[14]) + m[12] * (m[2] * m[11] - m[3] * m[10]);
+    c[6] = -(m[0] * (m[6] * m[15] - m[7] * m[14]) - m[4] * (m[2] * m[15] - m[3] * m[14]) + m[12] * (m[2] * m[7] - m[3] * m[6]));
+    c[7] = m[0] * (m[6] * m[11] - m[7] * m[10]) - m[4] * (m[2] * m[11] - m[3] * m[10]) + m[8] * (m[2] * m[7] - m[3] * m[6]);
+    c[8] = m[4] * (m[9] * m[15] - m[11] * m[13]) - m[8] * (m[5] * m[15] - m[7] * m[13]) + m[12] * (m[5] * m[11] - m[7] * m[9]);
+    c[9] = -(m[0] * (m[9] * m[15] - m[11] * m[13]) - m[8] * (m[1] * m[15] - m[3] * m[13]) + m[12] * (m[1] * m[11] - m[3] * m[9]));
+    c[10] = m[0] * (m[5] * m[15] - m[7] * m[13]) - m[4] * (m[1] * m[15] - m[3] * m[13]) + m[12] * (m[1] * m[7] - m[3] * m[5]);
+    c[11] = -(m[0] * (m[5] * m[11] - m[7] * m[9]) - m[4] * (m[1] * m[11] - m[3] * m[9]) + m[8] * (m[1] * m[7] - m[3] * m[5]));
+    c[12] = -(m[4] * (m[9] * m[14] - m[10] * m[13]) - m[8] * (m[5] * m[14] - m[6] * m[13]) + m[12] * (m[5] * m[10] - m[6] * m[9]));
+    c[13] = m[0] * (m[9] * m[14] - m[10] * m[13]) - m[8] * (m[1] * m[14] - m[2] * m[13]) + m[12] * (m[1] * m[10] - m[2] * m[9]);
+    c[14] = -(m[0] * (m[5] * m[14] - m[6] * m[13]) - m[4] * (m[1] * m[14] - m[2] * m[13]) + m[12] * (m[1] * m[6] - m[2] * m[5]));
+    c[15] = m[0] * (m[5] * m[10] - m[6] * m[9]) - m[4] * (m[1] * m[10] - m[2] * m[9]) + m[8] * (m[1] * m[6] - m[2] * m[5]);
+    double det = m[0] * c[0] + m[4] * c[1] + m[8] * c[2] + m[12] * c[3];
+    if (det == 0.0 || !(det == det)) return false;
+    double r = 1.0 / det;
+    for (int i = 0; i < 16; ++i) inv[i] = c[i] * r;
+    return true;
+}
+
+// ubo0: ObjectShaderData (vert.glsl:4-9), ubo1: GlobalShaderData as std140 reads it (frag.glsl:9-14)
+static bool decode_view(const unsigned char* ubo0, uint32_t n0, const unsigned char* ubo1, uint32_t n1, ViewConst* v) {
+    float u0[48], u1[36];
+    std::memset(u0, 0, sizeof u0); std::memset(u1, 0, sizeof u1);
+    std::memcpy(u0, ubo0, n0 < 192u ? n0 : 192u);      // bytes past the descriptor range read as zero
+    std::memcpy(u1, ubo1, n1 < 144u ? n1 : 144u);
+    const float *Model = u0, *View = u0 + 16, *Proj = u0 + 32;
+    double pv[16], pvi[16], md[16], mi[16];
+    mat_mul_d(Proj, View, pv);
+    for (int i = 0; i < 16; ++i) md[i] = Model[i];
+    if (!inverse_d(pv, pvi) || !inverse_d(md, mi)) return false;
+    for (int i = 0; i < 16; ++i) {
+        v->inv_pv[i] = (float)pvi[i]; v->inv_model[i] = (float)mi[i];
+        v->model[i] = Model[i]; v->w2l[i] = u1[i];
+    }
+    for (int i = 0; i < 3; ++i) v->cam[i] = u1[16 + i];
+    const float* MS = u1 + 20;                          // std140: MediaScroll at byte 80
+    for (int col = 0; col < 3; ++col) {
+        v->scroll_y[col] = MS[col * 4 + 1];             // (MS[0].y, MS[1].y, MS[2].y)  frag.glsl:67
+        v->scroll_z[col] = MS[col * 4 + 2];
+        v->scroll_w[col] = MS[col * 4 + 3];
+    }
+    return true;
+}
+
+extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!p || p->struct_size < sizeof(vr_params)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: null or struct_size too small");
+    if (p->max_steps == 0 || p->max_steps > (1u << 20)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: max_steps out of range");
+    if (!(p->step_scale > 0.0f)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: step_scale must be > 0");
+    if (p->density_mode > VR_DENSITY_FBM) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: unknown density_mode");
+    if (p->density_mode == VR_DENSITY_FBM && (p->fbm_octaves < 1 || p->fbm_octaves > 16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: fbm_octaves must be in 1..16");
+    if (p->light_steps > 0 && !(p->sigma_t > 0.0f)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: light_steps needs sigma_t > 0 (compositing mode)");
+    if (p->light_steps > 1024) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: light_steps out of range");
+    uint32_t views = p->view_count ? p->view_count : 1;
+    if (views > c->max_views) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: view_count exceeds vr_create_info.max_views");
+    if (views > 1 && !p->view_ubos) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: view_count > 1 needs view_ubos");
+    if (!p->view_ubos && (!p->ubo0 || !p->ubo1)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: ubo0/ubo1 are null");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    // the pinned staging block may still be in flight from the previous frame
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    for (uint32_t k = 0; k < views; ++k) {
+        bool ok;
+        if (p->view_ubos) {
+            const unsigned char* b = (const unsigned char*)p->view_ubos + (size_t)k * 336;
+            ok = decode_view(b, 192, b + 192, 144, &c->h_views[k]);
+        } else {
+            ok = decode_view((const unsigned char*)p->ubo0, p->ubo0_size, (const unsigned char*)p->ubo1, p->ubo1_size, &c->h_views[k]);
+        }
+        if (!ok) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: Model or Projection*View is singular");
+    }
+    VR_CUDA(c, cudaMemcpyAsync(c->d_views, c->h_views, sizeof(ViewConst) * views, cudaMemcpyHostToDevice, c->stream));
+    c->params = *p;
+    c->params.ubo0 = c->params.ubo1 = c->params.view_ubos = nullptr;   // bytes were copied; do not keep caller pointers
+    c->view_count = views;
+    c->has_params = true;
+    return VR_OK;
+}
+
+// ------------------------------------------------------------------ render
+static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) {
+    const vr_params& p = c->params;
+    std::memset(&m, 0, sizeof m);
+    m.width = (int)c->width; m.height = (int)c->height;
+    m.row_begin = 0; m.row_end = (int)c->height;
+    m.out = c->frame; m.row_pitch = c->row_pitch; m.view_stride = c->view_stride;
+    m.out_format = (int)c->format;
+    m.views = c->d_views;
+    m.max_steps = (int)p.max_steps;
+    m.step_scale = p.step_scale; m.density = p.density; m.sample_scale = p.sample_scale;
+    for (int i = 0; i < 4; ++i) { m.coord_scale[i] = p.coord_scale[i]; m.scroll_weight[i] = p.scroll_weight[i]; }
+    m.light_steps = (int)p.light_steps; m.light_step_len = p.light_step_len;
+    for (int i = 0; i < 3; ++i) { m.sun_dir[i] = p.sun_dir[i]; m.sun_color[i] = p.sun_color[i]; }
+    m.ambient = p.ambient; m.sigma_t = p.sigma_t; m.early_term_eps = p.early_term_eps;
+    m.fbm_octaves = p.fbm_octaves; m.fbm_seed = p.fbm_seed; m.fbm_frequency = p.fbm_frequency;
+    m.fbm_gain = p.fbm_gain; m.fbm_lacunarity = p.fbm_lacunarity; m.fbm_coverage = p.fbm_coverage;
+    m.fbm_falloff0 = p.fbm_falloff0; m.fbm_falloff1 = p.fbm_falloff1;
+    m.fbm_bounding = fbm_bounding(p.fbm_octaves, p.fbm_gain);
+    m.counters = c->d_counters;
+    if (p.density_mode == VR_DENSITY_FBM) { variant = MARCH_FBM; return VR_OK; }
+    if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_render: no volume uploaded (vr_upload_volume / vr_generate_volume)");
+    const vr_volume_desc& d = c->vdesc;
+    m.tex = c->tex; m.lin = c->lin;
+    m.vw = (int)d.width; m.vh = (int)d.height; m.vd = (int)d.depth;
+    m.vol_format = (int)d.format; m.address_mode = (int)d.address_mode;
+    m.bricks = c->bricks;
+    m.skip_empty = p.skip_empty ? 1 : 0;
+    const bool tex = d.layout == VR_LAYOUT_TEXTURE;
+    if (p.density_mode == VR_DENSITY_RGBA_PRODUCT) {
+        if (d.format != VR_VOL_RGBA8_UNORM) return fail(c, VR_ERR_BAD_STATE, "vr_render: VR_DENSITY_RGBA_PRODUCT needs an RGBA8 volume");
+        variant = tex ? MARCH_RGBA_TEX : MARCH_RGBA_LINEAR;
+    } else {
+        if (d.format == VR_VOL_RGBA8_UNORM) return fail(c, VR_ERR_BAD_STATE, "vr_render: VR_DENSITY_SINGLE needs a one-channel volume (R16F / R8)");
+        variant = tex ? MARCH_SINGLE_TEX : MARCH_SINGLE_LINEAR;
+    }
+    return VR_OK;
+}
+
+extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!c->has_params) return fail(c, VR_ERR_BAD_STATE, "vr_render: vr_set_params has not been called");
+    vr_target def = {};
+    def.struct_size = sizeof(vr_target);
+    if (!t) t = &def;
+    if (t->struct_size < sizeof(vr_target)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: target struct_size too small");
+    if (t->memory_kind > VR_MEM_DEVICE) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: unknown memory_kind");
+    if (t->memory_kind != VR_MEM_NONE && !t->dst) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: dst is null");
+    const bool direct = (t->flags & VR_RENDER_DIRECT) != 0;
+    if (direct && t->memory_kind != VR_MEM_DEVICE) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: VR_RENDER_DIRECT needs VR_MEM_DEVICE");
+    uint32_t r0 = t->row_begin, r1 = t->row_end;
+    if (r0 == 0 && r1 == 0) r1 = c->height;
+    if (r0 > r1 || r1 > c->height) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: row band out of range");
+    uint32_t v0 = t->view_begin, v1 = t->view_end;
+    if (v0 == 0 && v1 == 0) v1 = c->view_count;
+    if (v0 > v1 || v1 > c->view_count) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: view range out of range");
+    const size_t pitch = t->row_pitch ? t->row_pitch : c->row_pitch;
+    if (pitch < c->row_pitch) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: row_pitch smaller than a row");
+
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaStream_t s = t->stream ? (cudaStream_t)t->stream : c->stream;
+    MarchParams m;
+    int variant = 0;
+    vr_status st = fill_march_params(c, m, variant);
+    if (st != VR_OK) return st;
+    m.row_begin = (int)r0; m.row_end = (int)r1; m.view_begin = (int)v0;
+    if (direct) { m.out = t->dst; m.row_pitch = pitch; m.view_stride = pitch * c->height; }
+    const bool stats = (t->flags & VR_RENDER_STATS) != 0;
+    if (stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), s));
+    if (t->stream) {   // params were uploaded on the context stream
+        VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+        VR_CUDA(c, cudaStreamWaitEvent(s, c->ev1, 0));
+    }
+    VR_CUDA(c, cudaEventRecord(c->ev0, s));
+    VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
+    VR_CUDA(c, cudaEventRecord(c->ev1, s));
+    c->timed = true;
+    c->stats.kernel_launches = (r1 > r0 && v1 > v0) ? 1 : 0;
+    c->stats.rays = (uint64_t)(r1 - r0) * c->width * (v1 - v0);
+    if (stats) VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    else std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
+
+    if (t->memory_kind != VR_MEM_NONE && !direct && r1 > r0) {
+        for (uint32_t v = v0; v < v1; ++v) {
+            const char* src = (const char*)c->frame + (size_t)v * c->view_stride + (size_t)r0 * c->row_pitch;
+            char* dst = (char*)t->dst + (size_t)v * pitch * c->height + (size_t)r0 * pitch;
+            VR_CUDA(c, cudaMemcpy2DAsync(dst, pitch, src, c->row_pitch, c->row_pitch, r1 - r0,
+                                         t->memory_kind == VR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, s));
+        }
+    }
+    if (!(t->flags & VR_RENDER_ASYNC)) VR_CUDA(c, cudaStreamSynchronize(s));
+    return VR_OK;
+}
+
+extern "C" vr_status vr_wait(vr_context* c) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    if (c->timed) VR_CUDA(c, cudaEventSynchronize(c->ev1));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VR_OK;
+}
+
+extern "C" vr_status vr_get_stats(vr_context* c, vr_stats* out) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!out || out->struct_size < sizeof(vr_stats)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_get_stats: null or struct_size too small");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    if (c->timed) {
+        VR_CUDA(c, cudaEventSynchronize(c->ev1));
+        VR_CUDA(c, cudaEventElapsedTime(&c->stats.gpu_ms, c->ev0, c->ev1));
+    }
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->stats.covered = c->h_counters[0];
+    c->stats.steps = c->h_counters[1];
+    c->stats.early_terminated = c->h_counters[2];
+    c->stats.light_samples = c->h_counters[3];
+    c->stats.skipped_steps = c->h_counters[4];
+    *out = c->stats;
+    out->struct_size = sizeof(vr_stats);
+    return VR_OK;
+}
+
+extern "C" vr_status vr_frame_info(vr_context* c, void** dev_ptr, size_t* row_pitch, size_t* view_stride) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (dev_ptr) *dev_ptr = c->frame;
+    if (row_pitch) *row_pitch = c->row_pitch;
+    if (view_stride) *view_stride = c->view_stride;
+    return VR_OK;
+}
+
+// contiguous row bands of (nearly) equal estimated cost; bounds[0]=0 ... bounds[parts]=height
+extern "C" vr_status vr_row_bands(vr_context* c, uint32_t parts, uint32_t* bounds) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!bounds || parts == 0 || parts > 64) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_row_bands: parts must be in 1..64");
+    if (!c->has_params) return fail(c, VR_ERR_BAD_STATE, "vr_row_bands: vr_set_params has not been called");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    MarchParams m;
+    int variant = 0;
+    // the cost model only needs the ray set-up, so it works without a volume as well
+    bool had = c->has_volume;
+    vr_status st = VR_OK;
+    if (!had && c->params.density_mode != VR_DENSITY_FBM) {
+        vr_params saved = c->params;
+        c->params.density_mode = VR_DENSITY_FBM;
+        st = fill_march_params(c, m, variant);
+        c->params = saved;
+    } else st = fill_march_params(c, m, variant);
+    if (st != VR_OK) return st;
+    VR_CUDA(c, launch_row_cost(m, 0, c->d_row_cost, c->stream));
+    std::vector<float> cost(c->height);
+    VR_CUDA(c, cudaMemcpyAsync(cost.data(), c->d_row_cost, sizeof(float) * c->height, cudaMemcpyDeviceToHost, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    double total = 0.0;
+    for (float v : cost) total += v;
+    bounds[0] = 0;
+    double acc = 0.0;
+    uint32_t k = 1;
+    for (uint32_t y = 0; y < c->height && k < parts; ++y) {
+        acc += cost[y];
+        while (k < parts && acc >= total * (double)k / (double)parts) bounds[k++] = y + 1;
+    }
+    while (k <= parts) bounds[k++] = c->height;
+    return VR_OK;
+}
+
+// ------------------------------------------------------------------ NVLink peer gather across processes
+extern "C" vr_status vr_frame_export(vr_context* c, void* handle64) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!handle64) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_frame_export: null handle");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    VR_CUDA(c, cudaIpcGetMemHandle(&h, c->frame));
+    std::memcpy(handle64, &h, 64);
+    return VR_OK;
+}
+extern "C" vr_status vr_frame_import(vr_context* c, const void* handle64, void** mapped) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!handle64 || !mapped) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_frame_import: null argument");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    void* p = nullptr;
+    VR_CUDA(c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    *mapped = p;
+    return VR_OK;
+}
+extern "C" vr_status vr_frame_unmap(vr_context* c, void* mapped) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    VR_CUDA(c, cudaSetDevice(c->device));
+    VR_CUDA(c, cudaIpcCloseMemHandle(mapped));
+    return VR_OK;
+}

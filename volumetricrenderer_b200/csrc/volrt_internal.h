@@ -1,0 +1,92 @@
+// libvolrt internals: what crosses from the host side of the C ABI (volrt_api.cu) to the
+// kernels (march_kernels.cu, noise_kernels.cu).  Not installed; the public surface is
+// include/volrt.h only.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+#include "../../include/volrt.h"
+
+namespace volrt {
+
+// Per-view constants, decoded from the two UBOs at vr_set_params time.  Column-major mat4s.
+// inv_pv / inv_model are formed in double and rounded once (the oracle does the same).
+struct ViewConst {
+    float inv_pv[16];       // inverse(Projection * View)           vert.glsl:19
+    float inv_model[16];    // inverse(Model)
+    float model[16];        // Model                                 vert.glsl:20
+    float w2l[16];          // gsd.WorldToLocal                      frag.glsl:11
+    float cam[3];           // gsd.CameraPosition                    frag.glsl:12
+    float scroll_y[3];      // (MS[0].y, MS[1].y, MS[2].y)           frag.glsl:67
+    float scroll_z[3];      // (MS[0].z, ...)                        frag.glsl:68
+    float scroll_w[3];      // (MS[0].w, ...)                        frag.glsl:69
+};
+
+struct BrickInfo {          // min-max grid for empty-space skipping (8^3 voxel bricks)
+    const uint8_t* occupied;   // 1 byte per brick: 0 = density upper bound is exactly 0
+    int bx, by, bz;            // bricks per axis
+    float inv_brick[3];        // bricks per unit of texture coordinate
+};
+
+struct MarchParams {
+    // target
+    int width, height;
+    int row_begin, row_end;
+    int view_begin;             // blockIdx.z + view_begin = view index
+    void* out;                  // view 0 / row 0 of the destination frame
+    size_t row_pitch, view_stride;
+    int out_format;             // vr_output_format
+    const ViewConst* views;     // device array
+    // reference literals (frag.glsl:29-32,42,63,66-69)
+    int max_steps;
+    float step_scale, density, sample_scale;
+    float coord_scale[4], scroll_weight[4];
+    // volume
+    cudaTextureObject_t tex;    // TEXTURE layout
+    const void* lin;            // LINEAR layout (x fastest)
+    int vw, vh, vd;
+    int vol_format;             // vr_volume_format
+    int address_mode;
+    // extensions
+    int light_steps;
+    float light_step_len, sun_dir[3], sun_color[3], ambient, sigma_t, early_term_eps;
+    int skip_empty;
+    BrickInfo bricks;
+    int fbm_octaves, fbm_seed;
+    float fbm_frequency, fbm_gain, fbm_lacunarity, fbm_coverage, fbm_falloff0, fbm_falloff1, fbm_bounding;
+    // device counters (VR_RENDER_STATS): covered, steps, early, light samples, skipped
+    unsigned long long* counters;
+};
+
+enum MarchVariant {
+    MARCH_RGBA_TEX = 0,      // reference integrator, 4 HW-filtered fetches/step
+    MARCH_RGBA_LINEAR = 1,   // reference integrator, FP32 software trilinear from global memory
+    MARCH_SINGLE_TEX = 2,    // one-channel grid through the texture unit
+    MARCH_SINGLE_LINEAR = 3,
+    MARCH_FBM = 4            // procedural density
+};
+
+// launches one march over rows [row_begin,row_end) x views; returns cudaGetLastError()
+cudaError_t launch_march(const MarchParams& p, int variant, int n_views, bool stats, cudaStream_t stream);
+
+// analytic per-row cost (sum of chord steps) for band balancing; cost[height] on device
+cudaError_t launch_row_cost(const MarchParams& p, int view, float* row_cost, cudaStream_t stream);
+
+// ---- noise / bake (noise_kernels.cu) ----
+struct NoiseField { uint32_t generator; float frequency; int32_t seed; };
+// fills out[n^3] (x fastest) and atomically folds min/max into minmax_bits[2] (ordered-int floats)
+cudaError_t launch_noise_fill(const NoiseField& f, int n, float* out, unsigned int* minmax_bits, cudaStream_t s);
+cudaError_t launch_noise_minmax_only(const NoiseField& f, int n, unsigned int* minmax_bits, cudaStream_t s);
+struct PackChannel { const float* field; float mn, mx; uint32_t power; };
+cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_rgba8, cudaStream_t s);
+struct FbmField {
+    int octaves, seed;
+    float frequency, gain, lacunarity, coverage, falloff0, falloff1, bounding, threshold;
+};
+cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s);
+cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int address_mode,
+                             uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
+void minmax_init(unsigned int* bits2_host);
+float minmax_decode(unsigned int bits);
+
+}  // namespace volrt
