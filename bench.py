@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s of the volumetric ray-march hot path on B200 (one process per GPU).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c1|c3|c4] [--impl volrt|reference]
+
+A "step" is one frame: one pass of the march over every pixel of the configured target.
+Default workload = BASELINE.json configs[1]: 1920x1080 procedural fBm cloud, 128 primary steps per
+ray + 6-step sun light-march, synthetic (no volume input at all).
+  value      whole-job Mrays/s (W*H*frames / device time of the march kernels, CUDA events on the
+             launching stream, L2 flushed between frames, max over ranks)
+  e2e        the same through the public C ABI with HOST buffers: vr_set_params (UBO bytes, H2D) +
+             vr_render into pinned host memory (frame D2H) per step, wall clock around the synchronous calls
+  roofline   dominant kernel (march) against the FP32-FMA peak measured in the same process
+  cpu_baseline  the CPU oracle (a port of frag.glsl; the reference has no CPU path) on a bounded,
+             strided row sample of the same frame, all host threads
+N > 1: the frame is cut into cost-balanced row bands (vr_row_bands), one band per GPU; each GPU's
+march kernel stores its pixels straight into GPU 0's frame through an NVLink peer mapping
+(CUDA IPC), so the gather is fused into the march ("scaling": "strong").
+--impl reference: the oracle (the only CPU implementation of the path there is) timed on the host.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SUN = np.array([1.0, 1.0, 2.0], np.float32) / np.float32(np.sqrt(6.0))
+
+WORKLOADS = {
+    # name: (W, H, description, vr_params keyword overrides)
+    "c1": (1280, 720, "default frag.glsl scene, 128^3 RGBA8 baked volume, 128 steps, texture-unit trilinear", dict()),
+    "c2": (1920, 1080, "1920x1080 procedural fBm cloud (5-octave Perlin), 128 primary steps + 6-step sun light-march",
+           dict(density_mode=2, max_steps=128, sigma_t=8.0, light_steps=6, light_step_len=2 * 4.0 / 128, ambient=0.15,
+                sun_dir=SUN, sun_color=[1.0, 0.95, 0.85])),
+    "c3": (3840, 2160, "3840x2160 procedural fBm cloud, 256 primary steps + 8-step sun light-march",
+           dict(density_mode=2, max_steps=256, sigma_t=8.0, light_steps=8, light_step_len=2 * 4.0 / 256, ambient=0.15,
+                sun_dir=SUN, sun_color=[1.0, 0.95, 0.85])),
+    "c4": (1920, 1080, "512^3 fp16 smoke grid (device-baked fBm field), trilinear, 1 fetch/step, 512 steps",
+           dict(density_mode=1, max_steps=512, sample_scale=4.0)),
+}
+# algorithmic FP32 work: one Perlin octave = 60 flop, +20 per fBm sample for the
+# remap/falloff, 26 flop per step for the integrator; FMA = 2 flop.
+FLOP_PER_OCTAVE, FLOP_PER_SAMPLE, FLOP_PER_STEP = 60.0, 20.0, 26.0
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="volrt", choices=["volrt", "reference"])
+    ap.add_argument("--layout", default="texture", choices=["texture", "linear"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the oracle sample")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    """samples SM clock + throttle reasons of one GPU while the timed region runs (NVML)"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop_evt = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4)}
+        while not self._stop_evt.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.004)
+
+    def stop(self):
+        self._stop_evt.set()
+        if self.is_alive():
+            self.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def physical_gpu_index(local):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local])
+        except (ValueError, IndexError):
+            return local
+    return local
+
+
+def oracle_params_for(workload):
+    """vo_params of the workload (oracle side; used only by the cpu_baseline / reference legs)"""
+    from oracle import oracle
+    from volumetricrenderer_b200 import scene
+    W, H, _, kw = WORKLOADS[workload]
+    ubo0, ubo1 = scene.default_scene()
+    scal = {k: v for k, v in kw.items() if not hasattr(v, "__len__")}
+    vecs = {k: v for k, v in kw.items() if hasattr(v, "__len__")}
+    p = oracle.params_default(**scal)
+    oracle.set_params(p, **vecs)
+    oracle.set_scene(p, ubo0, ubo1)
+    return p
+
+
+def oracle_volume_for(workload):
+    from oracle import oracle
+    if workload == "c1":
+        vol = oracle.ref_bake_default(128)[0] if oracle.have_ref() else oracle.bake_default(128)
+        return oracle.make_volume(vol, oracle.VOL_RGBA8)
+    if workload == "c4":
+        p = oracle.params_default()
+        vol = oracle.bake_smoke_r16f(128, p, 0.0)          # CPU sample uses a 128^3 stand-in of the field
+        return oracle.make_volume(vol, oracle.VOL_R16F)
+    return None, None
+
+
+def time_oracle(workload, target_seconds, threads=0):
+    """Oracle on a bounded strided row sample -> dict(value Mrays/s, cores, sample, seconds)."""
+    from oracle import oracle
+    W, H, _, _ = WORKLOADS[workload]
+    p = oracle_params_for(workload)
+    vol, keep = oracle_volume_for(workload)
+    cores = threads or oracle.lib().vo_hw_threads()
+    probe = np.arange(8, H, 16, dtype=np.int32)              # calibration pass
+    t0 = time.perf_counter()
+    oracle.render_rows(vol, p, W, H, probe, threads)
+    t_probe = time.perf_counter() - t0
+    per_row = t_probe / len(probe)
+    stride = int(max(1, min(64, np.ceil(H * per_row / max(target_seconds, 0.1)))))
+    rows = np.arange(stride // 2, H, stride, dtype=np.int32)
+    t0 = time.perf_counter()
+    _, st = oracle.render_rows(vol, p, W, H, rows, threads)
+    dt = time.perf_counter() - t0
+    mrays = len(rows) * W / dt / 1e6
+    return {"value": mrays, "unit": "Mrays/s", "cores": int(cores), "kind": "port",
+            "sample": "%d of %d rows (every %d-th) of the %s frame, %.2f s, %d steps" % (len(rows), H, stride, workload, dt, st["steps"]),
+            "seconds": dt, "msamples_per_s": st["steps"] / dt / 1e6}
+
+
+# ---------------------------------------------------------------------------------------------
+def run_reference(args, rank, world):
+    """--impl reference: the CPU implementation of the path (the oracle port — the reference itself
+    has only GLSL for it and no graphics stack exists here) on all host threads, rank 0 only."""
+    if rank != 0:
+        return
+    W, H, desc, _ = WORKLOADS[args.workload]
+    per_step = max(2.0, min(args.cpu_seconds, 150.0 / max(1, args.steps + args.warmup)))
+    vals, last = [], None
+    for i in range(args.warmup + args.steps):
+        last = time_oracle(args.workload, per_step)
+        if i >= args.warmup:
+            vals.append(last)
+    secs = sum(v["seconds"] for v in vals)
+    # rays of the sample / time of the sample, aggregated over the timed steps
+    mrays = float(np.mean([v["value"] for v in vals]))
+    line = {
+        "impl": "reference", "metric": "Mrays/s", "value": mrays, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": W * H / (mrays * 1e6) * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "%s: %s" % (args.workload, desc), "width": W, "height": H,
+                   "note": "ms_per_step = full-frame time extrapolated from the timed row sample"},
+        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+        "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "sample_seconds": secs,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def setup_volume(r, workload, layout):
+    from volumetricrenderer_b200 import capi
+    lay = capi.LAYOUT_TEXTURE if layout == "texture" else capi.LAYOUT_LINEAR
+    if workload == "c1":
+        r.generate_volume(layout=lay)                                   # the reference's bake, on the device
+        return 128 ** 3 * 4
+    if workload == "c4":
+        r.generate_volume(size=512, format=capi.VOL_R16F, layout=lay)   # fBm smoke field, fp16
+        return 512 ** 3 * 2
+    return 0
+
+
+def run_volrt(args, rank, world, local):
+    import volumetricrenderer_b200 as vr
+    from volumetricrenderer_b200 import capi, scene
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    W, H, desc, kw = WORKLOADS[args.workload]
+    K, Wm = args.steps, max(args.warmup, 3)
+    ubo0, ubo1 = scene.default_scene()
+    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local)
+    vol_bytes = setup_volume(r, args.workload, args.layout)
+    r.set_params(ubo0, ubo1, **kw)
+
+    # ---- partition: cost-balanced row bands, peer-mapped frame of rank 0
+    rows, mapped = (0, H), None
+    if world > 1:
+        import torch
+        bounds = r.row_bands(world)
+        rows = (bounds[rank], bounds[rank + 1])
+        handle = [r.frame_export() if rank == 0 else None]
+        dist.broadcast_object_list(handle, src=0)
+        if rank != 0:
+            mapped = r.frame_import(handle[0])
+
+    def march(flags=0):
+        if rows[1] <= rows[0]:
+            return
+        if mapped is not None:
+            r.render_device(mapped, rows=rows, flags=capi.RENDER_DIRECT | flags)
+        else:
+            r.render(rows=rows, to_host=False, flags=flags)
+
+    def barrier():
+        r.wait()
+        if dist is not None:
+            import torch
+            dist.barrier(device_ids=[local])
+            torch.cuda.synchronize()
+
+    # ---- one counted pass (device counters): work actually done per frame
+    march(capi.RENDER_STATS)
+    st = r.stats()
+    counts = np.array([st["covered"], st["steps"], st["light_samples"], st["early_terminated"]], np.float64)
+    if dist is not None:
+        import torch
+        t = torch.tensor(counts, device="cuda", dtype=torch.float64)
+        dist.all_reduce(t)
+        counts = t.cpu().numpy()
+    covered, steps, light_samples = int(counts[0]), int(counts[1]), int(counts[2])
+
+    # ---- device-timed region: K frames, L2 flushed between frames, CUDA events on the launching stream
+    for _ in range(Wm):
+        r.flush_l2(); march(); r.wait()
+    sampler = ClockSampler(physical_gpu_index(local))
+    barrier()
+    sampler.start()
+    wall0 = time.perf_counter()
+    ms = []
+    for _ in range(K):
+        r.flush_l2()
+        march()
+        ms.append(r.stats()["gpu_ms"] if rows[1] > rows[0] else 0.0)
+    barrier()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.stop()
+    dev_ms = float(np.sum(ms))
+    if dist is not None:
+        import torch
+        t = torch.tensor([dev_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms = float(t.item())
+    ms_per_step = dev_ms / K
+    value = W * H / (ms_per_step * 1e-3) / 1e6
+
+    # ---- end to end through the public API with host buffers
+    host = r.new_frame_buffer(pinned=True) if rank == 0 else None
+    def e2e_step():
+        r.set_params(ubo0, ubo1, **kw)                     # UBO bytes -> device (H2D)
+        if world == 1:
+            r.render(out=host)                             # march + frame D2H into pinned memory, synchronous
+        else:
+            march()
+            barrier()                                      # every band has landed in GPU 0's frame
+            if rank == 0:
+                r.render(out=host, flags=capi.RENDER_NO_MARCH)
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / K
+    e2e = {"value": W * H / e2e_s / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_s * 1e3,
+           "h2d_bytes_per_step": 192 + 140, "d2h_bytes_per_step": W * H * 4}
+
+    if rank == 0:
+        line = {
+            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "%s: %s" % (args.workload, desc), "width": W, "height": H,
+                       "l2": "flushed between frames (256 MiB write); the procedural workloads read no input",
+                       "partition": "cost-balanced row bands, peer stores into GPU0's frame over NVLink (CUDA IPC)" if world > 1 else "single GPU",
+                       "volume_layout": args.layout if vol_bytes else None},
+            "e2e": e2e, "gpu_launches": K * (1 if rows[1] > rows[0] else 0),
+            "clocks": clocks, "wall_ms_per_step_incl_flush": wall / K * 1e3,
+            "covered_rays": covered, "steps_per_frame": steps, "light_samples_per_frame": light_samples,
+            "msamples_per_s": (steps + light_samples) / (ms_per_step * 1e-3) / 1e6,
+        }
+        line["roofline"] = roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world)
+        if not args.no_cpu_baseline and world == 1:
+            try:
+                cb = time_oracle(args.workload, args.cpu_seconds)
+                line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+            except Exception as e:                          # the baseline is a report, not the product
+                line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "port", "sample": "failed: %r" % e}
+        print(json.dumps(line), flush=True)
+    if mapped is not None:
+        r.frame_unmap(mapped)
+    barrier()
+    r.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world):
+    peaks = r.measure_peaks()
+    t = ms_per_step * 1e-3
+    measured = {}
+    try:
+        measured = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = measured.get("hbm_gbs", 6650.0)
+    compulsory = vol_bytes + W * H * 4
+    out = {"hbm_compulsory_gbs": compulsory / t / 1e9, "hbm_peak_gbs": hbm_peak,
+           "hbm_peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in measured else "fallback",
+           "traffic": None, "peaks_measured_here": peaks}
+    if kw.get("density_mode") == 2:
+        octaves = 5
+        per_sample = octaves * FLOP_PER_OCTAVE + FLOP_PER_SAMPLE
+        flops = (steps + light_samples) * per_sample + steps * FLOP_PER_STEP
+        out.update({"bound": "fp32", "achieved": flops / t / 1e12, "peak": peaks["fp32_tflops"] * world, "unit": "TFLOP/s",
+                    "peak_source": "FP32 FMA micro-benchmark in this process (dependent-free FMA chains)",
+                    "flop_per_frame": flops,
+                    "note": "flops = evaluated noise samples x (5 octaves x 60 + 20) + steps x 26 (SURVEY.md 8(d)); "
+                            "samples counted by the device (steps whose density is exactly 0 skip their light-march)"})
+    else:
+        fetches = steps * (4 if kw.get("density_mode", 0) == 0 else 1)
+        out.update({"bound": "tex", "achieved": fetches / t / 1e9, "peak": peaks["tex_gfetch"] * world, "unit": "Gfetch/s",
+                    "peak_source": "trilinear-fetch micro-benchmark in this process (L1/L2-resident RGBA8, warp-coherent)",
+                    "note": "the volume is cache-resident or streamed once; compulsory HBM traffic is in hbm_compulsory_gbs"})
+    out["frac"] = out["achieved"] / out["peak"] if out["peak"] else None
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    run_volrt(args, rank, world, local)
+
+
+if __name__ == "__main__":
+    main()

@@ -28,6 +28,12 @@
 extern "C" {
 #endif
 
+#if defined(_WIN32)
+#define VR_API __declspec(dllexport)
+#else
+#define VR_API __attribute__((visibility("default")))
+#endif
+
 #define VR_VERSION_MAJOR 0
 #define VR_VERSION_MINOR 1
 #define VR_MAX_DEVICES 8
@@ -94,7 +100,9 @@ enum {
     VR_RENDER_DIRECT = 1u << 1,    /* VR_MEM_DEVICE only: the march kernel stores its pixels straight
                                       into dst (which may be another GPU's memory mapped through
                                       NVLink peer access / CUDA IPC) instead of the context frame */
-    VR_RENDER_STATS = 1u << 2      /* count covered rays / steps on the device (slower variant) */
+    VR_RENDER_STATS = 1u << 2,     /* count covered rays / steps on the device (slower variant) */
+    VR_RENDER_NO_MARCH = 1u << 3   /* launch nothing; only copy the context frame (e.g. the one the
+                                      peers have just gathered into) to dst                         */
 };
 
 /* replaces renderer.Init() + AddRenderPass("BasePass", ...) + render-target creation:
@@ -215,28 +223,38 @@ typedef struct vr_stats {
     uint32_t kernel_launches;    /* kernels launched by the last vr_render                     */
 } vr_stats;
 
-uint32_t vr_version(void);
-vr_status vr_params_default(vr_params* p);           /* reference literals, extensions off */
-vr_status vr_create(const vr_create_info* info, vr_context** out);
-void vr_destroy(vr_context* ctx);                    /* replaces renderer.Shutdown(), TestMain.cpp:260 */
-const char* vr_last_error(const vr_context* ctx);    /* ctx may be NULL: last vr_create failure */
-vr_status vr_upload_volume(vr_context* ctx, const vr_volume_desc* desc, const void* texels);
-vr_status vr_generate_volume(vr_context* ctx, const vr_noise_desc* desc, const vr_params* fbm);
-vr_status vr_download_volume(vr_context* ctx, void* texels, size_t bytes);  /* x-fastest copy back */
-vr_status vr_noise_desc_default(vr_noise_desc* d);   /* the reference's bake incl. quirk Q1 */
-vr_status vr_set_params(vr_context* ctx, const vr_params* p);
-vr_status vr_render(vr_context* ctx, const vr_target* target);
-vr_status vr_wait(vr_context* ctx);
-vr_status vr_get_stats(vr_context* ctx, vr_stats* out);
+VR_API uint32_t vr_version(void);
+VR_API vr_status vr_params_default(vr_params* p);           /* reference literals, extensions off */
+VR_API vr_status vr_create(const vr_create_info* info, vr_context** out);
+VR_API void vr_destroy(vr_context* ctx);                    /* replaces renderer.Shutdown(), TestMain.cpp:260 */
+VR_API const char* vr_last_error(const vr_context* ctx);    /* ctx may be NULL: last vr_create failure */
+VR_API vr_status vr_upload_volume(vr_context* ctx, const vr_volume_desc* desc, const void* texels);
+VR_API vr_status vr_generate_volume(vr_context* ctx, const vr_noise_desc* desc, const vr_params* fbm);
+VR_API vr_status vr_download_volume(vr_context* ctx, void* texels, size_t bytes);  /* x-fastest copy back */
+VR_API vr_status vr_noise_desc_default(vr_noise_desc* d);   /* the reference's bake incl. quirk Q1 */
+VR_API vr_status vr_set_params(vr_context* ctx, const vr_params* p);
+VR_API vr_status vr_render(vr_context* ctx, const vr_target* target);
+VR_API vr_status vr_wait(vr_context* ctx);
+VR_API vr_status vr_get_stats(vr_context* ctx, vr_stats* out);
 /* the context's device frame (view 0, row 0) and its layout, for zero-copy consumers */
-vr_status vr_frame_info(vr_context* ctx, void** dev_ptr, size_t* row_pitch, size_t* view_stride);
+VR_API vr_status vr_frame_info(vr_context* ctx, void** dev_ptr, size_t* row_pitch, size_t* view_stride);
 /* row bands of equal estimated cost for `parts` GPUs: bounds[parts+1] */
-vr_status vr_row_bands(vr_context* ctx, uint32_t parts, uint32_t* bounds);
+VR_API vr_status vr_row_bands(vr_context* ctx, uint32_t parts, uint32_t* bounds);
 /* NVLink peer gather across processes: rank 0 exports its frame, the others map it and render
  * their band with VR_RENDER_DIRECT into the mapped pointer. handle = 64 bytes (cudaIpcMemHandle_t) */
-vr_status vr_frame_export(vr_context* ctx, void* handle64);
-vr_status vr_frame_import(vr_context* ctx, const void* handle64, void** mapped);
-vr_status vr_frame_unmap(vr_context* ctx, void* mapped);
+VR_API vr_status vr_frame_export(vr_context* ctx, void* handle64);
+VR_API vr_status vr_frame_import(vr_context* ctx, const void* handle64, void** mapped);
+VR_API vr_status vr_frame_unmap(vr_context* ctx, void* mapped);
+/* measurement helpers: evict the 126 MB L2 between timed frames (writes a 256 MiB scratch buffer on
+ * the context's stream); page-locked host memory so that vr_render's D2H copy and
+ * vr_upload_volume's H2D copy run at full PCIe rate (the reference maps its UBOs and stages
+ * its texture through host-visible Vulkan memory: VulkanUniformBuffer.h:30-45, VulkanTexture.cpp:121-128) */
+VR_API vr_status vr_flush_l2(vr_context* ctx);
+/* roofline denominators measured on this device: peaks4 = { FP32-FMA TFLOP/s, trilinear RGBA8 texture
+ * fetches G/s (0 without a TEXTURE-layout RGBA8 volume), SM count, max SM clock MHz } */
+VR_API vr_status vr_measure_peaks(vr_context* ctx, float* peaks4);
+VR_API void* vr_host_alloc(size_t bytes);
+VR_API void vr_host_free(void* p);
 
 #ifdef __cplusplus
 }

@@ -67,6 +67,9 @@ def lib():
         L.vo_render.argtypes = [C.POINTER(VoVolume), C.POINTER(VoParams), C.c_int, C.c_int, C.c_int, C.c_int,
                                 fp, ip, C.POINTER(C.c_uint64), C.c_int]
         L.vo_render.restype = C.c_int
+        L.vo_render_rows.argtypes = [C.POINTER(VoVolume), C.POINTER(VoParams), C.c_int, C.c_int, ip, C.c_int,
+                                     fp, ip, C.POINTER(C.c_uint64), C.c_int]
+        L.vo_render_rows.restype = C.c_int
         L.vo_encode.argtypes = [fp, C.c_int64, C.c_int, C.c_void_p]
         L.vo_noise.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
         L.vo_noise.restype = C.c_float
@@ -197,6 +200,18 @@ def render(vol, p, W, H, rows=None, threads=0, want_steps=False):
         raise ValueError("vo_render rc=%d" % rc)
     stats = {"covered": int(st[0]), "steps": int(st[1]), "early": int(st[2]), "light_samples": int(st[3])}
     return (out, stats, steps) if want_steps else (out, stats)
+
+
+def render_rows(vol, p, W, H, rows, threads=0):
+    """shade only the listed screen rows -> (rgba float32 (len(rows),W,4), stats dict)"""
+    rows = np.ascontiguousarray(rows, np.int32)
+    out = np.zeros((len(rows), W, 4), np.float32)
+    st = (C.c_uint64 * 4)()
+    rc = lib().vo_render_rows(C.byref(vol) if vol is not None else None, C.byref(p), W, H,
+                              rows.ctypes.data_as(C.POINTER(C.c_int32)), len(rows), _fp(out), None, st, threads)
+    if rc != 0:
+        raise ValueError("vo_render_rows rc=%d" % rc)
+    return out, {"covered": int(st[0]), "steps": int(st[1]), "early": int(st[2]), "light_samples": int(st[3])}
 
 
 def encode(rgba, fmt):

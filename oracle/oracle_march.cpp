@@ -264,9 +264,11 @@ void inverse_d(const double* m, double* out) {
 
 extern "C" void vo_sample(const vo_volume* v, float u, float vv, float w, float out4[4]) { sample(v, {u, vv, w}, out4); }
 
-extern "C" int vo_render(const vo_volume* v, const vo_params* p, int W, int H, int row0, int row1,
-                         float* out_rgba, int32_t* out_steps, uint64_t stats[4], int threads) {
-    if (!p || W <= 0 || H <= 0 || row0 < 0 || row1 > H || row0 > row1 || p->max_steps <= 0) return 1;
+// rows[n_rows]: the screen rows to shade, in the order their output is stored (W float4 each)
+extern "C" int vo_render_rows(const vo_volume* v, const vo_params* p, int W, int H, const int32_t* rows, int n_rows,
+                              float* out_rgba, int32_t* out_steps, uint64_t stats[4], int threads) {
+    if (!p || W <= 0 || H <= 0 || n_rows < 0 || (n_rows && !rows) || p->max_steps <= 0) return 1;
+    for (int r = 0; r < n_rows; ++r) if (rows[r] < 0 || rows[r] >= H) return 1;
     if (p->density_mode != VO_DENSITY_FBM && (!v || !v->texels)) return 2;
     // frame constants: inverse(Projection·View) and inverse(Model), formed in double and
     // rounded to binary32 once.
@@ -287,8 +289,8 @@ extern "C" int vo_render(const vo_volume* v, const vo_params* p, int W, int H, i
 
     int nt = threads > 0 ? threads : vo_hw_threads();
     std::vector<uint64_t> acc((size_t)nt * 4, 0);
-    parallel_for(row1 - row0, nt, [&](int r, int t) {
-        int py = row0 + r;
+    parallel_for(n_rows, nt, [&](int r, int t) {
+        int py = rows[r];
         uint64_t* a = &acc[(size_t)t * 4];
         for (int px = 0; px < W; ++px) {
             float* o = out_rgba + ((size_t)r * W + px) * 4;
@@ -301,6 +303,14 @@ extern "C" int vo_render(const vo_volume* v, const vo_params* p, int W, int H, i
         for (int k = 0; k < 4; ++k) { stats[k] = 0; for (int t = 0; t < nt; ++t) stats[k] += acc[(size_t)t * 4 + k]; }
     }
     return 0;
+}
+
+extern "C" int vo_render(const vo_volume* v, const vo_params* p, int W, int H, int row0, int row1,
+                         float* out_rgba, int32_t* out_steps, uint64_t stats[4], int threads) {
+    if (row0 < 0 || row1 > H || row0 > row1) return 1;
+    std::vector<int32_t> rows((size_t)(row1 - row0));
+    for (int r = row0; r < row1; ++r) rows[(size_t)(r - row0)] = r;
+    return vo_render_rows(v, p, W, H, rows.data(), row1 - row0, out_rgba, out_steps, stats, threads);
 }
 
 // ---------------------------------------------------------------- A.5 output conversion

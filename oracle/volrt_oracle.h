@@ -96,6 +96,10 @@ void vo_sample(const vo_volume* v, float u, float vv, float w, float out4[4]);
 int vo_render(const vo_volume* v, const vo_params* p, int W, int H, int row0, int row1,
               float* out_rgba, int32_t* out_steps, uint64_t stats[4], int threads);
 
+/* same for an arbitrary list of screen rows (the bounded, strided sample bench.py times) */
+int vo_render_rows(const vo_volume* v, const vo_params* p, int W, int H, const int32_t* rows, int n_rows,
+                   float* out_rgba, int32_t* out_steps, uint64_t stats[4], int threads);
+
 /* ---- output conversion ---- */
 void vo_encode(const float* rgba, int64_t n_px, int fmt, void* out);
 

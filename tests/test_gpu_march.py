@@ -1,0 +1,255 @@
+"""GPU parity: libvolrt's march kernels (through the C ABI) vs the CPU oracle, same inputs.
+
+Bars (BASELINE.json north_star): per-pixel max abs error <= 2/255 and PSNR >= 50 dB in 8-bit for the
+hardware-filtered TEXTURE layout; the FP32-filtered LINEAR layout follows the oracle's operation
+order and must match its binary32 output BIT FOR BIT.
+"""
+import numpy as np
+import pytest
+
+import volumetricrenderer_b200 as vr
+from volumetricrenderer_b200 import capi, scene
+from util import psnr8, max_abs8, oracle_params, smoke_volume
+
+pytestmark = pytest.mark.gpu
+
+TOL8 = 2          # /255, stated by north_star
+PSNR_MIN = 50.0   # dB, stated by north_star
+
+
+def _oracle_frame(oracle, vol, fmt, p, W, H, rows=None):
+    ovol, keep = oracle.make_volume(vol, fmt)
+    img, st, steps = oracle.render(ovol, p, W, H, rows=rows, want_steps=True)
+    return img, st, steps
+
+
+def test_default_scene_linear_is_bit_exact(oracle, default_volume):
+    """config 1: the reference's default scene, 1280x720, FP32 software trilinear."""
+    W, H = 1280, 720
+    ubo0, ubo1 = scene.default_scene()
+    p = oracle_params(oracle, ubo0, ubo1)
+    ref, st, _ = _oracle_frame(oracle, default_volume, oracle.VOL_RGBA8, p, W, H)
+    assert st["covered"] == 196251 and abs(st["steps"] - 7439290) < 2000
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0, ubo1)
+        img = r.render(flags=capi.RENDER_STATS)[0]
+        s = r.stats()
+    assert s["covered"] == st["covered"] and s["steps"] == st["steps"]
+    assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+
+
+@pytest.mark.parametrize("fmt,ofmt", [(capi.OUT_RGBA8_UNORM, 0), (capi.OUT_RGBA8_SRGB, 1)])
+def test_default_scene_texture_within_tolerance(oracle, default_volume, fmt, ofmt):
+    """config 1 through the texture unit (fixed-point trilinear weights), both target encodings (Q3)."""
+    W, H = 1280, 720
+    ubo0, ubo1 = scene.default_scene()
+    p = oracle_params(oracle, ubo0, ubo1)
+    ref, _, _ = _oracle_frame(oracle, default_volume, oracle.VOL_RGBA8, p, W, H)
+    ref8 = oracle.encode(ref, ofmt)
+    with vr.Renderer(W, H, fmt) as r:
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        r.set_params(ubo0, ubo1)
+        img = r.render()[0]
+    assert img[..., 3].min() == 255
+    assert max_abs8(img, ref8) <= TOL8
+    assert psnr8(img, ref8) >= PSNR_MIN
+    assert ref8[..., 0].max() > 40            # the cloud is actually there
+
+
+@pytest.mark.parametrize("phi,theta", [(30.0, 0.0), (-77.0, 41.0), (180.0, 90.0), (12.3, -160.0)])
+def test_rotated_model_random_volume(oracle, phi, theta):
+    """A/D/W/S orbit (TestMain.cpp:177-184), non-cubic random volume, 16F target, frame time != 0."""
+    W, H = 640, 360
+    rng = np.random.default_rng(int(abs(phi) * 10))
+    vol = rng.integers(0, 256, size=(24, 40, 56, 4), dtype=np.uint8)
+    ubo0, ubo1 = scene.default_scene(phi, theta, 2.5)
+    p = oracle_params(oracle, ubo0, ubo1)
+    ref, st, _ = _oracle_frame(oracle, vol, oracle.VOL_RGBA8, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0, ubo1)
+        lin = r.render()[0]
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        tex = r.render()[0]
+    assert st["covered"] > 1000
+    assert np.array_equal(lin.view(np.uint32), ref.view(np.uint32))
+    assert np.abs(tex - ref).max() <= 2.0 / 255.0
+    with vr.Renderer(W, H, capi.OUT_RGBA16F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0, ubo1)
+        h = r.render()[0]
+    assert np.array_equal(h.view(np.uint16), oracle.encode(ref, oracle.OUT_RGBA16F))
+
+
+def test_media_scroll_std140_decoding(oracle):
+    """A host that fills a real std140 block (144 B) animates the fetches; the reference's 140-byte
+    C++ struct does not (quirk Q2) — both decode like the shader would read them."""
+    W, H = 320, 180
+    rng = np.random.default_rng(5)
+    vol = rng.integers(0, 256, size=(32, 32, 32, 4), dtype=np.uint8)
+    ubo0, ubo1_host = scene.default_scene(10.0, 5.0, 3.0)
+    std140 = np.zeros(36, np.float32)
+    std140[:19] = ubo1_host[:19]
+    std140[20:36] = rng.uniform(-1, 1, 16).astype(np.float32)
+    outs = []
+    for u1 in (ubo1_host, std140):
+        p = oracle_params(oracle, ubo0, u1)
+        ref, _, _ = _oracle_frame(oracle, vol, oracle.VOL_RGBA8, p, W, H)
+        with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+            r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+            r.set_params(ubo0, u1)
+            img = r.render()[0]
+        assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+        outs.append(img)
+    assert not np.array_equal(outs[0], outs[1])
+    # frame time lands in std140 padding: the image is time-invariant with the C++ layout
+    ubo0b, ubo1b = scene.default_scene(10.0, 5.0, 77.0)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0b, ubo1b)
+        assert np.array_equal(r.render()[0], outs[0])
+
+
+def test_max_steps_and_literals(oracle, default_volume):
+    """runtime maxSteps / step factor / scales (frag.glsl:29-32,42,63 as vr_params fields)."""
+    W, H = 480, 270
+    ubo0, ubo1 = scene.default_scene(33.0, 12.0)
+    kw = dict(max_steps=256, step_scale=3.0, density=1.7, sample_scale=0.35)
+    p = oracle_params(oracle, ubo0, ubo1, **kw)
+    oracle.set_params(p, coord_scale=[1.0, 0.9, 0.6, 0.5])
+    ref, st, _ = _oracle_frame(oracle, default_volume, oracle.VOL_RGBA8, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0, ubo1, coord_scale=[1.0, 0.9, 0.6, 0.5], **kw)
+        img = r.render(flags=capi.RENDER_STATS)[0]
+        assert r.stats()["steps"] == st["steps"]
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        tex = r.render()[0]
+    assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+    assert np.abs(tex - ref).max() <= 2.0 / 255.0
+
+
+def test_row_bands_and_views(oracle):
+    """row-band rendering (the multi-GPU partition) and a multi-view batch equal the full frames."""
+    W, H = 320, 200
+    rng = np.random.default_rng(11)
+    vol = rng.integers(0, 256, size=(16, 16, 16, 4), dtype=np.uint8)
+    views = scene.orbit_views(4)
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, max_views=4) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(view_ubos=views)
+        full = r.render().copy()
+        banded = np.zeros_like(full)
+        bounds = r.row_bands(3)
+        assert bounds[0] == 0 and bounds[-1] == H and all(b1 >= b0 for b0, b1 in zip(bounds, bounds[1:]))
+        for b0, b1 in zip(bounds, bounds[1:]):
+            if b1 > b0:
+                r.render(out=banded, rows=(b0, b1))
+        assert np.array_equal(full, banded)
+        for k in range(4):
+            u0 = views[k, :192].view(np.float32)
+            u1 = views[k, 192:332].view(np.float32)
+            p = oracle_params(oracle, u0, u1)
+            ref, _, _ = _oracle_frame(oracle, vol, oracle.VOL_RGBA8, p, W, H)
+            assert np.array_equal(full[k], oracle.encode(ref, oracle.OUT_RGBA8_UNORM))
+
+
+@pytest.mark.parametrize("layout", [capi.LAYOUT_LINEAR, capi.LAYOUT_TEXTURE])
+def test_single_channel_fp16_grid(oracle, layout):
+    """config 4 shape at test size: one-channel fp16 grid, one fetch per step."""
+    W, H = 480, 270
+    vol = smoke_volume(48, 3)
+    ubo0, ubo1 = scene.default_scene(25.0, 15.0)
+    p = oracle_params(oracle, ubo0, ubo1, density_mode=oracle.DENSITY_SINGLE, sample_scale=0.5, max_steps=192)
+    ref, st, _ = _oracle_frame(oracle, vol.view(np.uint16), oracle.VOL_R16F, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_R16F, layout)
+        r.set_params(ubo0, ubo1, density_mode=capi.DENSITY_SINGLE, sample_scale=0.5, max_steps=192)
+        img = r.render()[0]
+        r.set_params(ubo0, ubo1, density_mode=capi.DENSITY_SINGLE, sample_scale=0.5, max_steps=192, skip_empty=1)
+        skipped = r.render(flags=capi.RENDER_STATS)[0]
+        s = r.stats()
+    assert ref[..., 0].max() > 0.3
+    if layout == capi.LAYOUT_LINEAR:
+        assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+    else:
+        assert np.abs(img - ref).max() <= 2.0 / 255.0
+    # empty-space skipping only ever skips samples that are exactly zero
+    assert s["skipped_steps"] > 0
+    assert np.abs(skipped - img).max() <= 1e-6
+
+
+def test_compositing_light_march_and_early_termination(oracle):
+    """A.6 extensions vs the oracle's restatement of them (self-referential parity)."""
+    W, H = 384, 216
+    vol = smoke_volume(40, 9)
+    ubo0, ubo1 = scene.default_scene(-20.0, 30.0)
+    sun = np.array([1.0, 1.0, 2.0], np.float32)
+    sun /= np.linalg.norm(sun)
+    kw = dict(sample_scale=1.0, max_steps=128, sigma_t=8.0, light_steps=6, light_step_len=2 * 4.0 / 128,
+              ambient=0.15)
+    p = oracle_params(oracle, ubo0, ubo1, density_mode=oracle.DENSITY_SINGLE, **kw)
+    oracle.set_params(p, sun_dir=sun, sun_color=[1.0, 0.95, 0.85])
+    ref, st, _ = _oracle_frame(oracle, vol.view(np.uint16), oracle.VOL_R16F, p, W, H)
+    oracle.set_params(p, early_term_eps=1.0 / 64)
+    ref_et, st_et, _ = _oracle_frame(oracle, vol.view(np.uint16), oracle.VOL_R16F, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_R16F, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0, ubo1, density_mode=capi.DENSITY_SINGLE, sun_dir=sun, sun_color=[1.0, 0.95, 0.85], **kw)
+        img = r.render()[0]
+        r.set_params(ubo0, ubo1, density_mode=capi.DENSITY_SINGLE, sun_dir=sun, sun_color=[1.0, 0.95, 0.85],
+                     early_term_eps=1.0 / 64, **kw)
+        img_et = r.render(flags=capi.RENDER_STATS)[0]
+        s = r.stats()
+    assert ref[..., :3].max() > 0.3
+    assert np.abs(img - ref).max() <= 1e-4            # expf / FMA contraction vs libm, unfused
+    assert np.abs(img_et - ref_et).max() <= 1e-4
+    assert st_et["early"] > 0 and abs(s["early_terminated"] - st_et["early"]) <= max(2, st_et["early"] // 100)
+
+
+def test_procedural_fbm_cloud(oracle):
+    """config 2 shape at test size: in-kernel FastNoise2-semantics fBm density + sun light-march."""
+    W, H = 320, 180
+    ubo0, ubo1 = scene.default_scene()
+    sun = np.array([1.0, 1.0, 2.0], np.float32)
+    sun /= np.linalg.norm(sun)
+    kw = dict(max_steps=64, sigma_t=8.0, light_steps=4, light_step_len=2 * 4.0 / 64, ambient=0.15)
+    p = oracle_params(oracle, ubo0, ubo1, density_mode=oracle.DENSITY_FBM, **kw)
+    oracle.set_params(p, sun_dir=sun, sun_color=[1.0, 0.95, 0.85])
+    ref, st = oracle.render(None, p, W, H)
+    ref8 = oracle.encode(ref, oracle.OUT_RGBA8_UNORM)
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM) as r:
+        r.set_params(ubo0, ubo1, density_mode=capi.DENSITY_FBM, sun_dir=sun, sun_color=[1.0, 0.95, 0.85], **kw)
+        img = r.render()[0]
+    assert ref8[..., 0].max() > 60
+    assert max_abs8(img, ref8) <= TOL8
+    assert psnr8(img, ref8) >= PSNR_MIN
+
+
+def test_known_answers_on_gpu():
+    """closed forms that do not depend on the oracle: constant volume, axis-aligned centre ray."""
+    W, H = 256, 256
+    vol = np.full((8, 8, 8, 4), 255, np.uint8)
+    # camera on the +X axis looking at the origin; square aspect
+    ubo0 = np.zeros(48, np.float32)
+    ubo0[0:16] = scene.identity()
+    ubo0[16:32] = scene.look_at((4.0, 0.0, 0.0), (0.0, 0.0, 0.0), (0.0, 0.0, 1.0))
+    proj = scene.perspective(scene.radians(30.0), 1.0, 0.1, 10.0)
+    proj[5] *= -1
+    ubo0[32:48] = proj
+    ubo1 = np.zeros(36, np.float32)
+    ubo1[0:16] = scene.identity()
+    ubo1[16:19] = (4.0, 0.0, 0.0)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        r.set_params(ubo0, ubo1)
+        img = r.render()[0]
+    # rho = (1*1)*(1+1)*0.2 = 0.4 per step; chord 2 / stepSize 0.03125 = 64 steps on the axis
+    c = img[H // 2, W // 2, 0]
+    n = np.round(-np.log1p(-c) / (0.4 * 0.03125))
+    assert n in (63.0, 64.0)
+    assert abs(c - (1 - np.exp(-0.4 * n * 0.03125))) < 1e-5
+    assert np.all(img[..., 3] == 1.0)
+    assert np.all(img[0, 0, :3] == 0.0)           # clear colour outside the silhouette
+    assert np.array_equal(img[..., 0], img[..., 1]) and np.array_equal(img[..., 0], img[..., 2])

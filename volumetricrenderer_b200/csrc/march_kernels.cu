@@ -16,6 +16,7 @@
 // that discipline through the whole loop and reproduce the oracle's binary32 values bit for bit;
 // the TEX variants use the texture unit's fixed-point trilinear weights and FMA contraction.
 #include "volrt_internal.h"
+#include "noise_device.cuh"
 #include <math_constants.h>
 
 namespace volrt {
@@ -195,64 +196,6 @@ __device__ __forceinline__ float sample_single_linear(const MarchParams& P, cons
     return trilerp(t, c);
 }
 
-// ------------------------------------------------------------------ procedural density
-// FastNoise2 0.10.0 Perlin 3-D (vendor/noise/include/FastNoise/Generators/Perlin.inl:34-64) with
-// HashPrimes / GetGradientDot / InterpQuintic / Lerp of Utils.inl:229-247,294-340, and
-// FractalFBm (Fractal.inl:17-39).  FMAs are contracted here (FastNoise2's AVX2/AVX-512 levels do
-// the same); the oracle evaluates unfused like its SSE2 level — they agree to ~1e-6.
-__device__ __forceinline__ float grad_dot(int hash, float fx, float fy, float fz) {
-    int h13 = hash & 13;
-    float u = h13 < 8 ? fx : fy;
-    float v = h13 == 12 ? fx : fz;
-    v = h13 < 2 ? fy : v;
-    return __int_as_float(__float_as_int(u) ^ (hash << 31)) + __int_as_float(__float_as_int(v) ^ ((hash & 2) << 30));
-}
-__device__ __forceinline__ int hash3(int seed_xz, int xy) {   // (seed ^ x ^ y ^ z) * C; (h >> 15) ^ h
-    int h = (seed_xz ^ xy) * 0x27d4eb2d;
-    return (h >> 15) ^ h;
-}
-__device__ __forceinline__ float quintic(float t) { return t * t * t * fmaf(t, fmaf(t, 6.0f, -15.0f), 10.0f); }
-__device__ __forceinline__ float lerpf(float a, float b, float t) { return fmaf(t, b - a, a); }
-
-__device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
-    float xs = floorf(x), ys = floorf(y), zs = floorf(z);
-    int x0 = __float2int_rn(xs) * 501125321, y0 = __float2int_rn(ys) * 1136930381, z0 = __float2int_rn(zs) * 1720413743;
-    int x1 = x0 + 501125321, y1 = y0 + 1136930381, z1 = z0 + 1720413743;
-    float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
-    float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
-    xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
-    int sz0 = seed ^ z0, sz1 = seed ^ z1;
-    int xy00 = x0 ^ y0, xy10 = x1 ^ y0, xy01 = x0 ^ y1, xy11 = x1 ^ y1;
-    float a = lerpf(lerpf(grad_dot(hash3(sz0, xy00), xf0, yf0, zf0), grad_dot(hash3(sz0, xy10), xf1, yf0, zf0), xs),
-                    lerpf(grad_dot(hash3(sz0, xy01), xf0, yf1, zf0), grad_dot(hash3(sz0, xy11), xf1, yf1, zf0), xs), ys);
-    float b = lerpf(lerpf(grad_dot(hash3(sz1, xy00), xf0, yf0, zf1), grad_dot(hash3(sz1, xy10), xf1, yf0, zf1), xs),
-                    lerpf(grad_dot(hash3(sz1, xy01), xf0, yf1, zf1), grad_dot(hash3(sz1, xy11), xf1, yf1, zf1), xs), ys);
-    return 0.964921414852142333984375f * lerpf(a, b, zs);
-}
-
-__device__ __forceinline__ float fbm_perlin(const MarchParams& P, float x, float y, float z) {
-    int seed = P.fbm_seed;
-    float amp = P.fbm_bounding;
-    float sum = perlin3(seed, x, y, z) * amp;
-    for (int i = 1; i < P.fbm_octaves; ++i) {
-        seed += 1;
-        amp *= P.fbm_gain;
-        x *= P.fbm_lacunarity; y *= P.fbm_lacunarity; z *= P.fbm_lacunarity;
-        sum = fmaf(perlin3(seed, x, y, z), amp, sum);
-    }
-    return sum;
-}
-
-// rho = max(0, .5 fbm + .5 - coverage) * (1 - smoothstep(f0, f1, maxabs(P - 1/2)))
-__device__ __forceinline__ float density_fbm(const MarchParams& P, f3 u) {
-    float m = fmaxf(fmaxf(fabsf(u.x - 0.5f), fabsf(u.y - 0.5f)), fabsf(u.z - 0.5f));
-    float t = __saturatef((m - P.fbm_falloff0) / (P.fbm_falloff1 - P.fbm_falloff0));
-    float edge = 1.0f - t * t * (3.0f - 2.0f * t);
-    if (edge <= 0.0f) return 0.0f;
-    float f = fbm_perlin(P, u.x * P.fbm_frequency, u.y * P.fbm_frequency, u.z * P.fbm_frequency);
-    return fmaxf(0.0f, (0.5f * f + 0.5f) - P.fbm_coverage) * edge;
-}
-
 // ------------------------------------------------------------------ density functors
 struct RayConst {           // per-ray constants of frag.glsl:67-69: cX * scroll_weight, rounded once
     f3 off1, off2, off3;
@@ -282,7 +225,7 @@ __device__ __forceinline__ float density_at(const MarchParams& P, const RayConst
     } else if (VARIANT == MARCH_SINGLE_LINEAR) {
         return mul(sample_single_linear(P, unorm, p), P.sample_scale);
     } else {
-        return density_fbm(P, p);
+        return density_fbm(P.fbm, p.x, p.y, p.z);
     }
 }
 

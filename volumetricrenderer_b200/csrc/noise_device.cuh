@@ -11,15 +11,12 @@
 // results agree to ~1e-5, i.e. <= 1 LSB of the packed texel.
 #pragma once
 #include <cuda_runtime.h>
+#include <math_constants.h>
+#include "volrt_internal.h"
 
 namespace volrt {
 
 constexpr int kPrimeX = 501125321, kPrimeY = 1136930381, kPrimeZ = 1720413743;   // Utils.inl:9-11
-
-struct FbmField {
-    int octaves, seed;
-    float frequency, gain, lacunarity, coverage, falloff0, falloff1, bounding, threshold;
-};
 
 __device__ __forceinline__ float grad_dot(int hash, float fx, float fy, float fz) {
     int h13 = hash & 13;

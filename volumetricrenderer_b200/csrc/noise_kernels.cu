@@ -1,0 +1,172 @@
+// libvolrt volume-bake kernels for sm_100a: the device-side replacement of the reference's
+// start-up bake (source/Etna/TestMain.cpp:43-92), i.e. FastNoise2's uniform-grid driver
+// (vendor/noise/include/FastNoise/Generators/Generator.inl:124-176) over the three generators of
+// noise_device.cuh, the global min/max it returns (Generator.h:43-61), and the app's
+// normalise / power / truncate-to-byte loop (TestMain.cpp:64-92).
+//
+// Layout: x fastest, then y, then z (VulkanCore.cpp:621-648), one voxel per thread, so a warp
+// writes 128 contiguous bytes of a float plane / of the packed RGBA8 volume.
+// The bake is ALU-bound (cellular: 27 hashed cells per voxel) and runs once per volume.
+#include "noise_device.cuh"
+
+namespace volrt {
+
+// ---- order-preserving float <-> uint map so that min/max fold with integer atomics
+__host__ __device__ __forceinline__ unsigned int ordered_bits(float f) {
+#ifdef __CUDA_ARCH__
+    unsigned int b = __float_as_uint(f);
+#else
+    unsigned int b; memcpy(&b, &f, 4);
+#endif
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+void minmax_init(unsigned int* bits2) { bits2[0] = 0xffffffffu; bits2[1] = 0u; }
+float minmax_decode(unsigned int o) {
+    unsigned int b = (o & 0x80000000u) ? (o & 0x7fffffffu) : ~o;
+    float f; memcpy(&f, &b, 4); return f;
+}
+
+template <int GEN>
+__device__ __forceinline__ float eval_noise(int seed, float x, float y, float z) {
+    if (GEN == VR_NOISE_CELLULAR_DISTANCE) return cellular3(seed, x, y, z);
+    if (GEN == VR_NOISE_PERLIN) return perlin3(seed, x, y, z);
+    return simplex3(seed, x, y, z);
+}
+
+// Generator.inl:148-167: pos = float(idx) * frequency (int -> float, then ONE multiply), x fastest.
+template <int GEN, bool STORE>
+__global__ void __launch_bounds__(256) noise_fill_kernel(int n, float frequency, int seed, float* __restrict__ out,
+                                                         unsigned int* __restrict__ minmax_bits) {
+    const size_t total = (size_t)n * n * n;
+    float mn = CUDART_INF_F, mx = -CUDART_INF_F;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int x = (int)(i % n), y = (int)((i / n) % n), z = (int)(i / ((size_t)n * n));
+        float v = eval_noise<GEN>(seed, __fmul_rn((float)x, frequency), __fmul_rn((float)y, frequency), __fmul_rn((float)z, frequency));
+        if (STORE) out[i] = v;
+        mn = fminf(mn, v); mx = fmaxf(mx, v);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    __shared__ float smn[8], smx[8];
+    if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+        if (mn <= mx) {
+            atomicMin(&minmax_bits[0], ordered_bits(mn));
+            atomicMax(&minmax_bits[1], ordered_bits(mx));
+        }
+    }
+}
+
+static int fill_grid(int n) {
+    size_t total = (size_t)n * n * n;
+    size_t blocks = (total + 255) / 256;
+    const size_t cap = 148u * 8u * 16u;          // grid-stride beyond 16 waves of 8 CTAs/SM
+    return (int)(blocks < cap ? blocks : cap);
+}
+
+template <bool STORE>
+static cudaError_t fill_dispatch(const NoiseField& f, int n, float* out, unsigned int* mm, cudaStream_t s) {
+    int g = fill_grid(n);
+    switch (f.generator) {
+        case VR_NOISE_CELLULAR_DISTANCE: noise_fill_kernel<VR_NOISE_CELLULAR_DISTANCE, STORE><<<g, 256, 0, s>>>(n, f.frequency, f.seed, out, mm); break;
+        case VR_NOISE_PERLIN: noise_fill_kernel<VR_NOISE_PERLIN, STORE><<<g, 256, 0, s>>>(n, f.frequency, f.seed, out, mm); break;
+        case VR_NOISE_SIMPLEX: noise_fill_kernel<VR_NOISE_SIMPLEX, STORE><<<g, 256, 0, s>>>(n, f.frequency, f.seed, out, mm); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+cudaError_t launch_noise_fill(const NoiseField& f, int n, float* out, unsigned int* mm, cudaStream_t s) {
+    return fill_dispatch<true>(f, n, out, mm, s);
+}
+cudaError_t launch_noise_minmax_only(const NoiseField& f, int n, unsigned int* mm, cudaStream_t s) {
+    return fill_dispatch<false>(f, n, nullptr, mm, s);
+}
+
+// TestMain.cpp:64-92.  The app is compiled -O0 (CMakeLists.txt:6-7) with no contraction, so
+// every operator is one rounded binary32 op:  s = 1 - (v - min) * (1 / (max - min));
+// s1 *= s1*s1*s1;  byte = (unsigned char)(s * 255.0f)  (truncation toward zero).
+struct PackArgs { PackChannel ch[4]; float inv[4]; };
+
+__device__ __forceinline__ unsigned int pack_one(float v, float mn, float inv, unsigned int power) {
+    float s = __fsub_rn(1.0f, __fmul_rn(__fsub_rn(v, mn), inv));
+    if (power == 4) s = __fmul_rn(s, __fmul_rn(__fmul_rn(s, s), s));       // :80  s *= s*s*s
+    else { float b = s; for (unsigned int k = 1; k < power; ++k) s = __fmul_rn(s, b); }
+    return (unsigned int)__float2int_rz(__fmul_rn(s, 255.0f)) & 0xffu;      // :84-87
+}
+
+__global__ void __launch_bounds__(256) noise_pack_kernel(const __grid_constant__ PackArgs A, long long n, uchar4* __restrict__ out) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        unsigned int b[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            float v = A.ch[k].field ? __ldg(A.ch[k].field + i) : 0.0f;      // :54 zero-initialised buffer
+            b[k] = pack_one(v, A.ch[k].mn, A.inv[k], A.ch[k].power);
+        }
+        out[i] = make_uchar4((unsigned char)b[0], (unsigned char)b[1], (unsigned char)b[2], (unsigned char)b[3]);
+    }
+}
+
+cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_rgba8, cudaStream_t s) {
+    PackArgs a;
+    for (int k = 0; k < 4; ++k) {
+        a.ch[k] = ch[k];
+        volatile float d = ch[k].mx - ch[k].mn;     // binary32, like `1 / (max - min)` at :70-73
+        a.inv[k] = 1.0f / d;
+    }
+    size_t blocks = ((size_t)n + 255) / 256;
+    const size_t cap = 148u * 8u * 16u;
+    noise_pack_kernel<<<(int)(blocks < cap ? blocks : cap), 256, 0, s>>>(a, (long long)n, (uchar4*)out_rgba8);
+    return cudaGetLastError();
+}
+
+// C4/C5 smoke grid: the C2 density field at voxel centres, minus threshold, clamped at 0, as fp16
+__global__ void __launch_bounds__(256) smoke_fill_kernel(const __grid_constant__ FbmField F, int n, __half* __restrict__ out) {
+    const size_t total = (size_t)n * n * n;
+    const float fn = (float)n;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int x = (int)(i % n), y = (int)((i / n) % n), z = (int)(i / ((size_t)n * n));
+        float ux = __fdiv_rn((float)x + 0.5f, fn), uy = __fdiv_rn((float)y + 0.5f, fn), uz = __fdiv_rn((float)z + 0.5f, fn);
+        float rho = fmaxf(0.0f, density_fbm(F, ux, uy, uz) - F.threshold);
+        out[i] = __float2half_rn(rho);
+    }
+}
+cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s) {
+    smoke_fill_kernel<<<fill_grid(n), 256, 0, s>>>(f, n, out);
+    return cudaGetLastError();
+}
+
+// Occupancy of 8^3-voxel bricks: a trilinear fetch at a position inside brick b touches texels
+// 8b-1 .. 8b+8 per axis, so the brick is "empty" iff all of those are exactly zero.  Index -1
+// and N wrap to 0 and N-1 in both addressing modes, so clamping the apron is exact.
+// One CTA per brick, 10x10 (y,z) rows spread over the threads, each reads 10 x-texels.
+__global__ void __launch_bounds__(128) occupancy_kernel(const void* __restrict__ lin, int vol_format, int w, int h, int d,
+                                                        unsigned char* __restrict__ occupied, int bx, int by) {
+    const int b = blockIdx.x;
+    const int ix = b % bx, iy = (b / bx) % by, iz = b / (bx * by);
+    int any = 0;
+    if (threadIdx.x < 100) {
+        int yy = min(max(iy * 8 - 1 + (int)(threadIdx.x % 10), 0), h - 1);
+        int zz = min(max(iz * 8 - 1 + (int)(threadIdx.x / 10), 0), d - 1);
+        size_t row = ((size_t)zz * h + yy) * w;
+        for (int k = 0; k < 10; ++k) {
+            int xx = min(max(ix * 8 - 1 + k, 0), w - 1);
+            size_t idx = row + xx;
+            if (vol_format == VR_VOL_R16F) any |= (((const unsigned short*)lin)[idx] & 0x7fffu) != 0;
+            else if (vol_format == VR_VOL_R8_UNORM) any |= ((const unsigned char*)lin)[idx] != 0;
+            else any |= ((const unsigned int*)lin)[idx] != 0;
+        }
+    }
+    any = __syncthreads_or(any);
+    if (threadIdx.x == 0) occupied[b] = any ? 1 : 0;
+}
+cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int /*address_mode*/,
+                             uint8_t* occupied, int bx, int by, int bz, cudaStream_t s) {
+    occupancy_kernel<<<bx * by * bz, 128, 0, s>>>(lin, vol_format, w, h, d, occupied, bx, by);
+    return cudaGetLastError();
+}
+
+}  // namespace volrt

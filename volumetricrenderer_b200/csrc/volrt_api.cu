@@ -37,6 +37,7 @@ struct vr_context {
     unsigned long long* d_counters = nullptr;
     unsigned long long* h_counters = nullptr;   // pinned
     float* d_row_cost = nullptr;
+    void* flush_buf = nullptr;      // 256 MiB scratch, allocated by the first vr_flush_l2
     vr_stats stats{};
     std::string err;
 };
@@ -158,6 +159,7 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->d_row_cost) cudaFree(c->d_row_cost);
+    if (c->flush_buf) cudaFree(c->flush_buf);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -467,10 +469,8 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.light_steps = (int)p.light_steps; m.light_step_len = p.light_step_len;
     for (int i = 0; i < 3; ++i) { m.sun_dir[i] = p.sun_dir[i]; m.sun_color[i] = p.sun_color[i]; }
     m.ambient = p.ambient; m.sigma_t = p.sigma_t; m.early_term_eps = p.early_term_eps;
-    m.fbm_octaves = p.fbm_octaves; m.fbm_seed = p.fbm_seed; m.fbm_frequency = p.fbm_frequency;
-    m.fbm_gain = p.fbm_gain; m.fbm_lacunarity = p.fbm_lacunarity; m.fbm_coverage = p.fbm_coverage;
-    m.fbm_falloff0 = p.fbm_falloff0; m.fbm_falloff1 = p.fbm_falloff1;
-    m.fbm_bounding = fbm_bounding(p.fbm_octaves, p.fbm_gain);
+    m.fbm = {p.fbm_octaves, p.fbm_seed, p.fbm_frequency, p.fbm_gain, p.fbm_lacunarity, p.fbm_coverage,
+             p.fbm_falloff0, p.fbm_falloff1, fbm_bounding(p.fbm_octaves, p.fbm_gain), 0.0f};
     m.counters = c->d_counters;
     if (p.density_mode == VR_DENSITY_FBM) { variant = MARCH_FBM; return VR_OK; }
     if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_render: no volume uploaded (vr_upload_volume / vr_generate_volume)");
@@ -525,11 +525,12 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
         VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
         VR_CUDA(c, cudaStreamWaitEvent(s, c->ev1, 0));
     }
+    const bool no_march = (t->flags & VR_RENDER_NO_MARCH) != 0;
     VR_CUDA(c, cudaEventRecord(c->ev0, s));
-    VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
+    if (!no_march) VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
     VR_CUDA(c, cudaEventRecord(c->ev1, s));
     c->timed = true;
-    c->stats.kernel_launches = (r1 > r0 && v1 > v0) ? 1 : 0;
+    c->stats.kernel_launches = (!no_march && r1 > r0 && v1 > v0) ? 1 : 0;
     c->stats.rays = (uint64_t)(r1 - r0) * c->width * (v1 - v0);
     if (stats) VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     else std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
@@ -642,5 +643,67 @@ extern "C" vr_status vr_frame_unmap(vr_context* c, void* mapped) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaIpcCloseMemHandle(mapped));
+    return VR_OK;
+}
+
+// ------------------------------------------------------------------ measurement helpers
+extern "C" vr_status vr_flush_l2(vr_context* c) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    const size_t bytes = (size_t)256 << 20;             // 2x the 126 MB L2
+    VR_CUDA(c, cudaSetDevice(c->device));
+    if (!c->flush_buf) VR_CUDA(c, cudaMalloc(&c->flush_buf, bytes));
+    VR_CUDA(c, cudaMemsetAsync(c->flush_buf, 0xA5, bytes, c->stream));
+    return VR_OK;
+}
+extern "C" void* vr_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void vr_host_free(void* p) { if (p) cudaFreeHost(p); }
+
+// peaks[0] = FP32 FMA TFLOP/s (FMA = 2 flop); peaks[1] = trilinear RGBA8 texture fetches, G/s
+// (needs a TEXTURE-layout volume, else 0); peaks[2] = SM count; peaks[3] = SM clock MHz (max).
+extern "C" vr_status vr_measure_peaks(vr_context* c, float* peaks4) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!peaks4) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_measure_peaks: null output");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaDeviceProp prop;
+    VR_CUDA(c, cudaGetDeviceProperties(&prop, c->device));
+    int clock_khz = 0;
+    cudaDeviceGetAttribute(&clock_khz, cudaDevAttrClockRate, c->device);
+    const int sms = prop.multiProcessorCount;
+    float* sink = (float*)c->d_counters;
+    cudaEvent_t e0, e1;
+    VR_CUDA(c, cudaEventCreate(&e0));
+    VR_CUDA(c, cudaEventCreate(&e1));
+    float best_fma = 0.0f, best_tex = 0.0f;
+    const int blocks = sms * 8, iters = 8192;
+    for (int rep = 0; rep < 6; ++rep) {               // first reps warm the clocks up
+        cudaEventRecord(e0, c->stream);
+        cudaError_t e = launch_fma_peak(sink, blocks, iters, c->stream);
+        cudaEventRecord(e1, c->stream);
+        if (e != cudaSuccess || cudaEventSynchronize(e1) != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return fail(c, VR_ERR_CUDA, "fma_peak", e); }
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        double flop = 2.0 * 16.0 * (double)iters * 256.0 * (double)blocks;
+        float tf = (float)(flop / (ms * 1e-3) / 1e12);
+        if (rep >= 2 && tf > best_fma) best_fma = tf;
+    }
+    if (c->tex && c->vdesc.format == VR_VOL_RGBA8_UNORM) {
+        const int tblocks = sms * 16, titers = 2048;
+        for (int rep = 0; rep < 5; ++rep) {
+            cudaEventRecord(e0, c->stream);
+            cudaError_t e = launch_tex_peak(c->tex, sink, tblocks, titers, c->stream);
+            cudaEventRecord(e1, c->stream);
+            if (e != cudaSuccess || cudaEventSynchronize(e1) != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return fail(c, VR_ERR_CUDA, "tex_peak", e); }
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, e0, e1);
+            float g = (float)(4.0 * (double)titers * 128.0 * (double)tblocks / (ms * 1e-3) / 1e9);
+            if (rep >= 1 && g > best_tex) best_tex = g;
+        }
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    peaks4[0] = best_fma; peaks4[1] = best_tex; peaks4[2] = (float)sms; peaks4[3] = (float)clock_khz / 1000.0f;
     return VR_OK;
 }

@@ -28,6 +28,12 @@ struct BrickInfo {          // min-max grid for empty-space skipping (8^3 voxel 
     float inv_brick[3];        // bricks per unit of texture coordinate
 };
 
+// procedural density: FastNoise2 FractalFBm over Perlin, remapped
+struct FbmField {
+    int octaves, seed;
+    float frequency, gain, lacunarity, coverage, falloff0, falloff1, bounding, threshold;
+};
+
 struct MarchParams {
     // target
     int width, height;
@@ -52,8 +58,7 @@ struct MarchParams {
     float light_step_len, sun_dir[3], sun_color[3], ambient, sigma_t, early_term_eps;
     int skip_empty;
     BrickInfo bricks;
-    int fbm_octaves, fbm_seed;
-    float fbm_frequency, fbm_gain, fbm_lacunarity, fbm_coverage, fbm_falloff0, fbm_falloff1, fbm_bounding;
+    FbmField fbm;
     // device counters (VR_RENDER_STATS): covered, steps, early, light samples, skipped
     unsigned long long* counters;
 };
@@ -79,13 +84,12 @@ cudaError_t launch_noise_fill(const NoiseField& f, int n, float* out, unsigned i
 cudaError_t launch_noise_minmax_only(const NoiseField& f, int n, unsigned int* minmax_bits, cudaStream_t s);
 struct PackChannel { const float* field; float mn, mx; uint32_t power; };
 cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_rgba8, cudaStream_t s);
-struct FbmField {
-    int octaves, seed;
-    float frequency, gain, lacunarity, coverage, falloff0, falloff1, bounding, threshold;
-};
 cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s);
 cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int address_mode,
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
+// ---- peak_kernels.cu: measured roofline denominators
+cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s);
+cudaError_t launch_tex_peak(cudaTextureObject_t tex, float* sink, int blocks, int iters, cudaStream_t s);
 void minmax_init(unsigned int* bits2_host);
 float minmax_decode(unsigned int bits);
 

@@ -1,0 +1,249 @@
+"""Host-side mirror of the reference's renderer surface for the hot path, over the libvolrt C ABI.
+
+Reference call site (source/Etna/TestMain.cpp)            ->  here
+    renderer.Init(); AddRenderPass("BasePass", ...) :121-166  ->  Renderer(width, height, format)
+    vkc::Texture3D texture(pixelData, extent)       :128      ->  Renderer.upload_volume(texels)
+    the start-up bake                               :43-92    ->  Renderer.generate_volume()
+    object/globalUniformBuffer.Update(&osd/&gsd)    :248-249  ->  Renderer.set_params(ubo0, ubo1, ...)
+    EnqueueRenderPass + BeginFrame/EndFrame         :194-255  ->  Renderer.render()
+    renderer.Shutdown()                             :260      ->  Renderer.close()
+
+Every method is one C-ABI call into libvolrt.so (CUDA, sm_100a).  There is no CPU path: errors
+(including "no CUDA device") raise VolrtError carrying vr_last_error().
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+
+_OUT_DTYPE = {capi.OUT_RGBA8_UNORM: np.uint8, capi.OUT_RGBA8_SRGB: np.uint8, capi.OUT_RGBA16F: np.float16,
+              capi.OUT_RGBA32F: np.float32}
+_VOL_DTYPE = {capi.VOL_RGBA8_UNORM: (np.uint8, 4), capi.VOL_R16F: (np.float16, 1), capi.VOL_R8_UNORM: (np.uint8, 1)}
+
+
+class VolrtError(RuntimeError):
+    def __init__(self, status, message):
+        name = capi.STATUS_NAMES[status] if 0 <= status < len(capi.STATUS_NAMES) else str(status)
+        super().__init__("%s: %s" % (name, message))
+        self.status = status
+
+
+class PinnedArray:
+    """numpy view over page-locked host memory from vr_host_alloc (frees on close / GC)."""
+
+    def __init__(self, shape, dtype):
+        self._lib = capi.load()
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self.ptr = self._lib.vr_host_alloc(nbytes)
+        if not self.ptr:
+            raise VolrtError(capi.VR_ERR_OUT_OF_MEMORY, "vr_host_alloc(%d) failed" % nbytes)
+        buf = (C.c_char * nbytes).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def close(self):
+        if self.ptr:
+            self.array = None
+            self._lib.vr_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Renderer:
+    def __init__(self, width=1280, height=720, fmt=capi.OUT_RGBA8_UNORM, device=0, max_views=1):
+        self._lib = capi.load()
+        self._ctx = C.c_void_p()
+        self.width, self.height, self.format, self.max_views = width, height, fmt, max_views
+        info = capi.vr_create_info(C.sizeof(capi.vr_create_info), device, width, height, fmt, max_views, 0)
+        st = self._lib.vr_create(C.byref(info), C.byref(self._ctx))
+        if st != capi.VR_OK:
+            msg = self._lib.vr_last_error(None)
+            self._ctx = C.c_void_p()
+            raise VolrtError(st, (msg or b"").decode())
+        self.view_count = 1
+        self._keep = []
+
+    # ---- plumbing
+    def _check(self, st):
+        if st != capi.VR_OK:
+            raise VolrtError(st, (self._lib.vr_last_error(self._ctx) or b"").decode())
+
+    def close(self):
+        if self._ctx:
+            self._lib.vr_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- volume
+    def upload_volume(self, texels, fmt=capi.VOL_RGBA8_UNORM, layout=capi.LAYOUT_AUTO,
+                      address_mode=capi.ADDRESS_MIRRORED_REPEAT):
+        """texels: array shaped (depth, height, width[, 4]), tightly packed, x fastest."""
+        dt, ch = _VOL_DTYPE[fmt]
+        t = np.ascontiguousarray(texels)
+        if t.dtype == np.uint16 and dt == np.float16:
+            t = t.view(np.float16)
+        if t.dtype != dt:
+            raise TypeError("volume dtype %s does not match format (want %s)" % (t.dtype, np.dtype(dt)))
+        if t.ndim != (4 if ch == 4 else 3) or (ch == 4 and t.shape[3] != 4):
+            raise ValueError("volume must be shaped (d,h,w%s)" % (",4" if ch == 4 else ""))
+        d, h, w = t.shape[:3]
+        desc = capi.vr_volume_desc(C.sizeof(capi.vr_volume_desc), w, h, d, fmt, address_mode, layout)
+        self._check(self._lib.vr_upload_volume(self._ctx, C.byref(desc), t.ctypes.data))
+        self._vol_shape, self._vol_fmt = t.shape, fmt
+
+    def default_noise_desc(self):
+        d = capi.vr_noise_desc()
+        self._check(self._lib.vr_noise_desc_default(C.byref(d)))
+        return d
+
+    def generate_volume(self, desc=None, fbm_params=None, **kw):
+        """Bake on the device (TestMain.cpp:43-92).  kw overrides fields of the default recipe."""
+        d = desc if desc is not None else self.default_noise_desc()
+        for k, v in kw.items():
+            setattr(d, k, v)
+        self._check(self._lib.vr_generate_volume(self._ctx, C.byref(d), C.byref(fbm_params) if fbm_params is not None else None))
+        n = d.size
+        self._vol_fmt = d.format
+        self._vol_shape = (n, n, n, 4) if d.format == capi.VOL_RGBA8_UNORM else (n, n, n)
+
+    def download_volume(self):
+        dt, _ = _VOL_DTYPE[self._vol_fmt]
+        out = np.empty(self._vol_shape, dt)
+        self._check(self._lib.vr_download_volume(self._ctx, out.ctypes.data, out.nbytes))
+        return out
+
+    # ---- params
+    def default_params(self):
+        p = capi.vr_params()
+        self._check(self._lib.vr_params_default(C.byref(p)))
+        return p
+
+    def set_params(self, ubo0=None, ubo1=None, view_ubos=None, params=None, **kw):
+        """ubo0 / ubo1: the byte images the host writes (arrays or bytes; 192 B and 140 or 144 B).
+        view_ubos: uint8[count, 336] for a multi-view batch.  kw sets any other vr_params field."""
+        p = params if params is not None else self.default_params()
+        keep = []
+        if ubo0 is not None:
+            b0 = np.frombuffer(np.ascontiguousarray(ubo0).tobytes(), np.uint8).copy()
+            p.ubo0, p.ubo0_size = b0.ctypes.data, b0.size
+            keep.append(b0)
+        if ubo1 is not None:
+            b1 = np.frombuffer(np.ascontiguousarray(ubo1).tobytes(), np.uint8).copy()
+            p.ubo1, p.ubo1_size = b1.ctypes.data, b1.size
+            keep.append(b1)
+        if view_ubos is not None:
+            bv = np.ascontiguousarray(view_ubos, np.uint8)
+            if bv.ndim != 2 or bv.shape[1] != 336:
+                raise ValueError("view_ubos must be uint8[count, 336]")
+            p.view_ubos, p.view_count = bv.ctypes.data, bv.shape[0]
+            keep.append(bv)
+        for k, v in kw.items():
+            cur = getattr(p, k)
+            if hasattr(cur, "__len__"):
+                vals = [float(x) for x in np.asarray(v, np.float32).ravel()]
+                if len(vals) != len(cur):
+                    raise ValueError("%s needs %d values" % (k, len(cur)))
+                for i, x in enumerate(vals):
+                    cur[i] = x
+            else:
+                setattr(p, k, v)
+        self._check(self._lib.vr_set_params(self._ctx, C.byref(p)))
+        self.view_count = max(1, p.view_count)
+        return p
+
+    # ---- render
+    def new_frame_buffer(self, views=None, pinned=True):
+        """Host buffer shaped (views, H, W, 4) in the context's output format."""
+        shape = (views or self.view_count, self.height, self.width, 4)
+        if pinned:
+            pa = PinnedArray(shape, _OUT_DTYPE[self.format])
+            self._keep.append(pa)
+            return pa.array
+        return np.empty(shape, _OUT_DTYPE[self.format])
+
+    def render(self, out=None, rows=None, views=None, flags=0, to_host=True):
+        """Render; returns the frame(s) as (views, rows, W, 4) host array (or None if to_host=False)."""
+        r0, r1 = rows if rows is not None else (0, self.height)
+        v0, v1 = views if views is not None else (0, self.view_count)
+        t = capi.vr_target()
+        t.struct_size = C.sizeof(capi.vr_target)
+        t.row_begin, t.row_end, t.view_begin, t.view_end, t.flags = r0, r1, v0, v1, flags
+        if r0 == 0 and r1 == 0:
+            raise ValueError("empty row band")
+        if to_host:
+            if out is None:
+                out = np.empty((self.view_count, self.height, self.width, 4), _OUT_DTYPE[self.format])
+            if out.shape[-3:] != (self.height, self.width, 4) or not out.flags.c_contiguous:
+                raise ValueError("out must be a contiguous (views, H, W, 4) array")
+            t.memory_kind, t.dst = capi.MEM_HOST, out.ctypes.data
+        self._check(self._lib.vr_render(self._ctx, C.byref(t)))
+        if not to_host:
+            return None
+        full = out.reshape(-1, self.height, self.width, 4)
+        return full[v0:v1, r0:r1]
+
+    def render_device(self, dst_ptr, rows=None, row_pitch=0, flags=capi.RENDER_DIRECT):
+        """Render a row band straight into device memory (own or peer-mapped) — the NVLink gather."""
+        r0, r1 = rows if rows is not None else (0, self.height)
+        t = capi.vr_target()
+        t.struct_size = C.sizeof(capi.vr_target)
+        t.memory_kind, t.dst, t.row_pitch = capi.MEM_DEVICE, dst_ptr, row_pitch
+        t.row_begin, t.row_end, t.flags = r0, r1, flags
+        self._check(self._lib.vr_render(self._ctx, C.byref(t)))
+
+    def wait(self):
+        self._check(self._lib.vr_wait(self._ctx))
+
+    def flush_l2(self):
+        self._check(self._lib.vr_flush_l2(self._ctx))
+
+    def measure_peaks(self):
+        out = (C.c_float * 4)()
+        self._check(self._lib.vr_measure_peaks(self._ctx, out))
+        return {"fp32_tflops": out[0], "tex_gfetch": out[1], "sms": int(out[2]), "sm_max_mhz": out[3]}
+
+    def stats(self):
+        s = capi.vr_stats()
+        s.struct_size = C.sizeof(capi.vr_stats)
+        self._check(self._lib.vr_get_stats(self._ctx, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in capi.vr_stats._fields_ if k != "struct_size"}
+
+    def frame_info(self):
+        ptr, pitch, stride = C.c_void_p(), C.c_size_t(), C.c_size_t()
+        self._check(self._lib.vr_frame_info(self._ctx, C.byref(ptr), C.byref(pitch), C.byref(stride)))
+        return ptr.value, pitch.value, stride.value
+
+    def row_bands(self, parts):
+        b = (C.c_uint32 * (parts + 1))()
+        self._check(self._lib.vr_row_bands(self._ctx, parts, b))
+        return list(b)
+
+    def frame_export(self):
+        h = (C.c_char * 64)()
+        self._check(self._lib.vr_frame_export(self._ctx, C.cast(h, C.c_void_p)))
+        return bytes(h)
+
+    def frame_import(self, handle):
+        buf = (C.c_char * 64).from_buffer_copy(handle)
+        mapped = C.c_void_p()
+        self._check(self._lib.vr_frame_import(self._ctx, C.cast(buf, C.c_void_p), C.byref(mapped)))
+        return mapped.value
+
+    def frame_unmap(self, mapped):
+        self._check(self._lib.vr_frame_unmap(self._ctx, mapped))
