@@ -184,7 +184,10 @@ int shade_pixel(const Ctx& c, const float* invPV, const float* invModel, int W, 
                 if (accumDist * stepSize * p->density > stop) { ++i; ++*early; break; }
             }
             accumDist *= stepSize;
-            float color = 1.0f - std::exp(p->density * std::fmin(-accumDist, 0.0f));
+            // exp(): GLSL leaves its precision to the implementation; the oracle takes the correctly
+            // rounded binary32 value (double exp, rounded once) so that an independent implementation
+            // can land on the same bits.
+            float color = 1.0f - (float)std::exp((double)(p->density * std::fmin(-accumDist, 0.0f)));
             out[0] = out[1] = out[2] = color; out[3] = 1.0f;
         } else {
             // --- compositing integrator (A.6)

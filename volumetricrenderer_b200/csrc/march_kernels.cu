@@ -289,7 +289,9 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
             if (et && mul(mul(acc, step_size), P.density) > stop) { early = true; break; }
         }
         acc = mul(acc, step_size);                                                     // :76
-        float c = sub(1.0f, expf(mul(P.density, fminf(-acc, 0.0f))));                  // :79
+        const float e = mul(P.density, fminf(-acc, 0.0f));
+        // STRICT: correctly rounded exp (double, rounded once) like the oracle; one per ray
+        float c = STRICT ? sub(1.0f, (float)exp((double)e)) : 1.0f - __expf(e);            // :79
         cr = cg = cb = c;
     } else {
         // front-to-back compositing with a sun light-march
