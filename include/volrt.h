@@ -240,6 +240,9 @@ VR_API vr_status vr_get_stats(vr_context* ctx, vr_stats* out);
 VR_API vr_status vr_frame_info(vr_context* ctx, void** dev_ptr, size_t* row_pitch, size_t* view_stride);
 /* row bands of equal estimated cost for `parts` GPUs: bounds[parts+1] */
 VR_API vr_status vr_row_bands(vr_context* ctx, uint32_t parts, uint32_t* bounds);
+/* the host half of vr_row_bands (no device needed): cut `height` rows with per-row cost[] into `parts`
+ * contiguous bands of nearly equal cost; bounds[0] = 0 ... bounds[parts] = height */
+VR_API vr_status vr_split_rows(const float* cost, uint32_t height, uint32_t parts, uint32_t* bounds);
 /* NVLink peer gather across processes: rank 0 exports its frame, the others map it and render
  * their band with VR_RENDER_DIRECT into the mapped pointer. handle = 64 bytes (cudaIpcMemHandle_t) */
 VR_API vr_status vr_frame_export(vr_context* ctx, void* handle64);

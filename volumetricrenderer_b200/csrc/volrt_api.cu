@@ -604,16 +604,22 @@ extern "C" vr_status vr_row_bands(vr_context* c, uint32_t parts, uint32_t* bound
     std::vector<float> cost(c->height);
     VR_CUDA(c, cudaMemcpyAsync(cost.data(), c->d_row_cost, sizeof(float) * c->height, cudaMemcpyDeviceToHost, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    return vr_split_rows(cost.data(), c->height, parts, bounds);
+}
+
+extern "C" vr_status vr_split_rows(const float* cost, uint32_t height, uint32_t parts, uint32_t* bounds) {
+    if (!cost || !bounds || parts == 0 || parts > 64 || height == 0) return VR_ERR_INVALID_ARGUMENT;
     double total = 0.0;
-    for (float v : cost) total += v;
+    for (uint32_t y = 0; y < height; ++y) total += cost[y] > 0.0f ? cost[y] : 0.0f;
     bounds[0] = 0;
     double acc = 0.0;
     uint32_t k = 1;
-    for (uint32_t y = 0; y < c->height && k < parts; ++y) {
-        acc += cost[y];
-        while (k < parts && acc >= total * (double)k / (double)parts) bounds[k++] = y + 1;
+    for (uint32_t y = 0; y < height && k < parts; ++y) {
+        acc += cost[y] > 0.0f ? cost[y] : 0.0f;
+        while (k < parts && acc >= total * (double)k / (double)parts && total > 0.0) bounds[k++] = y + 1;
     }
-    while (k <= parts) bounds[k++] = c->height;
+    if (total <= 0.0) for (; k < parts; ++k) bounds[k] = (uint32_t)((uint64_t)height * k / parts);   // no cost: equal heights
+    while (k <= parts) bounds[k++] = height;
     return VR_OK;
 }
 
