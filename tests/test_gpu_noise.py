@@ -1,0 +1,132 @@
+"""GPU parity of the volume bake (noise_fill / noise_pack / smoke_fill kernels) through the C ABI.
+
+Anchors: the reference's own FastNoise2 outputs (tests/golden/, generated from /root/reference) and
+the CPU oracle.  FastNoise2's SIMD levels differ among themselves by <= 1 LSB of the packed byte
+(SURVEY.md Appendix B.1), so the bar for the packed RGBA8 volume is: every byte within 1 LSB of the
+reference's, with a small mismatch rate; channel G == 255 exactly (quirk Q1)."""
+import os
+
+import numpy as np
+import pytest
+
+import volumetricrenderer_b200 as vr
+from volumetricrenderer_b200 import capi
+
+pytestmark = pytest.mark.gpu
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(os.path.join(HERE, "golden", "fastnoise2_golden.npz"))
+
+
+@pytest.fixture(scope="module")
+def device_bake():
+    with vr.Renderer(64, 64, capi.OUT_RGBA8_UNORM) as r:
+        r.generate_volume()                       # vr_noise_desc_default = TestMain.cpp:43-92
+        return r.download_volume()
+
+
+def test_default_bake_vs_reference_fixture(device_bake, golden):
+    vol = device_bake
+    assert vol.shape == (128, 128, 128, 4) and vol.dtype == np.uint8
+    assert vol[..., 1].min() == 255 and vol[..., 1].max() == 255                      # Q1
+    for level in ("sse2", "avx2"):
+        d = np.abs(vol[40:56, 60:76, 100:116].astype(np.int32) - golden["bake_crop_" + level].astype(np.int32))
+        assert d.max() <= 1
+        assert (d > 0).mean() <= 0.03
+        assert np.abs(vol.reshape(-1, 4).mean(axis=0) - golden["bake_mean_" + level]).max() <= 0.05
+        h = np.bincount(vol[..., 0].ravel(), minlength=256)
+        assert np.abs(h - golden["bake_hist_r_" + level]).sum() <= 0.03 * vol[..., 0].size
+
+
+def test_default_bake_vs_oracle(device_bake, default_volume):
+    d = np.abs(device_bake.astype(np.int32) - default_volume.astype(np.int32))
+    assert d.max() <= 1
+    rate = (d > 0).reshape(-1, 4).mean(axis=0)
+    assert rate[1] == 0.0 and rate.max() <= 0.02, rate
+
+
+def test_custom_recipe_and_size(oracle):
+    """a non-default recipe at 48^3: Perlin in R (power 1), Simplex in G, Cellular in B and A (power 4)"""
+    n = 48
+    with vr.Renderer(64, 64, capi.OUT_RGBA8_UNORM) as r:
+        d = r.default_noise_desc()
+        d.size = n
+        d.channel[0] = capi.vr_noise_channel(capi.NOISE_PERLIN, 0.11, 7, capi.NOISE_SAME, 0.0, 0, 1)
+        d.channel[1] = capi.vr_noise_channel(capi.NOISE_SIMPLEX, 0.07, 8, capi.NOISE_SAME, 0.0, 0, 1)
+        d.channel[2] = capi.vr_noise_channel(capi.NOISE_CELLULAR_DISTANCE, 0.05, 9, capi.NOISE_SAME, 0.0, 0, 1)
+        d.channel[3] = capi.vr_noise_channel(capi.NOISE_CELLULAR_DISTANCE, 0.05, 9, capi.NOISE_SAME, 0.0, 0, 4)
+        r.generate_volume(desc=d)
+        vol = r.download_volume()
+    assert vol.shape == (n, n, n, 4)
+    import ctypes as C
+    fields, mm = [], []
+    for gen, f, s in [(oracle.NOISE_PERLIN, 0.11, 7), (oracle.NOISE_SIMPLEX, 0.07, 8), (oracle.NOISE_CELLULAR, 0.05, 9)]:
+        g, m = oracle.noise_grid(gen, n, f, s)
+        fields.append(g)
+        mm.append(m)
+    # the oracle's pack raises channel 0 to the 4th power (TestMain.cpp:80): feed Cellular there
+    ref = np.zeros((n, n, n, 4), np.uint8)
+    fp = C.POINTER(C.c_float)
+    m8 = np.concatenate([mm[2], mm[1], mm[0], mm[2]]).astype(np.float32)
+    oracle.lib().vo_pack_rgba8(fields[2].ctypes.data_as(fp), fields[1].ctypes.data_as(fp), fields[0].ctypes.data_as(fp),
+                               fields[2].ctypes.data_as(fp), m8.ctypes.data_as(fp), n ** 3,
+                               ref.ctypes.data_as(C.POINTER(C.c_uint8)))
+    assert np.abs(vol[..., 3].astype(np.int32) - ref[..., 0]).max() <= 1      # cellular ^4
+    assert np.abs(vol[..., 1].astype(np.int32) - ref[..., 1]).max() <= 1      # simplex
+    assert np.abs(vol[..., 0].astype(np.int32) - ref[..., 2]).max() <= 1      # perlin
+    assert np.abs(vol[..., 2].astype(np.int32) - ref[..., 3]).max() <= 1      # cellular ^1
+    assert vol[..., 0].std() > 20 and vol[..., 2].std() > 20
+
+
+def test_smoke_field_fp16_vs_oracle(oracle):
+    """C4/C5 grid: the C2 fBm density at voxel centres as fp16 (vr_generate_volume, VR_VOL_R16F)"""
+    n = 40
+    p = oracle.params_default()
+    ref = oracle.bake_smoke_r16f(n, p, 0.1).view(np.float16).astype(np.float32)
+    with vr.Renderer(64, 64, capi.OUT_RGBA8_UNORM) as r:
+        r.generate_volume(size=n, format=capi.VOL_R16F, threshold=0.1)
+        vol = r.download_volume().astype(np.float32)
+    assert vol.shape == (n, n, n)
+    assert ref.max() > 0.2 and (ref == 0).mean() > 0.2
+    assert np.abs(vol - ref).max() <= 2e-4                   # FMA contraction vs unfused + fp16 rounding
+    assert ((vol == 0) != (ref == 0)).mean() <= 1e-3
+
+
+def test_generate_then_render_equals_upload_then_render(device_bake):
+    """the device-baked volume and the same bytes uploaded from the host render the same frame"""
+    from volumetricrenderer_b200 import scene
+    u0, u1 = scene.default_scene()
+    with vr.Renderer(640, 360, capi.OUT_RGBA8_UNORM) as r:
+        r.generate_volume()
+        r.set_params(u0, u1)
+        a = r.render()[0].copy()
+        r.upload_volume(device_bake, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        b = r.render()[0].copy()
+    assert np.array_equal(a, b) and a[..., 0].max() > 40
+
+
+def test_error_paths():
+    with vr.Renderer(32, 32) as r:
+        with pytest.raises(vr.VolrtError) as e:
+            r.render()
+        assert e.value.status == capi.VR_ERR_BAD_STATE          # no params yet
+        from volumetricrenderer_b200 import scene
+        u0, u1 = scene.default_scene()
+        r.set_params(u0, u1)
+        with pytest.raises(vr.VolrtError) as e:
+            r.render()
+        assert e.value.status == capi.VR_ERR_BAD_STATE and "no volume" in str(e.value)
+        with pytest.raises(vr.VolrtError):
+            r.set_params(u0, u1, max_steps=0)
+        bad = u0.copy()
+        bad[0:16] = 0                                            # singular Model
+        with pytest.raises(vr.VolrtError):
+            r.set_params(bad, u1)
+        with pytest.raises(vr.VolrtError) as e:
+            r.upload_volume(np.zeros((4, 4, 4), np.float16), capi.VOL_R16F, capi.LAYOUT_TEXTURE)
+            r.set_params(u0, u1)
+            r.render()                                           # RGBA product needs an RGBA8 volume
+        assert e.value.status == capi.VR_ERR_BAD_STATE

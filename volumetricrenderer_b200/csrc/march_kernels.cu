@@ -202,7 +202,8 @@ struct RayConst {           // per-ray constants of frag.glsl:67-69: cX * scroll
 };
 
 template <int VARIANT>
-__device__ __forceinline__ float density_at(const MarchParams& P, const RayConst& rc, const float* __restrict__ unorm, f3 p) {
+__device__ __forceinline__ float density_at(const MarchParams& P, const RayConst& rc, const float* __restrict__ unorm,
+                                            const GradLut* lut, f3 p) {
     if (VARIANT == MARCH_RGBA_TEX) {
         // frag.glsl:66-71.  coord = Pin*scale_k + cK*weight_k
         float s1 = tex3D<float4>(P.tex, p.x * P.coord_scale[0], p.y * P.coord_scale[0], p.z * P.coord_scale[0]).x;
@@ -225,7 +226,7 @@ __device__ __forceinline__ float density_at(const MarchParams& P, const RayConst
     } else if (VARIANT == MARCH_SINGLE_LINEAR) {
         return mul(sample_single_linear(P, unorm, p), P.sample_scale);
     } else {
-        return density_fbm(P.fbm, p.x, p.y, p.z);
+        return density_fbm(lut, P.fbm, p.x, p.y, p.z);
     }
 }
 
@@ -240,6 +241,13 @@ __device__ __forceinline__ bool inside01(f3 p) {
     return p.x >= 0.0f && p.x <= 1.0f && p.y >= 0.0f && p.y <= 1.0f && p.z >= 0.0f && p.z <= 1.0f;
 }
 
+// k-th index of 0..n-1 in centre-out order: m, m+1, m-1, m+2, ... (a bijection)
+__device__ __forceinline__ int centre_out(int k, int n) {
+    const int m = n >> 1;
+    int c = (k & 1) ? m + ((k + 1) >> 1) : m - (k >> 1);
+    return c >= n ? 0 : c;
+}
+
 // ------------------------------------------------------------------ the march
 template <int VARIANT, bool COMPOSITE, bool STATS>
 __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ MarchParams P) {
@@ -247,13 +255,23 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
     constexpr bool STRICT = LINEAR;                       // bit-for-bit with the oracle
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
     __shared__ float unorm[LINEAR ? 256 : 1];
+    __shared__ GradLut lut;                               // used by the FBM variant only
     if (LINEAR) {
         for (int i = threadIdx.x; i < 256; i += 128) unorm[i] = dvd((float)i, 255.0f);
         __syncthreads();
     }
+    if (VARIANT == MARCH_FBM) {
+        grad_lut_init(&lut, threadIdx.x);
+        __syncthreads();
+    }
+    // Tile order: CTAs are dispatched in blockIdx order, and a heavy CTA (long chords) lives for a large
+    // part of the frame, so whatever is dispatched last sets the tail.  Visit tile rows and columns
+    // from the screen centre outwards: the object sits around the centre (the reference camera looks
+    // at the origin, TestMain.cpp:225), so the last CTAs are silhouette-edge and empty tiles.
+    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int px = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
-    const int py = P.row_begin + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
+    const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
     const int view = P.view_begin + blockIdx.z;
     if (px >= P.width || py >= P.row_end) return;
     const ViewConst* __restrict__ V = P.views + view;
@@ -283,7 +301,7 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
         const float stop = et ? -logf(P.early_term_eps) : CUDART_INF_F;
         for (int i = 0; i < n; ++i) {
             if (skip && !brick_occupied(P, p)) { if (STATS) ++n_skipped; p = add3(p, ray.step); continue; }
-            float d = density_at<VARIANT>(P, rc, unorm, p);
+            float d = density_at<VARIANT>(P, rc, unorm, &lut, p);
             acc = STRICT ? add(acc, d) : acc + d;
             p = add3(p, ray.step);                                                     // running add, :74
             if (et && mul(mul(acc, step_size), P.density) > stop) { early = true; break; }
@@ -301,7 +319,7 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
         for (int i = 0; i < n; ++i) {
             float rho = 0.0f;
             if (skip && !brick_occupied(P, p)) { if (STATS) ++n_skipped; }
-            else rho = density_at<VARIANT>(P, rc, unorm, p);
+            else rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
             if (rho > 0.0f) {                       // rho == 0 contributes exactly nothing
                 float a = 1.0f - expf(-P.sigma_t * rho * step_size);
                 float S = 1.0f;
@@ -312,7 +330,7 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
                         pl = {pl.x + lv.x, pl.y + lv.y, pl.z + lv.z};
                         if (!inside01(pl)) break;   // the march leaves the box for good (box is convex)
                         if (skip && !brick_occupied(P, pl)) continue;
-                        sumL += density_at<VARIANT>(P, rc, unorm, pl);
+                        sumL += density_at<VARIANT>(P, rc, unorm, &lut, pl);
                         if (STATS) ++n_light;
                     }
                     S = expf(-P.sigma_t * sumL * P.light_step_len);

@@ -48,6 +48,58 @@ __device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
     return 0.964921414852142333984375f * lerpf(a, b, zs);
 }
 
+// ---- Perlin with the gradient taken from a 16-entry shared-memory table --------------------------
+// The select/sign form above costs ~11 ALU-pipe instructions per lattice corner (LOP3 / ISETP / FSEL /
+// SHF) and the ALU pipe issues one warp instruction every other cycle, which made the fBm march
+// ALU-bound at 85 % (profiles/r01_march_fbm_baseline.txt).  GetGradientDot only looks at the low
+// nibble of the hash, so the 16 possible gradients (cx,cy,cz in {-1,0,+1}) are tabulated once per
+// CTA: dot = fx*cx + fy*cy + fz*cz is bit-identical to (u ^ h1) + (v ^ h2) (products by +-1 and
+// the added zero are exact, so the one rounding is that of the same two-term sum).
+// Layout: GradLut::xy[n] = (cx,cy) (LDS.64, 16 entries x 8 B cover each bank once) and z[n].x = cz at
+// the same 8-byte stride (16 distinct even banks), so every lane pattern is bank-conflict free.
+// The table offset n*8 comes straight from the integer pipe of the FMA unit:
+//   h = t*C, h8 = t*(C<<3) = h<<3, off = (h8 ^ (h >> 12)) & 0x78  ==  (((h >> 15) ^ h) & 15) * 8
+struct GradLut { float2 xy[16]; float2 z[16]; };
+
+__device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
+    if (tid < 16) {
+        const int n = tid, h13 = n & 13;
+        const int iu = h13 < 8 ? 0 : 1;
+        int iv = h13 == 12 ? 0 : 2;
+        iv = h13 < 2 ? 1 : iv;
+        const float su = (n & 1) ? -1.0f : 1.0f, sv = (n & 2) ? -1.0f : 1.0f;
+        const float cx = (iu == 0 ? su : 0.0f) + (iv == 0 ? sv : 0.0f);
+        const float cy = (iu == 1 ? su : 0.0f) + (iv == 1 ? sv : 0.0f);
+        const float cz = iv == 2 ? sv : 0.0f;
+        lut->xy[n] = make_float2(cx, cy);
+        lut->z[n] = make_float2(cz, 0.0f);
+    }
+}
+
+__device__ __forceinline__ float grad_dot_lut(const GradLut* lut, int t, float fx, float fy, float fz) {
+    const unsigned int h = (unsigned int)t * 0x27d4eb2du;
+    const unsigned int h8 = (unsigned int)t * (0x27d4eb2du << 3);
+    const unsigned int off = (h8 ^ (h >> 12)) & 0x78u;
+    const float2 gxy = *reinterpret_cast<const float2*>(reinterpret_cast<const char*>(lut->xy) + off);
+    const float gz = *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lut->z) + off);
+    return fmaf(fz, gz, fmaf(fy, gxy.y, fx * gxy.x));
+}
+
+__device__ __forceinline__ float perlin3_lut(const GradLut* lut, int seed, float x, float y, float z) {
+    float xs = floorf(x), ys = floorf(y), zs = floorf(z);
+    int x0 = __float2int_rn(xs) * kPrimeX, y0 = __float2int_rn(ys) * kPrimeY, z0 = __float2int_rn(zs) * kPrimeZ;
+    int x1 = x0 + kPrimeX, y1 = y0 + kPrimeY, z1 = z0 + kPrimeZ;
+    float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
+    float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
+    xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
+    int sz0 = seed ^ z0, sz1 = seed ^ z1;
+    float a = lerpf(lerpf(grad_dot_lut(lut, sz0 ^ x0 ^ y0, xf0, yf0, zf0), grad_dot_lut(lut, sz0 ^ x1 ^ y0, xf1, yf0, zf0), xs),
+                    lerpf(grad_dot_lut(lut, sz0 ^ x0 ^ y1, xf0, yf1, zf0), grad_dot_lut(lut, sz0 ^ x1 ^ y1, xf1, yf1, zf0), xs), ys);
+    float b = lerpf(lerpf(grad_dot_lut(lut, sz1 ^ x0 ^ y0, xf0, yf0, zf1), grad_dot_lut(lut, sz1 ^ x1 ^ y0, xf1, yf0, zf1), xs),
+                    lerpf(grad_dot_lut(lut, sz1 ^ x0 ^ y1, xf0, yf1, zf1), grad_dot_lut(lut, sz1 ^ x1 ^ y1, xf1, yf1, zf1), xs), ys);
+    return 0.964921414852142333984375f * lerpf(a, b, zs);
+}
+
 __device__ __forceinline__ float simplex3(int seed, float x, float y, float z) {
     const float F3 = 1.0f / 3.0f, G3 = 1.0f / 2.0f;
     float s = F3 * (x + y + z);
@@ -109,26 +161,26 @@ __device__ __forceinline__ float cellular3(int seed, float x, float y, float z) 
     return best;
 }
 
-__device__ __forceinline__ float fbm_perlin(const FbmField& F, float x, float y, float z) {
+__device__ __forceinline__ float fbm_perlin(const GradLut* lut, const FbmField& F, float x, float y, float z) {
     int seed = F.seed;
     float amp = F.bounding;
-    float sum = perlin3(seed, x, y, z) * amp;
+    float sum = perlin3_lut(lut, seed, x, y, z) * amp;
     for (int i = 1; i < F.octaves; ++i) {
         seed += 1;
         amp *= F.gain;
         x *= F.lacunarity; y *= F.lacunarity; z *= F.lacunarity;
-        sum = fmaf(perlin3(seed, x, y, z), amp, sum);
+        sum = fmaf(perlin3_lut(lut, seed, x, y, z), amp, sum);
     }
     return sum;
 }
 
 // rho = max(0, .5 fbm + .5 - coverage) * (1 - smoothstep(f0, f1, maxabs(P - 1/2)))
-__device__ __forceinline__ float density_fbm(const FbmField& F, float ux, float uy, float uz) {
+__device__ __forceinline__ float density_fbm(const GradLut* lut, const FbmField& F, float ux, float uy, float uz) {
     float m = fmaxf(fmaxf(fabsf(ux - 0.5f), fabsf(uy - 0.5f)), fabsf(uz - 0.5f));
     float t = __saturatef((m - F.falloff0) / (F.falloff1 - F.falloff0));
     float edge = 1.0f - t * t * (3.0f - 2.0f * t);
     if (edge <= 0.0f) return 0.0f;
-    float f = fbm_perlin(F, ux * F.frequency, uy * F.frequency, uz * F.frequency);
+    float f = fbm_perlin(lut, F, ux * F.frequency, uy * F.frequency, uz * F.frequency);
     return fmaxf(0.0f, (0.5f * f + 0.5f) - F.coverage) * edge;
 }
 

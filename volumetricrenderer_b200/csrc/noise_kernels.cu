@@ -125,12 +125,15 @@ cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_r
 
 // C4/C5 smoke grid: the C2 density field at voxel centres, minus threshold, clamped at 0, as fp16
 __global__ void __launch_bounds__(256) smoke_fill_kernel(const __grid_constant__ FbmField F, int n, __half* __restrict__ out) {
+    __shared__ GradLut lut;
+    grad_lut_init(&lut, threadIdx.x);
+    __syncthreads();
     const size_t total = (size_t)n * n * n;
     const float fn = (float)n;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         int x = (int)(i % n), y = (int)((i / n) % n), z = (int)(i / ((size_t)n * n));
         float ux = __fdiv_rn((float)x + 0.5f, fn), uy = __fdiv_rn((float)y + 0.5f, fn), uz = __fdiv_rn((float)z + 0.5f, fn);
-        float rho = fmaxf(0.0f, density_fbm(F, ux, uy, uz) - F.threshold);
+        float rho = fmaxf(0.0f, density_fbm(&lut, F, ux, uy, uz) - F.threshold);
         out[i] = __float2half_rn(rho);
     }
 }
