@@ -105,6 +105,14 @@ enum {
                                       peers have just gathered into) to dst                         */
 };
 
+/* vr_create_info.flags: how pixels are handed to warps.  Default (0) = by cost of a step: cheap steps
+ * (texture fetches) use one CTA per 16x8 tile; heavy steps (procedural density, light-march) use
+ * persistent warps pulling 8x4 tiles off a device-side queue (one vr_render in flight per context). */
+enum {
+    VR_CREATE_SCHEDULE_DIRECT = 1u << 0,
+    VR_CREATE_SCHEDULE_PERSISTENT = 1u << 1
+};
+
 /* replaces renderer.Init() + AddRenderPass("BasePass", ...) + render-target creation:
  * source/Etna/TestMain.cpp:121-122,156-166; Core/Vulkan/VulkanRenderer.cpp:17-118,232-256 */
 typedef struct vr_create_info {

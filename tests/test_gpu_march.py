@@ -177,7 +177,9 @@ def test_single_channel_fp16_grid(oracle, layout):
         assert np.abs(img - ref).max() <= 2.0 / 255.0
     # empty-space skipping only ever skips samples that are exactly zero
     assert s["skipped_steps"] > 0
-    assert np.abs(skipped - img).max() <= 1e-6
+    # same samples; the ray-split schedule of the texture path re-associates the sum and takes positions as
+    # Pin + i*stepVec (a 1e-5 shift can move a hardware filter weight by one 1/256 step)
+    assert np.abs(skipped - img).max() <= (1e-6 if layout == capi.LAYOUT_LINEAR else 2e-4)
 
 
 def test_compositing_light_march_and_early_termination(oracle):

@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvolrt.so")
+LIB_PATH = os.environ.get("VOLRT_LIB") or os.path.join(HERE, "libvolrt.so")   # VOLRT_LIB: A/B builds
 
 VR_OK, VR_ERR_INVALID_ARGUMENT, VR_ERR_CUDA, VR_ERR_OUT_OF_MEMORY, VR_ERR_UNSUPPORTED, VR_ERR_BAD_STATE = range(6)
 STATUS_NAMES = ["VR_OK", "VR_ERR_INVALID_ARGUMENT", "VR_ERR_CUDA", "VR_ERR_OUT_OF_MEMORY", "VR_ERR_UNSUPPORTED",

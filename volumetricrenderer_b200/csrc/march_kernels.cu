@@ -241,39 +241,15 @@ __device__ __forceinline__ bool inside01(f3 p) {
     return p.x >= 0.0f && p.x <= 1.0f && p.y >= 0.0f && p.y <= 1.0f && p.z >= 0.0f && p.z <= 1.0f;
 }
 
-// k-th index of 0..n-1 in centre-out order: m, m+1, m-1, m+2, ... (a bijection)
-__device__ __forceinline__ int centre_out(int k, int n) {
-    const int m = n >> 1;
-    int c = (k & 1) ? m + ((k + 1) >> 1) : m - (k >> 1);
-    return c >= n ? 0 : c;
-}
-
 // ------------------------------------------------------------------ the march
+// one pixel: ray set-up, step loop, resolve, store  (frag.glsl:34-81 + A.6 extensions)
 template <int VARIANT, bool COMPOSITE, bool STATS>
-__global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ MarchParams P) {
+__device__ __forceinline__ void march_pixel(const MarchParams& P, const float* __restrict__ unorm, const GradLut& lut,
+                                            int px, int py, int view) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     constexpr bool STRICT = LINEAR;                       // bit-for-bit with the oracle
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
-    __shared__ float unorm[LINEAR ? 256 : 1];
-    __shared__ GradLut lut;                               // used by the FBM variant only
-    if (LINEAR) {
-        for (int i = threadIdx.x; i < 256; i += 128) unorm[i] = dvd((float)i, 255.0f);
-        __syncthreads();
-    }
-    if (VARIANT == MARCH_FBM) {
-        grad_lut_init(&lut, threadIdx.x);
-        __syncthreads();
-    }
-    // Tile order: CTAs are dispatched in blockIdx order, and a heavy CTA (long chords) lives for a large
-    // part of the frame, so whatever is dispatched last sets the tail.  Visit tile rows and columns
-    // from the screen centre outwards: the object sits around the centre (the reference camera looks
-    // at the origin, TestMain.cpp:225), so the last CTAs are silhouette-edge and empty tiles.
-    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
-    const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
-    const int view = P.view_begin + blockIdx.z;
-    if (px >= P.width || py >= P.row_end) return;
+    constexpr bool TEXTURED = (VARIANT == MARCH_RGBA_TEX || VARIANT == MARCH_SINGLE_TEX);
     const ViewConst* __restrict__ V = P.views + view;
 
     const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);          // frag.glsl:42
@@ -299,7 +275,25 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
         float acc = 0.0f;
         const bool et = P.early_term_eps > 0.0f;
         const float stop = et ? -logf(P.early_term_eps) : CUDART_INF_F;
-        for (int i = 0; i < n; ++i) {
+        int i = 0;
+        if (TEXTURED && !skip && !et) {
+            // The texture path is latency-bound at the end of a frame (the long rays outlive the
+            // short ones and too few fetches stay in flight to keep the TEX unit busy), so issue the
+            // fetches of STEP_BATCH consecutive steps before consuming any of them.  Positions still come
+            // from the running add of frag.glsl:74 and the sum keeps its order.
+            constexpr int STEP_BATCH = 4;
+            for (; i + STEP_BATCH <= n; i += STEP_BATCH) {
+                float d[STEP_BATCH];
+#pragma unroll
+                for (int k = 0; k < STEP_BATCH; ++k) {
+                    d[k] = density_at<VARIANT>(P, rc, unorm, &lut, p);
+                    p = add3(p, ray.step);
+                }
+#pragma unroll
+                for (int k = 0; k < STEP_BATCH; ++k) acc += d[k];
+            }
+        }
+        for (; i < n; ++i) {
             if (skip && !brick_occupied(P, p)) { if (STATS) ++n_skipped; p = add3(p, ray.step); continue; }
             float d = density_at<VARIANT>(P, rc, unorm, &lut, p);
             acc = STRICT ? add(acc, d) : acc + d;
@@ -355,6 +349,158 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
     }
 }
 
+// k-th index of 0..n-1 in centre-out order: m, m+1, m-1, m+2, ... (a bijection)
+__device__ __forceinline__ int centre_out(int k, int n) {
+    const int m = n >> 1;
+    int c = (k & 1) ? m + ((k + 1) >> 1) : m - (k >> 1);
+    return c >= n ? 0 : c;
+}
+
+template <int VARIANT>
+__device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
+    constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
+    if (LINEAR) for (int i = threadIdx.x; i < 256; i += blockDim.x) unorm[i] = dvd((float)i, 255.0f);
+    if (VARIANT == MARCH_FBM) grad_lut_init(lut, threadIdx.x);
+    if (LINEAR || VARIANT == MARCH_FBM) __syncthreads();
+}
+
+// (a) direct mapping: one CTA of 4 warps per 16x8-pixel tile, a warp per 8x4 sub-tile.  Used where a step
+// is cheap (texture fetches), i.e. the whole frame is ~100 us and a work queue would cost more than it saves.
+// Tile order: CTAs are dispatched in blockIdx order, so visit tile rows and columns from the screen centre
+// outwards — the object sits around the centre (the reference camera looks at the origin,
+// TestMain.cpp:225), which makes the last CTAs silhouette-edge and empty tiles (a short tail).
+template <int VARIANT, bool COMPOSITE, bool STATS>
+__global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ MarchParams P) {
+    constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
+    __shared__ float unorm[LINEAR ? 256 : 1];
+    __shared__ GradLut lut;                               // used by the FBM variant only
+    stage_tables<VARIANT>(unorm, &lut);
+    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
+    const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const int view = P.view_begin + blockIdx.z;
+    if (px >= P.width || py >= P.row_end) return;
+    march_pixel<VARIANT, COMPOSITE, STATS>(P, unorm, lut, px, py, view);
+}
+
+// (b) persistent warps: the grid is sized to the machine (SMs x resident CTAs) and every WARP pulls 8x4-pixel
+// tiles off a global counter, centre-out.  A CTA of the direct mapping keeps its registers until its slowest
+// warp retires — at the silhouette half of a CTA's warps exit at once and their slots idle (measured:
+// 14 % of SM cycles idle, profiles/r01_march_fbm_lut.txt) — and a heavy CTA lives for a third of the
+// frame, so the dispatch tail is long.  With warp-granular pulls no slot waits for a sibling.
+// queue[0] = next tile, queue[1] = warps finished; the last warp out resets both for the next launch.
+#ifndef VOLRT_PERSISTENT_MIN_CTAS
+#define VOLRT_PERSISTENT_MIN_CTAS 9
+#endif
+template <int VARIANT, bool COMPOSITE, bool STATS>
+__global__ void __launch_bounds__(128, VOLRT_PERSISTENT_MIN_CTAS) march_kernel_persistent(const __grid_constant__ MarchParams P) {
+    constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
+    __shared__ float unorm[LINEAR ? 256 : 1];
+    __shared__ GradLut lut;
+    stage_tables<VARIANT>(unorm, &lut);
+    const int lane = threadIdx.x & 31;
+    const int tiles_x = (P.width + 7) >> 3, tiles_y = (P.row_end - P.row_begin + 3) >> 2;
+    const int per_view = tiles_x * tiles_y, total = per_view * P.n_views;
+    // a pull claims `chunk` consecutive tiles: one same-address atomic costs a few cycles at the L2, and a
+    // frame has tens of thousands of (mostly empty) tiles
+    const int chunk = P.queue_chunk > 0 ? P.queue_chunk : 1;
+    for (;;) {
+        int t0 = 0;
+        if (lane == 0) t0 = (int)atomicAdd(&P.queue[0], (unsigned)chunk);
+        t0 = __shfl_sync(0xffffffffu, t0, 0);
+        if (t0 >= total) break;
+        const int t1 = min(t0 + chunk, total);
+        for (int t = t0; t < t1; ++t) {
+            const int v = t / per_view, r = t - v * per_view;
+            const int ky = r / tiles_x, kx = r - ky * tiles_x;
+            const int px = centre_out(kx, tiles_x) * 8 + (lane & 7);
+            const int py = P.row_begin + centre_out(ky, tiles_y) * 4 + (lane >> 3);
+            if (px < P.width && py < P.row_end) march_pixel<VARIANT, COMPOSITE, STATS>(P, unorm, lut, px, py, P.view_begin + v);
+            __syncwarp();
+        }
+    }
+    if (lane == 0) {
+        const unsigned int warps = gridDim.x * (blockDim.x >> 5);
+        __threadfence();
+        if (atomicAdd(&P.queue[1], 1u) == warps - 1) { P.queue[0] = 0u; P.queue[1] = 0u; __threadfence(); }
+    }
+}
+
+// (c) ray-split texture march: S lanes share one ray (lane s takes steps s, s+S, s+2S, ...), a warp holds
+// 32/S rays as a (32/S/2) x 2 pixel tile, and the partial optical depths meet in a shuffle reduction.
+// Why: at 720p the default scene has ~6 100 warps of covered rays for ~5 900 warp slots — a single wave
+// whose duration is the longest ray's dependent chain (110 steps x loaded TEX latency), with the
+// SMs 29 % idle (profiles/r01_march_tex_c1_baseline.txt).  Splitting rays multiplies the warps and
+// divides the chain.  The sum is re-associated and positions are Pin + i*stepVec instead of the running
+// add (difference <= 1e-5 texture units, far below the 2^-8 texel resolution of the hardware
+// filter), so this mapping serves the hardware-filtered variants only; parity for them is the
+// north-star tolerance (2/255, PSNR 50 dB), the strict LINEAR variants keep one thread per ray.
+template <int VARIANT, int S>
+__global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_constant__ MarchParams P) {
+    constexpr int RAYS = 32 / S;            // rays per warp
+    constexpr int RW = RAYS / 2;            // warp tile = RW x 2 pixels
+    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int r = lane / S, sub = lane % S;
+    // CTA tile = (2*RW) x 4 pixels: warps 0,1 side by side on rows 0-1, warps 2,3 on rows 2-3
+    const int px = tx * (2 * RW) + (warp & 1) * RW + (r % RW);
+    const int py = P.row_begin + ty * 4 + (warp >> 1) * 2 + (r / RW);
+    const int view = P.view_begin + blockIdx.z;
+    const bool in_frame = px < P.width && py < P.row_end;
+    const ViewConst* __restrict__ V = P.views + view;
+    const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);
+    Ray ray;
+    const bool covered = in_frame && setup_ray(P, V, px, py, step_size, ray);
+    float acc = 0.0f;
+    if (covered) {
+        RayConst rc;
+        rc.off1 = {mul(V->scroll_y[0], P.scroll_weight[1]), mul(V->scroll_y[1], P.scroll_weight[1]), mul(V->scroll_y[2], P.scroll_weight[1])};
+        rc.off2 = {mul(V->scroll_z[0], P.scroll_weight[2]), mul(V->scroll_z[1], P.scroll_weight[2]), mul(V->scroll_z[2], P.scroll_weight[2])};
+        rc.off3 = {mul(V->scroll_w[0], P.scroll_weight[3]), mul(V->scroll_w[1], P.scroll_weight[3]), mul(V->scroll_w[2], P.scroll_weight[3])};
+        const GradLut* no_lut = nullptr;
+        const int n = ray.n;
+        int i = sub;
+        constexpr int BATCH = 2;
+        for (; i + (BATCH - 1) * S < n; i += BATCH * S) {
+            float d[BATCH];
+#pragma unroll
+            for (int k = 0; k < BATCH; ++k) {
+                const float fi = (float)(i + k * S);
+                f3 p = {fmaf(ray.step.x, fi, ray.pin.x), fmaf(ray.step.y, fi, ray.pin.y), fmaf(ray.step.z, fi, ray.pin.z)};
+                d[k] = density_at<VARIANT>(P, rc, nullptr, no_lut, p);
+            }
+#pragma unroll
+            for (int k = 0; k < BATCH; ++k) acc += d[k];
+        }
+        for (; i < n; i += S) {
+            const float fi = (float)i;
+            f3 p = {fmaf(ray.step.x, fi, ray.pin.x), fmaf(ray.step.y, fi, ray.pin.y), fmaf(ray.step.z, fi, ray.pin.z)};
+            acc += density_at<VARIANT>(P, rc, nullptr, no_lut, p);
+        }
+    }
+#pragma unroll
+    for (int o = 1; o < S; o <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (sub != 0 || !in_frame) return;
+    if (!covered) { store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f); return; }
+    acc *= step_size;                                                                  // frag.glsl:76
+    const float c = 1.0f - __expf(P.density * fminf(-acc, 0.0f));                      // :79
+    store_pixel(P, view, px, py, c, c, c, 1.0f);
+}
+
+template <int VARIANT>
+static cudaError_t launch_split(const MarchParams& p, int split, int rows, int n_views, cudaStream_t s) {
+    const int rw = 32 / split / 2;
+    dim3 grid((p.width + 2 * rw - 1) / (2 * rw), (rows + 3) / 4, n_views);
+    switch (split) {
+        case 2: march_tex_split_kernel<VARIANT, 2><<<grid, 128, 0, s>>>(p); break;
+        case 4: march_tex_split_kernel<VARIANT, 4><<<grid, 128, 0, s>>>(p); break;
+        case 8: march_tex_split_kernel<VARIANT, 8><<<grid, 128, 0, s>>>(p); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
 // per-row sum of step counts (the cost model for row bands)
 __global__ void __launch_bounds__(256) row_cost_kernel(const __grid_constant__ MarchParams P, int view, float* __restrict__ row_cost) {
     const int py = blockIdx.x;
@@ -376,29 +522,66 @@ __global__ void __launch_bounds__(256) row_cost_kernel(const __grid_constant__ M
     }
 }
 
-template <int VARIANT>
-static cudaError_t launch_v(const MarchParams& p, dim3 grid, bool composite, bool stats, cudaStream_t s) {
-    if (composite) {
-        if (stats) march_kernel<VARIANT, true, true><<<grid, 128, 0, s>>>(p);
-        else march_kernel<VARIANT, true, false><<<grid, 128, 0, s>>>(p);
+template <int VARIANT, bool COMPOSITE, bool STATS>
+static cudaError_t launch_one(const MarchParams& p, dim3 grid, bool persistent, cudaStream_t s) {
+    if (persistent) {
+        // resident CTAs per SM x SM count, from the occupancy calculator (registers decide)
+        static int resident = 0;       // per instantiation
+        if (resident == 0) {
+            int dev = 0, sms = 0, per_sm = 0;
+            cudaGetDevice(&dev);
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, march_kernel_persistent<VARIANT, COMPOSITE, STATS>, 128, 0);
+            resident = sms * (per_sm > 0 ? per_sm : 1);
+        }
+        const long long tiles = (long long)((p.width + 7) / 8) * ((p.row_end - p.row_begin + 3) / 4) * p.n_views;
+        const long long want = (tiles + 3) / 4;
+        march_kernel_persistent<VARIANT, COMPOSITE, STATS><<<(unsigned)(want < resident ? want : resident), 128, 0, s>>>(p);
     } else {
-        if (stats) march_kernel<VARIANT, false, true><<<grid, 128, 0, s>>>(p);
-        else march_kernel<VARIANT, false, false><<<grid, 128, 0, s>>>(p);
+        march_kernel<VARIANT, COMPOSITE, STATS><<<grid, 128, 0, s>>>(p);
     }
     return cudaGetLastError();
 }
 
-cudaError_t launch_march(const MarchParams& p, int variant, int n_views, bool stats, cudaStream_t stream) {
-    int rows = p.row_end - p.row_begin;
+template <int VARIANT>
+static cudaError_t launch_v(const MarchParams& p, dim3 grid, bool composite, bool stats, bool persistent, cudaStream_t s) {
+    if (composite) return stats ? launch_one<VARIANT, true, true>(p, grid, persistent, s) : launch_one<VARIANT, true, false>(p, grid, persistent, s);
+    return stats ? launch_one<VARIANT, false, true>(p, grid, persistent, s) : launch_one<VARIANT, false, false>(p, grid, persistent, s);
+}
+
+cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool stats, cudaStream_t stream) {
+    int rows = p_in.row_end - p_in.row_begin;
     if (rows <= 0 || n_views <= 0) return cudaSuccess;
+    MarchParams p = p_in;
+    p.n_views = n_views;
     dim3 grid((p.width + 15) / 16, (rows + 7) / 8, n_views);
     bool composite = p.sigma_t > 0.0f;
+    // schedule: 0 = direct tiles, 1 = persistent warps, -1 = auto
+    bool persistent = p.schedule > 0;    // auto = direct: the queue did not pay off on B200 (measurements)
+    if (!p.queue) persistent = false;
+    if (!p.queue) persistent = false;
+    // ray split (texture variants of the reference integrator only; no skipping / early-out / counters)
+    if ((variant == MARCH_RGBA_TEX || variant == MARCH_SINGLE_TEX) && !composite && !stats && !persistent &&
+        !(p.skip_empty && variant == MARCH_SINGLE_TEX) && !(p.early_term_eps > 0.0f)) {
+        int split = p.ray_split;
+        if (split < 0) {
+            // auto: two lanes per ray while the covered rays (about a quarter of the pixels) would not fill two
+            // waves of the machine; measured on B200 at 1280x720: 1 -> 0.099 ms, 2 -> 0.095, 4 -> 0.138, 8 -> 0.171
+            // (more lanes per ray spread a warp's footprint along the ray and cost L1 data-stage wavefronts)
+            const double warps = (double)p.width * rows * n_views * 0.25 / 32.0;
+            const double slots = 148.0 * 40.0;
+            split = warps >= 2.0 * slots ? 1 : 2;
+        }
+        if (split == 2 || split == 4 || split == 8)
+            return variant == MARCH_RGBA_TEX ? launch_split<MARCH_RGBA_TEX>(p, split, rows, n_views, stream)
+                                             : launch_split<MARCH_SINGLE_TEX>(p, split, rows, n_views, stream);
+    }
     switch (variant) {
-        case MARCH_RGBA_TEX: return launch_v<MARCH_RGBA_TEX>(p, grid, composite, stats, stream);
-        case MARCH_RGBA_LINEAR: return launch_v<MARCH_RGBA_LINEAR>(p, grid, composite, stats, stream);
-        case MARCH_SINGLE_TEX: return launch_v<MARCH_SINGLE_TEX>(p, grid, composite, stats, stream);
-        case MARCH_SINGLE_LINEAR: return launch_v<MARCH_SINGLE_LINEAR>(p, grid, composite, stats, stream);
-        case MARCH_FBM: return launch_v<MARCH_FBM>(p, grid, composite, stats, stream);
+        case MARCH_RGBA_TEX: return launch_v<MARCH_RGBA_TEX>(p, grid, composite, stats, persistent, stream);
+        case MARCH_RGBA_LINEAR: return launch_v<MARCH_RGBA_LINEAR>(p, grid, composite, stats, persistent, stream);
+        case MARCH_SINGLE_TEX: return launch_v<MARCH_SINGLE_TEX>(p, grid, composite, stats, persistent, stream);
+        case MARCH_SINGLE_LINEAR: return launch_v<MARCH_SINGLE_LINEAR>(p, grid, composite, stats, persistent, stream);
+        case MARCH_FBM: return launch_v<MARCH_FBM>(p, grid, composite, stats, persistent, stream);
     }
     return cudaErrorInvalidValue;
 }

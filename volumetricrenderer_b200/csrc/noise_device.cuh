@@ -58,7 +58,8 @@ __device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
 // Layout: GradLut::xy[n] = (cx,cy) (LDS.64, 16 entries x 8 B cover each bank once) and z[n].x = cz at
 // the same 8-byte stride (16 distinct even banks), so every lane pattern is bank-conflict free.
 // The table offset n*8 comes straight from the integer pipe of the FMA unit:
-//   h = t*C, h8 = t*(C<<3) = h<<3, off = (h8 ^ (h >> 12)) & 0x78  ==  (((h >> 15) ^ h) & 15) * 8
+//   h = t*C;  h8 = t*(C<<3) = h<<3;  off = (h8 ^ (h8 >> 15)) & 0x78  ==  (((h >> 15) ^ h) & 15) * 8
+// (bits 3..6 of h8>>15 are bits 15..18 of h: the three bits the left shift drops are never looked at)
 struct GradLut { float2 xy[16]; float2 z[16]; };
 
 __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
@@ -77,9 +78,8 @@ __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
 }
 
 __device__ __forceinline__ float grad_dot_lut(const GradLut* lut, int t, float fx, float fy, float fz) {
-    const unsigned int h = (unsigned int)t * 0x27d4eb2du;
-    const unsigned int h8 = (unsigned int)t * (0x27d4eb2du << 3);
-    const unsigned int off = (h8 ^ (h >> 12)) & 0x78u;
+    const unsigned int h8 = (unsigned int)t * (0x27d4eb2du << 3);      // = h << 3 (mod 2^32)
+    const unsigned int off = (h8 ^ (h8 >> 15)) & 0x78u;
     const float2 gxy = *reinterpret_cast<const float2*>(reinterpret_cast<const char*>(lut->xy) + off);
     const float gz = *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lut->z) + off);
     return fmaf(fz, gz, fmaf(fy, gxy.y, fx * gxy.x));

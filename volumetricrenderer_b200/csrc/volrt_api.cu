@@ -5,6 +5,7 @@
 #include "volrt_internal.h"
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -37,6 +38,10 @@ struct vr_context {
     unsigned long long* d_counters = nullptr;
     unsigned long long* h_counters = nullptr;   // pinned
     float* d_row_cost = nullptr;
+    unsigned int* d_queue = nullptr;   // tile queue of the persistent-warp schedule (self-resetting)
+    int schedule = -1;                 // -1 auto, 0 direct, 1 persistent
+    int queue_chunk = 1;
+    int ray_split = -1;                // lanes per ray (texture march): -1 auto
     void* flush_buf = nullptr;      // 256 MiB scratch, allocated by the first vr_flush_l2
     vr_stats stats{};
     std::string err;
@@ -135,6 +140,16 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
     if ((e = cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMalloc(counters)", e);
     if ((e = cudaMallocHost(&c->h_counters, 8 * sizeof(unsigned long long))) != cudaSuccess) return bail("cudaMallocHost(counters)", e);
     if ((e = cudaMalloc(&c->d_row_cost, sizeof(float) * c->height)) != cudaSuccess) return bail("cudaMalloc(row_cost)", e);
+    if ((e = cudaMalloc(&c->d_queue, 2 * sizeof(unsigned int))) != cudaSuccess) return bail("cudaMalloc(queue)", e);
+    if ((e = cudaMemset(c->d_queue, 0, 2 * sizeof(unsigned int))) != cudaSuccess) return bail("cudaMemset(queue)", e);
+    c->schedule = (info->flags & VR_CREATE_SCHEDULE_DIRECT) ? 0 : (info->flags & VR_CREATE_SCHEDULE_PERSISTENT) ? 1 : -1;
+    if (const char* ev = std::getenv("VOLRT_SCHEDULE")) {            // experiment knob: direct | persistent | auto
+        if (!std::strcmp(ev, "direct")) c->schedule = 0;
+        else if (!std::strcmp(ev, "persistent")) c->schedule = 1;
+        else if (!std::strcmp(ev, "auto")) c->schedule = -1;
+    }
+    if (const char* ev = std::getenv("VOLRT_RAY_SPLIT")) c->ray_split = std::atoi(ev);
+    if (const char* ev = std::getenv("VOLRT_QUEUE_CHUNK")) { int v = std::atoi(ev); if (v > 0 && v <= 1024) c->queue_chunk = v; }
     *out = c;
     return VR_OK;
 }
@@ -159,6 +174,7 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->d_row_cost) cudaFree(c->d_row_cost);
+    if (c->d_queue) cudaFree(c->d_queue);
     if (c->flush_buf) cudaFree(c->flush_buf);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -472,6 +488,10 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.fbm = {p.fbm_octaves, p.fbm_seed, p.fbm_frequency, p.fbm_gain, p.fbm_lacunarity, p.fbm_coverage,
              p.fbm_falloff0, p.fbm_falloff1, fbm_bounding(p.fbm_octaves, p.fbm_gain), 0.0f};
     m.counters = c->d_counters;
+    m.queue = c->d_queue;
+    m.schedule = c->schedule;
+    m.queue_chunk = c->queue_chunk;
+    m.ray_split = c->ray_split;
     if (p.density_mode == VR_DENSITY_FBM) { variant = MARCH_FBM; return VR_OK; }
     if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_render: no volume uploaded (vr_upload_volume / vr_generate_volume)");
     const vr_volume_desc& d = c->vdesc;

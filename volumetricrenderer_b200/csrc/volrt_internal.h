@@ -39,6 +39,11 @@ struct MarchParams {
     int width, height;
     int row_begin, row_end;
     int view_begin;             // blockIdx.z + view_begin = view index
+    int n_views;                // views in this launch (set by launch_march)
+    int schedule;               // -1 auto, 0 direct tiles, 1 persistent warps pulling tiles off `queue`
+    unsigned int* queue;        // [0] next tile, [1] warps finished (self-resetting)
+    int queue_chunk;            // tiles claimed per pull
+    int ray_split;              // lanes per ray of the texture march: -1 auto, 1 none, 2/4/8
     void* out;                  // view 0 / row 0 of the destination frame
     size_t row_pitch, view_stride;
     int out_format;             // vr_output_format
