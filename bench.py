@@ -289,25 +289,43 @@ def run_volrt(args, rank, world, local):
     value = W * H / (ms_per_step * 1e-3) / 1e6
 
     # ---- end to end through the public API with host buffers
-    host = r.new_frame_buffer(pinned=True) if rank == 0 else None
-    def e2e_step():
+    # every step: vr_set_params (the UBO bytes the reference host writes) + vr_render into page-locked
+    # host memory (frame D2H).  N == 1: two frames in flight (VR_RENDER_ASYNC), as the reference's
+    # frame loop has (MAX_FRAMES_IN_FLIGHT = 2, VulkanRenderer.cpp:13): frame k+1 marches while frame k is
+    # copied out; all K frames are complete in host memory when the clock stops.  The synchronous
+    # per-frame latency (set_params + render + copy, nothing overlapped) is reported beside it.
+    hosts = [r.new_frame_buffer(pinned=True), r.new_frame_buffer(pinned=True)] if rank == 0 else [None, None]
+
+    def e2e_step(i, flags=0):
         r.set_params(ubo0, ubo1, **kw)                     # UBO bytes -> device (H2D)
         if world == 1:
-            r.render(out=host)                             # march + frame D2H into pinned memory, synchronous
+            r.render(out=hosts[i & 1], flags=flags)        # march + frame D2H into pinned memory
         else:
             march()
             barrier()                                      # every band has landed in GPU 0's frame
             if rank == 0:
-                r.render(out=host, flags=capi.RENDER_NO_MARCH)
-    for _ in range(3):
-        e2e_step()
+                r.render(out=hosts[i & 1], flags=capi.RENDER_NO_MARCH)
+
+    for i in range(3):
+        e2e_step(i)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(K):
-        e2e_step()
+    for i in range(K):
+        e2e_step(i)
     barrier()
-    e2e_s = (time.perf_counter() - t0) / K
+    sync_s = (time.perf_counter() - t0) / K
+    e2e_s = sync_s
+    if world == 1:
+        for i in range(3):
+            e2e_step(i, capi.RENDER_ASYNC)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(K):
+            e2e_step(i, capi.RENDER_ASYNC)
+        barrier()                                          # vr_wait: every frame is in host memory
+        e2e_s = (time.perf_counter() - t0) / K
     e2e = {"value": W * H / e2e_s / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_s * 1e3,
+           "sync_ms_per_frame": sync_s * 1e3, "frames_in_flight": 2 if world == 1 else 1,
            "h2d_bytes_per_step": 192 + 140, "d2h_bytes_per_step": W * H * 4}
 
     if rank == 0:

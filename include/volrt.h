@@ -96,7 +96,10 @@ typedef enum vr_memory_kind {
 } vr_memory_kind;
 
 enum {
-    VR_RENDER_ASYNC = 1u << 0,     /* return after enqueueing; complete with vr_wait            */
+    VR_RENDER_ASYNC = 1u << 0,     /* return after enqueueing; complete with vr_wait.  With VR_MEM_HOST the
+                                      context keeps two frames in flight (the reference's
+                                      MAX_FRAMES_IN_FLIGHT = 2, VulkanRenderer.cpp:13): the march of the
+                                      next frame overlaps this frame's device-to-host copy          */
     VR_RENDER_DIRECT = 1u << 1,    /* VR_MEM_DEVICE only: the march kernel stores its pixels straight
                                       into dst (which may be another GPU's memory mapped through
                                       NVLink peer access / CUDA IPC) instead of the context frame */

@@ -250,7 +250,7 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
     constexpr bool STRICT = LINEAR;                       // bit-for-bit with the oracle
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
     constexpr bool TEXTURED = (VARIANT == MARCH_RGBA_TEX || VARIANT == MARCH_SINGLE_TEX);
-    const ViewConst* __restrict__ V = P.views + view;
+    const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
 
     const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);          // frag.glsl:42
     Ray ray;
@@ -448,7 +448,7 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
     const int py = P.row_begin + ty * 4 + (warp >> 1) * 2 + (r / RW);
     const int view = P.view_begin + blockIdx.z;
     const bool in_frame = px < P.width && py < P.row_end;
-    const ViewConst* __restrict__ V = P.views + view;
+    const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
     const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);
     Ray ray;
     const bool covered = in_frame && setup_ray(P, V, px, py, step_size, ray);
@@ -504,7 +504,7 @@ static cudaError_t launch_split(const MarchParams& p, int split, int rows, int n
 // per-row sum of step counts (the cost model for row bands)
 __global__ void __launch_bounds__(256) row_cost_kernel(const __grid_constant__ MarchParams P, int view, float* __restrict__ row_cost) {
     const int py = blockIdx.x;
-    const ViewConst* __restrict__ V = P.views + view;
+    const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
     const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);
     float s = 0.0f;
     for (int px = threadIdx.x; px < P.width; px += blockDim.x) {

@@ -19,6 +19,19 @@ struct vr_context {
     void* frame = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // frames in flight (VR_RENDER_ASYNC into host memory): the march of frame k+1 overlaps the D2H copy of
+    // frame k, like the reference's MAX_FRAMES_IN_FLIGHT = 2 (VulkanRenderer.cpp:13).  frame2 = second
+    // device frame, allocated by the first asynchronous host render.
+    cudaStream_t copy_stream = nullptr;
+    void* frame2 = nullptr;
+    cudaEvent_t ev_render_done[2] = {nullptr, nullptr}, ev_copy_done[2] = {nullptr, nullptr};
+    bool copy_pending[2] = {false, false};
+    int slot = 0;
+    cudaEvent_t ev_params = nullptr;   // the H2D copy of the pinned view block has completed
+    bool params_pending = false;
+    bool views_on_device = false;
+    bool foreign_stream_pending = false;   // last render ran on a caller stream (ev1 marks its end)
+    ViewConst view0;
     bool timed = false;
     // volume
     bool has_volume = false;
@@ -133,6 +146,12 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
     if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate", e);
     if ((e = cudaEventCreate(&c->ev0)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaEventCreate(&c->ev1)) != cudaSuccess) return bail("cudaEventCreate", e);
+    if ((e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return bail("cudaStreamCreate(copy)", e);
+    for (int i = 0; i < 2; ++i) {
+        if ((e = cudaEventCreateWithFlags(&c->ev_render_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        if ((e = cudaEventCreateWithFlags(&c->ev_copy_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+    }
+    if ((e = cudaEventCreateWithFlags(&c->ev_params, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     if ((e = cudaMalloc(&c->frame, c->view_stride * c->max_views)) != cudaSuccess) return bail("cudaMalloc(frame)", e);
     c->view_capacity = c->max_views;
     if ((e = cudaMalloc(&c->d_views, sizeof(ViewConst) * c->view_capacity)) != cudaSuccess) return bail("cudaMalloc(views)", e);
@@ -168,7 +187,15 @@ extern "C" void vr_destroy(vr_context* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     release_volume(c);
+    if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     if (c->frame) cudaFree(c->frame);
+    if (c->frame2) cudaFree(c->frame2);
+    for (int i = 0; i < 2; ++i) {
+        if (c->ev_render_done[i]) cudaEventDestroy(c->ev_render_done[i]);
+        if (c->ev_copy_done[i]) cudaEventDestroy(c->ev_copy_done[i]);
+    }
+    if (c->ev_params) cudaEventDestroy(c->ev_params);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->d_views) cudaFree(c->d_views);
     if (c->h_views) cudaFreeHost(c->h_views);
     if (c->d_counters) cudaFree(c->d_counters);
@@ -450,19 +477,26 @@ extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
     if (views > 1 && !p->view_ubos) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: view_count > 1 needs view_ubos");
     if (!p->view_ubos && (!p->ubo0 || !p->ubo1)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: ubo0/ubo1 are null");
     VR_CUDA(c, cudaSetDevice(c->device));
-    // the pinned staging block may still be in flight from the previous frame
-    VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    for (uint32_t k = 0; k < views; ++k) {
-        bool ok;
-        if (p->view_ubos) {
+    if (views == 1 && !p->view_ubos) {
+        // the reference's case: one view per frame.  Its constants travel in the kernel parameters.
+        if (!decode_view((const unsigned char*)p->ubo0, p->ubo0_size, (const unsigned char*)p->ubo1, p->ubo1_size, &c->view0))
+            return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: Model or Projection*View is singular");
+    } else {
+        // the pinned staging block may still be in flight from the previous batch
+        if (c->params_pending) { VR_CUDA(c, cudaEventSynchronize(c->ev_params)); c->params_pending = false; }
+        for (uint32_t k = 0; k < views; ++k) {
             const unsigned char* b = (const unsigned char*)p->view_ubos + (size_t)k * 336;
-            ok = decode_view(b, 192, b + 192, 144, &c->h_views[k]);
-        } else {
-            ok = decode_view((const unsigned char*)p->ubo0, p->ubo0_size, (const unsigned char*)p->ubo1, p->ubo1_size, &c->h_views[k]);
+            if (!decode_view(b, 192, b + 192, 144, &c->h_views[k]))
+                return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: Model or Projection*View is singular");
         }
-        if (!ok) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: Model or Projection*View is singular");
+        // d_views may still be read by a march that was enqueued on a caller's stream
+        if (c->foreign_stream_pending) { VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev1, 0)); c->foreign_stream_pending = false; }
+        VR_CUDA(c, cudaMemcpyAsync(c->d_views, c->h_views, sizeof(ViewConst) * views, cudaMemcpyHostToDevice, c->stream));
+        VR_CUDA(c, cudaEventRecord(c->ev_params, c->stream));
+        c->params_pending = true;
+        c->view0 = c->h_views[0];
     }
-    VR_CUDA(c, cudaMemcpyAsync(c->d_views, c->h_views, sizeof(ViewConst) * views, cudaMemcpyHostToDevice, c->stream));
+    c->views_on_device = !(views == 1 && !p->view_ubos);
     c->params = *p;
     c->params.ubo0 = c->params.ubo1 = c->params.view_ubos = nullptr;   // bytes were copied; do not keep caller pointers
     c->view_count = views;
@@ -478,7 +512,8 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.row_begin = 0; m.row_end = (int)c->height;
     m.out = c->frame; m.row_pitch = c->row_pitch; m.view_stride = c->view_stride;
     m.out_format = (int)c->format;
-    m.views = c->d_views;
+    m.views = c->views_on_device ? c->d_views : nullptr;
+    m.view0 = c->view0;
     m.max_steps = (int)p.max_steps;
     m.step_scale = p.step_scale; m.density = p.density; m.sample_scale = p.sample_scale;
     for (int i = 0; i < 4; ++i) { m.coord_scale[i] = p.coord_scale[i]; m.scroll_weight[i] = p.scroll_weight[i]; }
@@ -541,27 +576,47 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
     if (direct) { m.out = t->dst; m.row_pitch = pitch; m.view_stride = pitch * c->height; }
     const bool stats = (t->flags & VR_RENDER_STATS) != 0;
     if (stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), s));
-    if (t->stream) {   // params were uploaded on the context stream
-        VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-        VR_CUDA(c, cudaStreamWaitEvent(s, c->ev1, 0));
+    if (t->stream && c->views_on_device) {   // the view block was uploaded on the context stream
+        VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_params, 0));
+    }
+    // asynchronous render into host memory: alternate between two device frames and hand the D2H copy to
+    // the copy stream, so that the next frame's march overlaps it
+    const bool pipelined = (t->flags & VR_RENDER_ASYNC) && t->memory_kind == VR_MEM_HOST && !direct && !t->stream;
+    char* frame = (char*)c->frame;
+    int slot = 0;
+    if (pipelined) {
+        if (!c->frame2) VR_CUDA(c, cudaMalloc(&c->frame2, c->view_stride * c->max_views));
+        slot = c->slot;
+        c->slot ^= 1;
+        if (slot == 1) frame = (char*)c->frame2;
+        if (c->copy_pending[slot]) VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_copy_done[slot], 0));   // frame slot is free again
+        m.out = frame;
     }
     const bool no_march = (t->flags & VR_RENDER_NO_MARCH) != 0;
     VR_CUDA(c, cudaEventRecord(c->ev0, s));
     if (!no_march) VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
     VR_CUDA(c, cudaEventRecord(c->ev1, s));
     c->timed = true;
+    c->foreign_stream_pending = t->stream != nullptr;
     c->stats.kernel_launches = (!no_march && r1 > r0 && v1 > v0) ? 1 : 0;
     c->stats.rays = (uint64_t)(r1 - r0) * c->width * (v1 - v0);
     if (stats) VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     else std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
 
     if (t->memory_kind != VR_MEM_NONE && !direct && r1 > r0) {
+        cudaStream_t cs = s;
+        if (pipelined) {
+            VR_CUDA(c, cudaEventRecord(c->ev_render_done[slot], s));
+            VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_render_done[slot], 0));
+            cs = c->copy_stream;
+        }
         for (uint32_t v = v0; v < v1; ++v) {
-            const char* src = (const char*)c->frame + (size_t)v * c->view_stride + (size_t)r0 * c->row_pitch;
+            const char* src = frame + (size_t)v * c->view_stride + (size_t)r0 * c->row_pitch;
             char* dst = (char*)t->dst + (size_t)v * pitch * c->height + (size_t)r0 * pitch;
             VR_CUDA(c, cudaMemcpy2DAsync(dst, pitch, src, c->row_pitch, c->row_pitch, r1 - r0,
-                                         t->memory_kind == VR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, s));
+                                         t->memory_kind == VR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, cs));
         }
+        if (pipelined) { VR_CUDA(c, cudaEventRecord(c->ev_copy_done[slot], c->copy_stream)); c->copy_pending[slot] = true; }
     }
     if (!(t->flags & VR_RENDER_ASYNC)) VR_CUDA(c, cudaStreamSynchronize(s));
     return VR_OK;
@@ -572,6 +627,8 @@ extern "C" vr_status vr_wait(vr_context* c) {
     VR_CUDA(c, cudaSetDevice(c->device));
     if (c->timed) VR_CUDA(c, cudaEventSynchronize(c->ev1));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    c->copy_pending[0] = c->copy_pending[1] = false;
     return VR_OK;
 }
 
@@ -716,11 +773,32 @@ extern "C" vr_status vr_measure_peaks(vr_context* c, float* peaks4) {
         float tf = (float)(flop / (ms * 1e-3) / 1e12);
         if (rep >= 2 && tf > best_fma) best_fma = tf;
     }
-    if (c->tex && c->vdesc.format == VR_VOL_RGBA8_UNORM) {
+    // the fetch peak is measured on the context's RGBA8 texture when it has one, else on a scratch 64^3 one
+    cudaTextureObject_t ptex = (c->tex && c->vdesc.format == VR_VOL_RGBA8_UNORM) ? c->tex : 0;
+    cudaArray_t scratch = nullptr;
+    if (!ptex) {
+        const int n = 64;
+        std::vector<unsigned char> host((size_t)n * n * n * 4);
+        for (size_t i = 0; i < host.size(); ++i) host[i] = (unsigned char)(i * 2654435761u >> 24);
+        cudaChannelFormatDesc cd = cudaCreateChannelDesc<uchar4>();
+        cudaExtent ext = make_cudaExtent(n, n, n);
+        if (cudaMalloc3DArray(&scratch, &cd, ext) == cudaSuccess) {
+            cudaMemcpy3DParms cp = {};
+            cp.srcPtr = make_cudaPitchedPtr(host.data(), n * 4, n, n);
+            cp.dstArray = scratch; cp.extent = ext; cp.kind = cudaMemcpyHostToDevice;
+            cudaResourceDesc rd = {}; rd.resType = cudaResourceTypeArray; rd.res.array.array = scratch;
+            cudaTextureDesc td = {};
+            td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeMirror;
+            td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeNormalizedFloat; td.normalizedCoords = 1;
+            if (cudaMemcpy3D(&cp) != cudaSuccess || cudaCreateTextureObject(&ptex, &rd, &td, nullptr) != cudaSuccess) ptex = 0;
+        }
+        cudaGetLastError();
+    }
+    if (ptex) {
         const int tblocks = sms * 16, titers = 2048;
         for (int rep = 0; rep < 5; ++rep) {
             cudaEventRecord(e0, c->stream);
-            cudaError_t e = launch_tex_peak(c->tex, sink, tblocks, titers, c->stream);
+            cudaError_t e = launch_tex_peak(ptex, sink, tblocks, titers, c->stream);
             cudaEventRecord(e1, c->stream);
             if (e != cudaSuccess || cudaEventSynchronize(e1) != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return fail(c, VR_ERR_CUDA, "tex_peak", e); }
             float ms = 0.0f;
@@ -729,6 +807,7 @@ extern "C" vr_status vr_measure_peaks(vr_context* c, float* peaks4) {
             if (rep >= 1 && g > best_tex) best_tex = g;
         }
     }
+    if (scratch) { if (ptex) cudaDestroyTextureObject(ptex); cudaFreeArray(scratch); }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     peaks4[0] = best_fma; peaks4[1] = best_tex; peaks4[2] = (float)sms; peaks4[3] = (float)clock_khz / 1000.0f;
     return VR_OK;

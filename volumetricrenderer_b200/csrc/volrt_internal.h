@@ -47,7 +47,8 @@ struct MarchParams {
     void* out;                  // view 0 / row 0 of the destination frame
     size_t row_pitch, view_stride;
     int out_format;             // vr_output_format
-    const ViewConst* views;     // device array
+    const ViewConst* views;     // device array (multi-view batches); nullptr = the single view below
+    ViewConst view0;            // single view, carried in the kernel parameters (no H2D copy per frame)
     // reference literals (frag.glsl:29-32,42,63,66-69)
     int max_steps;
     float step_scale, density, sample_scale;
