@@ -228,17 +228,15 @@ def run_volrt(args, rank, world, local):
     r.set_params(ubo0, ubo1, **kw)
 
     # ---- partition: cost-balanced row bands, peer-mapped frame of rank 0
-    rows, mapped = (0, H), None
+    from volumetricrenderer_b200 import multigpu
+    bg = multigpu.BandGather(dist, rank, world, H, mode="peer")
+    row_cost = r.row_cost() if world > 1 else None
     if world > 1:
-        import torch
-        bounds = r.row_bands(world)
-        rows = (bounds[rank], bounds[rank + 1])
-        handle = [r.frame_export() if rank == 0 else None]
-        dist.broadcast_object_list(handle, src=0)
-        if rank != 0:
-            mapped = r.frame_import(handle[0])
+        bg.plan(row_cost=row_cost)
+    mapped = bg.connect_peer(r) if world > 1 else None
 
     def march(flags=0):
+        rows = bg.rows
         if rows[1] <= rows[0]:
             return
         if mapped is not None:
@@ -267,6 +265,13 @@ def run_volrt(args, rank, world, local):
     # ---- device-timed region: K frames, L2 flushed between frames, CUDA events on the launching stream
     for _ in range(Wm):
         r.flush_l2(); march(); r.wait()
+    if world > 1:
+        # feedback re-cut of the bands from measured band times (a renderer does this every frame; here: during
+        # warm-up only, the cut is frozen for the timed frames)
+        for _ in range(4):
+            r.flush_l2(); march(); r.wait()
+            bg.rebalance(row_cost, r.stats()["gpu_ms"] if bg.rows[1] > bg.rows[0] else 0.0)
+    rows = bg.rows
     sampler = ClockSampler(physical_gpu_index(local))
     barrier()
     sampler.start()
@@ -281,6 +286,10 @@ def run_volrt(args, rank, world, local):
     clocks = sampler.stop()
     dev_ms = float(np.sum(ms))
     if dist is not None:
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, dev_ms / K)
+        if rank == 0:
+            print("bands %s  ms per rank %s" % (bg.bounds, ["%.3f" % x for x in per_rank]), file=sys.stderr)
         import torch
         t = torch.tensor([dev_ms], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -350,8 +359,7 @@ def run_volrt(args, rank, world, local):
             except Exception as e:                          # the baseline is a report, not the product
                 line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "port", "sample": "failed: %r" % e}
         print(json.dumps(line), flush=True)
-    if mapped is not None:
-        r.frame_unmap(mapped)
+    bg.disconnect_peer(r)
     barrier()
     r.close()
     if dist is not None:

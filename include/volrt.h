@@ -251,6 +251,8 @@ VR_API vr_status vr_get_stats(vr_context* ctx, vr_stats* out);
 VR_API vr_status vr_frame_info(vr_context* ctx, void** dev_ptr, size_t* row_pitch, size_t* view_stride);
 /* row bands of equal estimated cost for `parts` GPUs: bounds[parts+1] */
 VR_API vr_status vr_row_bands(vr_context* ctx, uint32_t parts, uint32_t* bounds);
+/* the device half of vr_row_bands: cost[height] = per-row sum of step counts from the ray set-up alone */
+VR_API vr_status vr_row_cost(vr_context* ctx, float* cost);
 /* the host half of vr_row_bands (no device needed): cut `height` rows with per-row cost[] into `parts`
  * contiguous bands of nearly equal cost; bounds[0] = 0 ... bounds[parts] = height */
 VR_API vr_status vr_split_rows(const float* cost, uint32_t height, uint32_t parts, uint32_t* bounds);

@@ -90,6 +90,7 @@ EXPORTS = {
     "vr_get_stats": (C.c_int32, [_VP, C.POINTER(vr_stats)]),
     "vr_frame_info": (C.c_int32, [_VP, C.POINTER(_VP), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "vr_row_bands": (C.c_int32, [_VP, C.c_uint32, C.POINTER(C.c_uint32)]),
+    "vr_row_cost": (C.c_int32, [_VP, C.POINTER(C.c_float)]),
     "vr_split_rows": (C.c_int32, [C.POINTER(C.c_float), C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]),
     "vr_frame_export": (C.c_int32, [_VP, _VP]),
     "vr_frame_import": (C.c_int32, [_VP, _VP, C.POINTER(_VP)]),

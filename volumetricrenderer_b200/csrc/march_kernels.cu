@@ -488,6 +488,119 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
     store_pixel(P, view, px, py, c, c, c, 1.0f);
 }
 
+// (d) ray-split compositing march: S lanes share one ray and take consecutive steps of a round
+// (lane s -> step r*S + s), so the expensive part of a step — density plus the sun light-march — runs S
+// steps at a time, and the order-dependent part is stitched with a segmented prefix product:
+//     T_i = T_round * prod_{lanes before}(1 - a),   C += T_i * a_i * L_i,   T_round *= prod_{all lanes}(1 - a)
+// Why: with one thread per ray the heaviest warps of the fBm frame execute ~0.5 M instructions each and share
+// a scheduler with 8 other warps, so their dependent chain is as long as the whole frame: half a frame
+// (a 2-GPU row band) took 80 % of the full frame's time.  Splitting divides that chain by S.
+// Lanes of a ray sit at neighbouring steps, so they mostly agree on "is there density here" and the
+// light-march branch stays coherent.  The sum and the products are re-associated and positions are
+// Pin + i*stepVec: parity is tolerance-based (as it already is for every compositing variant).
+template <int VARIANT, int S>
+__global__ void __launch_bounds__(128) march_composite_split_kernel(const __grid_constant__ MarchParams P) {
+    constexpr int RAYS = 32 / S, RW = RAYS / 2;
+    constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
+    constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
+    __shared__ float unorm[LINEAR ? 256 : 1];
+    __shared__ GradLut lut;
+    stage_tables<VARIANT>(unorm, &lut);
+    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int r = lane / S, sub = lane % S;
+    const int px = tx * (2 * RW) + (warp & 1) * RW + (r % RW);
+    const int py = P.row_begin + ty * 4 + (warp >> 1) * 2 + (r / RW);
+    const int view = P.view_begin + blockIdx.z;
+    const bool in_frame = px < P.width && py < P.row_end;
+    const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
+    const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);
+    Ray ray;
+    const bool covered = in_frame && setup_ray(P, V, px, py, step_size, ray);
+    const int n = covered ? ray.n : 0;
+    int rounds = (n + S - 1) / S;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) rounds = max(rounds, __shfl_xor_sync(0xffffffffu, rounds, o));
+    if (rounds == 0) {
+        if (sub == 0 && in_frame) store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);
+        return;
+    }
+    RayConst rc;
+    rc.off1 = {mul(V->scroll_y[0], P.scroll_weight[1]), mul(V->scroll_y[1], P.scroll_weight[1]), mul(V->scroll_y[2], P.scroll_weight[1])};
+    rc.off2 = {mul(V->scroll_z[0], P.scroll_weight[2]), mul(V->scroll_z[1], P.scroll_weight[2]), mul(V->scroll_z[2], P.scroll_weight[2])};
+    rc.off3 = {mul(V->scroll_w[0], P.scroll_weight[3]), mul(V->scroll_w[1], P.scroll_weight[3]), mul(V->scroll_w[2], P.scroll_weight[3])};
+    const bool skip = CAN_SKIP && P.skip_empty;
+    const bool et = P.early_term_eps > 0.0f;
+    const f3 lv = {P.sun_dir[0] * P.light_step_len * 0.5f, P.sun_dir[1] * P.light_step_len * 0.5f, P.sun_dir[2] * P.light_step_len * 0.5f};
+    float T = 1.0f, cr = 0.0f, cg = 0.0f, cb = 0.0f;
+    bool done = !covered;
+    for (int round = 0; round < rounds; ++round) {
+        const int i = round * S + sub;
+        float a = 0.0f, Sl = 1.0f;
+        if (!done && i < n) {
+            const float fi = (float)i;
+            const f3 p = {fmaf(ray.step.x, fi, ray.pin.x), fmaf(ray.step.y, fi, ray.pin.y), fmaf(ray.step.z, fi, ray.pin.z)};
+            float rho = 0.0f;
+            if (!(skip && !brick_occupied(P, p))) rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
+            if (rho > 0.0f) {
+                a = 1.0f - expf(-P.sigma_t * rho * step_size);
+                if (P.light_steps > 0) {
+                    float sumL = 0.0f;
+                    f3 pl = p;
+                    for (int j = 1; j <= P.light_steps; ++j) {
+                        pl = {pl.x + lv.x, pl.y + lv.y, pl.z + lv.z};
+                        if (!inside01(pl)) break;
+                        if (skip && !brick_occupied(P, pl)) continue;
+                        sumL += density_at<VARIANT>(P, rc, unorm, &lut, pl);
+                    }
+                    Sl = expf(-P.sigma_t * sumL * P.light_step_len);
+                }
+            }
+        }
+        // inclusive prefix product of (1 - a) over the S lanes of the ray
+        float incl = 1.0f - a;
+#pragma unroll
+        for (int o = 1; o < S; o <<= 1) {
+            const float v = __shfl_up_sync(0xffffffffu, incl, o, S);
+            if (sub >= o) incl *= v;
+        }
+        float excl = __shfl_up_sync(0xffffffffu, incl, 1, S);
+        if (sub == 0) excl = 1.0f;
+        const float total = __shfl_sync(0xffffffffu, incl, S - 1, S);
+        const float Ti = T * excl;                        // transmittance in front of this lane's step
+        if (!(et && Ti < P.early_term_eps)) {            // the reference loop would have stopped before this step
+            const float w = Ti * a;
+            cr = fmaf(w, fmaf(P.sun_color[0], Sl, P.ambient), cr);
+            cg = fmaf(w, fmaf(P.sun_color[1], Sl, P.ambient), cg);
+            cb = fmaf(w, fmaf(P.sun_color[2], Sl, P.ambient), cb);
+        }
+        T *= total;
+        if (et && T < P.early_term_eps) done = true;     // same value in all lanes of the ray
+    }
+#pragma unroll
+    for (int o = 1; o < S; o <<= 1) {
+        cr += __shfl_xor_sync(0xffffffffu, cr, o);
+        cg += __shfl_xor_sync(0xffffffffu, cg, o);
+        cb += __shfl_xor_sync(0xffffffffu, cb, o);
+    }
+    if (sub != 0 || !in_frame) return;
+    if (!covered) { store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f); return; }
+    store_pixel(P, view, px, py, cr, cg, cb, 1.0f);
+}
+
+template <int VARIANT>
+static cudaError_t launch_composite_split(const MarchParams& p, int split, int rows, int n_views, cudaStream_t s) {
+    const int rw = 32 / split / 2;
+    dim3 grid((p.width + 2 * rw - 1) / (2 * rw), (rows + 3) / 4, n_views);
+    switch (split) {
+        case 2: march_composite_split_kernel<VARIANT, 2><<<grid, 128, 0, s>>>(p); break;
+        case 4: march_composite_split_kernel<VARIANT, 4><<<grid, 128, 0, s>>>(p); break;
+        case 8: march_composite_split_kernel<VARIANT, 8><<<grid, 128, 0, s>>>(p); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
 template <int VARIANT>
 static cudaError_t launch_split(const MarchParams& p, int split, int rows, int n_views, cudaStream_t s) {
     const int rw = 32 / split / 2;
@@ -560,6 +673,27 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     bool persistent = p.schedule > 0;    // auto = direct: the queue did not pay off on B200 (measurements)
     if (!p.queue) persistent = false;
     if (!p.queue) persistent = false;
+    // ray split of the compositing integrator (any density source; not with device counters)
+    if (composite && !stats && !persistent) {
+        int split = p.ray_split_composite;
+        if (split < 0) {
+            // auto: by how many waves of the machine the covered rays (about a quarter of the pixels) make.
+            // Measured on B200 (fBm, ms/frame): 1080p one GPU 2.13 / 2.03 / 2.14 / 2.52 for 1/2/4/8 lanes;
+            // half of it (2-GPU band) 1.70 / 1.35 / 1.25 / 1.41; 4K one GPU 19.5 (1 lane) vs 20.6 (4 lanes).
+            const double warps = (double)p.width * rows * n_views * 0.25 / 32.0;
+            const double waves = warps / (148.0 * 32.0);
+            split = waves >= 10.0 ? 1 : waves >= 2.5 ? 2 : 4;
+        }
+        if (split == 2 || split == 4 || split == 8) {
+            switch (variant) {
+                case MARCH_RGBA_TEX: return launch_composite_split<MARCH_RGBA_TEX>(p, split, rows, n_views, stream);
+                case MARCH_RGBA_LINEAR: return launch_composite_split<MARCH_RGBA_LINEAR>(p, split, rows, n_views, stream);
+                case MARCH_SINGLE_TEX: return launch_composite_split<MARCH_SINGLE_TEX>(p, split, rows, n_views, stream);
+                case MARCH_SINGLE_LINEAR: return launch_composite_split<MARCH_SINGLE_LINEAR>(p, split, rows, n_views, stream);
+                case MARCH_FBM: return launch_composite_split<MARCH_FBM>(p, split, rows, n_views, stream);
+            }
+        }
+    }
     // ray split (texture variants of the reference integrator only; no skipping / early-out / counters)
     if ((variant == MARCH_RGBA_TEX || variant == MARCH_SINGLE_TEX) && !composite && !stats && !persistent &&
         !(p.skip_empty && variant == MARCH_SINGLE_TEX) && !(p.early_term_eps > 0.0f)) {

@@ -55,6 +55,7 @@ struct vr_context {
     int schedule = -1;                 // -1 auto, 0 direct, 1 persistent
     int queue_chunk = 1;
     int ray_split = -1;                // lanes per ray (texture march): -1 auto
+    int ray_split_composite = -1;      // lanes per ray (compositing march): -1 auto
     void* flush_buf = nullptr;      // 256 MiB scratch, allocated by the first vr_flush_l2
     vr_stats stats{};
     std::string err;
@@ -168,6 +169,7 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
         else if (!std::strcmp(ev, "auto")) c->schedule = -1;
     }
     if (const char* ev = std::getenv("VOLRT_RAY_SPLIT")) c->ray_split = std::atoi(ev);
+    if (const char* ev = std::getenv("VOLRT_RAY_SPLIT_COMPOSITE")) c->ray_split_composite = std::atoi(ev);
     if (const char* ev = std::getenv("VOLRT_QUEUE_CHUNK")) { int v = std::atoi(ev); if (v > 0 && v <= 1024) c->queue_chunk = v; }
     *out = c;
     return VR_OK;
@@ -527,6 +529,7 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.schedule = c->schedule;
     m.queue_chunk = c->queue_chunk;
     m.ray_split = c->ray_split;
+    m.ray_split_composite = c->ray_split_composite;
     if (p.density_mode == VR_DENSITY_FBM) { variant = MARCH_FBM; return VR_OK; }
     if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_render: no volume uploaded (vr_upload_volume / vr_generate_volume)");
     const vr_volume_desc& d = c->vdesc;
@@ -659,18 +662,17 @@ extern "C" vr_status vr_frame_info(vr_context* c, void** dev_ptr, size_t* row_pi
     return VR_OK;
 }
 
-// contiguous row bands of (nearly) equal estimated cost; bounds[0]=0 ... bounds[parts]=height
-extern "C" vr_status vr_row_bands(vr_context* c, uint32_t parts, uint32_t* bounds) {
+// analytic per-row cost (sum of the rows' step counts from the ray set-up alone); cost[height]
+extern "C" vr_status vr_row_cost(vr_context* c, float* cost) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
-    if (!bounds || parts == 0 || parts > 64) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_row_bands: parts must be in 1..64");
-    if (!c->has_params) return fail(c, VR_ERR_BAD_STATE, "vr_row_bands: vr_set_params has not been called");
+    if (!cost) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_row_cost: null output");
+    if (!c->has_params) return fail(c, VR_ERR_BAD_STATE, "vr_row_cost: vr_set_params has not been called");
     VR_CUDA(c, cudaSetDevice(c->device));
     MarchParams m;
     int variant = 0;
     // the cost model only needs the ray set-up, so it works without a volume as well
-    bool had = c->has_volume;
     vr_status st = VR_OK;
-    if (!had && c->params.density_mode != VR_DENSITY_FBM) {
+    if (!c->has_volume && c->params.density_mode != VR_DENSITY_FBM) {
         vr_params saved = c->params;
         c->params.density_mode = VR_DENSITY_FBM;
         st = fill_march_params(c, m, variant);
@@ -678,9 +680,18 @@ extern "C" vr_status vr_row_bands(vr_context* c, uint32_t parts, uint32_t* bound
     } else st = fill_march_params(c, m, variant);
     if (st != VR_OK) return st;
     VR_CUDA(c, launch_row_cost(m, 0, c->d_row_cost, c->stream));
-    std::vector<float> cost(c->height);
-    VR_CUDA(c, cudaMemcpyAsync(cost.data(), c->d_row_cost, sizeof(float) * c->height, cudaMemcpyDeviceToHost, c->stream));
+    VR_CUDA(c, cudaMemcpyAsync(cost, c->d_row_cost, sizeof(float) * c->height, cudaMemcpyDeviceToHost, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VR_OK;
+}
+
+// contiguous row bands of (nearly) equal estimated cost; bounds[0]=0 ... bounds[parts]=height
+extern "C" vr_status vr_row_bands(vr_context* c, uint32_t parts, uint32_t* bounds) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!bounds || parts == 0 || parts > 64) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_row_bands: parts must be in 1..64");
+    std::vector<float> cost(c->height);
+    vr_status st = vr_row_cost(c, cost.data());
+    if (st != VR_OK) return st;
     return vr_split_rows(cost.data(), c->height, parts, bounds);
 }
 

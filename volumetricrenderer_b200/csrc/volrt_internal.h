@@ -44,6 +44,7 @@ struct MarchParams {
     unsigned int* queue;        // [0] next tile, [1] warps finished (self-resetting)
     int queue_chunk;            // tiles claimed per pull
     int ray_split;              // lanes per ray of the texture march: -1 auto, 1 none, 2/4/8
+    int ray_split_composite;    // lanes per ray of the compositing march: -1 auto, 1 none, 2/4/8
     void* out;                  // view 0 / row 0 of the destination frame
     size_t row_pitch, view_stride;
     int out_format;             // vr_output_format

@@ -42,6 +42,17 @@ def shard_views(view_count, world):
     return out
 
 
+def rescale_and_split(row_cost, bounds, times):
+    """row_cost: model cost per row; bounds: current cut; times: measured time per band -> new bounds"""
+    cost = np.array(row_cost, np.float64, copy=True)
+    for r, t in enumerate(times):
+        b0, b1 = bounds[r], bounds[r + 1]
+        s = cost[b0:b1].sum()
+        if b1 > b0 and s > 0 and t > 0:
+            cost[b0:b1] *= t / s
+    return split_rows(cost.astype(np.float32), len(times))
+
+
 class BandGather:
     """Row-band partition of ONE frame over `world` ranks and its gather on rank 0.
 
@@ -68,6 +79,18 @@ class BandGather:
         self.bounds = box[0]
         if len(self.bounds) != self.world + 1 or self.bounds[0] != 0 or self.bounds[-1] != self.height:
             raise ValueError("bad band bounds %r" % (self.bounds,))
+        return self.bounds
+
+    def rebalance(self, row_cost, my_ms):
+        """Feedback re-cut between frames: every rank reports the device time of its band; the model
+        cost of each row is rescaled by its band's measured time per unit of model cost, and the rows are
+        cut again.  (The analytic model counts primary steps only; how many of them carry a light-march
+        depends on the density field, which the previous frame has just measured.)"""
+        if self.world == 1:
+            return self.bounds
+        times = [None] * self.world
+        self.dist.all_gather_object(times, float(my_ms))
+        self.bounds = rescale_and_split(row_cost, self.bounds, times)
         return self.bounds
 
     @property

@@ -234,6 +234,11 @@ class Renderer:
         self._check(self._lib.vr_row_bands(self._ctx, parts, b))
         return list(b)
 
+    def row_cost(self):
+        cost = np.zeros(self.height, np.float32)
+        self._check(self._lib.vr_row_cost(self._ctx, cost.ctypes.data_as(C.POINTER(C.c_float))))
+        return cost
+
     def frame_export(self):
         h = (C.c_char * 64)()
         self._check(self._lib.vr_frame_export(self._ctx, C.cast(h, C.c_void_p)))
