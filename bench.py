@@ -44,7 +44,16 @@ WORKLOADS = {
                 sun_dir=SUN, sun_color=[1.0, 0.95, 0.85])),
     "c4": (1920, 1080, "512^3 fp16 smoke grid (device-baked fBm field), trilinear, 1 fetch/step, 512 steps",
            dict(density_mode=1, max_steps=512, sample_scale=4.0)),
+    "c4s128": (1920, 1080, "512^3 fp16 smoke grid (device-baked fBm field), trilinear, 1 fetch/step, 128 steps",
+               dict(density_mode=1, max_steps=128, sample_scale=16.0)),
+    "c4s1024": (1920, 1080, "512^3 fp16 smoke grid (device-baked fBm field), trilinear, 1 fetch/step, 1024 steps",
+                dict(density_mode=1, max_steps=1024, sample_scale=2.0)),
+    "c5": (1920, 1080, "64 orbit views over a 1024^3 fp16 smoke grid (device-baked, thresholded), 512 steps, compositing with "
+                       "empty-space skipping (8^3 bricks) and early termination (T < 1/512), views sharded over the GPUs",
+           dict(density_mode=1, max_steps=512, sample_scale=1.0, sigma_t=400.0, early_term_eps=1.0 / 512, skip_empty=1,
+                ambient=1.0, sun_color=[0.0, 0.0, 0.0])),
 }
+C5_VIEWS, C5_GRID, C5_THRESHOLD = 64, 1024, 0.07
 # algorithmic FP32 work: one Perlin octave = 60 flop, +20 per fBm sample for the
 # remap/falloff, 26 flop per step for the integrator; FMA = 2 flop.
 FLOP_PER_OCTAVE, FLOP_PER_SAMPLE, FLOP_PER_STEP = 60.0, 20.0, 26.0
@@ -57,7 +66,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="volrt", choices=["volrt", "reference"])
-    ap.add_argument("--layout", default="texture", choices=["texture", "linear"])
+    ap.add_argument("--layout", default="texture", choices=["texture", "linear", "brick"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the oracle sample")
     return ap.parse_args()
@@ -138,7 +147,7 @@ def oracle_volume_for(workload):
     if workload == "c1":
         vol = oracle.ref_bake_default(128)[0] if oracle.have_ref() else oracle.bake_default(128)
         return oracle.make_volume(vol, oracle.VOL_RGBA8)
-    if workload == "c4":
+    if workload.startswith("c4"):
         p = oracle.params_default()
         vol = oracle.bake_smoke_r16f(128, p, 0.0)          # CPU sample uses a 128^3 stand-in of the field
         return oracle.make_volume(vol, oracle.VOL_R16F)
@@ -200,11 +209,13 @@ def run_reference(args, rank, world):
 
 def setup_volume(r, workload, layout):
     from volumetricrenderer_b200 import capi
-    lay = capi.LAYOUT_TEXTURE if layout == "texture" else capi.LAYOUT_LINEAR
+    lay = {"texture": capi.LAYOUT_TEXTURE, "linear": capi.LAYOUT_LINEAR, "brick": capi.LAYOUT_BRICK}[layout]
+    if layout == "brick" and not workload.startswith("c4"):
+        lay = capi.LAYOUT_TEXTURE
     if workload == "c1":
         r.generate_volume(layout=lay)                                   # the reference's bake, on the device
         return 128 ** 3 * 4
-    if workload == "c4":
+    if workload.startswith("c4"):
         r.generate_volume(size=512, format=capi.VOL_R16F, layout=lay)   # fBm smoke field, fp16
         return 512 ** 3 * 2
     return 0
@@ -352,6 +363,7 @@ def run_volrt(args, rank, world, local):
             "msamples_per_s": (steps + light_samples) / (ms_per_step * 1e-3) / 1e6,
         }
         line["roofline"] = roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world)
+        line["ray_split"] = os.environ.get("VOLRT_RAY_SPLIT_COMPOSITE", "auto")
         if not args.no_cpu_baseline and world == 1:
             try:
                 cb = time_oracle(args.workload, args.cpu_seconds)
@@ -366,7 +378,108 @@ def run_volrt(args, rank, world, local):
         dist.destroy_process_group()
 
 
+def run_views(args, rank, world, local):
+    """C5: a batch of independent views, sharded contiguously over the ranks (no exchange: every rank delivers its own
+    views).  value = W*H*views / max-over-ranks device time."""
+    import volumetricrenderer_b200 as vr
+    from volumetricrenderer_b200 import capi, scene, multigpu
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    W, H, desc, kw = WORKLOADS[args.workload]
+    K, Wm = args.steps, max(args.warmup, 3)
+    v0, v1 = multigpu.shard_views(C5_VIEWS, world)[rank]
+    nv = v1 - v0
+    views = scene.orbit_views(C5_VIEWS)[v0:v1]
+    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local, max_views=max(nv, 1))
+    grid = int(os.environ.get("VOLRT_C5_GRID", C5_GRID))
+    r.generate_volume(size=grid, format=capi.VOL_R16F, layout=capi.LAYOUT_TEXTURE, threshold=C5_THRESHOLD)
+    vol_bytes = grid ** 3 * 2
+    r.set_params(view_ubos=views, **kw)
+
+    def barrier():
+        r.wait()
+        if dist is not None:
+            import torch
+            dist.barrier(device_ids=[local])
+            torch.cuda.synchronize()
+
+    r.render(to_host=False, flags=capi.RENDER_STATS)
+    st = r.stats()
+    counts = np.array([st["covered"], st["steps"], st["early_terminated"], st["skipped_steps"]], np.float64)
+    if dist is not None:
+        import torch
+        t = torch.tensor(counts, device="cuda", dtype=torch.float64)
+        dist.all_reduce(t)
+        counts = t.cpu().numpy()
+    for _ in range(Wm):
+        r.flush_l2(); r.render(to_host=False); r.wait()
+    sampler = ClockSampler(physical_gpu_index(local))
+    barrier()
+    sampler.start()
+    ms = []
+    for _ in range(K):
+        r.flush_l2()
+        r.render(to_host=False)
+        ms.append(r.stats()["gpu_ms"])
+    barrier()
+    clocks = sampler.stop()
+    dev_ms = float(np.sum(ms))
+    if dist is not None:
+        import torch
+        t = torch.tensor([dev_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms = float(t.item())
+    ms_per_step = dev_ms / K
+    value = W * H * C5_VIEWS / (ms_per_step * 1e-3) / 1e6
+    # end to end: the view block (H2D) + every view of the shard read back into page-locked memory, two batches in flight
+    hosts = [r.new_frame_buffer(views=nv, pinned=True), r.new_frame_buffer(views=nv, pinned=True)]
+    def e2e_step(i):
+        r.set_params(view_ubos=views, **kw)
+        r.render(out=hosts[i & 1], flags=capi.RENDER_ASYNC)
+    for i in range(2):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        e2e_step(i)
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / K
+    if rank == 0:
+        covered, steps, early, skipped = (int(x) for x in counts)
+        peaks = r.measure_peaks()
+        t = ms_per_step * 1e-3
+        fetches = steps - skipped
+        line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": "%s: %s" % (args.workload, desc), "width": W, "height": H, "views": C5_VIEWS, "grid": grid,
+                           "l2": "flushed between batches; the %d MiB grid exceeds L2" % (vol_bytes >> 20),
+                           "partition": "contiguous view shards, no exchange"},
+                "e2e": {"value": W * H * C5_VIEWS / e2e_s / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_s * 1e3, "frames_in_flight": 2,
+                        "h2d_bytes_per_step": 336 * C5_VIEWS, "d2h_bytes_per_step": W * H * 4 * C5_VIEWS},
+                "gpu_launches": K, "clocks": clocks, "covered_rays": covered, "steps_per_frame": steps,
+                "early_terminated_frac": early / max(covered, 1), "skipped_step_frac": skipped / max(steps, 1),
+                "roofline": {"bound": "tex", "achieved": fetches / t / 1e9, "peak": peaks["tex_gfetch"] * world, "unit": "Gfetch/s",
+                             "frac": fetches / t / 1e9 / (peaks["tex_gfetch"] * world) if peaks["tex_gfetch"] else None,
+                             "note": "fetches = steps not skipped by the brick grid, before early termination (upper bound of the executed ones)",
+                             "traffic": None, "peaks_measured_here": peaks}}
+        print(json.dumps(line), flush=True)
+    barrier()
+    r.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world):
+    """Dominant kernel = the march (the only kernel in the timed region).  Neither HBM nor the tensor cores bound
+    this path: the procedural workloads read no input and the grid workloads' volumes are L2- or
+    TEX-bound, so `bound` is "fp32" (algorithmic flop of SURVEY.md §8(d) / the FP32-FMA peak measured in this
+    process) or "tex" (trilinear fetches / the fetch peak measured in this process).  The compulsory-HBM
+    figure against MEASURED_PEAKS.json is reported beside it."""
     peaks = r.measure_peaks()
     t = ms_per_step * 1e-3
     measured = {}
@@ -376,23 +489,38 @@ def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, wo
         pass
     hbm_peak = measured.get("hbm_gbs", 6650.0)
     compulsory = vol_bytes + W * H * 4
-    out = {"hbm_compulsory_gbs": compulsory / t / 1e9, "hbm_peak_gbs": hbm_peak,
-           "hbm_peak_source": "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in measured else "fallback",
-           "traffic": None, "peaks_measured_here": peaks}
+    traffic = None
+    try:                                                    # dram bytes per launch from the committed ncu capture
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+    except Exception:
+        pass
+    out = {"hbm": {"algorithmic_bytes": compulsory, "achieved": compulsory / t / 1e9, "peak": hbm_peak * world, "unit": "GB/s",
+                   "frac": compulsory / t / 1e9 / (hbm_peak * world),
+                   "peak_source": "of measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in measured else "of fallback (6650 GB/s)"},
+           "traffic": traffic, "peaks_measured_here": peaks}
     if kw.get("density_mode") == 2:
-        octaves = 5
+        octaves, L = 5, kw.get("light_steps", 0)
         per_sample = octaves * FLOP_PER_OCTAVE + FLOP_PER_SAMPLE
-        flops = (steps + light_samples) * per_sample + steps * FLOP_PER_STEP
-        out.update({"bound": "fp32", "achieved": flops / t / 1e12, "peak": peaks["fp32_tflops"] * world, "unit": "TFLOP/s",
-                    "peak_source": "FP32 FMA micro-benchmark in this process (dependent-free FMA chains)",
-                    "flop_per_frame": flops,
-                    "note": "flops = evaluated noise samples x (5 octaves x 60 + 20) + steps x 26 (SURVEY.md 8(d)); "
-                            "samples counted by the device (steps whose density is exactly 0 skip their light-march)"})
+        flop_per_step = (1 + L) * per_sample + FLOP_PER_STEP            # 2 266 (C2), 2 906 (C3)
+        flops = steps * flop_per_step
+        executed = (steps + light_samples) * per_sample + steps * FLOP_PER_STEP
+        peak = peaks["fp32_tflops"] * world
+        out.update({"bound": "fp32", "achieved": flops / t / 1e12, "peak": peak, "unit": "TFLOP/s",
+                    "peak_source": "FP32 FMA micro-benchmark in this process (dependent-free FMA chains; nominal 74.5)",
+                    "flop_per_step": flop_per_step, "flop_per_frame": flops,
+                    "achieved_executed": executed / t / 1e12, "frac_executed": executed / t / 1e12 / peak if peak else None,
+                    "note": "achieved = primary steps x SURVEY 8(d) flop/step (every step owes 1+L noise samples of 5 octaves x 60 + 20 flop, "
+                            "+26 for the integrator). The kernel evaluates fewer (achieved_executed): steps whose density is exactly 0 "
+                            "owe no light-march and light samples outside the box are not taken. INT32 hash / LDS / conversion "
+                            "instructions share the issue ports and are not counted as flop: ncu shows the kernel 88 % issue-active "
+                            "(profiles/)."})
     else:
         fetches = steps * (4 if kw.get("density_mode", 0) == 0 else 1)
-        out.update({"bound": "tex", "achieved": fetches / t / 1e9, "peak": peaks["tex_gfetch"] * world, "unit": "Gfetch/s",
-                    "peak_source": "trilinear-fetch micro-benchmark in this process (L1/L2-resident RGBA8, warp-coherent)",
-                    "note": "the volume is cache-resident or streamed once; compulsory HBM traffic is in hbm_compulsory_gbs"})
+        peak = peaks["tex_gfetch"] * world
+        out.update({"bound": "tex", "achieved": fetches / t / 1e9, "peak": peak, "unit": "Gfetch/s",
+                    "peak_source": "trilinear-fetch micro-benchmark in this process (L1/L2-resident RGBA8, warp-coherent; nominal 581)",
+                    "fetches_per_frame": fetches,
+                    "note": "the volume is cache-resident or streamed once; compulsory HBM traffic is under 'hbm'"})
     out["frac"] = out["achieved"] / out["peak"] if out["peak"] else None
     return out
 
@@ -404,6 +532,9 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+        return
+    if args.workload == "c5":
+        run_views(args, rank, world, local)
         return
     run_volrt(args, rank, world, local)
 

@@ -79,8 +79,10 @@ typedef enum vr_layout {
     VR_LAYOUT_TEXTURE = 1,   /* cudaArray + texture unit: hardware trilinear (fixed-point weights) */
     VR_LAYOUT_LINEAR = 2,    /* x-fastest global memory, trilinear in FP32 in the kernel (bit-exact
                                 against the CPU oracle) */
-    VR_LAYOUT_BRICK = 3      /* R16F only: bricked global layout, bricks staged to shared memory by
-                                TMA (cp.async.bulk.tensor.3d), trilinear in FP32 */
+    VR_LAYOUT_BRICK = 3      /* R16F only (width % 8 == 0): the march stages 32x24x24-voxel boxes of the volume
+                                in shared memory with TMA (cp.async.bulk.tensor.3d through a tiled tensor map
+                                over the x-fastest volume) and filters in FP32 — bit-exact like LINEAR.
+                                Serves the reference integrator; extensions run the LINEAR kernel */
 } vr_layout;
 
 typedef enum vr_density_mode {

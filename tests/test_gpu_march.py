@@ -155,7 +155,7 @@ def test_row_bands_and_views(oracle):
             assert np.array_equal(full[k], oracle.encode(ref, oracle.OUT_RGBA8_UNORM))
 
 
-@pytest.mark.parametrize("layout", [capi.LAYOUT_LINEAR, capi.LAYOUT_TEXTURE])
+@pytest.mark.parametrize("layout", [capi.LAYOUT_LINEAR, capi.LAYOUT_TEXTURE, capi.LAYOUT_BRICK])
 def test_single_channel_fp16_grid(oracle, layout):
     """config 4 shape at test size: one-channel fp16 grid, one fetch per step."""
     W, H = 480, 270
@@ -171,7 +171,7 @@ def test_single_channel_fp16_grid(oracle, layout):
         skipped = r.render(flags=capi.RENDER_STATS)[0]
         s = r.stats()
     assert ref[..., 0].max() > 0.3
-    if layout == capi.LAYOUT_LINEAR:
+    if layout in (capi.LAYOUT_LINEAR, capi.LAYOUT_BRICK):      # FP32 filtering in the oracle's order: bit-exact
         assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
     else:
         assert np.abs(img - ref).max() <= 2.0 / 255.0
@@ -179,7 +179,7 @@ def test_single_channel_fp16_grid(oracle, layout):
     assert s["skipped_steps"] > 0
     # same samples; the ray-split schedule of the texture path re-associates the sum and takes positions as
     # Pin + i*stepVec (a 1e-5 shift can move a hardware filter weight by one 1/256 step)
-    assert np.abs(skipped - img).max() <= (1e-6 if layout == capi.LAYOUT_LINEAR else 2e-4)
+    assert np.abs(skipped - img).max() <= (2e-4 if layout == capi.LAYOUT_TEXTURE else 1e-6)
 
 
 def test_compositing_light_march_and_early_termination(oracle):
@@ -255,3 +255,25 @@ def test_known_answers_on_gpu():
     assert np.all(img[..., 3] == 1.0)
     assert np.all(img[0, 0, :3] == 0.0)           # clear colour outside the silhouette
     assert np.array_equal(img[..., 0], img[..., 1]) and np.array_equal(img[..., 0], img[..., 2])
+
+
+@pytest.mark.parametrize("steps,phi,theta", [(96, 0.0, 0.0), (384, 40.0, -25.0), (700, 90.0, 90.0)])
+def test_tma_brick_march_is_bit_exact(oracle, steps, phi, theta):
+    """VR_LAYOUT_BRICK: boxes staged by TMA; sparse stepping (boxes shrink to fit), voxel-rate stepping, and an
+    axis-aligned view; non-cubic volume whose faces exercise the mirrored-tap fallback."""
+    W, H = 400, 240
+    rng = np.random.default_rng(steps)
+    vol = (rng.random((40, 56, 64), np.float32) ** 3).astype(np.float16)        # (d, h, w), w % 8 == 0
+    ubo0, ubo1 = scene.default_scene(phi, theta)
+    kw = dict(density_mode=1, sample_scale=0.7, max_steps=steps)
+    p = oracle_params(oracle, ubo0, ubo1, density_mode=oracle.DENSITY_SINGLE, sample_scale=0.7, max_steps=steps)
+    ref, st, _ = _oracle_frame(oracle, vol.view(np.uint16), oracle.VOL_R16F, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_R16F, capi.LAYOUT_BRICK)
+        r.set_params(ubo0, ubo1, **kw)
+        img = r.render()[0]
+    assert st["covered"] > 5000 and ref[..., 0].max() > 0.2
+    assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        with pytest.raises(vr.VolrtError):
+            r.upload_volume(np.zeros((8, 8, 12), np.float16), capi.VOL_R16F, capi.LAYOUT_BRICK)    # width % 8 != 0

@@ -18,6 +18,8 @@
 #include "volrt_internal.h"
 #include "noise_device.cuh"
 #include <math_constants.h>
+#include <cuda.h>          // CUtensorMap (type only; the encoder is fetched at run time in volrt_api.cu)
+#include <cstring>
 
 namespace volrt {
 
@@ -611,6 +613,158 @@ static cudaError_t launch_split(const MarchParams& p, int split, int rows, int n
         case 8: march_tex_split_kernel<VARIANT, 8><<<grid, 128, 0, s>>>(p); break;
         default: return cudaErrorInvalidValue;
     }
+    return cudaGetLastError();
+}
+
+// (e) TMA-staged brick march (VR_LAYOUT_BRICK, one-channel fp16 grids, reference integrator).
+// A CTA owns a 16x8-pixel tile and walks it through the volume in slabs of K steps.  For each slab it
+// takes the bounding box (in voxels) of every tap its rays will touch, has ONE thread fetch that box with
+// a single 3-D tiled TMA copy (cp.async.bulk.tensor.3d, straight out of the x-fastest volume — the
+// tensor map does the gather, no re-bricked copy of the volume is kept) into shared memory, and
+// filters from there in FP32 with the oracle's operation order (bit-exact, like the LINEAR layout).
+// Slabs shrink (K/2) while the box does not fit; taps that would need mirrored addressing (index -1 or N,
+// i.e. the first/last sample of a ray on a volume face) and anything else outside the staged box take the
+// global-memory path of the LINEAR variant.  Latency is hidden by occupancy (one 27 KB box per CTA,
+// up to 8 CTAs per SM) rather than by a second stage.
+constexpr int BRICK_X = 32, BRICK_Y = 24, BRICK_Z = 24;            // voxels.  TMA wants the box's first byte 16-byte aligned, so
+                                                                   // the x origin is rounded down to a multiple of 8 halves: usable x extent >= 25
+constexpr int BRICK_BYTES = BRICK_X * BRICK_Y * BRICK_Z * 2;
+constexpr int BRICK_KMAX = 8;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant__ MarchParams P,
+                                                          const __grid_constant__ CUtensorMap tmap) {
+    extern __shared__ __align__(128) unsigned char dyn_smem[];
+    __half* box = reinterpret_cast<__half*>(dyn_smem);
+    __shared__ __align__(8) unsigned long long bar;
+    __shared__ int red[8];            // lo xyz, hi xyz, n_max, (unused)
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        red[6] = 0;
+    }
+    __syncthreads();
+    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    const int warp = tid >> 5, lane = tid & 31;
+    const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
+    const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const int view = P.view_begin + blockIdx.z;
+    const bool in_frame = px < P.width && py < P.row_end;
+    const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
+    const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);
+    Ray ray;
+    const bool covered = in_frame && setup_ray(P, V, px, py, step_size, ray);
+    const int n = covered ? ray.n : 0;
+    {
+        const int wmax = __reduce_max_sync(0xffffffffu, n);
+        if (lane == 0) atomicMax(&red[6], wmax);
+    }
+    __syncthreads();
+    const int n_max = red[6];
+    const float fw = (float)P.vw, fh = (float)P.vh, fd = (float)P.vd;
+    f3 p = ray.pin;
+    float acc = 0.0f;
+    int K = BRICK_KMAX;
+    unsigned int phase = 0;
+    for (int i0 = 0; i0 < n_max;) {
+        // ---- bounding box of the slab's taps (analytic positions; 0.02-voxel slack against the running add)
+        int lo[3], hi[3];
+        bool fits;
+        for (;;) {
+            if (tid < 6) red[tid] = tid < 3 ? 0x7fffffff : (int)0x80000000;
+            __syncthreads();
+            int l0 = 0x7fffffff, l1 = l0, l2 = l0, h0 = (int)0x80000000, h1 = h0, h2 = h0;
+            if (i0 < n) {
+                const float fa = (float)i0, fb = (float)(min(i0 + K, n) - 1);
+                const float xa = fmaf(fmaf(ray.step.x, fa, ray.pin.x), fw, -0.5f), xb = fmaf(fmaf(ray.step.x, fb, ray.pin.x), fw, -0.5f);
+                const float ya = fmaf(fmaf(ray.step.y, fa, ray.pin.y), fh, -0.5f), yb = fmaf(fmaf(ray.step.y, fb, ray.pin.y), fh, -0.5f);
+                const float za = fmaf(fmaf(ray.step.z, fa, ray.pin.z), fd, -0.5f), zb = fmaf(fmaf(ray.step.z, fb, ray.pin.z), fd, -0.5f);
+                l0 = (int)floorf(fminf(xa, xb) - 0.02f); h0 = (int)floorf(fmaxf(xa, xb) + 0.02f) + 1;
+                l1 = (int)floorf(fminf(ya, yb) - 0.02f); h1 = (int)floorf(fmaxf(ya, yb) + 0.02f) + 1;
+                l2 = (int)floorf(fminf(za, zb) - 0.02f); h2 = (int)floorf(fmaxf(za, zb) + 0.02f) + 1;
+            }
+            l0 = __reduce_min_sync(0xffffffffu, l0); l1 = __reduce_min_sync(0xffffffffu, l1); l2 = __reduce_min_sync(0xffffffffu, l2);
+            h0 = __reduce_max_sync(0xffffffffu, h0); h1 = __reduce_max_sync(0xffffffffu, h1); h2 = __reduce_max_sync(0xffffffffu, h2);
+            if (lane == 0 && l0 != 0x7fffffff) {
+                atomicMin(&red[0], l0); atomicMin(&red[1], l1); atomicMin(&red[2], l2);
+                atomicMax(&red[3], h0); atomicMax(&red[4], h1); atomicMax(&red[5], h2);
+            }
+            __syncthreads();
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { lo[a] = red[a]; hi[a] = red[3 + a]; }
+            lo[0] &= ~7;                               // floor to a multiple of 8 (two's complement: also for negatives)
+            fits = hi[0] - lo[0] < BRICK_X && hi[1] - lo[1] < BRICK_Y && hi[2] - lo[2] < BRICK_Z;
+            __syncthreads();                       // red[] is rewritten by the next attempt / slab
+            if (fits || K == 1) break;
+            K >>= 1;
+        }
+        // ---- one TMA copy of the box (zero-filled outside the volume), everyone waits on the mbarrier
+        if (fits) {
+            if (tid == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar)), "r"(BRICK_BYTES) : "memory");
+                asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                             ::"r"(smem_u32(box)), "l"(&tmap), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(smem_u32(&bar)) : "memory");
+            }
+            unsigned int ok = 0;
+            while (!ok)
+                asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                             : "=r"(ok) : "r"(smem_u32(&bar)), "r"(phase) : "memory");
+            phase ^= 1u;
+        }
+        // ---- K steps out of shared memory
+        const int i1 = min(i0 + K, n);
+        for (int i = i0; i < i1; ++i) {
+            const float x = sub(mul(p.x, fw), 0.5f), y = sub(mul(p.y, fh), 0.5f), z = sub(mul(p.z, fd), 0.5f);
+            const float x0 = floorf(x), y0 = floorf(y), z0 = floorf(z);
+            const int gi = (int)x0, gj = (int)y0, gk = (int)z0;
+            const int li = gi - lo[0], lj = gj - lo[1], lk = gk - lo[2];
+            const bool staged = fits && gi >= 0 && gi + 1 < P.vw && gj >= 0 && gj + 1 < P.vh && gk >= 0 && gk + 1 < P.vd &&
+                                (unsigned)li < (unsigned)(BRICK_X - 1) && (unsigned)lj < (unsigned)(BRICK_Y - 1) && (unsigned)lk < (unsigned)(BRICK_Z - 1);
+            float s;
+            if (staged) {
+                Taps t;
+                t.fx = sub(x, x0); t.fy = sub(y, y0); t.fz = sub(z, z0);
+                const __half* b = box + (lk * BRICK_Y + lj) * BRICK_X + li;
+                float c[8];
+                c[0] = __half2float(b[0]); c[1] = __half2float(b[1]);
+                c[2] = __half2float(b[BRICK_X]); c[3] = __half2float(b[BRICK_X + 1]);
+                c[4] = __half2float(b[BRICK_X * BRICK_Y]); c[5] = __half2float(b[BRICK_X * BRICK_Y + 1]);
+                c[6] = __half2float(b[BRICK_X * BRICK_Y + BRICK_X]); c[7] = __half2float(b[BRICK_X * BRICK_Y + BRICK_X + 1]);
+                s = trilerp(t, c);
+            } else {
+                s = sample_single_linear(P, nullptr, p);          // mirrored taps / outside the box: global memory
+            }
+            acc = add(acc, mul(s, P.sample_scale));
+            p = add3(p, ray.step);                                  // running add, frag.glsl:74
+        }
+        i0 += K;
+        __syncthreads();                           // everyone is done with the box before the next copy lands
+    }
+    if (!in_frame) return;
+    if (!covered) { store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f); return; }
+    acc = mul(acc, step_size);
+    const float e = mul(P.density, fminf(-acc, 0.0f));
+    const float c = sub(1.0f, (float)exp((double)e));
+    store_pixel(P, view, px, py, c, c, c, 1.0f);
+}
+
+cudaError_t launch_march_brick(const MarchParams& p_in, const void* tensor_map, int n_views, cudaStream_t stream) {
+    int rows = p_in.row_end - p_in.row_begin;
+    if (rows <= 0 || n_views <= 0) return cudaSuccess;
+    MarchParams p = p_in;
+    p.n_views = n_views;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(march_brick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BRICK_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    CUtensorMap tm;
+    memcpy(&tm, tensor_map, sizeof tm);
+    dim3 grid((p.width + 15) / 16, (rows + 7) / 8, n_views);
+    march_brick_kernel<<<grid, 128, BRICK_BYTES, stream>>>(p, tm);
     return cudaGetLastError();
 }
 

@@ -3,6 +3,7 @@
 // buffer, launch configuration, row-band cost model, CUDA-IPC export of the frame for the
 // NVLink peer gather.  There is no CPU rendering path in this library.
 #include "volrt_internal.h"
+#include <cuda.h>              // CUtensorMap + enums (types only: cuTensorMapEncodeTiled is fetched at run time)
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -41,6 +42,8 @@ struct vr_context {
     cudaArray_t array = nullptr;
     cudaTextureObject_t tex = 0;
     uint8_t* occupied = nullptr;
+    alignas(64) unsigned char tensor_map[128] = {};   // BRICK layout: CUtensorMap over `lin`
+    bool has_tensor_map = false;
     BrickInfo bricks{};
     // params
     bool has_params = false;
@@ -241,6 +244,26 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
         td.normalizedCoords = 1;
         VR_CUDA(c, cudaCreateTextureObject(&c->tex, &rd, &td, nullptr));
     }
+    c->has_tensor_map = false;
+    if (layout == VR_LAYOUT_BRICK) {
+        // 3-D tiled tensor map over the x-fastest fp16 volume; the march kernel pulls 24^3-voxel boxes through it
+        typedef CUresult (*EncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                        const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        VR_CUDA(c, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr));
+        if (!fn || qr != cudaDriverEntryPointSuccess) return fail(c, VR_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available in this driver");
+        const cuuint64_t dims[3] = {d.width, d.height, d.depth};
+        const cuuint64_t strides[2] = {(cuuint64_t)d.width * 2, (cuuint64_t)d.width * d.height * 2};
+        const cuuint32_t boxdim[3] = {(cuuint32_t)kBrickBox[0], (cuuint32_t)kBrickBox[1], (cuuint32_t)kBrickBox[2]};
+        const cuuint32_t estr[3] = {1, 1, 1};
+        CUresult r = ((EncodeTiled)fn)((CUtensorMap*)c->tensor_map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, c->lin, dims, strides, boxdim, estr,
+                                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) return fail(c, VR_ERR_CUDA, "cuTensorMapEncodeTiled failed");
+        c->has_tensor_map = true;
+    }
     // min-max bricks (8^3 voxels + 1-texel apron) for empty-space skipping
     BrickInfo& B = c->bricks;
     B.bx = (d.width + 7) / 8; B.by = (d.height + 7) / 8; B.bz = (d.depth + 7) / 8;
@@ -262,7 +285,8 @@ static vr_status check_volume_desc(vr_context* c, const vr_volume_desc* d) {
     if (texel_bytes(d->format) == 0) return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: unknown format");
     if (d->address_mode > VR_ADDRESS_CLAMP_TO_EDGE) return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: unknown address mode");
     if (d->layout > VR_LAYOUT_BRICK) return fail(c, VR_ERR_INVALID_ARGUMENT, "volume desc: unknown layout");
-    if (d->layout == VR_LAYOUT_BRICK) return fail(c, VR_ERR_UNSUPPORTED, "volume desc: VR_LAYOUT_BRICK (TMA brick path) is not built yet");
+    if (d->layout == VR_LAYOUT_BRICK && (d->format != VR_VOL_R16F || d->width % 8 != 0))
+        return fail(c, VR_ERR_UNSUPPORTED, "volume desc: VR_LAYOUT_BRICK needs an R16F volume whose width is a multiple of 8 (TMA: 16-byte row pitch)");
     return VR_OK;
 }
 
@@ -545,6 +569,9 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     } else {
         if (d.format == VR_VOL_RGBA8_UNORM) return fail(c, VR_ERR_BAD_STATE, "vr_render: VR_DENSITY_SINGLE needs a one-channel volume (R16F / R8)");
         variant = tex ? MARCH_SINGLE_TEX : MARCH_SINGLE_LINEAR;
+        // TMA-staged boxes serve the reference integrator; the extensions fall back to the (bit-identical) LINEAR kernel
+        if (d.layout == VR_LAYOUT_BRICK && c->has_tensor_map && !(p.sigma_t > 0.0f) && !p.skip_empty && !(p.early_term_eps > 0.0f))
+            variant = MARCH_SINGLE_BRICK;
     }
     return VR_OK;
 }
@@ -597,7 +624,11 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
     }
     const bool no_march = (t->flags & VR_RENDER_NO_MARCH) != 0;
     VR_CUDA(c, cudaEventRecord(c->ev0, s));
-    if (!no_march) VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
+    if (variant == MARCH_SINGLE_BRICK && stats) variant = MARCH_SINGLE_LINEAR;     // device counters live in the generic kernel
+    if (!no_march) {
+        if (variant == MARCH_SINGLE_BRICK) VR_CUDA(c, launch_march_brick(m, c->tensor_map, (int)(v1 - v0), s));
+        else VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
+    }
     VR_CUDA(c, cudaEventRecord(c->ev1, s));
     c->timed = true;
     c->foreign_stream_pending = t->stream != nullptr;

@@ -75,11 +75,16 @@ enum MarchVariant {
     MARCH_RGBA_LINEAR = 1,   // reference integrator, FP32 software trilinear from global memory
     MARCH_SINGLE_TEX = 2,    // one-channel grid through the texture unit
     MARCH_SINGLE_LINEAR = 3,
-    MARCH_FBM = 4            // procedural density
+    MARCH_FBM = 4,           // procedural density
+    MARCH_SINGLE_BRICK = 5   // one-channel fp16 grid, boxes staged to shared memory by TMA
 };
 
 // launches one march over rows [row_begin,row_end) x views; returns cudaGetLastError()
 cudaError_t launch_march(const MarchParams& p, int variant, int n_views, bool stats, cudaStream_t stream);
+
+// TMA-staged brick march (VR_LAYOUT_BRICK): tensor_map = 128-byte CUtensorMap over the x-fastest fp16 volume
+cudaError_t launch_march_brick(const MarchParams& p, const void* tensor_map, int n_views, cudaStream_t stream);
+constexpr int kBrickBox[3] = {32, 24, 24};
 
 // analytic per-row cost (sum of chord steps) for band balancing; cost[height] on device
 cudaError_t launch_row_cost(const MarchParams& p, int view, float* row_cost, cudaStream_t stream);
