@@ -283,7 +283,10 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
             // short ones and too few fetches stay in flight to keep the TEX unit busy), so issue the
             // fetches of STEP_BATCH consecutive steps before consuming any of them.  Positions still come
             // from the running add of frag.glsl:74 and the sum keeps its order.
-            constexpr int STEP_BATCH = 4;
+#ifndef VOLRT_STEP_BATCH
+#define VOLRT_STEP_BATCH 4
+#endif
+            constexpr int STEP_BATCH = VOLRT_STEP_BATCH;
             for (; i + STEP_BATCH <= n; i += STEP_BATCH) {
                 float d[STEP_BATCH];
 #pragma unroll
