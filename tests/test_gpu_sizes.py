@@ -1,0 +1,177 @@
+"""Edge sizes and BASELINE.json's full sizes, through the C ABI.
+
+Small/ragged frames check every kernel mapping's bounds handling against the oracle; the full-size
+configurations (1080p / 4K procedural cloud, 512^3 fp16 grid) are checked on a strided sample of rows
+against the oracle plus size-independent properties: the union of row bands is the frame, rendering is
+idempotent, and a view batch equals its views rendered one by one."""
+import numpy as np
+import pytest
+
+import volumetricrenderer_b200 as vr
+from volumetricrenderer_b200 import capi, scene
+from util import psnr8, max_abs8, oracle_params, smoke_volume
+
+pytestmark = pytest.mark.gpu
+SUN = np.array([1.0, 1.0, 2.0], np.float32) / np.float32(np.sqrt(6.0))
+
+
+@pytest.mark.parametrize("W,H", [(1, 1), (7, 3), (33, 17), (331, 173), (16, 8), (130, 66)])
+def test_ragged_frames_every_mapping(oracle, W, H):
+    rng = np.random.default_rng(W * 1000 + H)
+    vol = rng.integers(0, 256, size=(12, 20, 16, 4), dtype=np.uint8)
+    u0, u1 = scene.default_scene(17.0, -8.0)
+    p = oracle_params(oracle, u0, u1)
+    ov, _k = oracle.make_volume(vol, oracle.VOL_RGBA8)
+    ref, st = oracle.render(ov, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(u0, u1)
+        assert np.array_equal(r.render()[0].view(np.uint32), ref.view(np.uint32))          # direct mapping, strict
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        assert np.abs(r.render()[0] - ref).max() <= 2.0 / 255.0                             # ray-split texture mapping
+    # one-channel grid: TMA brick mapping (bit-exact) and the ray-split compositing mapping
+    g = smoke_volume(16, 1)
+    ps = oracle_params(oracle, u0, u1, density_mode=oracle.DENSITY_SINGLE, sample_scale=0.5)
+    og, _k2 = oracle.make_volume(g.view(np.uint16), oracle.VOL_R16F)
+    refs, _ = oracle.render(og, ps, W, H)
+    pc = oracle_params(oracle, u0, u1, density_mode=oracle.DENSITY_SINGLE, sample_scale=1.0, sigma_t=6.0, light_steps=3,
+                       light_step_len=0.06, ambient=0.1)
+    oracle.set_params(pc, sun_dir=SUN, sun_color=[1.0, 0.9, 0.8])
+    refc, _ = oracle.render(og, pc, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(g, capi.VOL_R16F, capi.LAYOUT_BRICK)
+        r.set_params(u0, u1, density_mode=capi.DENSITY_SINGLE, sample_scale=0.5)
+        assert np.array_equal(r.render()[0].view(np.uint32), refs.view(np.uint32))
+        r.set_params(u0, u1, density_mode=capi.DENSITY_SINGLE, sample_scale=1.0, sigma_t=6.0, light_steps=3, light_step_len=0.06,
+                     ambient=0.1, sun_dir=SUN, sun_color=[1.0, 0.9, 0.8])
+        assert np.abs(r.render()[0] - refc).max() <= 1e-4
+
+
+def test_r8_volume_and_all_encodings_on_split_kernels(oracle):
+    W, H = 200, 120
+    rng = np.random.default_rng(3)
+    v8 = rng.integers(0, 256, size=(24, 24, 24), dtype=np.uint8)
+    u0, u1 = scene.default_scene(-30.0, 12.0)
+    p = oracle_params(oracle, u0, u1, density_mode=oracle.DENSITY_SINGLE, sample_scale=0.3)
+    ov, _k = oracle.make_volume(v8, oracle.VOL_R8)
+    ref, _ = oracle.render(ov, p, W, H)
+    for fmt, ofmt in ((capi.OUT_RGBA8_UNORM, oracle.OUT_RGBA8_UNORM), (capi.OUT_RGBA8_SRGB, oracle.OUT_RGBA8_SRGB)):
+        with vr.Renderer(W, H, fmt) as r:
+            r.upload_volume(v8, capi.VOL_R8_UNORM, capi.LAYOUT_LINEAR)
+            r.set_params(u0, u1, density_mode=capi.DENSITY_SINGLE, sample_scale=0.3)
+            assert np.array_equal(r.render()[0], oracle.encode(ref, ofmt))
+            r.upload_volume(v8, capi.VOL_R8_UNORM, capi.LAYOUT_TEXTURE)
+            assert max_abs8(r.render()[0], oracle.encode(ref, ofmt)) <= 2
+    with vr.Renderer(W, H, capi.OUT_RGBA16F) as r:
+        r.upload_volume(v8, capi.VOL_R8_UNORM, capi.LAYOUT_TEXTURE)
+        r.set_params(u0, u1, density_mode=capi.DENSITY_SINGLE, sample_scale=0.3)
+        h = r.render()[0].astype(np.float32)
+        assert np.abs(h - ref).max() <= 2.0 / 255.0 + 1e-3
+
+
+def test_clamp_address_mode_texture_vs_linear():
+    """CLAMP_TO_EDGE is not in the reference (its sampler mirrors); the two GPU samplers must agree with each other"""
+    W, H = 160, 90
+    rng = np.random.default_rng(8)
+    vol = rng.integers(0, 256, size=(8, 8, 8, 4), dtype=np.uint8)
+    u0, u1 = scene.default_scene(5.0, 5.0)
+    std140 = np.zeros(36, np.float32)
+    std140[:19] = u1[:19]
+    std140[20:32] = 3.0                     # 0.8 P + 0.6 etc.: fetches 2-4 cross the border
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR, capi.ADDRESS_CLAMP_TO_EDGE)
+        r.set_params(u0, std140)
+        a = r.render()[0].copy()
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE, capi.ADDRESS_CLAMP_TO_EDGE)
+        b = r.render()[0].copy()
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR, capi.ADDRESS_MIRRORED_REPEAT)
+        c = r.render()[0].copy()
+    assert np.abs(a - b).max() <= 2.0 / 255.0 and a[..., 0].max() > 0.05
+    assert np.abs(a - c).max() > 1e-3       # the address mode matters for these coordinates
+
+
+def _c2_kw(max_steps, light):
+    return dict(density_mode=2, max_steps=max_steps, sigma_t=8.0, light_steps=light, light_step_len=2 * 4.0 / max_steps,
+                ambient=0.15, sun_dir=SUN, sun_color=[1.0, 0.95, 0.85])
+
+
+@pytest.mark.parametrize("W,H,steps,light", [(1920, 1080, 128, 6), (3840, 2160, 256, 8)])
+def test_full_size_procedural_cloud(oracle, W, H, steps, light):
+    """BASELINE.json configs[1] and configs[2] at full size: oracle parity on a strided row sample (north-star
+    tolerance), bands == frame, idempotence."""
+    u0, u1 = scene.default_scene()
+    kw = _c2_kw(steps, light)
+    rows = np.arange(H // 12, H, H // 6, dtype=np.int32)[:5]
+    scal = {k: v for k, v in kw.items() if not hasattr(v, "__len__")}
+    p = oracle_params(oracle, u0, u1, **scal)
+    oracle.set_params(p, sun_dir=SUN, sun_color=[1.0, 0.95, 0.85])
+    ref, st = oracle.render_rows(None, p, W, H, rows)
+    ref8 = oracle.encode(ref, oracle.OUT_RGBA8_UNORM)
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM) as r:
+        r.set_params(u0, u1, **kw)
+        img = r.render()[0].copy()
+        again = r.render()[0].copy()
+        bands = np.zeros_like(img)[None]
+        b = r.row_bands(5)
+        for b0, b1 in zip(b, b[1:]):
+            if b1 > b0:
+                r.render(out=bands, rows=(b0, b1))
+    assert np.array_equal(img, again)
+    # a band of a different height may pick a different lanes-per-ray mapping: equal within re-association noise
+    assert max_abs8(img, bands[0]) <= 1
+    assert st["covered"] > 1000 and ref8[..., 0].max() > 60
+    assert max_abs8(img[rows], ref8) <= 2
+    assert psnr8(img[rows], ref8) >= 50.0
+    assert img[..., 3].min() == 255
+
+
+def test_full_size_fp16_grid_512(oracle):
+    """BASELINE.json configs[3]: 512^3 fp16 grid at 1080p; the device-baked grid is downloaded so that both sides
+    sample the same bytes; texture path within tolerance, TMA-brick path bit-exact, on a strided row sample."""
+    W, H, n = 1920, 1080, 512
+    u0, u1 = scene.default_scene()
+    rows = np.array([300, 540, 800], np.int32)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.generate_volume(size=n, format=capi.VOL_R16F, layout=capi.LAYOUT_TEXTURE)
+        vol = r.download_volume()
+        r.set_params(u0, u1, density_mode=capi.DENSITY_SINGLE, max_steps=512, sample_scale=4.0)
+        tex = r.render()[0][rows].copy()
+        r.upload_volume(vol, capi.VOL_R16F, capi.LAYOUT_BRICK)
+        brick = r.render()[0][rows].copy()
+    p = oracle_params(oracle, u0, u1, density_mode=oracle.DENSITY_SINGLE, max_steps=512, sample_scale=4.0)
+    ov, _k = oracle.make_volume(vol.view(np.uint16), oracle.VOL_R16F)
+    ref, st = oracle.render_rows(ov, p, W, H, rows)
+    assert ref[..., 0].max() > 0.3
+    assert np.array_equal(brick.view(np.uint32), ref.view(np.uint32))
+    assert np.abs(tex - ref).max() <= 2.0 / 255.0
+
+
+def test_view_batch_equals_single_views(oracle):
+    """C5 shape at test size: skipping + early termination over a view batch == each view alone"""
+    W, H = 320, 180
+    g = smoke_volume(64, 5)
+    g[g < np.float16(0.4)] = 0
+    views = scene.orbit_views(6)
+    kw = dict(density_mode=1, max_steps=256, sample_scale=1.0, sigma_t=30.0, early_term_eps=1.0 / 512, skip_empty=1,
+              ambient=1.0, sun_color=[0.0, 0.0, 0.0])
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, max_views=6) as r:
+        r.upload_volume(g, capi.VOL_R16F, capi.LAYOUT_TEXTURE)
+        r.set_params(view_ubos=views, **kw)
+        batch = r.render().copy()
+        some = r.render(views=(2, 5)).copy()
+        r.render(flags=capi.RENDER_STATS)
+        s = r.stats()
+    assert np.array_equal(batch[2:5], some)
+    assert s["skipped_steps"] > 0 and s["early_terminated"] > 0
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM) as r:
+        r.upload_volume(g, capi.VOL_R16F, capi.LAYOUT_TEXTURE)
+        for k in (0, 3, 5):
+            r.set_params(views[k, :192].view(np.float32), views[k, 192:332].view(np.float32), **kw)
+            assert np.array_equal(r.render()[0], batch[k])
+    # and against the oracle (which neither skips nor splits rays)
+    scal = {k: v for k, v in kw.items() if not hasattr(v, "__len__") and k != "skip_empty"}
+    p = oracle_params(oracle, views[1, :192].view(np.float32), views[1, 192:332].view(np.float32), **scal)
+    oracle.set_params(p, sun_color=[0.0, 0.0, 0.0])
+    ov, _k = oracle.make_volume(g.view(np.uint16), oracle.VOL_R16F)
+    ref, _ = oracle.render(ov, p, W, H)
+    assert max_abs8(batch[1], oracle.encode(ref, oracle.OUT_RGBA8_UNORM)) <= 2
