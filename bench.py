@@ -52,8 +52,13 @@ WORKLOADS = {
                        "empty-space skipping (8^3 bricks) and early termination (T < 1/512), views sharded over the GPUs",
            dict(density_mode=1, max_steps=512, sample_scale=1.0, sigma_t=400.0, early_term_eps=1.0 / 512, skip_empty=1,
                 ambient=1.0, sun_color=[0.0, 0.0, 0.0])),
+    "bake": (0, 0, "start-up bake of the 128^3 RGBA8 noise volume (TestMain.cpp:43-92: cellular x2, Perlin, simplex; min/max "
+                   "normalisation, quirk Q1 included) — 4 fields x 128^3 noise points per step", dict()),
 }
 C5_VIEWS, C5_GRID, C5_THRESHOLD = 64, 1024, 0.07
+BAKE_SIZE, BAKE_FIELDS = 128, 4
+# algorithmic FP32 work of the bake per voxel: 2 cellular fields (27 cells x 14 flop) + Perlin (60) + simplex (4 corners x 20)
+BAKE_FLOP_PER_VOXEL = 2 * 27 * 14.0 + 60.0 + 80.0
 # algorithmic FP32 work: one Perlin octave = 60 flop, +20 per fBm sample for the
 # remap/falloff, 26 flop per step for the integrator; FMA = 2 flop.
 FLOP_PER_OCTAVE, FLOP_PER_SAMPLE, FLOP_PER_STEP = 60.0, 20.0, 26.0
@@ -474,6 +479,115 @@ def run_views(args, rank, world, local):
         dist.destroy_process_group()
 
 
+def time_cpu_bake(repeats):
+    """the reference's own bake (FastNoise2 compiled from its sources, oracle/_ref) when present, else the oracle port"""
+    from oracle import oracle
+    n, pts = BAKE_SIZE, BAKE_FIELDS * BAKE_SIZE ** 3
+    use_ref = oracle.have_ref()
+    ts = []
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        if use_ref:
+            oracle.ref_bake_default(n)
+        else:
+            oracle.bake_default(n, threads=1)
+        ts.append(time.perf_counter() - t0)
+    t = float(np.median(ts))
+    return {"value": pts / t / 1e6, "unit": "Mpoints/s", "cores": 1, "kind": "reference" if use_ref else "port",
+            "sample": "%d full 128^3 bakes, median; %s, one thread like the reference's start-up code" %
+                      (repeats, "FastNoise2 (reference sources, best SIMD level of this CPU)" if use_ref else "scalar oracle port"),
+            "ms": t * 1e3}
+
+
+def run_bake(args, rank, world, local):
+    """The start-up bake as its own bench line.  N > 1: replicas (every rank needs the whole volume; 'weak')."""
+    W, H, desc, _ = WORKLOADS["bake"]
+    n, pts = BAKE_SIZE, BAKE_FIELDS * BAKE_SIZE ** 3
+    K, Wm = args.steps, max(args.warmup, 3)
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        cb = time_cpu_bake(max(3, min(K + Wm, 40)))
+        print(json.dumps({
+            "impl": "reference", "metric": "Mpoints/s", "value": cb["value"], "unit": "Mpoints/s", "n_gpus": args.gpus, "steps": K,
+            "warmup": Wm, "ms_per_step": cb["ms"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": "bake: " + desc, "size": n},
+            "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": cb["value"], "unit": "Mpoints/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}), flush=True)
+        return
+    import volumetricrenderer_b200 as vr
+    from volumetricrenderer_b200 import capi
+    from volumetricrenderer_b200.renderer import PinnedArray
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    r = vr.Renderer(64, 64, capi.OUT_RGBA8_UNORM, device=local)
+    host = PinnedArray((n, n, n, 4), np.uint8)
+
+    def barrier():
+        r.wait()
+        if dist is not None:
+            dist.barrier(device_ids=[local])
+
+    for _ in range(Wm):
+        r.generate_volume(size=n)
+    launches = r.stats()["kernel_launches"]
+    sampler = ClockSampler(physical_gpu_index(local))
+    barrier()
+    sampler.start()
+    dev_ms, t0 = 0.0, time.perf_counter()
+    for _ in range(K):
+        r.flush_l2()
+        r.generate_volume(size=n)
+        dev_ms += r.stats()["gpu_ms"]
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    # e2e: the call a host makes (synchronous bake) + the texels read back to pinned host memory
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        r.generate_volume(size=n)
+        r.download_volume(out=host.array)
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / K
+    ms = dev_ms / K
+    if dist is not None:
+        import torch
+        t = torch.tensor([ms, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1])
+    if rank == 0:
+        peaks = r.measure_peaks()
+        ach = BAKE_FLOP_PER_VOXEL * n ** 3 / (ms * 1e-3) / 1e12
+        line = {
+            "metric": "Mpoints/s", "value": world * pts / (ms * 1e-3) / 1e6, "unit": "Mpoints/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "bake: " + desc, "size": n, "l2": "flushed between bakes (256 MiB write)",
+                       "partition": "replicas (every GPU bakes its own copy of the volume)" if world > 1 else "single GPU"},
+            "e2e": {"value": world * pts / e2e_s / 1e6, "unit": "Mpoints/s", "ms_per_bake": e2e_s * 1e3,
+                    "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4 * n ** 3},
+            "gpu_launches": K * launches, "clocks": clocks, "wall_ms_per_step_incl_flush": wall / K * 1e3,
+            "roofline": {"bound": "fp32", "achieved": ach, "peak": peaks["fp32_tflops"], "unit": "TFLOP/s",
+                         "frac": ach / peaks["fp32_tflops"] if peaks["fp32_tflops"] else None, "traffic": None,
+                         "note": "whole bake (fill x3, min/max-only x1, pack, texture copy, occupancy) against the FP32 FMA peak measured in this "
+                                 "process; algorithmic %.0f flop/voxel; 128^3 is %d CTAs of work per field, launch latency is a visible share" %
+                                 (BAKE_FLOP_PER_VOXEL, n ** 3 // 256)},
+        }
+        if not args.no_cpu_baseline and world == 1:
+            cb = time_cpu_bake(20)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        print(json.dumps(line), flush=True)
+    barrier()
+    host.close()
+    r.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world):
     """Dominant kernel = the march (the only kernel in the timed region).  Neither HBM nor the tensor cores bound
     this path: the procedural workloads read no input and the grid workloads' volumes are L2- or
@@ -530,6 +644,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload == "bake":
+        run_bake(args, rank, world, local)
+        return
     if args.impl == "reference":
         run_reference(args, rank, world)
         return

@@ -226,7 +226,7 @@ typedef struct vr_target {
 
 typedef struct vr_stats {
     uint32_t struct_size;
-    float gpu_ms;                /* device time of the last vr_render's kernels (CUDA events)  */
+    float gpu_ms;                /* device time (CUDA events) of the last vr_render's kernels, or of the last upload / bake */
     uint64_t rays;               /* pixels shaded or cleared                                   */
     uint64_t covered;            /* VR_RENDER_STATS only from here on                          */
     uint64_t steps;

@@ -45,6 +45,11 @@ struct vr_context {
     alignas(64) unsigned char tensor_map[128] = {};   // BRICK layout: CUtensorMap over `lin`
     bool has_tensor_map = false;
     BrickInfo bricks{};
+    // bake scratch, kept between vr_generate_volume calls of the same size
+    float* bake_plane[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t bake_plane_bytes = 0;
+    unsigned int* d_mm = nullptr;
+    uint32_t fill_launches = 0;            // kernels the current upload / bake has launched so far
     // params
     bool has_params = false;
     vr_params params{};
@@ -207,6 +212,8 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->d_row_cost) cudaFree(c->d_row_cost);
     if (c->d_queue) cudaFree(c->d_queue);
+    for (float* pl : c->bake_plane) if (pl) cudaFree(pl);
+    if (c->d_mm) cudaFree(c->d_mm);
     if (c->flush_buf) cudaFree(c->flush_buf);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
@@ -225,7 +232,7 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
             default: cd = cudaCreateChannelDesc<unsigned char>(); break;
         }
         cudaExtent ext = make_cudaExtent(d.width, d.height, d.depth);
-        VR_CUDA(c, cudaMalloc3DArray(&c->array, &cd, ext));
+        if (!c->array) VR_CUDA(c, cudaMalloc3DArray(&c->array, &cd, ext));
         cudaMemcpy3DParms cp = {};
         cp.srcPtr = make_cudaPitchedPtr(c->lin, d.width * texel_bytes(d.format), d.width, d.height);
         cp.dstArray = c->array;
@@ -242,7 +249,7 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
         td.filterMode = cudaFilterModeLinear;
         td.readMode = d.format == VR_VOL_R16F ? cudaReadModeElementType : cudaReadModeNormalizedFloat;
         td.normalizedCoords = 1;
-        VR_CUDA(c, cudaCreateTextureObject(&c->tex, &rd, &td, nullptr));
+        if (!c->tex) VR_CUDA(c, cudaCreateTextureObject(&c->tex, &rd, &td, nullptr));
     }
     c->has_tensor_map = false;
     if (layout == VR_LAYOUT_BRICK) {
@@ -268,13 +275,39 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
     BrickInfo& B = c->bricks;
     B.bx = (d.width + 7) / 8; B.by = (d.height + 7) / 8; B.bz = (d.depth + 7) / 8;
     B.inv_brick[0] = (float)d.width / 8.0f; B.inv_brick[1] = (float)d.height / 8.0f; B.inv_brick[2] = (float)d.depth / 8.0f;
-    VR_CUDA(c, cudaMalloc(&c->occupied, (size_t)B.bx * B.by * B.bz));
+    if (!c->occupied) VR_CUDA(c, cudaMalloc(&c->occupied, (size_t)B.bx * B.by * B.bz));
     B.occupied = c->occupied;
     VR_CUDA(c, launch_occupancy(c->lin, d.format, d.width, d.height, d.depth, d.address_mode, c->occupied, B.bx, B.by, B.bz, c->stream));
+    VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->foreign_stream_pending = false;
+    c->stats.rays = 0;
+    c->stats.kernel_launches = c->fill_launches + 1;       // + the occupancy kernel
+    c->fill_launches = 0;
+    std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     c->vdesc = d;
     c->vdesc.layout = layout;
     c->has_volume = true;
+    return VR_OK;
+}
+
+// storage for a volume of this description: kept when the previous volume had the same shape (an interactive
+// host re-uploads or re-bakes every so often; allocation and texture-object creation cost far more than the fill)
+static vr_status prepare_volume(vr_context* c, const vr_volume_desc& d) {
+    const uint32_t layout = d.layout == VR_LAYOUT_AUTO ? (uint32_t)VR_LAYOUT_TEXTURE : d.layout;
+    const vr_volume_desc& o = c->vdesc;
+    const bool same = c->has_volume && o.width == d.width && o.height == d.height && o.depth == d.depth && o.format == d.format &&
+                      o.address_mode == d.address_mode && o.layout == layout;
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (same) c->has_volume = false;                         // storage stays; has_volume returns with finish_volume
+    else {
+        release_volume(c);
+        c->lin_bytes = (size_t)d.width * d.height * d.depth * texel_bytes(d.format);
+        VR_CUDA(c, cudaMalloc(&c->lin, c->lin_bytes));
+    }
+    c->fill_launches = 0;
+    VR_CUDA(c, cudaEventRecord(c->ev0, c->stream));          // vr_get_stats().gpu_ms of an upload / bake: fill + texture + occupancy
     return VR_OK;
 }
 
@@ -296,10 +329,8 @@ extern "C" vr_status vr_upload_volume(vr_context* c, const vr_volume_desc* d, co
     vr_status st = check_volume_desc(c, d);
     if (st != VR_OK) return st;
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    release_volume(c);
-    c->lin_bytes = (size_t)d->width * d->height * d->depth * texel_bytes(d->format);
-    VR_CUDA(c, cudaMalloc(&c->lin, c->lin_bytes));
+    st = prepare_volume(c, *d);
+    if (st != VR_OK) return st;
     // synchronous like the reference's staging copy + vkQueueWaitIdle (VulkanCore.cpp:529-541)
     VR_CUDA(c, cudaMemcpyAsync(c->lin, texels, c->lin_bytes, cudaMemcpyHostToDevice, c->stream));
     st = finish_volume(c, *d);
@@ -350,12 +381,10 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
     if (st != VR_OK) return st;
     if (d->format == VR_VOL_R8_UNORM) return fail(c, VR_ERR_UNSUPPORTED, "vr_generate_volume: RGBA8 (channel recipes) or R16F (fBm smoke) only");
     VR_CUDA(c, cudaSetDevice(c->device));
-    VR_CUDA(c, cudaStreamSynchronize(c->stream));
-    release_volume(c);
+    st = prepare_volume(c, vd);
+    if (st != VR_OK) return st;
     const int n = (int)d->size;
     const size_t vox = (size_t)n * n * n;
-    c->lin_bytes = vox * texel_bytes(d->format);
-    VR_CUDA(c, cudaMalloc(&c->lin, c->lin_bytes));
     if (d->format == VR_VOL_R16F) {
         vr_params def;
         vr_params_default(&def);
@@ -364,6 +393,7 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
         FbmField ff = {f->fbm_octaves, f->fbm_seed, f->fbm_frequency, f->fbm_gain, f->fbm_lacunarity, f->fbm_coverage,
                        f->fbm_falloff0, f->fbm_falloff1, fbm_bounding(f->fbm_octaves, f->fbm_gain), d->threshold};
         VR_CUDA(c, launch_smoke_fill(ff, n, (__half*)c->lin, c->stream));
+        c->fill_launches = 1;
     } else {
         // each distinct field is generated once; min/max folded on the device
         struct Gen { NoiseField f; float* buf; unsigned int* mm; bool keep; };
@@ -394,16 +424,23 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
             }
             if (norm_of[k] < 0) { release_volume(c); return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: a channel needs a non-zero field to normalise with"); }
         }
-        unsigned int* d_mm = nullptr;
+        // scratch planes (one fp32 plane per kept field, at most 4) and the min/max words live in the context
         std::vector<unsigned int> h_mm(gens.size() * 2);
         for (size_t i = 0; i < gens.size(); ++i) minmax_init(&h_mm[i * 2]);
-        auto cleanup = [&]() { for (auto& g : gens) if (g.buf) cudaFree(g.buf); if (d_mm) cudaFree(d_mm); };
-        cudaError_t e = cudaMalloc(&d_mm, h_mm.size() * sizeof(unsigned int));
+        cudaError_t e = cudaSuccess;
+        if (!c->d_mm) e = cudaMalloc(&c->d_mm, 16 * sizeof(unsigned int));     // <= 8 distinct fields (4 channels x {field, norm})
+        unsigned int* d_mm = c->d_mm;
+        if (c->bake_plane_bytes != vox * sizeof(float)) {
+            for (float*& pl : c->bake_plane) { if (pl) cudaFree(pl); pl = nullptr; }
+            c->bake_plane_bytes = vox * sizeof(float);
+        }
         if (e == cudaSuccess) e = cudaMemcpyAsync(d_mm, h_mm.data(), h_mm.size() * sizeof(unsigned int), cudaMemcpyHostToDevice, c->stream);
+        int plane = 0;
         for (size_t i = 0; i < gens.size() && e == cudaSuccess; ++i) {
             gens[i].mm = d_mm + i * 2;
             if (gens[i].keep) {
-                e = cudaMalloc(&gens[i].buf, vox * sizeof(float));
+                if (!c->bake_plane[plane]) e = cudaMalloc(&c->bake_plane[plane], c->bake_plane_bytes);
+                gens[i].buf = c->bake_plane[plane++];
                 if (e == cudaSuccess) e = launch_noise_fill(gens[i].f, n, gens[i].buf, gens[i].mm, c->stream);
             } else {
                 e = launch_noise_minmax_only(gens[i].f, n, gens[i].mm, c->stream);
@@ -420,9 +457,12 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
                 pc[k].power = d->channel[k].power;
             }
             e = launch_noise_pack(pc, (int64_t)vox, (uint8_t*)c->lin, c->stream);
+            c->fill_launches = (uint32_t)gens.size() + 1;
         }
-        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-        cleanup();
+        if (c->bake_plane_bytes > ((size_t)256 << 20)) {       // large bakes give their scratch back (cudaFree waits for the pack)
+            for (float*& pl : c->bake_plane) { if (pl) cudaFree(pl); pl = nullptr; }
+            c->bake_plane_bytes = 0;
+        }
         if (e != cudaSuccess) { release_volume(c); return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, "vr_generate_volume", e); }
     }
     st = finish_volume(c, vd);

@@ -122,9 +122,10 @@ class Renderer:
         self._vol_fmt = d.format
         self._vol_shape = (n, n, n, 4) if d.format == capi.VOL_RGBA8_UNORM else (n, n, n)
 
-    def download_volume(self):
+    def download_volume(self, out=None):
         dt, _ = _VOL_DTYPE[self._vol_fmt]
-        out = np.empty(self._vol_shape, dt)
+        if out is None:
+            out = np.empty(self._vol_shape, dt)
         self._check(self._lib.vr_download_volume(self._ctx, out.ctypes.data, out.nbytes))
         return out
 
