@@ -175,3 +175,40 @@ def test_view_batch_equals_single_views(oracle):
     ov, _k = oracle.make_volume(g.view(np.uint16), oracle.VOL_R16F)
     ref, _ = oracle.render(ov, p, W, H)
     assert max_abs8(batch[1], oracle.encode(ref, oracle.OUT_RGBA8_UNORM)) <= 2
+
+
+@pytest.mark.parametrize("fmt,shape", [(capi.VOL_R16F, (40, 24, 64)), (capi.VOL_R16F, (17, 23, 29)),
+                                        (capi.VOL_R8_UNORM, (32, 40, 48)), (capi.VOL_R8_UNORM, (9, 31, 50)),
+                                        (capi.VOL_RGBA8_UNORM, (24, 16, 36)), (capi.VOL_RGBA8_UNORM, (10, 13, 27))])
+def test_occupancy_grid_aprons(fmt, shape):
+    """Empty-space skipping must not change a single sample: isolated non-zero texels on and next to brick borders
+    (x, y, z = 7, 8 mod 8, first and last texel) light up the neighbouring bricks through the 1-texel apron.  Row
+    pitches that are and are not multiples of 16 bytes take the vector and the scalar path of the occupancy kernel."""
+    d, h, w = shape
+    rng = np.random.default_rng(d * 10000 + h * 100 + w)
+    ch = 4 if fmt == capi.VOL_RGBA8_UNORM else 1
+    vol = np.zeros((d, h, w, ch), np.float32)
+    pts = [(0, 0, 0), (d - 1, h - 1, w - 1), (7, 7, 7), (8, 8, 8), (7, 8, 15), (d // 2, 7, 16), (8, h // 2, 23), (d - 1, 0, 8)]
+    pts += [tuple(int(rng.integers(0, n)) for n in (d, h, w)) for _ in range(6)]
+    for z, y, x in pts:
+        vol[min(z, d - 1), min(y, h - 1), min(x, w - 1), :] = 1.0
+    if fmt == capi.VOL_R16F:
+        texels = vol[..., 0].astype(np.float16)
+    elif fmt == capi.VOL_R8_UNORM:
+        texels = (vol[..., 0] * 255).astype(np.uint8)
+    else:
+        texels = (vol * 255).astype(np.uint8)
+    W, H = 320, 200
+    u0, u1 = scene.default_scene(31.0, 12.0)
+    mode = capi.DENSITY_SINGLE if ch == 1 else 0
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(texels, fmt, capi.LAYOUT_LINEAR)
+        r.set_params(u0, u1, density_mode=mode, sample_scale=0.25, max_steps=400, density=40.0)
+        plain = r.render()[0].copy()
+        r.set_params(u0, u1, density_mode=mode, sample_scale=0.25, max_steps=400, density=40.0, skip_empty=1)
+        skipped = r.render(flags=capi.RENDER_STATS)[0]
+        s = r.stats()
+    assert plain[..., 0].max() > 0.0
+    if ch == 1:
+        assert s["skipped_steps"] > 0
+        assert np.array_equal(plain.view(np.uint32), skipped.view(np.uint32))

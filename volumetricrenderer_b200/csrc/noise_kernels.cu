@@ -145,30 +145,74 @@ cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_
 // Occupancy of 8^3-voxel bricks: a trilinear fetch at a position inside brick b touches texels
 // 8b-1 .. 8b+8 per axis, so the brick is "empty" iff all of those are exactly zero.  Index -1
 // and N wrap to 0 and N-1 in both addressing modes, so clamping the apron is exact.
-// One CTA per brick, 10x10 (y,z) rows spread over the threads, each reads 10 x-texels.
-__global__ void __launch_bounds__(128) occupancy_kernel(const void* __restrict__ lin, int vol_format, int w, int h, int d,
+// One CTA per row of bricks along x (fixed iy, iz): its 10x10 (y,z) texel rows are read once, whole and
+// coalesced (16 bytes per lane when the row pitch allows), and every non-zero texel marks its own brick plus the
+// x-neighbour whose apron it sits in.  The y/z aprons make the read 100/64 of the volume; the excess hits L2.
+__device__ __forceinline__ void occ_mark(unsigned char* s, int bx, int x0, unsigned m, int T) {
+    // m: non-zero mask of T consecutive texels starting at x0 (T divides 8 or is a multiple of 8, x0 % T == 0)
+    const int groups = T >= 8 ? T / 8 : 1, gw = T >= 8 ? 8 : T;
+    for (int g = 0; g < groups; ++g) {
+        const unsigned gm = T >= 8 ? (m >> (8 * g)) & 0xffu : m;
+        if (!gm) continue;
+        const int gx = x0 + 8 * g, brick = gx >> 3, off = gx & 7;
+        s[brick] = 1;
+        if ((gm & 1u) && off == 0 && brick > 0) s[brick - 1] = 1;
+        if ((gm & (1u << (gw - 1))) && off + gw == 8 && brick + 1 < bx) s[brick + 1] = 1;
+    }
+}
+__device__ __forceinline__ unsigned occ_mask16(uint4 q, int vol_format) {
+    const unsigned wv[4] = {q.x, q.y, q.z, q.w};
+    unsigned m = 0;
+    if (vol_format == VR_VOL_R16F) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) m |= ((wv[i] & 0x7fffu) ? 1u : 0u) << (2 * i) | ((wv[i] & 0x7fff0000u) ? 1u : 0u) << (2 * i + 1);
+    } else if (vol_format == VR_VOL_R8_UNORM) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) m |= ((wv[i] >> (8 * k)) & 0xffu ? 1u : 0u) << (4 * i + k);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) m |= (wv[i] ? 1u : 0u) << i;
+    }
+    return m;
+}
+__global__ void __launch_bounds__(256) occupancy_kernel(const void* __restrict__ lin, int vol_format, int w, int h, int d,
                                                         unsigned char* __restrict__ occupied, int bx, int by) {
-    const int b = blockIdx.x;
-    const int ix = b % bx, iy = (b / bx) % by, iz = b / (bx * by);
-    int any = 0;
-    if (threadIdx.x < 100) {
-        int yy = min(max(iy * 8 - 1 + (int)(threadIdx.x % 10), 0), h - 1);
-        int zz = min(max(iz * 8 - 1 + (int)(threadIdx.x / 10), 0), d - 1);
-        size_t row = ((size_t)zz * h + yy) * w;
-        for (int k = 0; k < 10; ++k) {
-            int xx = min(max(ix * 8 - 1 + k, 0), w - 1);
-            size_t idx = row + xx;
-            if (vol_format == VR_VOL_R16F) any |= (((const unsigned short*)lin)[idx] & 0x7fffu) != 0;
-            else if (vol_format == VR_VOL_R8_UNORM) any |= ((const unsigned char*)lin)[idx] != 0;
-            else any |= ((const unsigned int*)lin)[idx] != 0;
+    __shared__ unsigned char s[512];                       // bx <= 4096 / 8
+    const int iy = blockIdx.x % by, iz = blockIdx.x / by;
+    for (int i = threadIdx.x; i < bx; i += blockDim.x) s[i] = 0;
+    __syncthreads();
+    const int tb = vol_format == VR_VOL_R16F ? 2 : vol_format == VR_VOL_R8_UNORM ? 1 : 4;
+    const int T = 16 / tb;
+    const bool vec = ((size_t)w * tb) % 16 == 0;          // every row starts 16-byte aligned (lin comes from cudaMalloc)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int row = warp; row < 100; row += 8) {
+        const int yy = min(max(iy * 8 - 1 + row % 10, 0), h - 1);
+        const int zz = min(max(iz * 8 - 1 + row / 10, 0), d - 1);
+        const char* base = (const char*)lin + ((size_t)zz * h + yy) * w * tb;
+        if (vec) {
+            const int nvec = w / T;
+            for (int v = lane; v < nvec; v += 32) {
+                const unsigned m = occ_mask16(__ldg((const uint4*)base + v), vol_format);
+                if (m) occ_mark(s, bx, v * T, m, T);
+            }
+        } else {
+            for (int x = lane; x < w; x += 32) {
+                unsigned nz;
+                if (vol_format == VR_VOL_R16F) nz = (((const unsigned short*)base)[x] & 0x7fffu) != 0;
+                else if (vol_format == VR_VOL_R8_UNORM) nz = ((const unsigned char*)base)[x] != 0;
+                else nz = ((const unsigned int*)base)[x] != 0;
+                if (nz) occ_mark(s, bx, x, 1u, 1);
+            }
         }
     }
-    any = __syncthreads_or(any);
-    if (threadIdx.x == 0) occupied[b] = any ? 1 : 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < bx; i += blockDim.x) occupied[(size_t)blockIdx.x * bx + i] = s[i];
 }
 cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int /*address_mode*/,
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s) {
-    occupancy_kernel<<<bx * by * bz, 128, 0, s>>>(lin, vol_format, w, h, d, occupied, bx, by);
+    occupancy_kernel<<<by * bz, 256, 0, s>>>(lin, vol_format, w, h, d, occupied, bx, by);
     return cudaGetLastError();
 }
 

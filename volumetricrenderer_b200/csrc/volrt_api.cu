@@ -459,7 +459,7 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
             e = launch_noise_pack(pc, (int64_t)vox, (uint8_t*)c->lin, c->stream);
             c->fill_launches = (uint32_t)gens.size() + 1;
         }
-        if (c->bake_plane_bytes > ((size_t)256 << 20)) {       // large bakes give their scratch back (cudaFree waits for the pack)
+        if (c->bake_plane_bytes > ((size_t)1 << 30)) {         // very large bakes give their scratch back (cudaFree waits for the pack)
             for (float*& pl : c->bake_plane) { if (pl) cudaFree(pl); pl = nullptr; }
             c->bake_plane_bytes = 0;
         }
