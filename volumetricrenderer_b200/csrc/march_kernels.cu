@@ -239,6 +239,36 @@ __device__ __forceinline__ bool brick_occupied(const MarchParams& P, f3 p) {
     int bz = min(max((int)(p.z * B.inv_brick[2]), 0), B.bz - 1);
     return __ldg(B.occupied + ((size_t)bz * B.by + by) * B.bx + bx) != 0;
 }
+// 0 = the brick under p is occupied, else its Chebyshev distance (bricks) to the nearest occupied brick
+__device__ __forceinline__ int brick_distance(const MarchParams& P, f3 p) {
+    const BrickInfo& B = P.bricks;
+    int bx = min(max((int)(p.x * B.inv_brick[0]), 0), B.bx - 1);
+    int by = min(max((int)(p.y * B.inv_brick[1]), 0), B.by - 1);
+    int bz = min(max((int)(p.z * B.inv_brick[2]), 0), B.bz - 1);
+    return (int)__ldg(B.dist + ((size_t)bz * B.by + by) * B.bx + bx);
+}
+// Empty-space leaping.  From a sample in a brick of distance d >= 2, every sample whose coordinates have moved by less
+// than (d-1) bricks on every axis still lies in an empty brick, so m = floor(min_c((d-1)*brick_c - eps) / |step_c|)
+// further steps can be skipped without a lookup.  eps (1e-4 texture units) absorbs the rounding of the running add.
+struct Leap { float k, e; };
+__device__ __forceinline__ Leap leap_setup(const MarchParams& P, f3 step) {
+    const BrickInfo& B = P.bricks;
+    const float a[3] = {fabsf(step.x), fabsf(step.y), fabsf(step.z)};
+    Leap L = {1e30f, 0.0f};
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+        if (a[c] > 1e-20f) {
+            const float inv = 1.0f / a[c];
+            L.k = fminf(L.k, inv / B.inv_brick[c]);
+            L.e = fmaxf(L.e, 1e-4f * inv);
+        }
+    return L;
+}
+__device__ __forceinline__ int leap_steps(const Leap& L, int d, int left) {     // left = steps remaining after this one
+    if (d < 2) return 0;
+    const int m = (int)fmaf((float)(d - 1), L.k, -L.e);
+    return max(0, min(m, left));
+}
 __device__ __forceinline__ bool inside01(f3 p) {
     return p.x >= 0.0f && p.x <= 1.0f && p.y >= 0.0f && p.y <= 1.0f && p.z >= 0.0f && p.z <= 1.0f;
 }
@@ -268,6 +298,8 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
     f3 p = ray.pin;
     const int n = ray.n;
     const bool skip = CAN_SKIP && P.skip_empty;
+    Leap leap = {0.0f, 0.0f};
+    if (skip) leap = leap_setup(P, ray.step);
     unsigned long long n_light = 0, n_skipped = 0;
     bool early = false;
     float cr, cg, cb;
@@ -299,7 +331,17 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
             }
         }
         for (; i < n; ++i) {
-            if (skip && !brick_occupied(P, p)) { if (STATS) ++n_skipped; p = add3(p, ray.step); continue; }
+            if (skip) {
+                const int bd = brick_distance(P, p);
+                if (bd) {
+                    const int m = leap_steps(leap, bd, n - 1 - i);
+                    if (STATS) n_skipped += (unsigned long long)(m + 1);
+                    if (STRICT) { for (int j = 0; j <= m; ++j) p = add3(p, ray.step); }      // the oracle's running add, bit for bit
+                    else { const float fm = (float)(m + 1); p = {fmaf(fm, ray.step.x, p.x), fmaf(fm, ray.step.y, p.y), fmaf(fm, ray.step.z, p.z)}; }
+                    i += m;
+                    continue;
+                }
+            }
             float d = density_at<VARIANT>(P, rc, unorm, &lut, p);
             acc = STRICT ? add(acc, d) : acc + d;
             p = add3(p, ray.step);                                                     // running add, :74
@@ -317,8 +359,18 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
         const f3 lv = {P.sun_dir[0] * P.light_step_len * 0.5f, P.sun_dir[1] * P.light_step_len * 0.5f, P.sun_dir[2] * P.light_step_len * 0.5f};
         for (int i = 0; i < n; ++i) {
             float rho = 0.0f;
-            if (skip && !brick_occupied(P, p)) { if (STATS) ++n_skipped; }
-            else rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
+            if (skip) {
+                const int bd = brick_distance(P, p);
+                if (bd) {
+                    const int m = leap_steps(leap, bd, n - 1 - i);
+                    if (STATS) n_skipped += (unsigned long long)(m + 1);
+                    if (STRICT) { for (int j = 0; j <= m; ++j) p = add3(p, ray.step); }
+                    else { const float fm = (float)(m + 1); p = {fmaf(fm, ray.step.x, p.x), fmaf(fm, ray.step.y, p.y), fmaf(fm, ray.step.z, p.z)}; }
+                    i += m;
+                    continue;           // transmittance unchanged: nothing to test for early termination
+                }
+            }
+            rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
             if (rho > 0.0f) {                       // rho == 0 contributes exactly nothing
                 float a = 1.0f - expf(-P.sigma_t * rho * step_size);
                 float S = 1.0f;

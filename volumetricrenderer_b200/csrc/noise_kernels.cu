@@ -216,4 +216,36 @@ cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int 
     return cudaGetLastError();
 }
 
+// ---- brick distance map: dist[b] = 0 for an occupied brick, else the Chebyshev distance (in bricks, capped at 255)
+// to the nearest occupied one.  A ray sample in a brick of distance d can advance while no coordinate leaves the
+// (2d-1)^3 block of empty bricks around it, so the march leaps over empty space with one byte lookup per leap.
+// min-max is separable: min_q max(|dx|,|dy|,|dz|) = min_z' max(|dz|, min_y' max(|dy|, min_x' |dx|)), one pass per axis;
+// a pass only looks at offsets smaller than its current best, so it costs O(distance) per brick.
+template <int AXIS, bool FIRST>
+__global__ void __launch_bounds__(256) brick_distance_pass_kernel(const unsigned char* __restrict__ in, unsigned char* __restrict__ out,
+                                                                  int bx, int by, int bz) {
+    const int total = bx * by * bz, idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int ix = idx % bx, iy = (idx / bx) % by, iz = idx / (bx * by);
+    const int n = AXIS == 0 ? bx : AXIS == 1 ? by : bz, pos = AXIS == 0 ? ix : AXIS == 1 ? iy : iz;
+    const int stride = AXIS == 0 ? 1 : AXIS == 1 ? bx : bx * by;
+    auto val = [&](int q) -> int {
+        const int v = in[idx + (q - pos) * stride];
+        return FIRST ? (v ? 0 : 255) : v;
+    };
+    int best = val(pos);
+    for (int k = 1; k < best; ++k) {
+        if (pos - k >= 0) best = min(best, max(k, val(pos - k)));
+        if (pos + k < n) best = min(best, max(k, val(pos + k)));
+    }
+    out[idx] = (unsigned char)best;
+}
+cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_t* tmp, int bx, int by, int bz, cudaStream_t s) {
+    const int total = bx * by * bz, grid = (total + 255) / 256;
+    brick_distance_pass_kernel<0, true><<<grid, 256, 0, s>>>(occupied, dist, bx, by, bz);
+    brick_distance_pass_kernel<1, false><<<grid, 256, 0, s>>>(dist, tmp, bx, by, bz);
+    brick_distance_pass_kernel<2, false><<<grid, 256, 0, s>>>(tmp, dist, bx, by, bz);
+    return cudaGetLastError();
+}
+
 }  // namespace volrt

@@ -42,6 +42,7 @@ struct vr_context {
     cudaArray_t array = nullptr;
     cudaTextureObject_t tex = 0;
     uint8_t* occupied = nullptr;
+    uint8_t* brick_dist = nullptr;         // 2 planes: the distance map and the scratch of its passes
     alignas(64) unsigned char tensor_map[128] = {};   // BRICK layout: CUtensorMap over `lin`
     bool has_tensor_map = false;
     BrickInfo bricks{};
@@ -188,6 +189,7 @@ static void release_volume(vr_context* c) {
     if (c->array) { cudaFreeArray(c->array); c->array = nullptr; }
     if (c->lin) { cudaFree(c->lin); c->lin = nullptr; }
     if (c->occupied) { cudaFree(c->occupied); c->occupied = nullptr; }
+    if (c->brick_dist) { cudaFree(c->brick_dist); c->brick_dist = nullptr; }
     c->lin_bytes = 0;
     c->has_volume = false;
 }
@@ -277,12 +279,16 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
     B.inv_brick[0] = (float)d.width / 8.0f; B.inv_brick[1] = (float)d.height / 8.0f; B.inv_brick[2] = (float)d.depth / 8.0f;
     if (!c->occupied) VR_CUDA(c, cudaMalloc(&c->occupied, (size_t)B.bx * B.by * B.bz));
     B.occupied = c->occupied;
+    const size_t nbricks = (size_t)B.bx * B.by * B.bz;
+    if (!c->brick_dist) VR_CUDA(c, cudaMalloc(&c->brick_dist, 2 * nbricks));
+    B.dist = c->brick_dist;
     VR_CUDA(c, launch_occupancy(c->lin, d.format, d.width, d.height, d.depth, d.address_mode, c->occupied, B.bx, B.by, B.bz, c->stream));
+    VR_CUDA(c, launch_brick_distance(c->occupied, c->brick_dist, c->brick_dist + nbricks, B.bx, B.by, B.bz, c->stream));
     VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
     c->foreign_stream_pending = false;
     c->stats.rays = 0;
-    c->stats.kernel_launches = c->fill_launches + 1;       // + the occupancy kernel
+    c->stats.kernel_launches = c->fill_launches + 4;       // + the occupancy kernel and the 3 distance passes
     c->fill_launches = 0;
     std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));

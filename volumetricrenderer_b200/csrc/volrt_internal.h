@@ -24,6 +24,7 @@ struct ViewConst {
 
 struct BrickInfo {          // min-max grid for empty-space skipping (8^3 voxel bricks)
     const uint8_t* occupied;   // 1 byte per brick: 0 = density upper bound is exactly 0
+    const uint8_t* dist;       // 1 byte per brick: 0 = occupied, else Chebyshev distance (bricks, <= 255) to the nearest occupied brick
     int bx, by, bz;            // bricks per axis
     float inv_brick[3];        // bricks per unit of texture coordinate
 };
@@ -99,6 +100,7 @@ cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_r
 cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s);
 cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int address_mode,
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
+cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_t* tmp, int bx, int by, int bz, cudaStream_t s);
 // ---- peak_kernels.cu: measured roofline denominators
 cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_tex_peak(cudaTextureObject_t tex, float* sink, int blocks, int iters, cudaStream_t s);
