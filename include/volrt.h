@@ -47,7 +47,8 @@ enum {
     VR_ERR_CUDA = 2,
     VR_ERR_OUT_OF_MEMORY = 3,
     VR_ERR_UNSUPPORTED = 4,
-    VR_ERR_BAD_STATE = 5
+    VR_ERR_BAD_STATE = 5,
+    VR_ERR_IO = 6                /* volume files: open/read/write failed, bad magic, hash mismatch */
 };
 
 /* colour-target encodings.  The reference renders into the swapchain format, which prefers
@@ -273,6 +274,47 @@ VR_API vr_status vr_flush_l2(vr_context* ctx);
 VR_API vr_status vr_measure_peaks(vr_context* ctx, float* peaks4);
 VR_API void* vr_host_alloc(size_t bytes);
 VR_API void vr_host_free(void* p);
+
+/* ---- volume files.  The reference keeps its volume in memory only (TestMain.cpp:51-92) and its
+ * one loader is stb_image for 2-D pictures (VulkanTexture.cpp:14-55); this is the step in front of vr_upload_volume
+ * for volumes that are shared between runs (a 1024^3 fp16 grid is 2 GiB and 29 ms of bake, or minutes on the CPU).
+ * Layout, little-endian:   [0,128)  header          magic "VOLRTVOL", version 1, dims, format, address mode, section table
+ *                          texels   width*height*depth*texel_bytes, x fastest, tightly packed (what vr_upload_volume takes)
+ *                          pyramid  optional; min-max mip pyramid over 8^3-texel bricks (below)
+ * The header carries the SHA-256 of the texel section.
+ * Min-max pyramid: level 0 has one entry per 8^3 brick (ceil(dim/8) per axis), entry = channels x {min, max} as float32
+ * of the decoded texel values (UNORM8 -> v/255, fp16 -> float), taken over the brick plus a one-texel apron (clamped at
+ * the volume faces) — everything a trilinear fetch inside the brick can touch.  Level l+1 halves each axis (ceil) and
+ * reduces the up to 2x2x2 children.  Levels follow each other, x fastest, until a level is 1x1x1.  A NaN texel makes its
+ * bricks' max NaN on every level.  channels = 4 for RGBA8, else 1. */
+typedef struct vr_volume_file_info {
+    uint32_t struct_size;
+    uint32_t width, height, depth;
+    uint32_t format;             /* vr_volume_format  */
+    uint32_t address_mode;       /* vr_address_mode   */
+    uint32_t pyramid_levels;     /* 0 = the file has no pyramid section */
+    uint32_t reserved;
+    uint64_t texel_bytes;
+    uint64_t pyramid_bytes;
+    uint8_t  sha256[32];         /* of the texel section */
+} vr_volume_file_info;
+#define VR_FILE_VERIFY        1u     /* reading: recompute the SHA-256 of the texels and compare with the header */
+#define VR_FILE_WITH_PYRAMID  2u     /* vr_save_volume_file: append the min-max pyramid (computed on the device) */
+#define VR_FILE_TRUST_PYRAMID 4u     /* vr_upload_volume_file: take the brick occupancy from the file's pyramid level 0
+                                        instead of scanning the texels again */
+/* host only (no device needed) */
+VR_API vr_status vr_sha256(const void* data, size_t bytes, uint8_t out32[32]);
+VR_API vr_status vr_volume_file_write(const char* path, const vr_volume_desc* desc, const void* texels,
+                                      const float* pyramid, uint32_t pyramid_levels);   /* pyramid may be NULL */
+VR_API vr_status vr_volume_file_info_read(const char* path, vr_volume_file_info* info);
+VR_API vr_status vr_volume_file_read(const char* path, void* texels, size_t texel_bytes, float* pyramid, size_t pyramid_bytes,
+                                     uint32_t flags);                                    /* either destination may be NULL */
+VR_API size_t vr_pyramid_floats(uint32_t width, uint32_t height, uint32_t depth, uint32_t format, uint32_t* levels);
+/* device side: file -> pinned staging (two buffers) -> H2D, overlapped; then as vr_upload_volume */
+VR_API vr_status vr_upload_volume_file(vr_context* ctx, const char* path, uint32_t layout, uint32_t flags);
+VR_API vr_status vr_save_volume_file(vr_context* ctx, const char* path, uint32_t flags);
+/* min-max pyramid of the resident volume, computed on the device; out holds vr_pyramid_floats() floats */
+VR_API vr_status vr_volume_pyramid(vr_context* ctx, float* out, size_t out_bytes);
 
 #ifdef __cplusplus
 }

@@ -290,3 +290,52 @@ def ref_bake_default(size=128, level=LEVEL_AUTO):
     if ref().vref_bake_default(out.ctypes.data_as(C.POINTER(C.c_uint8)), size, level, _fp(mm)) != 0:
         raise RuntimeError("FastNoise2 level %d unavailable on this CPU" % level)
     return out, mm
+
+
+# ------------------------------------------------------------------ min-max pyramid (build-defined, include/volrt.h)
+def minmax_pyramid(texels, fmt):
+    """numpy restatement of the min-max pyramid definition in include/volrt.h ("volume files"): level 0 = per
+    8^3 brick over the brick plus a one-texel apron clamped at the faces, entry = channels x (min, max) of the
+    decoded values; level l+1 reduces up to 2x2x2 children.  NaN texels count for the max only.
+    texels: (d,h,w) float16/uint16-bits/uint8 or (d,h,w,4) uint8 -> list of (bz,by,bx,channels,2) float32 arrays.
+    The reference has no such structure (it has no empty-space skipping); parity for it is self-referential."""
+    t = np.asarray(texels)
+    if fmt == VOL_R16F:
+        v = (t.view(np.float16) if t.dtype == np.uint16 else t).astype(np.float32)[..., None]
+    elif t.ndim == 4:
+        v = t.astype(np.float32) / np.float32(255.0)
+    else:
+        v = (t.astype(np.float32) / np.float32(255.0))[..., None]
+    d, h, w, ch = v.shape
+    nb = [(n + 7) // 8 for n in (d, h, w)]
+    lo = np.where(np.isnan(v), np.float32(np.inf), v)                       # NaN ignored by the min
+    hi = np.where(np.isnan(v), np.float32(np.inf), v)
+    nan = np.isnan(v)
+    level = np.zeros((nb[0], nb[1], nb[2], ch, 2), np.float32)
+    for bz in range(nb[0]):
+        z0, z1 = max(bz * 8 - 1, 0), min(bz * 8 + 9, d)
+        for by in range(nb[1]):
+            y0, y1 = max(by * 8 - 1, 0), min(by * 8 + 9, h)
+            for bx in range(nb[2]):
+                x0, x1 = max(bx * 8 - 1, 0), min(bx * 8 + 9, w)
+                blk_lo = lo[z0:z1, y0:y1, x0:x1].reshape(-1, ch)
+                blk_hi = hi[z0:z1, y0:y1, x0:x1].reshape(-1, ch)
+                blk_nan = nan[z0:z1, y0:y1, x0:x1].reshape(-1, ch)
+                level[bz, by, bx, :, 0] = blk_lo.min(axis=0)
+                mx = np.where(blk_nan, -np.float32(np.inf), blk_hi).max(axis=0)
+                level[bz, by, bx, :, 1] = np.where(blk_nan.any(axis=0), np.float32(np.nan), mx)
+    out = [level]
+    while out[-1].shape[:3] != (1, 1, 1):
+        p = out[-1]
+        sz, sy, sx = p.shape[:3]
+        nz, ny, nx = (sz + 1) // 2, (sy + 1) // 2, (sx + 1) // 2
+        q = np.zeros((nz, ny, nx, ch, 2), np.float32)
+        for z in range(nz):
+            for y in range(ny):
+                for x in range(nx):
+                    blk = p[2 * z:2 * z + 2, 2 * y:2 * y + 2, 2 * x:2 * x + 2].reshape(-1, ch, 2)
+                    q[z, y, x, :, 0] = blk[..., 0].min(axis=0)
+                    mx = blk[..., 1]
+                    q[z, y, x, :, 1] = np.where(np.isnan(mx).any(axis=0), np.float32(np.nan), np.nanmax(np.where(np.isnan(mx), -np.inf, mx), axis=0))
+        out.append(q)
+    return out

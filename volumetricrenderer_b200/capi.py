@@ -11,9 +11,9 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("VOLRT_LIB") or os.path.join(HERE, "libvolrt.so")   # VOLRT_LIB: A/B builds
 
-VR_OK, VR_ERR_INVALID_ARGUMENT, VR_ERR_CUDA, VR_ERR_OUT_OF_MEMORY, VR_ERR_UNSUPPORTED, VR_ERR_BAD_STATE = range(6)
+VR_OK, VR_ERR_INVALID_ARGUMENT, VR_ERR_CUDA, VR_ERR_OUT_OF_MEMORY, VR_ERR_UNSUPPORTED, VR_ERR_BAD_STATE, VR_ERR_IO = range(7)
 STATUS_NAMES = ["VR_OK", "VR_ERR_INVALID_ARGUMENT", "VR_ERR_CUDA", "VR_ERR_OUT_OF_MEMORY", "VR_ERR_UNSUPPORTED",
-                "VR_ERR_BAD_STATE"]
+                "VR_ERR_BAD_STATE", "VR_ERR_IO"]
 
 OUT_RGBA8_UNORM, OUT_RGBA8_SRGB, OUT_RGBA16F, OUT_RGBA32F = 0, 1, 2, 3
 VOL_RGBA8_UNORM, VOL_R16F, VOL_R8_UNORM = 0, 1, 2
@@ -33,6 +33,15 @@ class vr_create_info(C.Structure):
 class vr_volume_desc(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32), ("depth", C.c_uint32),
                 ("format", C.c_uint32), ("address_mode", C.c_uint32), ("layout", C.c_uint32)]
+
+
+class vr_volume_file_info(C.Structure):
+    _fields_ = [("struct_size", C.c_uint32), ("width", C.c_uint32), ("height", C.c_uint32), ("depth", C.c_uint32),
+                ("format", C.c_uint32), ("address_mode", C.c_uint32), ("pyramid_levels", C.c_uint32), ("reserved", C.c_uint32),
+                ("texel_bytes", C.c_uint64), ("pyramid_bytes", C.c_uint64), ("sha256", C.c_uint8 * 32)]
+
+
+FILE_VERIFY, FILE_WITH_PYRAMID, FILE_TRUST_PYRAMID = 1, 2, 4
 
 
 class vr_noise_channel(C.Structure):
@@ -99,6 +108,14 @@ EXPORTS = {
     "vr_measure_peaks": (C.c_int32, [_VP, C.POINTER(C.c_float)]),
     "vr_host_alloc": (_VP, [C.c_size_t]),
     "vr_host_free": (None, [_VP]),
+    "vr_sha256": (C.c_int32, [_VP, C.c_size_t, C.POINTER(C.c_uint8)]),
+    "vr_volume_file_write": (C.c_int32, [C.c_char_p, C.POINTER(vr_volume_desc), _VP, C.POINTER(C.c_float), C.c_uint32]),
+    "vr_volume_file_info_read": (C.c_int32, [C.c_char_p, C.POINTER(vr_volume_file_info)]),
+    "vr_volume_file_read": (C.c_int32, [C.c_char_p, _VP, C.c_size_t, C.POINTER(C.c_float), C.c_size_t, C.c_uint32]),
+    "vr_pyramid_floats": (C.c_size_t, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32)]),
+    "vr_upload_volume_file": (C.c_int32, [_VP, C.c_char_p, C.c_uint32, C.c_uint32]),
+    "vr_save_volume_file": (C.c_int32, [_VP, C.c_char_p, C.c_uint32]),
+    "vr_volume_pyramid": (C.c_int32, [_VP, C.POINTER(C.c_float), C.c_size_t]),
 }
 
 _lib = None

@@ -248,4 +248,100 @@ cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_
     return cudaGetLastError();
 }
 
+// ---- min-max pyramid (include/volrt.h): level 0 = per 8^3 brick incl. the one-texel apron, then 2x2x2 reductions.
+// Same traversal as the occupancy kernel: one CTA per brick row, whole texel rows read coalesced; the 8 lanes that
+// share a brick fold their values with REDUX on order-preserving bits, and three lanes per group (the leader, and
+// the two texels that sit in a neighbour's apron) touch shared memory.  NaN texels count for the max only (as the
+// canonical quiet NaN, which is the largest ordered value), so a NaN anywhere keeps its bricks "occupied".
+__device__ __forceinline__ float decode_texel(const void* row, int vol_format, int x, int c) {
+    if (vol_format == VR_VOL_R16F) return __half2float(((const __half*)row)[x]);
+    if (vol_format == VR_VOL_R8_UNORM) return __fdiv_rn((float)((const unsigned char*)row)[x], 255.0f);
+    return __fdiv_rn((float)((const unsigned char*)row)[4 * x + c], 255.0f);
+}
+template <int CH>
+__global__ void __launch_bounds__(256) pyramid_base_kernel(const void* __restrict__ lin, int vol_format, int w, int h, int d,
+                                                           float* __restrict__ out, int bx, int by) {
+    __shared__ unsigned int smin[512 * CH], smax[512 * CH];
+    const int iy = blockIdx.x % by, iz = blockIdx.x / by;
+    for (int i = threadIdx.x; i < bx * CH; i += blockDim.x) { smin[i] = 0xffffffffu; smax[i] = 0u; }
+    __syncthreads();
+    const int tb = vol_format == VR_VOL_R16F ? 2 : vol_format == VR_VOL_R8_UNORM ? 1 : 4;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned int group = 0xffu << (lane & 24);                 // the 8 lanes of one brick
+    for (int row = warp; row < 100; row += 8) {
+        const int yy = min(max(iy * 8 - 1 + row % 10, 0), h - 1);
+        const int zz = min(max(iz * 8 - 1 + row / 10, 0), d - 1);
+        const char* base = (const char*)lin + ((size_t)zz * h + yy) * w * tb;
+        for (int x0 = 0; x0 < w; x0 += 32) {
+            const int x = x0 + lane, brick = x >> 3;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+                unsigned int lo = 0xffffffffu, hi = 0u;
+                if (x < w) {
+                    const float v = decode_texel(base, vol_format, x, c);
+                    if (v != v) hi = ordered_bits(__int_as_float(0x7fc00000));
+                    else lo = hi = ordered_bits(v);
+                }
+                const unsigned int gmin = __reduce_min_sync(group, lo), gmax = __reduce_max_sync(group, hi);
+                if (x < w) {
+                    if ((lane & 7) == 0) {
+                        atomicMin(&smin[brick * CH + c], gmin); atomicMax(&smax[brick * CH + c], gmax);
+                        if (brick > 0) { atomicMin(&smin[(brick - 1) * CH + c], lo); atomicMax(&smax[(brick - 1) * CH + c], hi); }
+                    } else if ((lane & 7) == 7 && brick + 1 < bx) {
+                        atomicMin(&smin[(brick + 1) * CH + c], lo); atomicMax(&smax[(brick + 1) * CH + c], hi);
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < bx * CH; i += blockDim.x) {
+        const unsigned int a = smin[i], b = smax[i];
+        const unsigned int ab = (a & 0x80000000u) ? (a & 0x7fffffffu) : ~a, bb = (b & 0x80000000u) ? (b & 0x7fffffffu) : ~b;
+        float2 mm = make_float2(a == 0xffffffffu ? CUDART_INF_F : __uint_as_float(ab), __uint_as_float(bb));
+        reinterpret_cast<float2*>(out)[(size_t)blockIdx.x * bx * CH + i] = mm;
+    }
+}
+cudaError_t launch_pyramid_base(const void* lin, int vol_format, int w, int h, int d, float* out, int bx, int by, int bz, cudaStream_t s) {
+    if (vol_format == VR_VOL_RGBA8_UNORM) pyramid_base_kernel<4><<<by * bz, 256, 0, s>>>(lin, vol_format, w, h, d, out, bx, by);
+    else pyramid_base_kernel<1><<<by * bz, 256, 0, s>>>(lin, vol_format, w, h, d, out, bx, by);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) pyramid_reduce_kernel(const float2* __restrict__ in, float2* __restrict__ out, int ch,
+                                                             int bx, int by, int bz, int ox, int oy, int oz) {
+    const int total = ox * oy * oz * ch, idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int c = idx % ch, e = idx / ch, x = e % ox, y = (e / ox) % oy, z = e / (ox * oy);
+    unsigned int lo = 0xffffffffu, hi = 0u;
+    for (int dz = 0; dz < 2; ++dz)
+        for (int dy = 0; dy < 2; ++dy)
+            for (int dx = 0; dx < 2; ++dx) {
+                const int sx = 2 * x + dx, sy = 2 * y + dy, sz = 2 * z + dz;
+                if (sx >= bx || sy >= by || sz >= bz) continue;
+                const float2 v = in[(((size_t)sz * by + sy) * bx + sx) * ch + c];
+                lo = min(lo, ordered_bits(v.x));
+                hi = max(hi, ordered_bits(v.y != v.y ? __int_as_float(0x7fc00000) : v.y));
+            }
+    const unsigned int ab = (lo & 0x80000000u) ? (lo & 0x7fffffffu) : ~lo, bb = (hi & 0x80000000u) ? (hi & 0x7fffffffu) : ~hi;
+    out[idx] = make_float2(__uint_as_float(ab), __uint_as_float(bb));
+}
+cudaError_t launch_pyramid_reduce(const float* in, float* out, int channels, int bx, int by, int bz, cudaStream_t s) {
+    const int ox = (bx + 1) / 2, oy = (by + 1) / 2, oz = (bz + 1) / 2, total = ox * oy * oz * channels;
+    pyramid_reduce_kernel<<<(total + 255) / 256, 256, 0, s>>>((const float2*)in, (float2*)out, channels, bx, by, bz, ox, oy, oz);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) occupancy_from_pyramid_kernel(const float2* __restrict__ level0, int ch, unsigned char* __restrict__ occupied, int nbricks) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nbricks) return;
+    int any = 0;
+    for (int c = 0; c < ch; ++c) { const float2 v = level0[(size_t)b * ch + c]; any |= (v.x != 0.0f) || (v.y != 0.0f); }
+    occupied[b] = any ? 1 : 0;
+}
+cudaError_t launch_occupancy_from_pyramid(const float* level0, int channels, uint8_t* occupied, int nbricks, cudaStream_t s) {
+    occupancy_from_pyramid_kernel<<<(nbricks + 255) / 256, 256, 0, s>>>((const float2*)level0, channels, occupied, nbricks);
+    return cudaGetLastError();
+}
+
 }  // namespace volrt

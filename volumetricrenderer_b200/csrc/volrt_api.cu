@@ -8,6 +8,11 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
+#include <mutex>
+#include <new>
+#include <thread>
+#include <unistd.h>
 #include <string>
 #include <vector>
 
@@ -50,6 +55,12 @@ struct vr_context {
     float* bake_plane[4] = {nullptr, nullptr, nullptr, nullptr};
     size_t bake_plane_bytes = 0;
     unsigned int* d_mm = nullptr;
+    // vr_upload_volume_file: ring of page-locked staging buffers + their copy-done events, kept for the next file
+    static constexpr int kFileRing = 6;
+    static constexpr size_t kFileChunk = (size_t)16 << 20;
+    unsigned char* file_stage[kFileRing] = {};
+    cudaEvent_t file_done[kFileRing] = {};
+    const float* trusted_level0 = nullptr; // device copy of a file's pyramid level 0 (VR_FILE_TRUST_PYRAMID), for one finish_volume
     uint32_t fill_launches = 0;            // kernels the current upload / bake has launched so far
     // params
     bool has_params = false;
@@ -214,6 +225,10 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->d_row_cost) cudaFree(c->d_row_cost);
     if (c->d_queue) cudaFree(c->d_queue);
+    for (int i = 0; i < vr_context::kFileRing; ++i) {
+        if (c->file_stage[i]) cudaFreeHost(c->file_stage[i]);
+        if (c->file_done[i]) cudaEventDestroy(c->file_done[i]);
+    }
     for (float* pl : c->bake_plane) if (pl) cudaFree(pl);
     if (c->d_mm) cudaFree(c->d_mm);
     if (c->flush_buf) cudaFree(c->flush_buf);
@@ -282,7 +297,8 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
     const size_t nbricks = (size_t)B.bx * B.by * B.bz;
     if (!c->brick_dist) VR_CUDA(c, cudaMalloc(&c->brick_dist, 2 * nbricks));
     B.dist = c->brick_dist;
-    VR_CUDA(c, launch_occupancy(c->lin, d.format, d.width, d.height, d.depth, d.address_mode, c->occupied, B.bx, B.by, B.bz, c->stream));
+    if (c->trusted_level0) VR_CUDA(c, launch_occupancy_from_pyramid(c->trusted_level0, d.format == VR_VOL_RGBA8_UNORM ? 4 : 1, c->occupied, (int)nbricks, c->stream));
+    else VR_CUDA(c, launch_occupancy(c->lin, d.format, d.width, d.height, d.depth, d.address_mode, c->occupied, B.bx, B.by, B.bz, c->stream));
     VR_CUDA(c, launch_brick_distance(c->occupied, c->brick_dist, c->brick_dist + nbricks, B.bx, B.by, B.bz, c->stream));
     VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
@@ -352,6 +368,192 @@ extern "C" vr_status vr_download_volume(vr_context* c, void* texels, size_t byte
     VR_CUDA(c, cudaMemcpyAsync(texels, c->lin, c->lin_bytes, cudaMemcpyDeviceToHost, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     return VR_OK;
+}
+
+// ------------------------------------------------------------------ min-max pyramid and volume files
+// device pyramid of c->lin into a fresh device buffer (caller frees)
+static vr_status build_pyramid(vr_context* c, float** d_out, size_t* floats, uint32_t* levels) {
+    const vr_volume_desc& d = c->vdesc;
+    *floats = pyramid_floats(d.width, d.height, d.depth, d.format, levels);
+    VR_CUDA(c, cudaMalloc(d_out, *floats * sizeof(float)));
+    const int ch = d.format == VR_VOL_RGBA8_UNORM ? 4 : 1;
+    int bx = (d.width + 7) / 8, by = (d.height + 7) / 8, bz = (d.depth + 7) / 8;
+    float* level = *d_out;
+    cudaError_t e = launch_pyramid_base(c->lin, d.format, d.width, d.height, d.depth, level, bx, by, bz, c->stream);
+    while (e == cudaSuccess && !(bx == 1 && by == 1 && bz == 1)) {
+        float* next = level + (size_t)bx * by * bz * ch * 2;
+        e = launch_pyramid_reduce(level, next, ch, bx, by, bz, c->stream);
+        level = next;
+        bx = (bx + 1) / 2; by = (by + 1) / 2; bz = (bz + 1) / 2;
+    }
+    if (e != cudaSuccess) { cudaFree(*d_out); *d_out = nullptr; return fail(c, VR_ERR_CUDA, "pyramid kernels", e); }
+    return VR_OK;
+}
+
+extern "C" vr_status vr_volume_pyramid(vr_context* c, float* out, size_t out_bytes) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_volume_pyramid: no volume");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    float* d_pyr = nullptr;
+    size_t floats = 0;
+    uint32_t levels = 0;
+    if (!out || out_bytes < pyramid_floats(c->vdesc.width, c->vdesc.height, c->vdesc.depth, c->vdesc.format, nullptr) * sizeof(float))
+        return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_volume_pyramid: buffer too small (vr_pyramid_floats)");
+    vr_status st = build_pyramid(c, &d_pyr, &floats, &levels);
+    if (st != VR_OK) return st;
+    cudaError_t e = cudaMemcpyAsync(out, d_pyr, floats * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_pyr);
+    if (e != cudaSuccess) return fail(c, VR_ERR_CUDA, "vr_volume_pyramid", e);
+    return VR_OK;
+}
+
+extern "C" vr_status vr_save_volume_file(vr_context* c, const char* path, uint32_t flags) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!path) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_save_volume_file: path is null");
+    if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_save_volume_file: no volume");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    std::vector<unsigned char> texels;
+    std::vector<float> pyr;
+    uint32_t levels = 0;
+    try {
+        texels.resize(c->lin_bytes);
+        if (flags & VR_FILE_WITH_PYRAMID) pyr.resize(pyramid_floats(c->vdesc.width, c->vdesc.height, c->vdesc.depth, c->vdesc.format, &levels));
+    } catch (const std::bad_alloc&) { return fail(c, VR_ERR_OUT_OF_MEMORY, "vr_save_volume_file: host memory"); }
+    vr_status st = vr_download_volume(c, texels.data(), texels.size());
+    if (st == VR_OK && !pyr.empty()) st = vr_volume_pyramid(c, pyr.data(), pyr.size() * sizeof(float));
+    if (st != VR_OK) return st;
+    st = vr_volume_file_write(path, &c->vdesc, texels.data(), pyr.empty() ? nullptr : pyr.data(), levels);
+    if (st != VR_OK) return fail(c, st, "vr_save_volume_file: cannot write the file");
+    return VR_OK;
+}
+
+// file -> ring of page-locked staging buffers -> device; reads, hashing and H2D copies overlap
+extern "C" vr_status vr_upload_volume_file(vr_context* c, const char* path, uint32_t layout, uint32_t flags) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!path) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_upload_volume_file: path is null");
+    std::FILE* f = std::fopen(path, "rb");
+    if (!f) return fail(c, VR_ERR_IO, "vr_upload_volume_file: cannot open the file");
+    VolumeFileHeader h{};
+    if (const char* err = read_volume_header(f, &h)) { std::fclose(f); return fail(c, VR_ERR_IO, (std::string("vr_upload_volume_file: ") + err).c_str()); }
+    vr_volume_desc vd = {sizeof(vr_volume_desc), h.width, h.height, h.depth, h.format, h.address_mode, layout};
+    vr_status st = check_volume_desc(c, &vd);
+    if (st != VR_OK) { std::fclose(f); return st; }
+    if ((flags & VR_FILE_TRUST_PYRAMID) && !h.pyramid_levels) { std::fclose(f); return fail(c, VR_ERR_BAD_STATE, "vr_upload_volume_file: the file has no pyramid to trust"); }
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) { std::fclose(f); return fail(c, VR_ERR_CUDA, "cudaSetDevice", e); }
+    st = prepare_volume(c, vd);
+    if (st != VR_OK) { std::fclose(f); return st; }
+    // kReaders threads pread() 16 MiB chunks into a ring of page-locked buffers and queue the H2D copies themselves;
+    // a buffer is reused once the copy that last read it has finished (event), and the SHA-256 (inherently
+    // sequential) is taken chunk by chunk in file order by whichever thread holds that chunk.
+    constexpr int kReaders = 4, kRing = vr_context::kFileRing;
+    const size_t chunk = vr_context::kFileChunk;
+    const size_t n_chunks = (size_t)((h.texel_bytes + chunk - 1) / chunk);
+    unsigned char** stage = c->file_stage;
+    cudaEvent_t* done = c->file_done;
+    float* d_level0 = nullptr;
+    const char* what = nullptr;
+    Sha256 sha;
+    sha.reset();
+    const int ring = (int)(n_chunks < (size_t)kRing ? n_chunks : (size_t)kRing);
+    for (int i = 0; i < ring && e == cudaSuccess; ++i) {
+        if (!stage[i]) e = cudaMallocHost(&stage[i], chunk);
+        if (e == cudaSuccess && !done[i]) e = cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) {
+        std::mutex mu;
+        std::condition_variable cv;
+        size_t next_chunk = 0, hash_turn = 0;
+        size_t issued[kRing];                      // issued[b] = number of copies queued from buffer b so far
+        for (size_t& v : issued) v = 0;
+        cudaError_t first_err = cudaSuccess;
+        const char* first_what = nullptr;
+        const int fd = fileno(f);
+        const bool verify = (flags & VR_FILE_VERIFY) != 0;
+        auto worker = [&]() {
+            cudaSetDevice(c->device);
+            for (;;) {
+                size_t k;
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    if (first_err != cudaSuccess || first_what || next_chunk >= n_chunks) return;
+                    k = next_chunk++;
+                }
+                const int b = (int)(k % ring);
+                const size_t off = k * chunk, n = h.texel_bytes - off < chunk ? (size_t)(h.texel_bytes - off) : chunk;
+                {   // wait until chunk k - ring has been queued from this buffer, then until its copy has finished
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv.wait(lk, [&] { return issued[b] == k / ring || first_err != cudaSuccess || first_what; });
+                    if (first_err != cudaSuccess || first_what) return;
+                }
+                cudaError_t le = k >= (size_t)ring ? cudaEventSynchronize(done[b]) : cudaSuccess;
+                const char* lw = nullptr;
+                if (le == cudaSuccess) {
+                    size_t got = 0;
+                    while (got < n) {
+                        const ssize_t rd = pread(fd, stage[b] + got, n - got, (off_t)(h.texel_offset + off + got));
+                        if (rd <= 0) { lw = "short read (texels)"; break; }
+                        got += (size_t)rd;
+                    }
+                }
+                if (le == cudaSuccess && !lw && verify) {
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv.wait(lk, [&] { return hash_turn == k || first_err != cudaSuccess || first_what; });
+                    if (hash_turn == k) {
+                        lk.unlock();
+                        sha.update(stage[b], n);
+                        lk.lock();
+                        ++hash_turn;
+                        cv.notify_all();
+                    }
+                }
+                if (le == cudaSuccess && !lw) le = cudaMemcpyAsync((char*)c->lin + off, stage[b], n, cudaMemcpyHostToDevice, c->stream);
+                if (le == cudaSuccess && !lw) le = cudaEventRecord(done[b], c->stream);
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    if (le != cudaSuccess && first_err == cudaSuccess) first_err = le;
+                    if (lw && !first_what) first_what = lw;
+                    ++issued[b];
+                    cv.notify_all();
+                }
+            }
+        };
+        std::vector<std::thread> pool;
+        const int nthreads = (int)(n_chunks < (size_t)kReaders ? n_chunks : (size_t)kReaders);
+        for (int t = 1; t < nthreads; ++t) pool.emplace_back(worker);
+        worker();
+        for (auto& t : pool) t.join();
+        e = first_err;
+        what = first_what;
+    }
+    if (e == cudaSuccess && !what && (flags & VR_FILE_VERIFY)) {
+        uint8_t got[32];
+        sha.finish(got);
+        if (std::memcmp(got, h.sha256, 32) != 0) what = "SHA-256 of the texels does not match the header";
+    }
+    if (e == cudaSuccess && !what && (flags & VR_FILE_TRUST_PYRAMID)) {
+        const size_t l0 = (size_t)((h.width + 7) / 8) * ((h.height + 7) / 8) * ((h.depth + 7) / 8) * (h.format == VR_VOL_RGBA8_UNORM ? 4 : 1) * 2 * sizeof(float);
+        std::vector<unsigned char> host(l0);
+        if (fseeko(f, (off_t)h.pyramid_offset, SEEK_SET) != 0 || std::fread(host.data(), 1, l0, f) != l0) what = "short read (pyramid)";
+        else {
+            e = cudaMalloc(&d_level0, l0);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(d_level0, host.data(), l0, cudaMemcpyHostToDevice, c->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);    // `host` goes out of scope
+        }
+    }
+    std::fclose(f);
+    if (e == cudaSuccess && !what) {
+        c->trusted_level0 = d_level0;
+        st = finish_volume(c, vd);
+        c->trusted_level0 = nullptr;
+    }
+    cudaStreamSynchronize(c->stream);
+    if (d_level0) cudaFree(d_level0);
+    if (what) { release_volume(c); return fail(c, VR_ERR_IO, (std::string("vr_upload_volume_file: ") + what).c_str()); }
+    if (e != cudaSuccess) { release_volume(c); return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, "vr_upload_volume_file", e); }
+    if (st != VR_OK) release_volume(c);
+    return st;
 }
 
 // ------------------------------------------------------------------ volume bake on the device

@@ -5,6 +5,8 @@
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
 #include <stdint.h>
+#include <stddef.h>
+#include <stdio.h>
 #include "../../include/volrt.h"
 
 namespace volrt {
@@ -104,6 +106,37 @@ cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_
 // ---- peak_kernels.cu: measured roofline denominators
 cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_tex_peak(cudaTextureObject_t tex, float* sink, int blocks, int iters, cudaStream_t s);
+// ---- min-max pyramid (noise_kernels.cu; layout in include/volrt.h)
+// level 0 from the texels: out[brick][channel][{min,max}]
+cudaError_t launch_pyramid_base(const void* lin, int vol_format, int w, int h, int d, float* out, int bx, int by, int bz, cudaStream_t s);
+// one reduction step: (bx,by,bz) entries -> ceil(/2) entries
+cudaError_t launch_pyramid_reduce(const float* in, float* out, int channels, int bx, int by, int bz, cudaStream_t s);
+// occupancy from level 0: occupied = some channel has min != 0 or max != 0 (NaN counts as occupied)
+cudaError_t launch_occupancy_from_pyramid(const float* level0, int channels, uint8_t* occupied, int nbricks, cudaStream_t s);
+
+// ---- volume files (volume_file.cu; host code)
+struct Sha256 {
+    uint32_t h[8];
+    uint64_t total;
+    uint8_t buf[64];
+    size_t fill;
+    void reset();
+    void update(const void* data, size_t n);
+    void finish(uint8_t out[32]);
+private:
+    void block(const uint8_t* p);
+};
+constexpr uint32_t kVolumeFileHeaderBytes = 128;
+struct VolumeFileHeader {
+    uint32_t width, height, depth, format, address_mode, pyramid_levels;
+    uint64_t texel_offset, texel_bytes, pyramid_offset, pyramid_bytes;
+    uint8_t sha256[32];
+    void encode(uint8_t out[kVolumeFileHeaderBytes]) const;
+    const char* decode(const uint8_t in[kVolumeFileHeaderBytes], uint64_t file_size);   // nullptr = ok, else what is wrong
+};
+const char* read_volume_header(FILE* f, VolumeFileHeader* h);
+size_t pyramid_floats(uint32_t w, uint32_t h, uint32_t d, uint32_t format, uint32_t* levels);
+
 void minmax_init(unsigned int* bits2_host);
 float minmax_decode(unsigned int bits);
 

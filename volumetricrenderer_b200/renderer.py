@@ -129,6 +129,26 @@ class Renderer:
         self._check(self._lib.vr_download_volume(self._ctx, out.ctypes.data, out.nbytes))
         return out
 
+    # ---- volume files (volfile.py has the host-only half)
+    def upload_volume_file(self, path, layout=capi.LAYOUT_AUTO, flags=capi.FILE_VERIFY):
+        from . import volfile
+        self._check(self._lib.vr_upload_volume_file(self._ctx, path.encode(), layout, flags))
+        i = volfile.info(path)
+        self._vol_fmt = i["format"]
+        self._vol_shape = (i["depth"], i["height"], i["width"]) + ((4,) if i["format"] == capi.VOL_RGBA8_UNORM else ())
+
+    def save_volume_file(self, path, with_pyramid=False):
+        self._check(self._lib.vr_save_volume_file(self._ctx, path.encode(), capi.FILE_WITH_PYRAMID if with_pyramid else 0))
+
+    def volume_pyramid(self):
+        """min-max pyramid of the resident volume (device-computed) -> list of (bz,by,bx,channels,2) float32 arrays"""
+        from . import volfile
+        d, h, w = self._vol_shape[:3]
+        n = self._lib.vr_pyramid_floats(w, h, d, self._vol_fmt, None)
+        flat = np.empty(n, np.float32)
+        self._check(self._lib.vr_volume_pyramid(self._ctx, flat.ctypes.data_as(C.POINTER(C.c_float)), flat.nbytes))
+        return volfile.split_pyramid(flat, w, h, d, self._vol_fmt)
+
     # ---- params
     def default_params(self):
         p = capi.vr_params()
