@@ -55,12 +55,14 @@ __device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
 // nibble of the hash, so the 16 possible gradients (cx,cy,cz in {-1,0,+1}) are tabulated once per
 // CTA: dot = fx*cx + fy*cy + fz*cz is bit-identical to (u ^ h1) + (v ^ h2) (products by +-1 and
 // the added zero are exact, so the one rounding is that of the same two-term sum).
-// Layout: GradLut::xy[n] = (cx,cy) (LDS.64, 16 entries x 8 B cover each bank once) and z[n].x = cz at
-// the same 8-byte stride (16 distinct even banks), so every lane pattern is bank-conflict free.
-// The table offset n*8 comes straight from the integer pipe of the FMA unit:
-//   h = t*C;  h8 = t*(C<<3) = h<<3;  off = (h8 ^ (h8 >> 15)) & 0x78  ==  (((h >> 15) ^ h) & 15) * 8
-// (bits 3..6 of h8>>15 are bits 15..18 of h: the three bits the left shift drops are never looked at)
-struct GradLut { float2 xy[16]; float2 z[16]; };
+// Layout: GradLut::g[n] = (cx, cy, cz, 0): one LDS.128 per lattice corner.  An earlier layout (LDS.64 for (cx,cy) +
+// LDS.32 for cz at an 8-byte stride) was bank-conflict free but cost one more issue slot per corner; the kernel is
+// issue-bound, not LSU-bound, so the single wider load wins although entries n and n+8 share banks
+// (C2 2.04 -> 1.95 ms, C3 19.4 -> 18.7 ms).
+// The table offset n*16 comes straight from the integer pipe of the FMA unit:
+//   h = t*C;  h16 = t*(C<<4) = h<<4;  off = (h16 ^ (h16 >> 15)) & 0xF0  ==  (((h >> 15) ^ h) & 15) * 16
+// (bits 4..7 of h16>>15 are bits 15..18 of h: the four bits the left shift drops are never looked at)
+struct __align__(16) GradLut { float4 g[16]; };
 
 __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
     if (tid < 16) {
@@ -72,17 +74,27 @@ __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
         const float cx = (iu == 0 ? su : 0.0f) + (iv == 0 ? sv : 0.0f);
         const float cy = (iu == 1 ? su : 0.0f) + (iv == 1 ? sv : 0.0f);
         const float cz = iv == 2 ? sv : 0.0f;
-        lut->xy[n] = make_float2(cx, cy);
-        lut->z[n] = make_float2(cz, 0.0f);
+        lut->g[n] = make_float4(cx, cy, cz, 0.0f);
     }
 }
 
+__device__ __forceinline__ float4 grad_lut_fetch(const GradLut* lut, int t) {
+    const unsigned int h16 = (unsigned int)t * (0x27d4eb2du << 4);     // = h << 4 (mod 2^32)
+    const unsigned int off = (h16 ^ (h16 >> 15)) & 0xF0u;
+    return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
+}
 __device__ __forceinline__ float grad_dot_lut(const GradLut* lut, int t, float fx, float fy, float fz) {
-    const unsigned int h8 = (unsigned int)t * (0x27d4eb2du << 3);      // = h << 3 (mod 2^32)
-    const unsigned int off = (h8 ^ (h8 >> 15)) & 0x78u;
-    const float2 gxy = *reinterpret_cast<const float2*>(reinterpret_cast<const char*>(lut->xy) + off);
-    const float gz = *reinterpret_cast<const float*>(reinterpret_cast<const char*>(lut->z) + off);
-    return fmaf(fz, gz, fmaf(fy, gxy.y, fx * gxy.x));
+    const float4 g = grad_lut_fetch(lut, t);
+    return fmaf(fz, g.z, fmaf(fy, g.y, fx * g.x));
+}
+// lerp(d0, d1, s) over the two corners of an x edge, with d1 - d0 accumulated directly into the second dot product:
+// 7 instructions instead of 8 (the difference is re-associated by a few ulp; FastNoise2's own SIMD levels contract
+// and re-associate the same expression differently among themselves)
+__device__ __forceinline__ float grad_edge_lut(const GradLut* lut, int t0, int t1, float fx0, float fx1, float fy, float fz, float s) {
+    const float4 g0 = grad_lut_fetch(lut, t0), g1 = grad_lut_fetch(lut, t1);
+    const float d0 = fmaf(fz, g0.z, fmaf(fy, g0.y, fx0 * g0.x));
+    const float e = fmaf(fz, g1.z, fmaf(fy, g1.y, fmaf(fx1, g1.x, -d0)));
+    return fmaf(s, e, d0);
 }
 
 __device__ __forceinline__ float perlin3_lut(const GradLut* lut, int seed, float x, float y, float z) {
@@ -93,12 +105,13 @@ __device__ __forceinline__ float perlin3_lut(const GradLut* lut, int seed, float
     float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
     xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
     int sz0 = seed ^ z0, sz1 = seed ^ z1;
-    float a = lerpf(lerpf(grad_dot_lut(lut, sz0 ^ x0 ^ y0, xf0, yf0, zf0), grad_dot_lut(lut, sz0 ^ x1 ^ y0, xf1, yf0, zf0), xs),
-                    lerpf(grad_dot_lut(lut, sz0 ^ x0 ^ y1, xf0, yf1, zf0), grad_dot_lut(lut, sz0 ^ x1 ^ y1, xf1, yf1, zf0), xs), ys);
-    float b = lerpf(lerpf(grad_dot_lut(lut, sz1 ^ x0 ^ y0, xf0, yf0, zf1), grad_dot_lut(lut, sz1 ^ x1 ^ y0, xf1, yf0, zf1), xs),
-                    lerpf(grad_dot_lut(lut, sz1 ^ x0 ^ y1, xf0, yf1, zf1), grad_dot_lut(lut, sz1 ^ x1 ^ y1, xf1, yf1, zf1), xs), ys);
-    return 0.964921414852142333984375f * lerpf(a, b, zs);
+    float a = lerpf(grad_edge_lut(lut, sz0 ^ x0 ^ y0, sz0 ^ x1 ^ y0, xf0, xf1, yf0, zf0, xs),
+                    grad_edge_lut(lut, sz0 ^ x0 ^ y1, sz0 ^ x1 ^ y1, xf0, xf1, yf1, zf0, xs), ys);
+    float b = lerpf(grad_edge_lut(lut, sz1 ^ x0 ^ y0, sz1 ^ x1 ^ y0, xf0, xf1, yf0, zf1, xs),
+                    grad_edge_lut(lut, sz1 ^ x0 ^ y1, sz1 ^ x1 ^ y1, xf0, xf1, yf1, zf1, xs), ys);
+    return lerpf(a, b, zs);           // WITHOUT Perlin.inl:63's 0.9649... output scale: the caller folds it into the octave amplitude
 }
+constexpr float kPerlinScale = 0.964921414852142333984375f;
 
 __device__ __forceinline__ float simplex3(int seed, float x, float y, float z) {
     const float F3 = 1.0f / 3.0f, G3 = 1.0f / 2.0f;
@@ -163,7 +176,7 @@ __device__ __forceinline__ float cellular3(int seed, float x, float y, float z) 
 
 __device__ __forceinline__ float fbm_perlin(const GradLut* lut, const FbmField& F, float x, float y, float z) {
     int seed = F.seed;
-    float amp = F.bounding;
+    float amp = F.bounding * kPerlinScale;       // one multiply per fBm sample instead of one per octave
     float sum = perlin3_lut(lut, seed, x, y, z) * amp;
     for (int i = 1; i < F.octaves; ++i) {
         seed += 1;
