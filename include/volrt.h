@@ -148,6 +148,7 @@ typedef struct vr_volume_desc {
 #define VR_NOISE_PERLIN 1u
 #define VR_NOISE_SIMPLEX 2u
 #define VR_NOISE_ZERO 3u
+#define VR_NOISE_TREE 4u           /* the compiled FastNoise2 node tree in vr_noise_desc.tree[k]; the channel's frequency and seed apply */
 #define VR_NOISE_SAME 0xffffffffu
 typedef struct vr_noise_channel {
     uint32_t generator;          /* VR_NOISE_*: the field whose values are packed             */
@@ -159,6 +160,7 @@ typedef struct vr_noise_channel {
     uint32_t power;              /* 1 or 4 in the reference                                   */
 } vr_noise_channel;
 
+typedef struct vr_noise_tree vr_noise_tree;     /* "FastNoise2 node trees" below */
 /* replaces the start-up bake, TestMain.cpp:43-92 (FastNoise2 GenUniformGrid3D x4 + pack) */
 typedef struct vr_noise_desc {
     uint32_t struct_size;
@@ -170,6 +172,7 @@ typedef struct vr_noise_desc {
     uint32_t address_mode;       /* vr_address_mode                                           */
     float threshold;
     vr_noise_channel channel[4];
+    const vr_noise_tree* tree[4]; /* per channel, for generator VR_NOISE_TREE; read only when struct_size covers it */
 } vr_noise_desc;
 
 /* replaces objectUniformBuffer.Update(&osd, frame) / globalUniformBuffer.Update(&gsd, frame):
@@ -315,6 +318,25 @@ VR_API vr_status vr_upload_volume_file(vr_context* ctx, const char* path, uint32
 VR_API vr_status vr_save_volume_file(vr_context* ctx, const char* path, uint32_t flags);
 /* min-max pyramid of the resident volume, computed on the device; out holds vr_pyramid_floats() floats */
 VR_API vr_status vr_volume_pyramid(vr_context* ctx, float* out, size_t out_bytes);
+
+/* ---- FastNoise2 node trees.  The reference builds its generators in code
+ * (FastNoise::New<...>, TestMain.cpp:43-45); FastNoise2's portable form of a generator graph is the encoded node tree
+ * string (FastNoise::NewFromEncodedNodeTree, vendor/noise/include/FastNoise/FastNoise.h:49, the strings its NoiseTool
+ * exports).  vr_noise_tree_compile decodes such a string on the host (no device needed) into a straight-line
+ * program; vr_noise_tree_grid evaluates it on the device with GenUniformGrid3D semantics (Generator.inl:124-176):
+ * out[z][y][x] = tree((x0+x)*frequency, (y0+y)*frequency, (z0+z)*frequency; seed), min/max returned like
+ * FastNoise::OutputMinMax.  Built: Constant, White, SineWave, PositionOutput, DistanceToPoint, Value, Perlin, Simplex,
+ * OpenSimplex2, CellularValue/Distance/Lookup, FractalFBm/Ridged/PingPong, DomainWarpGradient,
+ * DomainWarpFractalProgressive/Independant, DomainScale/Offset/Rotate/AxisScale, SeedOffset, Remap, ConvertRGBA8, Terrace,
+ * Add/Subtract/Multiply/Divide/Min/Max/MinSmooth/MaxSmooth/Fade/PowFloat/PowInt, GeneratorCache; 3-D positions only.
+ * Anything else (Checkerboard, OpenSimplex2S, Add/RemoveDimension) -> VR_ERR_UNSUPPORTED with the node's name in err. */
+VR_API vr_status vr_noise_tree_compile(const char* encoded_node_tree, vr_noise_tree** out, char* err, size_t err_cap);
+VR_API void vr_noise_tree_free(vr_noise_tree* tree);
+VR_API vr_status vr_noise_tree_info(const vr_noise_tree* tree, uint32_t* nodes, uint32_t* instructions, uint32_t* value_regs,
+                                    uint32_t* position_regs);
+/* out_host may be NULL (min/max only); it holds nx*ny*nz floats, x fastest */
+VR_API vr_status vr_noise_tree_grid(vr_context* ctx, const vr_noise_tree* tree, int32_t x0, int32_t y0, int32_t z0, uint32_t nx,
+                                    uint32_t ny, uint32_t nz, float frequency, int32_t seed, float* out_host, float minmax[2]);
 
 #ifdef __cplusplus
 }

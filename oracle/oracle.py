@@ -105,6 +105,8 @@ def ref():
         R.vref_points.argtypes = [C.c_int, C.c_int, fp, C.c_int, fp, fp, fp, C.c_int]
         R.vref_fbm_points.argtypes = [C.c_int, fp, C.c_int, fp, fp, fp, C.c_int, C.c_int, C.c_float, C.c_float]
         R.vref_bake_default.argtypes = [C.POINTER(C.c_uint8), C.c_int, C.c_int, fp]
+        R.vref_tree_grid.argtypes = [C.c_char_p, C.c_int, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, fp]
+        R.vref_metadata_dump.argtypes = [C.c_char_p, C.c_int]
         _ref = R
     return _ref
 
@@ -339,3 +341,25 @@ def minmax_pyramid(texels, fmt):
                     q[z, y, x, :, 1] = np.where(np.isnan(mx).any(axis=0), np.float32(np.nan), np.nanmax(np.where(np.isnan(mx), -np.inf, mx), axis=0))
         out.append(q)
     return out
+
+
+# ------------------------------------------------------------------ reference FastNoise2 on encoded node trees
+def ref_tree_grid(encoded, shape, freq, seed, start=(0, 0, 0), level=LEVEL_AUTO):
+    """the reference's own decoder + generators (FastNoise::NewFromEncodedNodeTree -> GenUniformGrid3D);
+    shape = (nz, ny, nx) -> (grid float32, minmax float32[2])"""
+    nz, ny, nx = shape
+    out = np.zeros(shape, np.float32)
+    mm = np.zeros(2, np.float32)
+    rc = ref().vref_tree_grid(encoded.encode(), level, _fp(out), start[0], start[1], start[2], nx, ny, nz, freq, seed, _fp(mm))
+    if rc != 0:
+        raise RuntimeError("FastNoise2 could not build the tree (or SIMD level %d is unavailable)" % level)
+    return out, mm
+
+
+def ref_metadata():
+    import json
+    buf = C.create_string_buffer(1 << 18)
+    n = ref().vref_metadata_dump(buf, len(buf))
+    if n < 0:
+        raise RuntimeError("metadata dump needs %d bytes" % -n)
+    return [json.loads(l) for l in buf.value.decode().splitlines()]

@@ -6,7 +6,10 @@
 //
 // The calls mirror /root/reference/source/Etna/TestMain.cpp:43-62.
 #include <FastNoise/FastNoise.h>
+#include <FastNoise/Metadata.h>
 #include <cstdint>
+#include <cstdio>
+#include <string>
 #include <vector>
 
 namespace {
@@ -97,6 +100,52 @@ int vref_bake_default(uint8_t* pixelData, int size, int level, float mm_out[8]) 
     if (mm_out) { mm_out[0] = o1.min; mm_out[1] = o1.max; mm_out[2] = o2.min; mm_out[3] = o2.max;
                   mm_out[4] = o3.min; mm_out[5] = o3.max; mm_out[6] = o4.min; mm_out[7] = o4.max; }
     return 0;
+}
+
+// ---- node trees: the reference's own decoder and generators on an encoded tree
+// (FastNoise::NewFromEncodedNodeTree, FastNoise.h:49)
+int vref_tree_grid(const char* encoded, int level, float* out, int x0, int y0, int z0, int nx, int ny, int nz, float freq, int seed, float minmax[2]) {
+    auto node = FastNoise::NewFromEncodedNodeTree(encoded, pick_level(level));
+    if (!node) return 1;
+    auto mm = node->GenUniformGrid3D(out, x0, y0, z0, nx, ny, nz, freq, seed);
+    minmax[0] = mm.min; minmax[1] = mm.max;
+    return 0;
+}
+int vref_tree_points(const char* encoded, int level, float* out, int n, const float* xs, const float* ys, const float* zs, int seed) {
+    auto node = FastNoise::NewFromEncodedNodeTree(encoded, pick_level(level));
+    if (!node) return 1;
+    node->GenPositionArray3D(out, n, xs, ys, zs, 0.0f, 0.0f, 0.0f, seed);
+    return 0;
+}
+// every registered node class with its serialised members, as JSON lines: the wire format of an encoded tree is
+// {u16 id, i32 per variable, child per node lookup, (u8 is_node, child | f32) per hybrid} (Metadata.cpp:199-300)
+int vref_metadata_dump(char* buf, int cap) {
+    std::string o;
+    char tmp[256];
+    for (const FastNoise::Metadata* m : FastNoise::Metadata::GetAll()) {
+        std::snprintf(tmp, sizeof tmp, "{\"id\": %d, \"name\": \"%s\", \"variables\": [", (int)m->id, m->name);
+        o += tmp;
+        bool first = true;
+        for (const auto& v : m->memberVariables) {
+            const char* ty = v.type == FastNoise::Metadata::MemberVariable::EFloat ? "float" : v.type == FastNoise::Metadata::MemberVariable::EInt ? "int" : "enum";
+            std::snprintf(tmp, sizeof tmp, "%s{\"name\": \"%s\", \"dim\": %d, \"type\": \"%s\", \"default_f\": %.9g, \"default_i\": %d, \"enum\": [",
+                          first ? "" : ", ", v.name, v.dimensionIdx, ty, (double)v.valueDefault.f, v.valueDefault.i);
+            o += tmp;
+            for (size_t i = 0; i < v.enumNames.size(); ++i) { o += i ? ", \"" : "\""; o += v.enumNames[i]; o += "\""; }
+            o += "]}";
+            first = false;
+        }
+        o += "], \"nodes\": [";
+        first = true;
+        for (const auto& n : m->memberNodeLookups) { std::snprintf(tmp, sizeof tmp, "%s{\"name\": \"%s\", \"dim\": %d}", first ? "" : ", ", n.name, n.dimensionIdx); o += tmp; first = false; }
+        o += "], \"hybrids\": [";
+        first = true;
+        for (const auto& h : m->memberHybrids) { std::snprintf(tmp, sizeof tmp, "%s{\"name\": \"%s\", \"dim\": %d, \"default\": %.9g}", first ? "" : ", ", h.name, h.dimensionIdx, (double)h.valueDefault); o += tmp; first = false; }
+        o += "]}\n";
+    }
+    if ((int)o.size() + 1 > cap) return -(int)o.size() - 1;
+    std::snprintf(buf, cap, "%s", o.c_str());
+    return (int)o.size();
 }
 
 }  // extern "C"

@@ -31,7 +31,7 @@ def test_struct_sizes_match_the_header_layout():
     assert C.sizeof(capi.vr_create_info) == 28
     assert C.sizeof(capi.vr_volume_desc) == 28
     assert C.sizeof(capi.vr_noise_channel) == 28
-    assert C.sizeof(capi.vr_noise_desc) == 24 + 4 * 28
+    assert C.sizeof(capi.vr_noise_desc) == 24 + 4 * 28 + 4 * 8          # channel recipes + the per-channel node-tree pointers
     assert C.sizeof(capi.vr_target) == 56
     assert C.sizeof(capi.vr_stats) == 64
     p = capi.vr_params()

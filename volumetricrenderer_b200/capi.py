@@ -23,6 +23,7 @@ DENSITY_RGBA_PRODUCT, DENSITY_SINGLE, DENSITY_FBM = 0, 1, 2
 MEM_NONE, MEM_HOST, MEM_DEVICE = 0, 1, 2
 RENDER_ASYNC, RENDER_DIRECT, RENDER_STATS, RENDER_NO_MARCH = 1, 2, 4, 8
 NOISE_CELLULAR_DISTANCE, NOISE_PERLIN, NOISE_SIMPLEX, NOISE_ZERO, NOISE_SAME = 0, 1, 2, 3, 0xFFFFFFFF
+NOISE_TREE = 4
 
 
 class vr_create_info(C.Structure):
@@ -52,7 +53,8 @@ class vr_noise_channel(C.Structure):
 
 class vr_noise_desc(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("size", C.c_uint32), ("format", C.c_uint32), ("layout", C.c_uint32),
-                ("address_mode", C.c_uint32), ("threshold", C.c_float), ("channel", vr_noise_channel * 4)]
+                ("address_mode", C.c_uint32), ("threshold", C.c_float), ("channel", vr_noise_channel * 4),
+                ("tree", C.c_void_p * 4)]
 
 
 class vr_params(C.Structure):
@@ -116,6 +118,11 @@ EXPORTS = {
     "vr_upload_volume_file": (C.c_int32, [_VP, C.c_char_p, C.c_uint32, C.c_uint32]),
     "vr_save_volume_file": (C.c_int32, [_VP, C.c_char_p, C.c_uint32]),
     "vr_volume_pyramid": (C.c_int32, [_VP, C.POINTER(C.c_float), C.c_size_t]),
+    "vr_noise_tree_compile": (C.c_int32, [C.c_char_p, C.POINTER(_VP), C.c_char_p, C.c_size_t]),
+    "vr_noise_tree_free": (None, [_VP]),
+    "vr_noise_tree_info": (C.c_int32, [_VP, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "vr_noise_tree_grid": (C.c_int32, [_VP, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_int32,
+                                       C.POINTER(C.c_float), C.POINTER(C.c_float)]),
 }
 
 _lib = None

@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstddef>
 #include <cstring>
 #include <condition_variable>
 #include <mutex>
@@ -60,6 +61,9 @@ struct vr_context {
     static constexpr size_t kFileChunk = (size_t)16 << 20;
     unsigned char* file_stage[kFileRing] = {};
     cudaEvent_t file_done[kFileRing] = {};
+    TreeInstr* d_tree_prog = nullptr;       // vr_noise_tree_grid: program upload buffer and a grow-only output plane
+    float* d_tree_out = nullptr;
+    size_t tree_out_bytes = 0;
     const float* trusted_level0 = nullptr; // device copy of a file's pyramid level 0 (VR_FILE_TRUST_PYRAMID), for one finish_volume
     uint32_t fill_launches = 0;            // kernels the current upload / bake has launched so far
     // params
@@ -225,6 +229,8 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->d_row_cost) cudaFree(c->d_row_cost);
     if (c->d_queue) cudaFree(c->d_queue);
+    if (c->d_tree_prog) cudaFree(c->d_tree_prog);
+    if (c->d_tree_out) cudaFree(c->d_tree_out);
     for (int i = 0; i < vr_context::kFileRing; ++i) {
         if (c->file_stage[i]) cudaFreeHost(c->file_stage[i]);
         if (c->file_done[i]) cudaEventDestroy(c->file_done[i]);
@@ -583,7 +589,7 @@ static float fbm_bounding(int octaves, float gain) {    // Fractal.h:27-38
 
 extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, const vr_params* fbm) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
-    if (!d || d->struct_size < sizeof(vr_noise_desc)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: null desc or struct_size too small");
+    if (!d || d->struct_size < offsetof(vr_noise_desc, tree)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: null desc or struct_size too small");   // the tree pointers are optional
     vr_volume_desc vd = {sizeof(vr_volume_desc), d->size, d->size, d->size, d->format, d->address_mode, d->layout};
     vr_status st = check_volume_desc(c, &vd);
     if (st != VR_OK) return st;
@@ -604,31 +610,34 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
         c->fill_launches = 1;
     } else {
         // each distinct field is generated once; min/max folded on the device
-        struct Gen { NoiseField f; float* buf; unsigned int* mm; bool keep; };
+        struct Gen { NoiseField f; float* buf; unsigned int* mm; bool keep; const vr_noise_tree* tree; };
         std::vector<Gen> gens;
-        auto find = [&](uint32_t g, float fr, int32_t s) -> int {
+        auto find = [&](uint32_t g, float fr, int32_t s, const vr_noise_tree* tr) -> int {
             for (size_t i = 0; i < gens.size(); ++i)
-                if (gens[i].f.generator == g && gens[i].f.frequency == fr && gens[i].f.seed == s) return (int)i;
+                if (gens[i].f.generator == g && gens[i].f.frequency == fr && gens[i].f.seed == s && gens[i].tree == tr) return (int)i;
             return -1;
         };
+        const bool has_trees = d->struct_size >= offsetof(vr_noise_desc, tree) + sizeof(d->tree);
         int field_of[4], norm_of[4];
         for (int k = 0; k < 4; ++k) {
             const vr_noise_channel& ch = d->channel[k];
-            if (ch.generator > VR_NOISE_ZERO || (ch.norm_generator > VR_NOISE_ZERO && ch.norm_generator != VR_NOISE_SAME) || ch.power < 1 || ch.power > 8) {
+            const vr_noise_tree* tr = (ch.generator == VR_NOISE_TREE && has_trees) ? d->tree[k] : nullptr;
+            const bool bad_gen = ch.generator > VR_NOISE_TREE || (ch.generator == VR_NOISE_TREE && (!tr || tr->prog.empty()));
+            if (bad_gen || (ch.norm_generator > VR_NOISE_ZERO && ch.norm_generator != VR_NOISE_SAME) || ch.power < 1 || ch.power > 8) {
                 release_volume(c);
-                return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: bad channel recipe");
+                return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: bad channel recipe (a VR_NOISE_TREE channel needs desc.tree[k] and normalises with VR_NOISE_SAME or a built-in field)");
             }
             field_of[k] = -1;
             if (ch.generator != VR_NOISE_ZERO) {
-                field_of[k] = find(ch.generator, ch.frequency, ch.seed);
-                if (field_of[k] < 0) { gens.push_back({{ch.generator, ch.frequency, ch.seed}, nullptr, nullptr, true}); field_of[k] = (int)gens.size() - 1; }
+                field_of[k] = find(ch.generator, ch.frequency, ch.seed, tr);
+                if (field_of[k] < 0) { gens.push_back({{ch.generator, ch.frequency, ch.seed}, nullptr, nullptr, true, tr}); field_of[k] = (int)gens.size() - 1; }
                 gens[field_of[k]].keep = true;
             }
             if (ch.norm_generator == VR_NOISE_SAME) norm_of[k] = field_of[k];
             else if (ch.norm_generator == VR_NOISE_ZERO) norm_of[k] = -1;
             else {
-                norm_of[k] = find(ch.norm_generator, ch.norm_frequency, ch.norm_seed);
-                if (norm_of[k] < 0) { gens.push_back({{ch.norm_generator, ch.norm_frequency, ch.norm_seed}, nullptr, nullptr, false}); norm_of[k] = (int)gens.size() - 1; }
+                norm_of[k] = find(ch.norm_generator, ch.norm_frequency, ch.norm_seed, nullptr);
+                if (norm_of[k] < 0) { gens.push_back({{ch.norm_generator, ch.norm_frequency, ch.norm_seed}, nullptr, nullptr, false, nullptr}); norm_of[k] = (int)gens.size() - 1; }
             }
             if (norm_of[k] < 0) { release_volume(c); return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: a channel needs a non-zero field to normalise with"); }
         }
@@ -649,7 +658,13 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
             if (gens[i].keep) {
                 if (!c->bake_plane[plane]) e = cudaMalloc(&c->bake_plane[plane], c->bake_plane_bytes);
                 gens[i].buf = c->bake_plane[plane++];
-                if (e == cudaSuccess) e = launch_noise_fill(gens[i].f, n, gens[i].buf, gens[i].mm, c->stream);
+                if (e == cudaSuccess && gens[i].tree) {
+                    // a node tree: the same GenUniformGrid3D walk, interpreted (noise_tree.cu); the program buffer is reused in stream order
+                    if (!c->d_tree_prog) e = cudaMalloc(&c->d_tree_prog, kTreeMaxInstr * sizeof(TreeInstr));
+                    if (e == cudaSuccess) e = cudaMemcpyAsync(c->d_tree_prog, gens[i].tree->prog.data(), gens[i].tree->prog.size() * sizeof(TreeInstr), cudaMemcpyHostToDevice, c->stream);
+                    if (e == cudaSuccess) e = launch_tree_grid(c->d_tree_prog, (int)gens[i].tree->prog.size(), gens[i].tree->result_reg, 0, 0, 0, n, n, n,
+                                                               gens[i].f.frequency, gens[i].f.seed, gens[i].buf, gens[i].mm, c->stream);
+                } else if (e == cudaSuccess) e = launch_noise_fill(gens[i].f, n, gens[i].buf, gens[i].mm, c->stream);
             } else {
                 e = launch_noise_minmax_only(gens[i].f, n, gens[i].mm, c->stream);
             }
@@ -676,6 +691,43 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
     st = finish_volume(c, vd);
     if (st != VR_OK) release_volume(c);
     return st;
+}
+
+// ------------------------------------------------------------------ FastNoise2 node trees on the device
+extern "C" vr_status vr_noise_tree_grid(vr_context* c, const vr_noise_tree* t, int32_t x0, int32_t y0, int32_t z0, uint32_t nx, uint32_t ny,
+                                        uint32_t nz, float frequency, int32_t seed, float* out_host, float minmax[2]) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!t || t->prog.empty()) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_noise_tree_grid: no compiled tree");
+    if (nx == 0 || ny == 0 || nz == 0 || nx > 4096 || ny > 4096 || nz > 4096) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_noise_tree_grid: grid dimensions must be in 1..4096");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    const size_t bytes = (size_t)nx * ny * nz * sizeof(float);
+    if (!c->d_tree_prog) VR_CUDA(c, cudaMalloc(&c->d_tree_prog, kTreeMaxInstr * sizeof(TreeInstr)));
+    if (!c->d_mm) VR_CUDA(c, cudaMalloc(&c->d_mm, 16 * sizeof(unsigned int)));
+    if (c->tree_out_bytes < bytes) {
+        VR_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (c->d_tree_out) { cudaFree(c->d_tree_out); c->d_tree_out = nullptr; c->tree_out_bytes = 0; }
+        cudaError_t e = cudaMalloc(&c->d_tree_out, bytes);
+        if (e != cudaSuccess) return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, "vr_noise_tree_grid: output plane", e);
+        c->tree_out_bytes = bytes;
+    }
+    unsigned int h_mm[2];
+    minmax_init(h_mm);
+    VR_CUDA(c, cudaMemcpyAsync(c->d_tree_prog, t->prog.data(), t->prog.size() * sizeof(TreeInstr), cudaMemcpyHostToDevice, c->stream));
+    VR_CUDA(c, cudaMemcpyAsync(c->d_mm, h_mm, sizeof h_mm, cudaMemcpyHostToDevice, c->stream));
+    VR_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    VR_CUDA(c, launch_tree_grid(c->d_tree_prog, (int)t->prog.size(), t->result_reg, x0, y0, z0, (int)nx, (int)ny, (int)nz, frequency, seed,
+                                c->d_tree_out, c->d_mm, c->stream));
+    VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->foreign_stream_pending = false;
+    c->stats.rays = 0;
+    c->stats.kernel_launches = 1;
+    std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
+    VR_CUDA(c, cudaMemcpyAsync(h_mm, c->d_mm, sizeof h_mm, cudaMemcpyDeviceToHost, c->stream));
+    if (out_host) VR_CUDA(c, cudaMemcpyAsync(out_host, c->d_tree_out, bytes, cudaMemcpyDeviceToHost, c->stream));
+    VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (minmax) { minmax[0] = minmax_decode(h_mm[0]); minmax[1] = minmax_decode(h_mm[1]); }
+    return VR_OK;
 }
 
 // ------------------------------------------------------------------ params

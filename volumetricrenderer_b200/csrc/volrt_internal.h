@@ -7,6 +7,8 @@
 #include <stdint.h>
 #include <stddef.h>
 #include <stdio.h>
+#include <string>
+#include <vector>
 #include "../../include/volrt.h"
 
 namespace volrt {
@@ -113,6 +115,39 @@ cudaError_t launch_pyramid_base(const void* lin, int vol_format, int w, int h, i
 cudaError_t launch_pyramid_reduce(const float* in, float* out, int channels, int bx, int by, int bz, cudaStream_t s);
 // occupancy from level 0: occupied = some channel has min != 0 or max != 0 (NaN counts as occupied)
 cudaError_t launch_occupancy_from_pyramid(const float* level0, int channels, uint8_t* occupied, int nbricks, cudaStream_t s);
+
+// ---- FastNoise2 node trees (noise_tree.cu): an encoded tree is compiled on the host into a straight-line program
+// over value registers V[] and position registers P[][3]; fractal octaves are unrolled, domain modifiers become
+// position instructions, so the device needs no recursion and every thread runs the same instruction stream.
+enum TreeOp : uint16_t {
+    T_CONST = 0, T_WHITE, T_VALUE, T_PERLIN, T_SIMPLEX, T_OPENSIMPLEX2, T_SINE, T_POSITION_OUTPUT, T_DISTANCE_TO_POINT,
+    T_CELL_VALUE, T_CELL_DISTANCE, T_CELL_LOOKUP_POS,
+    T_ADD, T_SUB, T_MUL, T_DIV, T_MIN, T_MAX, T_MIN_SMOOTH, T_MAX_SMOOTH, T_FADE, T_POW_FLOAT, T_POW_INT, T_REMAP, T_TERRACE,
+    T_CONVERT_RGBA8, T_COPY,
+    T_FBM_FIRST, T_FBM_NEXT, T_RIDGED_FIRST, T_RIDGED_NEXT, T_PINGPONG_FIRST, T_PINGPONG_NEXT,
+    T_POS_COPY, T_POS_SCALE, T_POS_AXIS_SCALE, T_POS_OFFSET, T_POS_ROTATE, T_POS_WARP, T_WARP_AMP_NEXT,
+    T_OP_COUNT
+};
+struct TreeInstr {
+    uint16_t op;
+    uint8_t dst;          // value register written (or position register for T_POS_* / T_CELL_LOOKUP_POS)
+    uint8_t pos;          // position register read
+    uint8_t a, b, c, d;   // value-register operands
+    int32_t seed_off;     // added to the caller's seed
+    int32_t i0, i1, i2, i3;
+    float f[9];
+};
+constexpr int kTreeMaxInstr = 512, kTreeMaxValues = 64, kTreeMaxPositions = 16;
+// out[nz][ny][nx] = tree((x0+ix)*freq, (y0+iy)*freq, (z0+iz)*freq) with seed; min/max folded into minmax_bits[2]
+cudaError_t launch_tree_grid(const TreeInstr* d_prog, int n_instr, int result_reg, int x0, int y0, int z0, int nx, int ny, int nz,
+                             float frequency, int seed, float* out, unsigned int* minmax_bits, cudaStream_t s);
+}  // namespace volrt
+struct vr_noise_tree {           // the opaque handle of include/volrt.h
+    std::vector<volrt::TreeInstr> prog;
+    int result_reg = 0, n_nodes = 0, n_values = 0, n_positions = 0;
+    std::string encoded;
+};
+namespace volrt {
 
 // ---- volume files (volume_file.cu; host code)
 struct Sha256 {

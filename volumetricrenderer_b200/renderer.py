@@ -149,6 +149,26 @@ class Renderer:
         self._check(self._lib.vr_volume_pyramid(self._ctx, flat.ctypes.data_as(C.POINTER(C.c_float)), flat.nbytes))
         return volfile.split_pyramid(flat, w, h, d, self._vol_fmt)
 
+    # ---- FastNoise2 node trees (noisetree.py builds / compiles them)
+    def noise_tree_grid(self, tree, shape, frequency, seed, start=(0, 0, 0), want_grid=True):
+        """tree: encoded string, noisetree.N or noisetree.CompiledTree; shape = (nz, ny, nx) -> (grid float32, (min, max))"""
+        from . import noisetree
+        own = None
+        if isinstance(tree, noisetree.N):
+            tree = tree.encode()
+        if not isinstance(tree, noisetree.CompiledTree):
+            tree = own = noisetree.CompiledTree(tree)
+        nz, ny, nx = shape
+        out = np.empty(shape, np.float32) if want_grid else None
+        mm = (C.c_float * 2)()
+        try:
+            self._check(self._lib.vr_noise_tree_grid(self._ctx, tree.handle, start[0], start[1], start[2], nx, ny, nz, frequency, seed,
+                                                     out.ctypes.data_as(C.POINTER(C.c_float)) if want_grid else None, mm))
+        finally:
+            if own is not None:
+                own.close()
+        return out, (mm[0], mm[1])
+
     # ---- params
     def default_params(self):
         p = capi.vr_params()
