@@ -411,7 +411,11 @@ __device__ __forceinline__ float tree_eval(const TreeInstr* __restrict__ prog, i
             case T_POSITION_OUTPUT: V[in.dst] = ((px + in.f[3]) * in.f[0] + (py + in.f[4]) * in.f[1]) + (pz + in.f[5]) * in.f[2]; break;
             case T_DISTANCE_TO_POINT: V[in.dst] = calc_distance(in.i0, px - in.f[0], py - in.f[1], pz - in.f[2]); break;
             case T_CELL_VALUE: V[in.dst] = cellular_value3(s, px, py, pz, V[in.a], in.i0, in.i1); break;
-            case T_CELL_DISTANCE: V[in.dst] = cellular_distance3(s, px, py, pz, V[in.a], in.i0, in.i1, in.i2, in.i3); break;
+            case T_CELL_DISTANCE:
+                // the node's defaults (what the reference's bake uses, TestMain.cpp:43) keep only the nearest squared distance
+                if (in.i0 == 1 && in.i1 == 0 && in.i3 == 0 && V[in.a] == 1.0f) V[in.dst] = cellular3(s, px, py, pz);
+                else V[in.dst] = cellular_distance3(s, px, py, pz, V[in.a], in.i0, in.i1, in.i2, in.i3);
+                break;
             case T_CELL_LOOKUP_POS: {
                 float c[3];
                 cellular_lookup3(s, px, py, pz, V[in.a], in.i0, c);
@@ -527,9 +531,16 @@ __global__ void __launch_bounds__(128) tree_grid_kernel(const TreeInstr* __restr
         mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     }
-    if ((threadIdx.x & 31) == 0 && mn <= mx) {
-        atomicMin(&minmax_bits[0], tree_ordered_bits(mn));
-        atomicMax(&minmax_bits[1], tree_ordered_bits(mx));
+    // one pair of atomics per CTA: 65 k warps hammering the same two words cost more than a whole Perlin pass
+    __shared__ float smn[4], smx[4];
+    if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 4; ++w) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+        if (mn <= mx) {
+            atomicMin(&minmax_bits[0], tree_ordered_bits(mn));
+            atomicMax(&minmax_bits[1], tree_ordered_bits(mx));
+        }
     }
 }
 
@@ -537,7 +548,7 @@ cudaError_t launch_tree_grid(const TreeInstr* d_prog, int n_instr, int result_re
                              float frequency, int seed, float* out, unsigned int* minmax_bits, cudaStream_t s) {
     const size_t total = (size_t)nx * ny * nz;
     size_t blocks = (total + 127) / 128;
-    const size_t cap = 148u * 16u * 8u;
+    const size_t cap = 148u * 9u * 4u;              // 4 waves of the 9 CTAs an SM holds at 56 registers; grid-stride beyond
     if (blocks > cap) blocks = cap;
     if (blocks == 0) return cudaSuccess;
     tree_grid_kernel<<<(unsigned)blocks, 128, 0, s>>>(d_prog, n_instr, result_reg, x0, y0, z0, nx, ny, nz, frequency, seed, out, minmax_bits);
