@@ -555,8 +555,11 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
 // Lanes of a ray sit at neighbouring steps, so they mostly agree on "is there density here" and the
 // light-march branch stays coherent.  The sum and the products are re-associated and positions are
 // Pin + i*stepVec: parity is tolerance-based (as it already is for every compositing variant).
+#ifndef VOLRT_SPLIT_MIN_CTAS
+#define VOLRT_SPLIT_MIN_CTAS 1
+#endif
 template <int VARIANT, int S>
-__global__ void __launch_bounds__(128) march_composite_split_kernel(const __grid_constant__ MarchParams P) {
+__global__ void __launch_bounds__(128, VOLRT_SPLIT_MIN_CTAS) march_composite_split_kernel(const __grid_constant__ MarchParams P) {
     constexpr int RAYS = 32 / S, RW = RAYS / 2;
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
