@@ -142,34 +142,54 @@ __device__ __forceinline__ float simplex3(int seed, float x, float y, float z) {
     return 32.69428253173828125f * fmaf(n0, t0, fmaf(n1, t1, fmaf(n2, t2, n3 * t3)));
 }
 
+// (float)(v & 0x3ff) - 511.5 without the int->float conversion (an XU-pipe instruction, 16 lanes/clk/SM, and the cellular
+// walk needs 81 of them per point): with the 10 bits placed one position up in the mantissa of 2^22 (ulp 0.5) the float IS
+// 4194304 + v, and 4194304 + 511.5 is representable, so one FADD gives the exact same value.  t = the hash shifted so that the
+// wanted 10 bits sit at bits 1..10.
+// The mask and the exponent pattern cannot both be immediates of one LOP3, and left to itself the compiler emits two;
+// with the exponent pattern held in a register, (t & 0x7fe) | k is a single LOP3 (27 x 3 of them per point).
+__device__ __forceinline__ float cell_jitter_component(int t) {
+    unsigned k, r;
+    asm("mov.b32 %0, 0x4A800000;" : "=r"(k));
+    asm("lop3.b32 %0, %1, 0x7fe, %2, 0xEA;" : "=r"(r) : "r"(t), "r"(k));       // (a & b) | c
+    return __uint_as_float(r) - 4194815.5f;
+}
+
+// MUFU.RSQ alone: rsqrtf() wraps it in a denormal fix-up (FSETP + 2 FMUL) that the squared length of a jitter vector
+// (>= 0.75) never needs
+__device__ __forceinline__ float rsqrt_fast(float v) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+    return r;
+}
+
 __device__ __forceinline__ float cellular3(int seed, float x, float y, float z) {
     const float jitter = 0.396144f;                   // kJitter3D * jitter modifier 1
     float best = CUDART_INF_F;                        // Index0 of the sorted distances = the minimum
-    int xc = __float2int_rn(x) - 1, ycBase = __float2int_rn(y) - 1, zcBase = __float2int_rn(z) - 1;
-    float xcf = (float)xc - x, ycfBase = (float)ycBase - y, zcfBase = (float)zcBase - z;
-    xc *= kPrimeX; ycBase *= kPrimeY; zcBase *= kPrimeZ;
+    const int xb = __float2int_rn(x) - 1, yb = __float2int_rn(y) - 1, zb = __float2int_rn(z) - 1;
+    // the three offsets and primed coordinates per axis, formed once (the running += of Cellular.inl gives the same values:
+    // small integers and their sums are exact)
+    float xcf[3], ycf[3], zcf[3];
+    int xc[3], yc[3], zc[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        xcf[i] = ((float)xb - x) + (float)i; ycf[i] = ((float)yb - y) + (float)i; zcf[i] = ((float)zb - z) + (float)i;
+        xc[i] = (xb + i) * kPrimeX; yc[i] = (yb + i) * kPrimeY; zc[i] = (zb + i) * kPrimeZ;
+    }
 #pragma unroll
     for (int xi = 0; xi < 3; ++xi) {
-        float ycf = ycfBase; int yc = ycBase;
 #pragma unroll
         for (int yi = 0; yi < 3; ++yi) {
-            float zcf = zcfBase; int zc = zcBase;
-            int sxy = seed ^ xc ^ yc;
+            const int sxy = seed ^ xc[xi] ^ yc[yi];
 #pragma unroll
             for (int zi = 0; zi < 3; ++zi) {
-                int hash = (sxy ^ zc) * 0x27d4eb2d;   // HashPrimesHB, Utils.inl:304-312
-                float xd = (float)(hash & 0x3ff) - 511.5f;
-                float yd = (float)((hash >> 10) & 0x3ff) - 511.5f;
-                float zd = (float)((hash >> 20) & 0x3ff) - 511.5f;
-                float invMag = jitter * rsqrtf(fmaf(xd, xd, fmaf(yd, yd, zd * zd)));
-                xd = fmaf(xd, invMag, xcf); yd = fmaf(yd, invMag, ycf); zd = fmaf(zd, invMag, zcf);
-                float nd = fmaf(zd, zd, fmaf(yd, yd, xd * xd));
-                best = fminf(best, nd);
-                zcf += 1.0f; zc += kPrimeZ;
+                const int hash = (sxy ^ zc[zi]) * 0x27d4eb2d;   // HashPrimesHB, Utils.inl:304-312
+                float xd = cell_jitter_component(hash << 1), yd = cell_jitter_component(hash >> 9), zd = cell_jitter_component(hash >> 19);
+                const float invMag = jitter * rsqrt_fast(fmaf(xd, xd, fmaf(yd, yd, zd * zd)));
+                xd = fmaf(xd, invMag, xcf[xi]); yd = fmaf(yd, invMag, ycf[yi]); zd = fmaf(zd, invMag, zcf[zi]);
+                best = fminf(best, fmaf(zd, zd, fmaf(yd, yd, xd * xd)));
             }
-            ycf += 1.0f; yc += kPrimeY;
         }
-        xcf += 1.0f; xc += kPrimeX;
     }
     return best;
 }

@@ -96,10 +96,8 @@ __device__ __forceinline__ void cellular_walk(int seed, float x, float y, float 
 #pragma unroll
             for (int zi = 0; zi < 3; ++zi) {
                 const int hash = (sxy ^ zc) * 0x27d4eb2d;
-                float xd = (float)(hash & 0x3ff) - 511.5f;
-                float yd = (float)((hash >> 10) & 0x3ff) - 511.5f;
-                float zd = (float)((hash >> 20) & 0x3ff) - 511.5f;
-                const float invMag = jitter * rsqrtf(fmaf(xd, xd, fmaf(yd, yd, zd * zd)));
+                float xd = cell_jitter_component(hash << 1), yd = cell_jitter_component(hash >> 9), zd = cell_jitter_component(hash >> 19);
+                const float invMag = jitter * rsqrt_fast(fmaf(xd, xd, fmaf(yd, yd, zd * zd)));
                 xd = fmaf(xd, invMag, xcf); yd = fmaf(yd, invMag, ycf); zd = fmaf(zd, invMag, zcf);
                 visit(hash, xd, yd, zd);
                 zcf += 1.0f; zc += kPrimeZ;
