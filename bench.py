@@ -356,7 +356,7 @@ def run_volrt(args, rank, world, local):
     if rank == 0:
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "%s: %s" % (args.workload, desc), "width": W, "height": H,
                        "l2": "flushed between frames (256 MiB write); the procedural workloads read no input",
