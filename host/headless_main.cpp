@@ -4,7 +4,10 @@
 // without a window").  Everything heavy happens in libvolrt (CUDA); this file is host logic only.
 //
 //   volrt_headless [--frames N] [--keys "D*60,W*30,A*20"] [--out DIR] [--every K] [--size WxH]
-//                  [--host-bake]   (bake with the oracle-free path: the device bake is the default)
+//                  [--std140]      send GlobalShaderData in the shader's std140 layout (quirk Q2 "fixed": the medium scrolls)
+//                  [--dt SECONDS]  frameTime advances by this much per frame instead of following the wall clock
+//                  [--scroll-yzw]  also write -frameTime into MediaScroll[0].y/.z/.w — the only element the reference writes,
+//                                  [0].x, is read by a commented-out line of the shader (frag.glsl:65), so its medium never moves
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -27,6 +30,16 @@ struct GlobalShaderData {          // TestMain.cpp:34-39 — glm::vec3 is 12 byt
     glm::mat4 MediaScroll;
 };
 #pragma pack(pop)
+// What the SHADER declares (frag.glsl:9-14, std140: a vec3 is padded to 16 bytes, MediaScroll at byte 80).  The reference
+// never sends this layout — with its 140-byte struct the -frameTime it writes lands in padding and the medium does not
+// scroll.  --std140 sends this one instead: the animation the shader was written for.
+struct GlobalShaderDataStd140 {
+    glm::mat4 WorldToLocal;
+    glm::vec3 CameraPosition;
+    float pad0;
+    glm::mat4 MediaScroll;
+};
+static_assert(sizeof(GlobalShaderDataStd140) == 144, "std140 image of GlobalShaderData");
 static_assert(sizeof(ObjectShaderData) == 192, "ObjectShaderData");
 static_assert(sizeof(GlobalShaderData) == 140, "GlobalShaderData is 140 bytes in the reference's C++ layout");
 
@@ -60,6 +73,8 @@ static void write_ppm(const std::string& path, const unsigned char* rgba, uint32
 
 int main(int argc, char** argv) {
     int frames = 120, every = 0;
+    bool std140 = false, scroll_yzw = false;
+    float scripted_dt = -1.0f;
     uint32_t W = 1280, H = 720;                         // VulkanContext.cpp:24
     std::string keys = "D*60,W*30,A*30", out_dir;
     for (int i = 1; i < argc; ++i) {
@@ -68,6 +83,9 @@ int main(int argc, char** argv) {
         else if (a == "--keys" && i + 1 < argc) keys = argv[++i];
         else if (a == "--out" && i + 1 < argc) out_dir = argv[++i];
         else if (a == "--every" && i + 1 < argc) every = std::atoi(argv[++i]);
+        else if (a == "--std140") std140 = true;
+        else if (a == "--scroll-yzw") scroll_yzw = true;
+        else if (a == "--dt" && i + 1 < argc) scripted_dt = (float)std::atof(argv[++i]);
         else if (a == "--size" && i + 1 < argc) { if (std::sscanf(argv[++i], "%ux%u", &W, &H) != 2) return 2; }
         else { std::fprintf(stderr, "unknown argument %s\n", a.c_str()); return 2; }
     }
@@ -79,10 +97,12 @@ int main(int argc, char** argv) {
 
         vkc::UniformBuffer<ObjectShaderData> objectUniformBuffer(renderer.GetFramesCount());    // :130
         vkc::UniformBuffer<GlobalShaderData> globalUniformBuffer(renderer.GetFramesCount());
+        vkc::UniformBuffer<GlobalShaderDataStd140> globalUniformBufferStd140(renderer.GetFramesCount());
         std::vector<vkc::DescriptorSet> perFrameSets(renderer.GetFramesCount());                 // :138-154
         for (uint32_t i = 0; i < renderer.GetFramesCount(); ++i)
             perFrameSets[i].WriteBuffer(0, objectUniformBuffer.HostMappings[i], sizeof(ObjectShaderData))
-                           .WriteBuffer(1, globalUniformBuffer.HostMappings[i], sizeof(GlobalShaderData))
+                           .WriteBuffer(1, std140 ? globalUniformBufferStd140.HostMappings[i] : globalUniformBuffer.HostMappings[i],
+                                        std140 ? sizeof(GlobalShaderDataStd140) : sizeof(GlobalShaderData))
                            .WriteImage(2, texture);
 
         vkc::RenderPassCreateInfo createInfo;                                                    // :156-166
@@ -123,8 +143,10 @@ int main(int argc, char** argv) {
             glm::mat4 worldToLocal = glm::inverse(osd.Model);                                    // :230
             auto now = std::chrono::high_resolution_clock::now();
             float frameTime = std::chrono::duration<float>(now - startTime).count();            // :232
+            if (scripted_dt >= 0.0f) frameTime = scripted_dt * (float)frame;
             glm::mat4 mediaScroll;
             mediaScroll[0][0] = -frameTime;                                                      // :233-238
+            if (scroll_yzw) mediaScroll[0][1] = mediaScroll[0][2] = mediaScroll[0][3] = -frameTime;
             GlobalShaderData gsd;
             gsd.WorldToLocal = worldToLocal;
             gsd.CameraPosition = glm::vec3(3.0f, 3.0f, 3.0f);                                   // :242
@@ -132,6 +154,11 @@ int main(int argc, char** argv) {
 
             objectUniformBuffer.Update(&osd, renderer.GetCurrentFrame());                       // :248
             globalUniformBuffer.Update(&gsd, renderer.GetCurrentFrame());                       // :249
+            if (std140) {
+                GlobalShaderDataStd140 g2;
+                g2.WorldToLocal = gsd.WorldToLocal; g2.CameraPosition = gsd.CameraPosition; g2.pad0 = 0.0f; g2.MediaScroll = gsd.MediaScroll;
+                globalUniformBufferStd140.Update(&g2, renderer.GetCurrentFrame());
+            }
 
             renderer.BeginFrame();                                                               // :251
             renderer.EndFrame();                                                                 // :255

@@ -75,3 +75,23 @@ def test_headless_loop_matches_the_python_host(tmp_path):
     assert ppm.startswith(b"P6\n1280 720\n255\n")
     px = np.frombuffer(ppm[len(b"P6\n1280 720\n255\n"):], np.uint8).reshape(720, 1280, 3)
     assert int(px[..., 0].astype(np.int64).sum()) == sums[11]
+
+
+@pytest.mark.gpu
+def test_media_scroll_never_moves_in_the_reference_and_can_be_made_to():
+    """The reference writes -frameTime into MediaScroll[0][0] only (TestMain.cpp:233-238).  With its 140-byte struct that float
+    lands in std140 padding (quirk Q2); with the shader's own layout (--std140) it lands in MediaScroll[0].x, which only a
+    commented-out line reads (frag.glsl:65).  Either way the frames do not depend on time.  A host that also fills .y/.z/.w
+    in the std140 layout gets the scroll the shader implements (frag.glsl:67-69)."""
+    _build()
+
+    def sums(*extra):
+        r = subprocess.run([EXE, "--frames", "4", "--keys", "-", "--every", "1", "--dt", "0.5", *extra], capture_output=True, text=True, timeout=120)
+        assert r.returncode == 0, r.stderr
+        return [int(m.group(1)) for m in re.finditer(r"sum\(R\) (\d+)", r.stdout)]
+    q2 = sums()
+    fixed = sums("--std140")
+    moving = sums("--std140", "--scroll-yzw")
+    assert len(q2) == 4 and len(set(q2)) == 1
+    assert fixed == q2
+    assert moving[0] == q2[0] and len(set(moving)) == 4        # frame 0 has frameTime 0; later frames scroll
