@@ -208,10 +208,23 @@ __device__ __forceinline__ float density_at(const MarchParams& P, const RayConst
                                             const GradLut* lut, f3 p) {
     if (VARIANT == MARCH_RGBA_TEX) {
         // frag.glsl:66-71.  coord = Pin*scale_k + cK*weight_k
-        float s1 = tex3D<float4>(P.tex, p.x * P.coord_scale[0], p.y * P.coord_scale[0], p.z * P.coord_scale[0]).x;
-        float s2 = tex3D<float4>(P.tex, fmaf(p.x, P.coord_scale[1], rc.off1.x), fmaf(p.y, P.coord_scale[1], rc.off1.y), fmaf(p.z, P.coord_scale[1], rc.off1.z)).y;
-        float s3 = tex3D<float4>(P.tex, fmaf(p.x, P.coord_scale[2], rc.off2.x), fmaf(p.y, P.coord_scale[2], rc.off2.y), fmaf(p.z, P.coord_scale[2], rc.off2.z)).z;
-        float s4 = tex3D<float4>(P.tex, fmaf(p.x, P.coord_scale[3], rc.off3.x), fmaf(p.y, P.coord_scale[3], rc.off3.y), fmaf(p.z, P.coord_scale[3], rc.off3.z)).w;
+        const float x1 = p.x * P.coord_scale[0], y1 = p.y * P.coord_scale[0], z1 = p.z * P.coord_scale[0];
+        const float x2 = fmaf(p.x, P.coord_scale[1], rc.off1.x), y2 = fmaf(p.y, P.coord_scale[1], rc.off1.y), z2 = fmaf(p.z, P.coord_scale[1], rc.off1.z);
+        const float x3 = fmaf(p.x, P.coord_scale[2], rc.off2.x), y3 = fmaf(p.y, P.coord_scale[2], rc.off2.y), z3 = fmaf(p.z, P.coord_scale[2], rc.off2.z);
+        const float x4 = fmaf(p.x, P.coord_scale[3], rc.off3.x), y4 = fmaf(p.y, P.coord_scale[3], rc.off3.y), z4 = fmaf(p.z, P.coord_scale[3], rc.off3.z);
+        float s1, s2, s3, s4;
+        if (P.planar) {
+            // each fetch wants one channel: from a one-channel texture it moves a quarter of the bytes through L1/L2
+            s1 = tex3D<float>(P.tex_plane[0], x1, y1, z1);
+            s2 = tex3D<float>(P.tex_plane[1], x2, y2, z2);
+            s3 = tex3D<float>(P.tex_plane[2], x3, y3, z3);
+            s4 = tex3D<float>(P.tex_plane[3], x4, y4, z4);
+        } else {
+            s1 = tex3D<float4>(P.tex, x1, y1, z1).x;
+            s2 = tex3D<float4>(P.tex, x2, y2, z2).y;
+            s3 = tex3D<float4>(P.tex, x3, y3, z3).z;
+            s4 = tex3D<float4>(P.tex, x4, y4, z4).w;
+        }
         return (s1 * s2) * (s3 + s4) * P.sample_scale;
     } else if (VARIANT == MARCH_RGBA_LINEAR) {
         f3 u1 = mul3(p, P.coord_scale[0]);

@@ -344,4 +344,26 @@ cudaError_t launch_occupancy_from_pyramid(const float* level0, int channels, uin
     return cudaGetLastError();
 }
 
+// RGBA8 (x fastest) -> four tightly packed R8 planes; 4 voxels per thread so that every plane store is a 32-bit word
+__global__ void __launch_bounds__(256) deinterleave_rgba8_kernel(const uint4* __restrict__ rgba, unsigned char* __restrict__ planes, size_t voxels) {
+    const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q * 4 + 3 < voxels) {
+        const uint4 v = __ldg(rgba + q);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const unsigned sel = 0x0040u + 0x0011u * c;              // byte c of the first word, byte c of the second
+            const unsigned w = (__byte_perm(v.x, v.y, sel) & 0xffffu) | (__byte_perm(v.z, v.w, sel) << 16);
+            reinterpret_cast<unsigned*>(planes + (size_t)c * voxels)[q] = w;
+        }
+    } else {
+        for (size_t i = q * 4; i < voxels; ++i)
+            for (int c = 0; c < 4; ++c) planes[(size_t)c * voxels + i] = reinterpret_cast<const unsigned char*>(rgba)[i * 4 + c];
+    }
+}
+cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, cudaStream_t s) {
+    const size_t quads = (voxels + 3) / 4;
+    deinterleave_rgba8_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, s>>>((const uint4*)rgba, planes4, voxels);
+    return cudaGetLastError();
+}
+
 }  // namespace volrt

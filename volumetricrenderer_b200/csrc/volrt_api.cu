@@ -47,6 +47,11 @@ struct vr_context {
     size_t lin_bytes = 0;
     cudaArray_t array = nullptr;
     cudaTextureObject_t tex = 0;
+    // RGBA8 volumes are also kept as four one-channel textures: frag.glsl reads ONE channel from each of its four fetches
+    cudaArray_t plane_array[4] = {};
+    cudaTextureObject_t plane_tex[4] = {};
+    unsigned char* plane_lin = nullptr;    // de-interleave scratch (4 planes)
+    bool planar = false;
     uint8_t* occupied = nullptr;
     uint8_t* brick_dist = nullptr;         // 2 planes: the distance map and the scratch of its passes
     alignas(64) unsigned char tensor_map[128] = {};   // BRICK layout: CUtensorMap over `lin`
@@ -202,6 +207,12 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
 static void release_volume(vr_context* c) {
     if (c->tex) { cudaDestroyTextureObject(c->tex); c->tex = 0; }
     if (c->array) { cudaFreeArray(c->array); c->array = nullptr; }
+    for (int k = 0; k < 4; ++k) {
+        if (c->plane_tex[k]) { cudaDestroyTextureObject(c->plane_tex[k]); c->plane_tex[k] = 0; }
+        if (c->plane_array[k]) { cudaFreeArray(c->plane_array[k]); c->plane_array[k] = nullptr; }
+    }
+    if (c->plane_lin) { cudaFree(c->plane_lin); c->plane_lin = nullptr; }
+    c->planar = false;
     if (c->lin) { cudaFree(c->lin); c->lin = nullptr; }
     if (c->occupied) { cudaFree(c->occupied); c->occupied = nullptr; }
     if (c->brick_dist) { cudaFree(c->brick_dist); c->brick_dist = nullptr; }
@@ -273,6 +284,29 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
         td.readMode = d.format == VR_VOL_R16F ? cudaReadModeElementType : cudaReadModeNormalizedFloat;
         td.normalizedCoords = 1;
         if (!c->tex) VR_CUDA(c, cudaCreateTextureObject(&c->tex, &rd, &td, nullptr));
+        // planar copies of an RGBA8 volume (decision 11); VOLRT_PLANAR=0 keeps the interleaved texture only
+        static const bool want_planar = [] { const char* e = getenv("VOLRT_PLANAR"); return !e || atoi(e) != 0; }();
+        c->planar = false;
+        if (d.format == VR_VOL_RGBA8_UNORM && want_planar) {
+            const size_t vox = (size_t)d.width * d.height * d.depth;
+            if (!c->plane_lin) VR_CUDA(c, cudaMalloc(&c->plane_lin, 4 * vox));
+            VR_CUDA(c, launch_deinterleave_rgba8((const uint8_t*)c->lin, c->plane_lin, vox, c->stream));
+            const cudaChannelFormatDesc cd1 = cudaCreateChannelDesc<unsigned char>();
+            for (int k = 0; k < 4; ++k) {
+                if (!c->plane_array[k]) VR_CUDA(c, cudaMalloc3DArray(&c->plane_array[k], &cd1, ext));
+                cudaMemcpy3DParms pp = {};
+                pp.srcPtr = make_cudaPitchedPtr(c->plane_lin + (size_t)k * vox, d.width, d.width, d.height);
+                pp.dstArray = c->plane_array[k];
+                pp.extent = ext;
+                pp.kind = cudaMemcpyDeviceToDevice;
+                VR_CUDA(c, cudaMemcpy3DAsync(&pp, c->stream));
+                cudaResourceDesc rdk = {};
+                rdk.resType = cudaResourceTypeArray;
+                rdk.res.array.array = c->plane_array[k];
+                if (!c->plane_tex[k]) VR_CUDA(c, cudaCreateTextureObject(&c->plane_tex[k], &rdk, &td, nullptr));
+            }
+            c->planar = true;
+        }
     }
     c->has_tensor_map = false;
     if (layout == VR_LAYOUT_BRICK) {
@@ -858,6 +892,8 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_render: no volume uploaded (vr_upload_volume / vr_generate_volume)");
     const vr_volume_desc& d = c->vdesc;
     m.tex = c->tex; m.lin = c->lin;
+    m.planar = c->planar ? 1 : 0;
+    for (int k = 0; k < 4; ++k) m.tex_plane[k] = c->plane_tex[k];
     m.vw = (int)d.width; m.vh = (int)d.height; m.vd = (int)d.depth;
     m.vol_format = (int)d.format; m.address_mode = (int)d.address_mode;
     m.bricks = c->bricks;
