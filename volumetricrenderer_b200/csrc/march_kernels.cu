@@ -426,6 +426,23 @@ __device__ __forceinline__ int centre_out(int k, int n) {
     return c >= n ? 0 : c;
 }
 
+// Tile of this CTA.  CTAs are dispatched in linear order (blockIdx.x fastest); the SHORTER grid axis is made the fast one and
+// both axes run centre-out, so the tiles over the object's middle — the expensive ones — are all dispatched first and the
+// cheap silhouette and empty tiles fill the tail.  For a multi-GPU row band (a few tile rows, hundreds of columns) that is
+// column by column from the centre: with the rows as the slow axis heavy and empty tiles alternated every 240 CTAs and a
+// third of the SM time was idle (profiles/r01_band8_before.txt).
+__device__ __forceinline__ void tile_of_cta(int& tx, int& ty) {
+    const int gx = (int)gridDim.x, gy = (int)gridDim.y;
+    int kx = (int)blockIdx.x, ky = (int)blockIdx.y;
+    if (gy < gx) {
+        const int lin = kx + gx * ky;
+        kx = lin / gy;
+        ky = lin - kx * gy;
+    }
+    tx = centre_out(kx, gx);
+    ty = centre_out(ky, gy);
+}
+
 template <int VARIANT>
 __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
@@ -445,7 +462,8 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
     __shared__ float unorm[LINEAR ? 256 : 1];
     __shared__ GradLut lut;                               // used by the FBM variant only
     stage_tables<VARIANT>(unorm, &lut);
-    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    int tx, ty;
+    tile_of_cta(tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -510,7 +528,8 @@ template <int VARIANT, int S>
 __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_constant__ MarchParams P) {
     constexpr int RAYS = 32 / S;            // rays per warp
     constexpr int RW = RAYS / 2;            // warp tile = RW x 2 pixels
-    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    int tx, ty;
+    tile_of_cta(tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = lane / S, sub = lane % S;
     // CTA tile = (2*RW) x 4 pixels: warps 0,1 side by side on rows 0-1, warps 2,3 on rows 2-3
@@ -569,7 +588,7 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
 // light-march branch stays coherent.  The sum and the products are re-associated and positions are
 // Pin + i*stepVec: parity is tolerance-based (as it already is for every compositing variant).
 #ifndef VOLRT_SPLIT_MIN_CTAS
-#define VOLRT_SPLIT_MIN_CTAS 1
+#define VOLRT_SPLIT_MIN_CTAS 7
 #endif
 template <int VARIANT, int S>
 __global__ void __launch_bounds__(128, VOLRT_SPLIT_MIN_CTAS) march_composite_split_kernel(const __grid_constant__ MarchParams P) {
@@ -579,7 +598,8 @@ __global__ void __launch_bounds__(128, VOLRT_SPLIT_MIN_CTAS) march_composite_spl
     __shared__ float unorm[LINEAR ? 256 : 1];
     __shared__ GradLut lut;
     stage_tables<VARIANT>(unorm, &lut);
-    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    int tx, ty;
+    tile_of_cta(tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = lane / S, sub = lane % S;
     const int px = tx * (2 * RW) + (warp & 1) * RW + (r % RW);
@@ -717,7 +737,8 @@ __global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant_
         red[6] = 0;
     }
     __syncthreads();
-    const int tx = centre_out((int)blockIdx.x, (int)gridDim.x), ty = centre_out((int)blockIdx.y, (int)gridDim.y);
+    int tx, ty;
+    tile_of_cta(tx, ty);
     const int warp = tid >> 5, lane = tid & 31;
     const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
