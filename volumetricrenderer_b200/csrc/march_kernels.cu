@@ -426,12 +426,22 @@ __device__ __forceinline__ int centre_out(int k, int n) {
     return c >= n ? 0 : c;
 }
 
+// k-th index of 0..n-1 in order of distance from index c: c, c+1, c-1, c+2, ... and, once one side is used up, straight on
+// along the other (a bijection; centre_out is the case c = n/2)
+__device__ __forceinline__ int outward_from(int k, int n, int c) {
+    const int left = c, right = n - 1 - c, m = min(left, right);
+    if (k <= 2 * m) return (k & 1) ? c + ((k + 1) >> 1) : c - (k >> 1);
+    const int rest = k - 2 * m - 1;
+    return right > left ? c + m + 1 + rest : c - m - 1 - rest;
+}
+
 // Tile of this CTA.  CTAs are dispatched in linear order (blockIdx.x fastest); the SHORTER grid axis is made the fast one and
-// both axes run centre-out, so the tiles over the object's middle — the expensive ones — are all dispatched first and the
-// cheap silhouette and empty tiles fill the tail.  For a multi-GPU row band (a few tile rows, hundreds of columns) that is
-// column by column from the centre: with the rows as the slow axis heavy and empty tiles alternated every 240 CTAs and a
-// third of the SM time was idle (profiles/r01_band8_before.txt).
-__device__ __forceinline__ void tile_of_cta(int& tx, int& ty) {
+// both axes run outwards from the FRAME's centre, so the tiles over the object's middle — the expensive ones — are all
+// dispatched first and the cheap silhouette and empty tiles fill the tail.  For a multi-GPU row band (a few tile rows,
+// hundreds of columns) that is column by column from the middle, each column starting at the tile row nearest the frame's
+// centre row (which for most bands is an edge of the band, not its middle).  With x always fastest and the band's own
+// middle first, a third of the SM time of a 1/8 band was idle (profiles/r01_band8_before.txt).
+__device__ __forceinline__ void tile_of_cta(const MarchParams& P, int tile_h, int& tx, int& ty) {
     const int gx = (int)gridDim.x, gy = (int)gridDim.y;
     int kx = (int)blockIdx.x, ky = (int)blockIdx.y;
     if (gy < gx) {
@@ -439,8 +449,9 @@ __device__ __forceinline__ void tile_of_cta(int& tx, int& ty) {
         kx = lin / gy;
         ky = lin - kx * gy;
     }
+    const int cy = min(max((P.height / 2 - P.row_begin) / tile_h, 0), gy - 1);
     tx = centre_out(kx, gx);
-    ty = centre_out(ky, gy);
+    ty = outward_from(ky, gy, cy);
 }
 
 template <int VARIANT>
@@ -463,7 +474,7 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
     __shared__ GradLut lut;                               // used by the FBM variant only
     stage_tables<VARIANT>(unorm, &lut);
     int tx, ty;
-    tile_of_cta(tx, ty);
+    tile_of_cta(P, 8, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -529,7 +540,7 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
     constexpr int RAYS = 32 / S;            // rays per warp
     constexpr int RW = RAYS / 2;            // warp tile = RW x 2 pixels
     int tx, ty;
-    tile_of_cta(tx, ty);
+    tile_of_cta(P, 4, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = lane / S, sub = lane % S;
     // CTA tile = (2*RW) x 4 pixels: warps 0,1 side by side on rows 0-1, warps 2,3 on rows 2-3
@@ -599,7 +610,7 @@ __global__ void __launch_bounds__(128, VOLRT_SPLIT_MIN_CTAS) march_composite_spl
     __shared__ GradLut lut;
     stage_tables<VARIANT>(unorm, &lut);
     int tx, ty;
-    tile_of_cta(tx, ty);
+    tile_of_cta(P, 4, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = lane / S, sub = lane % S;
     const int px = tx * (2 * RW) + (warp & 1) * RW + (r % RW);
@@ -738,7 +749,7 @@ __global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant_
     }
     __syncthreads();
     int tx, ty;
-    tile_of_cta(tx, ty);
+    tile_of_cta(P, 8, tx, ty);
     const int warp = tid >> 5, lane = tid & 31;
     const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
