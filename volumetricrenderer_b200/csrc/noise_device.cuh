@@ -210,7 +210,7 @@ __device__ __forceinline__ float fbm_perlin(const GradLut* lut, const FbmField& 
 // rho = max(0, .5 fbm + .5 - coverage) * (1 - smoothstep(f0, f1, maxabs(P - 1/2)))
 __device__ __forceinline__ float density_fbm(const GradLut* lut, const FbmField& F, float ux, float uy, float uz) {
     float m = fmaxf(fmaxf(fabsf(ux - 0.5f), fabsf(uy - 0.5f)), fabsf(uz - 0.5f));
-    float t = __saturatef((m - F.falloff0) / (F.falloff1 - F.falloff0));
+    float t = __saturatef((m - F.falloff0) * F.inv_falloff);
     float edge = 1.0f - t * t * (3.0f - 2.0f * t);
     if (edge <= 0.0f) return 0.0f;
     float f = fbm_perlin(lut, F, ux * F.frequency, uy * F.frequency, uz * F.frequency);

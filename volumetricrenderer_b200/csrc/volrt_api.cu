@@ -639,7 +639,8 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
         const vr_params* f = fbm ? fbm : &def;
         if (f->fbm_octaves < 1 || f->fbm_octaves > 16) { release_volume(c); return fail(c, VR_ERR_INVALID_ARGUMENT, "fbm_octaves must be in 1..16"); }
         FbmField ff = {f->fbm_octaves, f->fbm_seed, f->fbm_frequency, f->fbm_gain, f->fbm_lacunarity, f->fbm_coverage,
-                       f->fbm_falloff0, f->fbm_falloff1, fbm_bounding(f->fbm_octaves, f->fbm_gain), d->threshold};
+                       f->fbm_falloff0, f->fbm_falloff1, fbm_bounding(f->fbm_octaves, f->fbm_gain), d->threshold,
+                       1.0f / (f->fbm_falloff1 - f->fbm_falloff0)};
         VR_CUDA(c, launch_smoke_fill(ff, n, (__half*)c->lin, c->stream));
         c->fill_launches = 1;
     } else {
@@ -881,7 +882,7 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     for (int i = 0; i < 3; ++i) { m.sun_dir[i] = p.sun_dir[i]; m.sun_color[i] = p.sun_color[i]; }
     m.ambient = p.ambient; m.sigma_t = p.sigma_t; m.early_term_eps = p.early_term_eps;
     m.fbm = {p.fbm_octaves, p.fbm_seed, p.fbm_frequency, p.fbm_gain, p.fbm_lacunarity, p.fbm_coverage,
-             p.fbm_falloff0, p.fbm_falloff1, fbm_bounding(p.fbm_octaves, p.fbm_gain), 0.0f};
+             p.fbm_falloff0, p.fbm_falloff1, fbm_bounding(p.fbm_octaves, p.fbm_gain), 0.0f, 1.0f / (p.fbm_falloff1 - p.fbm_falloff0)};
     m.counters = c->d_counters;
     m.queue = c->d_queue;
     m.schedule = c->schedule;

@@ -37,6 +37,7 @@ struct BrickInfo {          // min-max grid for empty-space skipping (8^3 voxel 
 struct FbmField {
     int octaves, seed;
     float frequency, gain, lacunarity, coverage, falloff0, falloff1, bounding, threshold;
+    float inv_falloff;      // 1 / (falloff1 - falloff0): a multiply per sample instead of a divide
 };
 
 struct MarchParams {
