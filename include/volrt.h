@@ -89,7 +89,8 @@ typedef enum vr_layout {
 typedef enum vr_density_mode {
     VR_DENSITY_RGBA_PRODUCT = 0,   /* frag.glsl:66-71: (s1*s2)*(s3+s4)*scale, four fetches  */
     VR_DENSITY_SINGLE = 1,         /* T(P).r * sample_scale, one fetch (smoke grids)        */
-    VR_DENSITY_FBM = 2             /* in-kernel FastNoise2-semantics fBm over Perlin        */
+    VR_DENSITY_FBM = 2,            /* in-kernel FastNoise2-semantics fBm over Perlin        */
+    VR_DENSITY_TREE = 3            /* a compiled FastNoise2 node tree, evaluated per sample */
 } vr_density_mode;
 
 typedef enum vr_memory_kind {
@@ -213,6 +214,13 @@ typedef struct vr_params {
      * view_count 0/1 with view_ubos NULL = the single view above */
     uint32_t view_count;
     const void* view_ubos;
+    /* VR_DENSITY_TREE: rho(P) = max(0, tree(P * tree_frequency; tree_seed)) * edge(P), P in texture
+     * coordinates, edge = the fbm_falloff0/1 fade above.  The program is copied at vr_set_params; the
+     * handle may be freed afterwards.  A caller built against the struct without these three fields
+     * (struct_size = offset of density_tree) is accepted for every other mode. */
+    const vr_noise_tree* density_tree;
+    float tree_frequency;
+    int32_t tree_seed;
 } vr_params;
 
 /* replaces EnqueueRenderPass + BeginFrame/EndFrame -> vkCmdDrawIndexed + submit:

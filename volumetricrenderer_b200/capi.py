@@ -19,7 +19,7 @@ OUT_RGBA8_UNORM, OUT_RGBA8_SRGB, OUT_RGBA16F, OUT_RGBA32F = 0, 1, 2, 3
 VOL_RGBA8_UNORM, VOL_R16F, VOL_R8_UNORM = 0, 1, 2
 ADDRESS_MIRRORED_REPEAT, ADDRESS_CLAMP_TO_EDGE = 0, 1
 LAYOUT_AUTO, LAYOUT_TEXTURE, LAYOUT_LINEAR, LAYOUT_BRICK = 0, 1, 2, 3
-DENSITY_RGBA_PRODUCT, DENSITY_SINGLE, DENSITY_FBM = 0, 1, 2
+DENSITY_RGBA_PRODUCT, DENSITY_SINGLE, DENSITY_FBM, DENSITY_TREE = 0, 1, 2, 3
 MEM_NONE, MEM_HOST, MEM_DEVICE = 0, 1, 2
 RENDER_ASYNC, RENDER_DIRECT, RENDER_STATS, RENDER_NO_MARCH = 1, 2, 4, 8
 NOISE_CELLULAR_DISTANCE, NOISE_PERLIN, NOISE_SIMPLEX, NOISE_ZERO, NOISE_SAME = 0, 1, 2, 3, 0xFFFFFFFF
@@ -68,6 +68,7 @@ class vr_params(C.Structure):
         ("fbm_seed", C.c_int32), ("fbm_frequency", C.c_float), ("fbm_gain", C.c_float),
         ("fbm_lacunarity", C.c_float), ("fbm_coverage", C.c_float), ("fbm_falloff0", C.c_float),
         ("fbm_falloff1", C.c_float), ("view_count", C.c_uint32), ("view_ubos", C.c_void_p),
+        ("density_tree", C.c_void_p), ("tree_frequency", C.c_float), ("tree_seed", C.c_int32),
     ]
 
 

@@ -17,6 +17,7 @@
 // the TEX variants use the texture unit's fixed-point trilinear weights and FMA contraction.
 #include "volrt_internal.h"
 #include "noise_device.cuh"
+#include "noise_tree_eval.cuh"
 #include <math_constants.h>
 #include <cuda.h>          // CUtensorMap (type only; the encoder is fetched at run time in volrt_api.cu)
 #include <cstring>
@@ -240,6 +241,13 @@ __device__ __forceinline__ float density_at(const MarchParams& P, const RayConst
         return tex3D<float>(P.tex, p.x, p.y, p.z) * P.sample_scale;
     } else if (VARIANT == MARCH_SINGLE_LINEAR) {
         return mul(sample_single_linear(P, unorm, p), P.sample_scale);
+    } else if (VARIANT == MARCH_TREE) {
+        // the same box-edge fade as the fBm field, around whatever the tree computes; the program is warp-uniform
+        const float m = fmaxf(fmaxf(fabsf(p.x - 0.5f), fabsf(p.y - 0.5f)), fabsf(p.z - 0.5f));
+        const float t = __saturatef((m - P.fbm.falloff0) * P.fbm.inv_falloff);
+        const float edge = 1.0f - t * t * (3.0f - 2.0f * t);
+        if (edge <= 0.0f) return 0.0f;
+        return fmaxf(0.0f, tree_eval(P.tree_prog, P.tree_n, P.tree_result, lut, P.tree_seed, p.x * P.tree_freq, p.y * P.tree_freq, p.z * P.tree_freq)) * edge;
     } else {
         return density_fbm(lut, P.fbm, p.x, p.y, p.z);
     }
@@ -458,8 +466,8 @@ template <int VARIANT>
 __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     if (LINEAR) for (int i = threadIdx.x; i < 256; i += blockDim.x) unorm[i] = dvd((float)i, 255.0f);
-    if (VARIANT == MARCH_FBM) grad_lut_init(lut, threadIdx.x);
-    if (LINEAR || VARIANT == MARCH_FBM) __syncthreads();
+    if (VARIANT == MARCH_FBM || VARIANT == MARCH_TREE) grad_lut_init(lut, threadIdx.x);
+    if (LINEAR || VARIANT == MARCH_FBM || VARIANT == MARCH_TREE) __syncthreads();
 }
 
 // (a) direct mapping: one CTA of 4 warps per 16x8-pixel tile, a warp per 8x4 sub-tile.  Used where a step
@@ -894,22 +902,24 @@ __global__ void __launch_bounds__(256) row_cost_kernel(const __grid_constant__ M
 
 template <int VARIANT, bool COMPOSITE, bool STATS>
 static cudaError_t launch_one(const MarchParams& p, dim3 grid, bool persistent, cudaStream_t s) {
-    if (persistent) {
-        // resident CTAs per SM x SM count, from the occupancy calculator (registers decide)
-        static int resident = 0;       // per instantiation
-        if (resident == 0) {
-            int dev = 0, sms = 0, per_sm = 0;
-            cudaGetDevice(&dev);
-            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, march_kernel_persistent<VARIANT, COMPOSITE, STATS>, 128, 0);
-            resident = sms * (per_sm > 0 ? per_sm : 1);
+    if constexpr (VARIANT != MARCH_TREE) {      // a tree sample is hundreds of instructions: no queue variant is built for it
+        if (persistent) {
+            // resident CTAs per SM x SM count, from the occupancy calculator (registers decide)
+            static int resident = 0;       // per instantiation
+            if (resident == 0) {
+                int dev = 0, sms = 0, per_sm = 0;
+                cudaGetDevice(&dev);
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, march_kernel_persistent<VARIANT, COMPOSITE, STATS>, 128, 0);
+                resident = sms * (per_sm > 0 ? per_sm : 1);
+            }
+            const long long tiles = (long long)((p.width + 7) / 8) * ((p.row_end - p.row_begin + 3) / 4) * p.n_views;
+            const long long want = (tiles + 3) / 4;
+            march_kernel_persistent<VARIANT, COMPOSITE, STATS><<<(unsigned)(want < resident ? want : resident), 128, 0, s>>>(p);
+            return cudaGetLastError();
         }
-        const long long tiles = (long long)((p.width + 7) / 8) * ((p.row_end - p.row_begin + 3) / 4) * p.n_views;
-        const long long want = (tiles + 3) / 4;
-        march_kernel_persistent<VARIANT, COMPOSITE, STATS><<<(unsigned)(want < resident ? want : resident), 128, 0, s>>>(p);
-    } else {
-        march_kernel<VARIANT, COMPOSITE, STATS><<<grid, 128, 0, s>>>(p);
     }
+    march_kernel<VARIANT, COMPOSITE, STATS><<<grid, 128, 0, s>>>(p);
     return cudaGetLastError();
 }
 
@@ -948,6 +958,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
                 case MARCH_SINGLE_TEX: return launch_composite_split<MARCH_SINGLE_TEX>(p, split, rows, n_views, stream);
                 case MARCH_SINGLE_LINEAR: return launch_composite_split<MARCH_SINGLE_LINEAR>(p, split, rows, n_views, stream);
                 case MARCH_FBM: return launch_composite_split<MARCH_FBM>(p, split, rows, n_views, stream);
+                case MARCH_TREE: return launch_composite_split<MARCH_TREE>(p, split, rows, n_views, stream);
             }
         }
     }
@@ -973,6 +984,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
         case MARCH_SINGLE_TEX: return launch_v<MARCH_SINGLE_TEX>(p, grid, composite, stats, persistent, stream);
         case MARCH_SINGLE_LINEAR: return launch_v<MARCH_SINGLE_LINEAR>(p, grid, composite, stats, persistent, stream);
         case MARCH_FBM: return launch_v<MARCH_FBM>(p, grid, composite, stats, persistent, stream);
+        case MARCH_TREE: return launch_v<MARCH_TREE>(p, grid, composite, stats, false, stream);
     }
     return cudaErrorInvalidValue;
 }

@@ -8,11 +8,13 @@
 // Device: one thread per grid point interprets that program; every thread runs the same instruction, so the
 // switch is warp-uniform.  Generators: noise_device.cuh / noise_nodes.cuh.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
 
 #include "noise_nodes.cuh"
+#include "noise_tree_eval.cuh"
 
 namespace volrt {
 
@@ -150,6 +152,7 @@ struct Compiler {
     const Tree& t;
     std::vector<TreeInstr> prog;
     int n_values = 0, n_positions = 1;              // P[0] is the input position
+    bool fuse = std::getenv("VOLRT_TREE_NO_FUSE") == nullptr;      // the unfused form stays reachable for tests
 
     int new_value() {
         if (n_values >= kTreeMaxValues) throw std::runtime_error("tree needs more than 64 value registers (octaves are unrolled)");
@@ -331,6 +334,20 @@ struct Compiler {
         const int octaves = n.vars[0];
         const float lac = n.varf(1);
         if (octaves < 1 || octaves > 16) unsupported(n, "octaves must be in 1..16");
+        // the usual case — constant gain and weighted strength over Value / Perlin / Simplex / OpenSimplex2 — is one
+        // instruction that loops over the octaves in registers (noise_tree_eval.cuh)
+        const Node& src = t.nodes[n.lookups[0]];
+        const bool leaf = src.id >= 6 && src.id <= 9;
+        const bool constants = n.hybrids[0].node < 0 && n.hybrids[1].node < 0 && (n.id != 14 || n.hybrids[2].node < 0);
+        if (fuse && leaf && constants) {
+            static const TreeOp gen[4] = {T_VALUE, T_PERLIN, T_SIMPLEX, T_OPENSIMPLEX2};
+            const int r = new_value();
+            TreeInstr& in = push(T_FRACTAL_LEAF, r, pos, so);
+            in.i0 = gen[src.id - 6]; in.i1 = octaves; in.i2 = n.id == 13 ? 0 : n.id == 15 ? 1 : 2;
+            in.f[0] = fractal_bounding(octaves, n.hybrids[0].value); in.f[1] = lac; in.f[2] = n.hybrids[0].value;
+            in.f[3] = n.hybrids[1].value; in.f[4] = n.id == 14 ? n.hybrids[2].value : 0.0f;
+            return r;
+        }
         const int gain = hybrid(n.hybrids[0], pos, so), ws = hybrid(n.hybrids[1], pos, so);
         const int strength = n.id == 14 ? hybrid(n.hybrids[2], pos, so) : 0;
         // bounding uses the constant part of the gain (1 when the gain is a generator, Fractal.h:12,27-38)
@@ -391,123 +408,6 @@ struct Compiler {
 
 }  // namespace
 
-// ------------------------------------------------------------------------------------------------ interpreter
-__device__ __forceinline__ float tree_eval(const TreeInstr* __restrict__ prog, int n_instr, int result_reg, int seed, float x, float y, float z) {
-    float V[kTreeMaxValues];
-    float P[kTreeMaxPositions][3];
-    P[0][0] = x; P[0][1] = y; P[0][2] = z;
-    for (int pc = 0; pc < n_instr; ++pc) {
-        const TreeInstr& in = prog[pc];
-        const int s = seed + in.seed_off;
-        const float px = P[in.pos][0], py = P[in.pos][1], pz = P[in.pos][2];
-        switch (in.op) {
-            case T_CONST: V[in.dst] = in.f[0]; break;
-            case T_WHITE: V[in.dst] = white3(s, px, py, pz); break;
-            case T_VALUE: V[in.dst] = value3(s, px, py, pz); break;
-            case T_PERLIN: V[in.dst] = perlin3(s, px, py, pz); break;
-            case T_SIMPLEX: V[in.dst] = simplex3(s, px, py, pz); break;
-            case T_OPENSIMPLEX2: V[in.dst] = opensimplex2_3(s, px, py, pz); break;
-            case T_SINE: V[in.dst] = (fs_sin(px * in.f[0]) * fs_sin(py * in.f[0])) * fs_sin(pz * in.f[0]); break;
-            case T_POSITION_OUTPUT: V[in.dst] = ((px + in.f[3]) * in.f[0] + (py + in.f[4]) * in.f[1]) + (pz + in.f[5]) * in.f[2]; break;
-            case T_DISTANCE_TO_POINT: V[in.dst] = calc_distance(in.i0, px - in.f[0], py - in.f[1], pz - in.f[2]); break;
-            case T_CELL_VALUE: V[in.dst] = cellular_value3(s, px, py, pz, V[in.a], in.i0, in.i1); break;
-            case T_CELL_DISTANCE:
-                // the node's defaults (what the reference's bake uses, TestMain.cpp:43) keep only the nearest squared distance
-                if (in.i0 == 1 && in.i1 == 0 && in.i3 == 0 && V[in.a] == 1.0f) V[in.dst] = cellular3(s, px, py, pz);
-                else V[in.dst] = cellular_distance3(s, px, py, pz, V[in.a], in.i0, in.i1, in.i2, in.i3);
-                break;
-            case T_CELL_LOOKUP_POS: {
-                float c[3];
-                cellular_lookup3(s, px, py, pz, V[in.a], in.i0, c);
-                P[in.dst][0] = c[0] * in.f[0]; P[in.dst][1] = c[1] * in.f[0]; P[in.dst][2] = c[2] * in.f[0];
-                break;
-            }
-            case T_ADD: V[in.dst] = V[in.a] + V[in.b]; break;
-            case T_SUB: V[in.dst] = V[in.a] - V[in.b]; break;
-            case T_MUL: V[in.dst] = V[in.a] * V[in.b]; break;
-            case T_DIV: V[in.dst] = V[in.a] / V[in.b]; break;
-            case T_MIN: V[in.dst] = fminf(V[in.a], V[in.b]); break;
-            case T_MAX: V[in.dst] = fmaxf(V[in.a], V[in.b]); break;
-            case T_MIN_SMOOTH: case T_MAX_SMOOTH: {                                      // Blends.inl (MinSmooth / MaxSmooth)
-                const float sg = in.op == T_MAX_SMOOTH ? -1.0f : 1.0f;
-                const float a = sg * V[in.a], b = sg * V[in.b];
-                const float sm = fmaxf(1.175494351e-38f, fabsf(V[in.c]));
-                float h = fmaxf(sm - fabsf(a - b), 0.0f);
-                h *= 1.0f / sm;
-                V[in.dst] = sg * fmaf(-(1.0f / 6.0f), h * h * h * sm, fminf(a, b));
-                break;
-            }
-            case T_FADE: { const float fd = fabsf(V[in.c]); V[in.dst] = fmaf(V[in.a], 1.0f - fd, V[in.b] * fd); break; }
-            case T_POW_FLOAT: V[in.dst] = fs_pow(V[in.a], V[in.b]); break;
-            case T_POW_INT: { const float v = V[in.a]; float p = v * v; for (int i = 2; i < in.i0; ++i) p *= v; V[in.dst] = p; break; }
-            case T_REMAP: V[in.dst] = in.f[3] + ((V[in.a] - in.f[0]) / in.f[1] * in.f[2]); break;
-            case T_TERRACE: {
-                const float src = V[in.a] * in.f[0];
-                float r = rintf(src);
-                if (in.f[1] != 0.0f) {
-                    float diff = r - src;
-                    const bool neg = diff < 0.0f;
-                    diff = fminf((0.5f - fabsf(diff)) * in.f[2], 0.5f);
-                    r += neg ? 0.5f - diff : diff - 0.5f;
-                }
-                V[in.dst] = r * in.f[3];
-                break;
-            }
-            case T_CONVERT_RGBA8: {
-                float v = fmaxf(fminf(V[in.a], in.f[1]), in.f[0]);
-                const int b = __float2int_rn((v - in.f[0]) * in.f[2]);
-                V[in.dst] = __int_as_float((int)(255u << 24) | b | (b << 8) | (b << 16));
-                break;
-            }
-            case T_COPY: V[in.dst] = V[in.a]; break;
-            // fractals (Fractal.inl): a = this octave's source value, b = amplitude register, c = gain, d = weighted strength,
-            // i0 = ping-pong strength register, i1 = the previous octave's source value
-            case T_FBM_FIRST: V[in.b] = in.f[0]; V[in.dst] = V[in.a] * in.f[0]; break;
-            case T_FBM_NEXT: {
-                float amp = V[in.b] * lerpf(1.0f, (V[in.i1] + 1.0f) * 0.5f, V[in.d]);
-                amp *= V[in.c];
-                V[in.b] = amp;
-                V[in.dst] = fmaf(V[in.a], amp, V[in.dst]);
-                break;
-            }
-            case T_RIDGED_FIRST: V[in.b] = in.f[0]; V[in.dst] = fmaf(fabsf(V[in.a]), -2.0f, 1.0f) * in.f[0]; break;
-            case T_RIDGED_NEXT: {
-                float amp = V[in.b] * lerpf(1.0f, 1.0f - fabsf(V[in.i1]), V[in.d]);
-                amp *= V[in.c];
-                V[in.b] = amp;
-                V[in.dst] = fmaf(fmaf(fabsf(V[in.a]), -2.0f, 1.0f), amp, V[in.dst]);
-                break;
-            }
-            case T_PINGPONG_FIRST: V[in.b] = in.f[0]; V[in.dst] = ping_pong((V[in.a] + 1.0f) * V[in.i0]) * in.f[0]; break;
-            case T_PINGPONG_NEXT: {
-                const float prev = ping_pong((V[in.i1] + 1.0f) * V[in.i0]);
-                float amp = V[in.b] * lerpf(1.0f, (prev + 1.0f) * 0.5f, V[in.d]);
-                amp *= V[in.c];
-                V[in.b] = amp;
-                V[in.dst] = fmaf(ping_pong((V[in.a] + 1.0f) * V[in.i0]), amp, V[in.dst]);
-                break;
-            }
-            case T_POS_COPY: P[in.dst][0] = px; P[in.dst][1] = py; P[in.dst][2] = pz; break;
-            case T_POS_SCALE: P[in.dst][0] = px * in.f[0]; P[in.dst][1] = py * in.f[0]; P[in.dst][2] = pz * in.f[0]; break;
-            case T_POS_AXIS_SCALE: P[in.dst][0] = px * in.f[0]; P[in.dst][1] = py * in.f[1]; P[in.dst][2] = pz * in.f[2]; break;
-            case T_POS_OFFSET: P[in.dst][0] = px + V[in.a]; P[in.dst][1] = py + V[in.b]; P[in.dst][2] = pz + V[in.c]; break;
-            case T_POS_ROTATE:
-                P[in.dst][0] = fmaf(px, in.f[0], fmaf(py, in.f[1], pz * in.f[2]));
-                P[in.dst][1] = fmaf(px, in.f[3], fmaf(py, in.f[4], pz * in.f[5]));
-                P[in.dst][2] = fmaf(px, in.f[6], fmaf(py, in.f[7], pz * in.f[8]));
-                break;
-            case T_POS_WARP: V[in.b] = warp_gradient3(s, V[in.a], px * in.f[0], py * in.f[0], pz * in.f[0], P[in.dst]); break;
-            case T_WARP_AMP_NEXT: {
-                float amp = V[in.dst] * lerpf(1.0f, 1.0f - V[in.a], V[in.b]);
-                V[in.dst] = amp * V[in.c];
-                break;
-            }
-            default: break;
-        }
-    }
-    return V[result_reg];
-}
-
 // the min/max fold of noise_kernels.cu, on order-preserving bits
 __device__ __forceinline__ unsigned int tree_ordered_bits(float f) {
     const unsigned int b = __float_as_uint(f);
@@ -518,11 +418,14 @@ __device__ __forceinline__ unsigned int tree_ordered_bits(float f) {
 __global__ void __launch_bounds__(128) tree_grid_kernel(const TreeInstr* __restrict__ prog, int n_instr, int result_reg, int x0, int y0, int z0,
                                                         int nx, int ny, int nz, float frequency, int seed, float* __restrict__ out,
                                                         unsigned int* __restrict__ minmax_bits) {
+    __shared__ GradLut lut;
+    grad_lut_init(&lut, threadIdx.x);
+    __syncthreads();
     const size_t total = (size_t)nx * ny * nz;
     float mn = CUDART_INF_F, mx = -CUDART_INF_F;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         const int ix = (int)(i % nx), iy = (int)((i / nx) % ny), iz = (int)(i / ((size_t)nx * ny));
-        const float v = tree_eval(prog, n_instr, result_reg, seed, __fmul_rn((float)(x0 + ix), frequency), __fmul_rn((float)(y0 + iy), frequency),
+        const float v = tree_eval(prog, n_instr, result_reg, &lut, seed, __fmul_rn((float)(x0 + ix), frequency), __fmul_rn((float)(y0 + iy), frequency),
                                   __fmul_rn((float)(z0 + iz), frequency));
         out[i] = v;
         mn = fminf(mn, v); mx = fmaxf(mx, v);

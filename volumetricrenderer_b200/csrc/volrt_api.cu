@@ -66,6 +66,8 @@ struct vr_context {
     static constexpr size_t kFileChunk = (size_t)16 << 20;
     unsigned char* file_stage[kFileRing] = {};
     cudaEvent_t file_done[kFileRing] = {};
+    TreeInstr* d_march_tree = nullptr;      // VR_DENSITY_TREE: the program the march interprets (copied at vr_set_params)
+    int march_tree_n = 0, march_tree_result = 0;
     TreeInstr* d_tree_prog = nullptr;       // vr_noise_tree_grid: program upload buffer and a grow-only output plane
     float* d_tree_out = nullptr;
     size_t tree_out_bytes = 0;
@@ -144,6 +146,7 @@ extern "C" vr_status vr_params_default(vr_params* p) {
     p->fbm_gain = 0.5f; p->fbm_lacunarity = 2.0f; p->fbm_coverage = 0.45f;
     p->fbm_falloff0 = 0.35f; p->fbm_falloff1 = 0.5f;
     p->view_count = 1;
+    p->tree_frequency = 1.0f; p->tree_seed = 1337;
     return VR_OK;
 }
 
@@ -241,6 +244,7 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->d_row_cost) cudaFree(c->d_row_cost);
     if (c->d_queue) cudaFree(c->d_queue);
     if (c->d_tree_prog) cudaFree(c->d_tree_prog);
+    if (c->d_march_tree) cudaFree(c->d_march_tree);
     if (c->d_tree_out) cudaFree(c->d_tree_out);
     for (int i = 0; i < vr_context::kFileRing; ++i) {
         if (c->file_stage[i]) cudaFreeHost(c->file_stage[i]);
@@ -826,10 +830,21 @@ static bool decode_view(const unsigned char* ubo0, uint32_t n0, const unsigned c
 
 extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
-    if (!p || p->struct_size < sizeof(vr_params)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: null or struct_size too small");
+    // a caller built before the VR_DENSITY_TREE fields were appended passes the shorter struct
+    if (!p || p->struct_size < offsetof(vr_params, density_tree)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: null or struct_size too small");
+    vr_params full;
+    if (p->struct_size < sizeof(vr_params)) {
+        std::memset(&full, 0, sizeof full);
+        std::memcpy(&full, p, offsetof(vr_params, density_tree));
+        p = &full;
+    }
     if (p->max_steps == 0 || p->max_steps > (1u << 20)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: max_steps out of range");
     if (!(p->step_scale > 0.0f)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: step_scale must be > 0");
-    if (p->density_mode > VR_DENSITY_FBM) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: unknown density_mode");
+    if (p->density_mode > VR_DENSITY_TREE) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: unknown density_mode");
+    if (p->density_mode == VR_DENSITY_TREE) {
+        if (!p->density_tree || p->density_tree->prog.empty()) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: VR_DENSITY_TREE needs density_tree (vr_noise_tree_compile)");
+        if (!(p->tree_frequency > 0.0f)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: tree_frequency must be > 0");
+    }
     if (p->density_mode == VR_DENSITY_FBM && (p->fbm_octaves < 1 || p->fbm_octaves > 16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: fbm_octaves must be in 1..16");
     if (p->light_steps > 0 && !(p->sigma_t > 0.0f)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: light_steps needs sigma_t > 0 (compositing mode)");
     if (p->light_steps > 1024) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: light_steps out of range");
@@ -857,8 +872,19 @@ extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
         c->params_pending = true;
         c->view0 = c->h_views[0];
     }
+    if (p->density_mode == VR_DENSITY_TREE) {
+        // the march reads its own copy of the program: the caller may free or recompile the handle right away
+        const vr_noise_tree* t = p->density_tree;
+        if (!c->d_march_tree) VR_CUDA(c, cudaMalloc(&c->d_march_tree, kTreeMaxInstr * sizeof(TreeInstr)));
+        if (c->foreign_stream_pending) { VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev1, 0)); c->foreign_stream_pending = false; }
+        VR_CUDA(c, cudaMemcpyAsync(c->d_march_tree, t->prog.data(), t->prog.size() * sizeof(TreeInstr), cudaMemcpyHostToDevice, c->stream));
+        VR_CUDA(c, cudaStreamSynchronize(c->stream));          // t->prog is pageable and the caller's
+        c->march_tree_n = (int)t->prog.size();
+        c->march_tree_result = t->result_reg;
+    }
     c->views_on_device = !(views == 1 && !p->view_ubos);
     c->params = *p;
+    c->params.density_tree = nullptr;
     c->params.ubo0 = c->params.ubo1 = c->params.view_ubos = nullptr;   // bytes were copied; do not keep caller pointers
     c->view_count = views;
     c->has_params = true;
@@ -890,6 +916,13 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.ray_split = c->ray_split;
     m.ray_split_composite = c->ray_split_composite;
     if (p.density_mode == VR_DENSITY_FBM) { variant = MARCH_FBM; return VR_OK; }
+    if (p.density_mode == VR_DENSITY_TREE) {
+        m.tree_prog = c->d_march_tree; m.tree_n = c->march_tree_n; m.tree_result = c->march_tree_result;
+        m.tree_seed = p.tree_seed; m.tree_freq = p.tree_frequency;
+        if (!(p.fbm_falloff1 > p.fbm_falloff0)) { m.fbm.falloff0 = 0.0f; m.fbm.inv_falloff = 0.0f; }   // no fade: edge == 1
+        variant = MARCH_TREE;
+        return VR_OK;
+    }
     if (!c->has_volume) return fail(c, VR_ERR_BAD_STATE, "vr_render: no volume uploaded (vr_upload_volume / vr_generate_volume)");
     const vr_volume_desc& d = c->vdesc;
     m.tex = c->tex; m.lin = c->lin;

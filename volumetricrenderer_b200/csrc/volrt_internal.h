@@ -34,6 +34,7 @@ struct BrickInfo {          // min-max grid for empty-space skipping (8^3 voxel 
 };
 
 // procedural density: FastNoise2 FractalFBm over Perlin, remapped
+struct TreeInstr;
 struct FbmField {
     int octaves, seed;
     float frequency, gain, lacunarity, coverage, falloff0, falloff1, bounding, threshold;
@@ -74,6 +75,10 @@ struct MarchParams {
     int skip_empty;
     BrickInfo bricks;
     FbmField fbm;
+    // VR_DENSITY_TREE: the compiled program (device copy owned by the context), evaluated at P * tree_freq
+    const TreeInstr* tree_prog;
+    int tree_n, tree_result, tree_seed;
+    float tree_freq;
     // device counters (VR_RENDER_STATS): covered, steps, early, light samples, skipped
     unsigned long long* counters;
 };
@@ -84,7 +89,8 @@ enum MarchVariant {
     MARCH_SINGLE_TEX = 2,    // one-channel grid through the texture unit
     MARCH_SINGLE_LINEAR = 3,
     MARCH_FBM = 4,           // procedural density
-    MARCH_SINGLE_BRICK = 5   // one-channel fp16 grid, boxes staged to shared memory by TMA
+    MARCH_SINGLE_BRICK = 5,  // one-channel fp16 grid, boxes staged to shared memory by TMA
+    MARCH_TREE = 6           // procedural density from a compiled FastNoise2 node tree (noise_tree_eval.cuh)
 };
 
 // launches one march over rows [row_begin,row_end) x views; returns cudaGetLastError()
@@ -130,6 +136,7 @@ enum TreeOp : uint16_t {
     T_CONVERT_RGBA8, T_COPY,
     T_FBM_FIRST, T_FBM_NEXT, T_RIDGED_FIRST, T_RIDGED_NEXT, T_PINGPONG_FIRST, T_PINGPONG_NEXT,
     T_POS_COPY, T_POS_SCALE, T_POS_AXIS_SCALE, T_POS_OFFSET, T_POS_ROTATE, T_POS_WARP, T_WARP_AMP_NEXT,
+    T_FRACTAL_LEAF,
     T_OP_COUNT
 };
 struct TreeInstr {

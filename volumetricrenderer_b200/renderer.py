@@ -194,6 +194,10 @@ class Renderer:
                 raise ValueError("view_ubos must be uint8[count, 336]")
             p.view_ubos, p.view_count = bv.ctypes.data, bv.shape[0]
             keep.append(bv)
+        tree = kw.get("density_tree")
+        if tree is not None and hasattr(tree, "handle"):        # a noisetree.CompiledTree: pass its handle
+            kw = dict(kw, density_tree=tree.handle)
+            kw.setdefault("density_mode", capi.DENSITY_TREE)
         for k, v in kw.items():
             cur = getattr(p, k)
             if hasattr(cur, "__len__"):
