@@ -55,7 +55,10 @@ def test_known_encoded_string():
     # the FastNoise2 wiki's example shape: FractalFBm(5 octaves, lacunarity 2, gain 0.5, weighted strength 0) over a coherent source
     enc = N("FractalFBm", Octaves=5, Source=N("Simplex")).encode()
     assert enc == "DQAFAAAAAAAAQAgAAAAAAD8AAAAAAA=="
-    assert CompiledTree(enc).info() == {"nodes": 2, "instructions": 17, "value_regs": 9, "position_regs": 2}
+    # constant gain over a lattice generator: one looping instruction; with a gain that is itself a node, one per octave step
+    assert CompiledTree(enc).info() == {"nodes": 2, "instructions": 1, "value_regs": 1, "position_regs": 1}
+    unrolled = CompiledTree(N("FractalFBm", Octaves=5, Source=N("Simplex"), Gain=N("Constant", Value=0.5)).encode()).info()
+    assert unrolled["nodes"] == 3 and unrolled["instructions"] == 17 and unrolled["position_regs"] == 2
 
 
 def test_fixture_strings_are_what_the_encoder_writes_and_compile():
@@ -79,8 +82,11 @@ def test_malformed_streams_are_rejected():
     with pytest.raises(ValueError):
         CompiledTree("not base64 !!")
     with pytest.raises(ValueError) as e:                       # unrolled octaves overflow the register file: refused, not truncated
-        CompiledTree(N("FractalFBm", Octaves=16, Source=N("FractalFBm", Octaves=16, Source=N("Perlin"))).encode())
+        g = N("Constant", Value=0.5)                            # a gain that is a node keeps the inner fractal unrolled too
+        CompiledTree(N("FractalFBm", Octaves=16, Source=N("FractalFBm", Octaves=16, Gain=g, Source=N("Perlin"))).encode())
     assert "VR_ERR_UNSUPPORTED" in str(e.value)
+    # with constant gains the inner fractal is one looping instruction and the same nesting fits
+    assert CompiledTree(N("FractalFBm", Octaves=16, Source=N("FractalFBm", Octaves=16, Source=N("Perlin"))).encode()).info()["instructions"] < 64
     with pytest.raises(KeyError):
         N("Perlin", Frequency=2.0)
     with pytest.raises(ValueError):
