@@ -249,7 +249,7 @@ __device__ __forceinline__ float density_at(const MarchParams& P, const RayConst
         if (edge <= 0.0f) return 0.0f;
         return fmaxf(0.0f, tree_eval(P.tree_prog, P.tree_n, P.tree_result, lut, P.tree_seed, p.x * P.tree_freq, p.y * P.tree_freq, p.z * P.tree_freq)) * edge;
     } else {
-        return density_fbm(lut, P.fbm, p.x, p.y, p.z);
+        return density_fbm(GradLutFixed{}, P.fbm, p.x, p.y, p.z);     // the table's place is checked by stage_tables()
     }
 }
 
@@ -292,6 +292,43 @@ __device__ __forceinline__ int leap_steps(const Leap& L, int d, int left) {     
 }
 __device__ __forceinline__ bool inside01(f3 p) {
     return p.x >= 0.0f && p.x <= 1.0f && p.y >= 0.0f && p.y <= 1.0f && p.z >= 0.0f && p.z <= 1.0f;
+}
+
+// Sum of the densities along the sun light-march from p: samples at p + j*lv, j = 1..light_steps, until
+// the march leaves the box (convex, so for good).  The fBm field takes the samples two at a time on the packed FP32
+// instructions (noise_device.cuh: density_fbm2, same operations per point, same order of the sum).
+#ifndef VOLRT_FBM_PAIRS
+#define VOLRT_FBM_PAIRS 1
+#endif
+template <int VARIANT>
+__device__ __forceinline__ float light_sum(const MarchParams& P, const RayConst& rc, const float* __restrict__ unorm,
+                                           const GradLut* lut, f3 p, f3 lv, bool skip) {
+    float sumL = 0.0f;
+    f3 pl = p;
+    if constexpr (VARIANT == MARCH_FBM && VOLRT_FBM_PAIRS) {
+        for (int j = 1; j <= P.light_steps; j += 2) {
+            const f3 pa = {pl.x + lv.x, pl.y + lv.y, pl.z + lv.z};
+            if (!inside01(pa)) break;
+            const f3 pb = {pa.x + lv.x, pa.y + lv.y, pa.z + lv.z};
+            if (j < P.light_steps && inside01(pb)) {
+                const f2 r = density_fbm2(GradLutFixed{}, P.fbm, make_f2(pa.x, pb.x), make_f2(pa.y, pb.y), make_f2(pa.z, pb.z));
+                sumL += f2_a(r);
+                sumL += f2_b(r);
+            } else {
+                sumL += density_fbm(GradLutFixed{}, P.fbm, pa.x, pa.y, pa.z);
+                break;
+            }
+            pl = pb;
+        }
+    } else {
+        for (int j = 1; j <= P.light_steps; ++j) {
+            pl = {pl.x + lv.x, pl.y + lv.y, pl.z + lv.z};
+            if (!inside01(pl)) break;
+            if (skip && !brick_occupied(P, pl)) continue;
+            sumL += density_at<VARIANT>(P, rc, unorm, lut, pl);
+        }
+    }
+    return sumL;
 }
 
 // ------------------------------------------------------------------ the march
@@ -395,7 +432,9 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
             if (rho > 0.0f) {                       // rho == 0 contributes exactly nothing
                 float a = 1.0f - expf(-P.sigma_t * rho * step_size);
                 float S = 1.0f;
-                if (P.light_steps > 0) {
+                if (!STATS && P.light_steps > 0) {
+                    S = expf(-P.sigma_t * light_sum<VARIANT>(P, rc, unorm, &lut, p, lv, skip) * P.light_step_len);
+                } else if (P.light_steps > 0) {
                     float sumL = 0.0f;
                     f3 pl = p;
                     for (int j = 1; j <= P.light_steps; ++j) {
@@ -462,10 +501,21 @@ __device__ __forceinline__ void tile_of_cta(const MarchParams& P, int tile_h, in
     ty = outward_from(ky, gy, cy);
 }
 
+// static shared memory of the march kernels: the gradient table first, so that it starts the CTA's shared window
+template <bool LINEAR>
+struct __align__(256) MarchSmem {
+    GradLut lut;                       // FBM / TREE variants
+    float unorm[LINEAR ? 256 : 1];     // LINEAR variants: i / 255
+};
+
 template <int VARIANT>
 __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     if (LINEAR) for (int i = threadIdx.x; i < 256; i += blockDim.x) unorm[i] = dvd((float)i, 255.0f);
+    if (VARIANT == MARCH_FBM) {
+        // the fBm march fetches gradients at an immediate shared address (noise_device.cuh: GradLutFixed)
+        if ((unsigned)__cvta_generic_to_shared(lut) != (unsigned)VOLRT_LUT_FIXED_ADDR) __trap();
+    }
     if (VARIANT == MARCH_FBM || VARIANT == MARCH_TREE) grad_lut_init(lut, threadIdx.x);
     if (LINEAR || VARIANT == MARCH_FBM || VARIANT == MARCH_TREE) __syncthreads();
 }
@@ -475,17 +525,25 @@ __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
 // Tile order: CTAs are dispatched in blockIdx order, so visit tile rows and columns from the screen centre
 // outwards — the object sits around the centre (the reference camera looks at the origin,
 // TestMain.cpp:225), which makes the last CTAs silhouette-edge and empty tiles (a short tail).
+#ifndef VOLRT_CTA_WX
+#define VOLRT_CTA_WX 2          // warps per CTA along x (8 pixels each)
+#endif
+#ifndef VOLRT_CTA_WY
+#define VOLRT_CTA_WY 2          // warps per CTA along y (4 pixels each)
+#endif
+constexpr int kCtaWx = VOLRT_CTA_WX, kCtaWy = VOLRT_CTA_WY, kCtaThreads = 32 * kCtaWx * kCtaWy;
 template <int VARIANT, bool COMPOSITE, bool STATS>
-__global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ MarchParams P) {
+__global__ void __launch_bounds__(kCtaThreads) march_kernel(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
-    __shared__ float unorm[LINEAR ? 256 : 1];
-    __shared__ GradLut lut;                               // used by the FBM variant only
+    __shared__ MarchSmem<LINEAR> smem;
+    float* const unorm = smem.unorm;
+    GradLut& lut = smem.lut;
     stage_tables<VARIANT>(unorm, &lut);
     int tx, ty;
-    tile_of_cta(P, 8, tx, ty);
+    tile_of_cta(P, 4 * kCtaWy, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
-    const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const int px = tx * (8 * kCtaWx) + (warp % kCtaWx) * 8 + (lane & 7);
+    const int py = P.row_begin + ty * (4 * kCtaWy) + (warp / kCtaWx) * 4 + (lane >> 3);
     const int view = P.view_begin + blockIdx.z;
     if (px >= P.width || py >= P.row_end) return;
     march_pixel<VARIANT, COMPOSITE, STATS>(P, unorm, lut, px, py, view);
@@ -503,8 +561,9 @@ __global__ void __launch_bounds__(128) march_kernel(const __grid_constant__ Marc
 template <int VARIANT, bool COMPOSITE, bool STATS>
 __global__ void __launch_bounds__(128, VOLRT_PERSISTENT_MIN_CTAS) march_kernel_persistent(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
-    __shared__ float unorm[LINEAR ? 256 : 1];
-    __shared__ GradLut lut;
+    __shared__ MarchSmem<LINEAR> smem;
+    float* const unorm = smem.unorm;
+    GradLut& lut = smem.lut;
     stage_tables<VARIANT>(unorm, &lut);
     const int lane = threadIdx.x & 31;
     const int tiles_x = (P.width + 7) >> 3, tiles_y = (P.row_end - P.row_begin + 3) >> 2;
@@ -607,15 +666,16 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
 // light-march branch stays coherent.  The sum and the products are re-associated and positions are
 // Pin + i*stepVec: parity is tolerance-based (as it already is for every compositing variant).
 #ifndef VOLRT_SPLIT_MIN_CTAS
-#define VOLRT_SPLIT_MIN_CTAS 7
+#define VOLRT_SPLIT_MIN_CTAS 5      // 96 registers: the two-point fBm light-march spills at 72 (7 CTAs/SM) — measured 4/5/6/7
 #endif
 template <int VARIANT, int S>
 __global__ void __launch_bounds__(128, VOLRT_SPLIT_MIN_CTAS) march_composite_split_kernel(const __grid_constant__ MarchParams P) {
     constexpr int RAYS = 32 / S, RW = RAYS / 2;
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
-    __shared__ float unorm[LINEAR ? 256 : 1];
-    __shared__ GradLut lut;
+    __shared__ MarchSmem<LINEAR> smem;
+    float* const unorm = smem.unorm;
+    GradLut& lut = smem.lut;
     stage_tables<VARIANT>(unorm, &lut);
     int tx, ty;
     tile_of_cta(P, 4, tx, ty);
@@ -656,17 +716,7 @@ __global__ void __launch_bounds__(128, VOLRT_SPLIT_MIN_CTAS) march_composite_spl
             if (!(skip && !brick_occupied(P, p))) rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
             if (rho > 0.0f) {
                 a = 1.0f - expf(-P.sigma_t * rho * step_size);
-                if (P.light_steps > 0) {
-                    float sumL = 0.0f;
-                    f3 pl = p;
-                    for (int j = 1; j <= P.light_steps; ++j) {
-                        pl = {pl.x + lv.x, pl.y + lv.y, pl.z + lv.z};
-                        if (!inside01(pl)) break;
-                        if (skip && !brick_occupied(P, pl)) continue;
-                        sumL += density_at<VARIANT>(P, rc, unorm, &lut, pl);
-                    }
-                    Sl = expf(-P.sigma_t * sumL * P.light_step_len);
-                }
+                if (P.light_steps > 0) Sl = expf(-P.sigma_t * light_sum<VARIANT>(P, rc, unorm, &lut, p, lv, skip) * P.light_step_len);
             }
         }
         // inclusive prefix product of (1 - a) over the S lanes of the ray
@@ -874,7 +924,7 @@ cudaError_t launch_march_brick(const MarchParams& p_in, const void* tensor_map, 
     }
     CUtensorMap tm;
     memcpy(&tm, tensor_map, sizeof tm);
-    dim3 grid((p.width + 15) / 16, (rows + 7) / 8, n_views);
+    dim3 grid((p.width + 8 * kCtaWx - 1) / (8 * kCtaWx), (rows + 4 * kCtaWy - 1) / (4 * kCtaWy), n_views);
     march_brick_kernel<<<grid, 128, BRICK_BYTES, stream>>>(p, tm);
     return cudaGetLastError();
 }
@@ -919,7 +969,7 @@ static cudaError_t launch_one(const MarchParams& p, dim3 grid, bool persistent, 
             return cudaGetLastError();
         }
     }
-    march_kernel<VARIANT, COMPOSITE, STATS><<<grid, 128, 0, s>>>(p);
+    march_kernel<VARIANT, COMPOSITE, STATS><<<grid, kCtaThreads, 0, s>>>(p);
     return cudaGetLastError();
 }
 
@@ -934,7 +984,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     if (rows <= 0 || n_views <= 0) return cudaSuccess;
     MarchParams p = p_in;
     p.n_views = n_views;
-    dim3 grid((p.width + 15) / 16, (rows + 7) / 8, n_views);
+    dim3 grid((p.width + 8 * kCtaWx - 1) / (8 * kCtaWx), (rows + 4 * kCtaWy - 1) / (4 * kCtaWy), n_views);
     bool composite = p.sigma_t > 0.0f;
     // schedule: 0 = direct tiles, 1 = persistent warps, -1 = auto
     bool persistent = p.schedule > 0;    // auto = direct: the queue did not pay off on B200 (measurements)
@@ -945,11 +995,12 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
         int split = p.ray_split_composite;
         if (split < 0) {
             // auto: by how many waves of the machine the covered rays (about a quarter of the pixels) make.
-            // Measured on B200 (fBm, ms/frame): 1080p one GPU 2.13 / 2.03 / 2.14 / 2.52 for 1/2/4/8 lanes;
-            // half of it (2-GPU band) 1.70 / 1.35 / 1.25 / 1.41; 4K one GPU 19.5 (1 lane) vs 20.6 (4 lanes).
+            // Measured on B200 with the two-point fBm light-march (ms, 1 / 2 / 4 lanes per ray): 1080p frame (3.4 waves)
+            // 1.776 / 1.799 / 1.99; its half (1.7 waves) 0.97 / 0.935 / 1.0; its quarter 0.68 / 0.51 / 0.52; its eighth
+            // 0.48 / 0.33 / 0.28; 4K frame 17.0 / 17.4 / -; its eighth (1.7 waves) 2.44 / 2.26 / -.
             const double warps = (double)p.width * rows * n_views * 0.25 / 32.0;
             const double waves = warps / (148.0 * 32.0);
-            split = waves >= 10.0 ? 1 : waves >= 2.5 ? 2 : 4;
+            split = waves >= 3.0 ? 1 : waves >= 0.8 ? 2 : 4;
         }
         if (split == 2 || split == 4 || split == 8) {
             switch (variant) {

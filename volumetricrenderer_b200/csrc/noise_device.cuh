@@ -78,10 +78,28 @@ __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
     }
 }
 
-__device__ __forceinline__ float4 grad_lut_fetch(const GradLut* lut, int t) {
+// A table the kernel guarantees to sit at shared-window address kLutFixedAddr (the first static __shared__ object of a
+// non-cluster launch on sm_100a: the window starts with 1 KiB the system keeps).  The table base then is an immediate
+// of the LDS and the per-corner address add disappears.  ptxas used to find that form itself (LDS [R + UR]), but in the
+// two-point march kernel it demotes the base to a vector register and spends one IADD3 per fetch (16 of 214 per octave
+// pair).  stage_tables() traps if the table is anywhere else, so a toolchain that lays shared memory out differently
+// fails loudly instead of reading garbage.
+#ifndef VOLRT_LUT_FIXED_ADDR
+#define VOLRT_LUT_FIXED_ADDR 1024
+#endif
+struct GradLutFixed {};     // tag type: "the table is at VOLRT_LUT_FIXED_ADDR"
+
+__device__ __forceinline__ unsigned int grad_lut_offset(int t) {
     const unsigned int h16 = (unsigned int)t * (0x27d4eb2du << 4);     // = h << 4 (mod 2^32)
-    const unsigned int off = (h16 ^ (h16 >> 15)) & 0xF0u;
-    return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
+    return (h16 ^ (h16 >> 15)) & 0xF0u;
+}
+__device__ __forceinline__ float4 grad_lut_fetch(const GradLut* lut, int t) {
+    return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + grad_lut_offset(t));
+}
+__device__ __forceinline__ float4 grad_lut_fetch(GradLutFixed, int t) {
+    float4 g;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4 + %5];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(grad_lut_offset(t)), "n"(VOLRT_LUT_FIXED_ADDR));
+    return g;
 }
 __device__ __forceinline__ float grad_dot_lut(const GradLut* lut, int t, float fx, float fy, float fz) {
     const float4 g = grad_lut_fetch(lut, t);
@@ -90,14 +108,16 @@ __device__ __forceinline__ float grad_dot_lut(const GradLut* lut, int t, float f
 // lerp(d0, d1, s) over the two corners of an x edge, with d1 - d0 accumulated directly into the second dot product:
 // 7 instructions instead of 8 (the difference is re-associated by a few ulp; FastNoise2's own SIMD levels contract
 // and re-associate the same expression differently among themselves)
-__device__ __forceinline__ float grad_edge_lut(const GradLut* lut, int t0, int t1, float fx0, float fx1, float fy, float fz, float s) {
+template <class LUT>
+__device__ __forceinline__ float grad_edge_lut(LUT lut, int t0, int t1, float fx0, float fx1, float fy, float fz, float s) {
     const float4 g0 = grad_lut_fetch(lut, t0), g1 = grad_lut_fetch(lut, t1);
     const float d0 = fmaf(fz, g0.z, fmaf(fy, g0.y, fx0 * g0.x));
     const float e = fmaf(fz, g1.z, fmaf(fy, g1.y, fmaf(fx1, g1.x, -d0)));
     return fmaf(s, e, d0);
 }
 
-__device__ __forceinline__ float perlin3_lut(const GradLut* lut, int seed, float x, float y, float z) {
+template <class LUT>
+__device__ __forceinline__ float perlin3_lut(LUT lut, int seed, float x, float y, float z) {
     float xs = floorf(x), ys = floorf(y), zs = floorf(z);
     int x0 = __float2int_rn(xs) * kPrimeX, y0 = __float2int_rn(ys) * kPrimeY, z0 = __float2int_rn(zs) * kPrimeZ;
     int x1 = x0 + kPrimeX, y1 = y0 + kPrimeY, z1 = z0 + kPrimeZ;
@@ -194,7 +214,8 @@ __device__ __forceinline__ float cellular3(int seed, float x, float y, float z) 
     return best;
 }
 
-__device__ __forceinline__ float fbm_perlin(const GradLut* lut, const FbmField& F, float x, float y, float z) {
+template <class LUT>
+__device__ __forceinline__ float fbm_perlin(LUT lut, const FbmField& F, float x, float y, float z) {
     int seed = F.seed;
     float amp = F.bounding * kPerlinScale;       // one multiply per fBm sample instead of one per octave
     float sum = perlin3_lut(lut, seed, x, y, z) * amp;
@@ -207,8 +228,121 @@ __device__ __forceinline__ float fbm_perlin(const GradLut* lut, const FbmField& 
     return sum;
 }
 
+// ---- two sample points per thread on sm_100a's packed FP32 (FFMA2 / FMUL2 / FADD2) ---------------------
+// The fBm march is issue-bound, not FMA-pipe bound (profiles/r01_march_fbm_lds128.txt: 88 % issue-active, FMA pipe
+// 51 %).  Blackwell's fma/mul/add.f32x2 do two IEEE binary32 operations per instruction on a 64-bit register pair at
+// the same FMA rate (tools/probes/ffma2_probe.cu: 126.6 FMA/clk/SM packed vs 123.7 scalar), i.e. half the issue
+// slots.  Evaluating the lattice arithmetic of TWO points (A, B = two consecutive samples of the sun light-march) in
+// the two halves packs everything that is not a hash, a table fetch or a gradient dot product (those read
+// per-point LDS results): position scaling, fractions, the quintic fades, all seven lerps and the octave
+// accumulation: 39 of ~117 instructions per octave and point become 20.  Each half performs exactly the operations
+// of perlin3_lut/fbm_perlin in the same order with the same roundings, so the result is bit-identical to them.
+struct f2 { unsigned long long v; };        // low half = point A, high half = point B, in one 64-bit register pair
+__device__ __forceinline__ f2 make_f2(float a, float b) {
+    f2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r.v) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float f2_a(f2 v) { float a; asm("{ .reg .b32 t; mov.b64 {%0, t}, %1; }" : "=f"(a) : "l"(v.v)); return a; }
+__device__ __forceinline__ float f2_b(f2 v) { float b; asm("{ .reg .b32 t; mov.b64 {t, %0}, %1; }" : "=f"(b) : "l"(v.v)); return b; }
+__device__ __forceinline__ f2 splat2(float s) { return make_f2(s, s); }
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    f2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d.v) : "l"(a.v), "l"(b.v), "l"(c.v));
+    return d;
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    f2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d.v) : "l"(a.v), "l"(b.v));
+    return d;
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+    f2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d.v) : "l"(a.v), "l"(b.v));
+    return d;
+}
+__device__ __forceinline__ f2 sub2(f2 a, f2 b) {
+    f2 d;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d.v) : "l"(a.v), "l"(b.v));
+    return d;
+}
+__device__ __forceinline__ f2 quintic2(f2 t) {        // t*t*t * fma(t, fma(t, 6, -15), 10), as quintic()
+    const f2 p = fma2(t, fma2(t, splat2(6.0f), splat2(-15.0f)), splat2(10.0f));
+    return mul2(mul2(mul2(t, t), t), p);
+}
+__device__ __forceinline__ f2 lerp2(f2 a, f2 b, f2 t) { return fma2(t, sub2(b, a), a); }
+
+// the two corners of an x edge for both points; returns lerp(d0, d1, s) per point like grad_edge_lut
+template <class LUT>
+__device__ __forceinline__ f2 grad_edge_lut2(LUT lut, int tA0, int tA1, int tB0, int tB1,
+                                             f2 fx0, f2 fx1, f2 fy, f2 fz, f2 s) {
+    const float4 a0 = grad_lut_fetch(lut, tA0), a1 = grad_lut_fetch(lut, tA1);
+    const float4 b0 = grad_lut_fetch(lut, tB0), b1 = grad_lut_fetch(lut, tB1);
+    const float fyA = f2_a(fy), fyB = f2_b(fy), fzA = f2_a(fz), fzB = f2_b(fz);
+    const float d0A = fmaf(fzA, a0.z, fmaf(fyA, a0.y, f2_a(fx0) * a0.x));
+    const float d0B = fmaf(fzB, b0.z, fmaf(fyB, b0.y, f2_b(fx0) * b0.x));
+    const float eA = fmaf(fzA, a1.z, fmaf(fyA, a1.y, fmaf(f2_a(fx1), a1.x, -d0A)));
+    const float eB = fmaf(fzB, b1.z, fmaf(fyB, b1.y, fmaf(f2_b(fx1), b1.x, -d0B)));
+    const f2 d0 = make_f2(d0A, d0B), e = make_f2(eA, eB);
+    return fma2(s, e, d0);
+}
+
+template <class LUT>
+__device__ __forceinline__ f2 perlin3_lut2(LUT lut, int seed, f2 x, f2 y, f2 z) {
+    const float xsA = floorf(f2_a(x)), xsB = floorf(f2_b(x)), ysA = floorf(f2_a(y)), ysB = floorf(f2_b(y)), zsA = floorf(f2_a(z)), zsB = floorf(f2_b(z));
+    f2 xs = make_f2(xsA, xsB), ys = make_f2(ysA, ysB), zs = make_f2(zsA, zsB);
+    const int ax0 = __float2int_rn(xsA) * kPrimeX, ay0 = __float2int_rn(ysA) * kPrimeY, az0 = __float2int_rn(zsA) * kPrimeZ;
+    const int bx0 = __float2int_rn(xsB) * kPrimeX, by0 = __float2int_rn(ysB) * kPrimeY, bz0 = __float2int_rn(zsB) * kPrimeZ;
+    const int ax1 = ax0 + kPrimeX, ay1 = ay0 + kPrimeY, az1 = az0 + kPrimeZ;
+    const int bx1 = bx0 + kPrimeX, by1 = by0 + kPrimeY, bz1 = bz0 + kPrimeZ;
+    const f2 xf0 = sub2(x, xs), yf0 = sub2(y, ys), zf0 = sub2(z, zs);
+    const f2 m1 = splat2(-1.0f);
+    const f2 xf1 = add2(xf0, m1), yf1 = add2(yf0, m1), zf1 = add2(zf0, m1);
+    xs = quintic2(xf0); ys = quintic2(yf0); zs = quintic2(zf0);
+    const int asz0 = seed ^ az0, asz1 = seed ^ az1, bsz0 = seed ^ bz0, bsz1 = seed ^ bz1;
+    const f2 a = lerp2(grad_edge_lut2(lut, asz0 ^ ax0 ^ ay0, asz0 ^ ax1 ^ ay0, bsz0 ^ bx0 ^ by0, bsz0 ^ bx1 ^ by0, xf0, xf1, yf0, zf0, xs),
+                       grad_edge_lut2(lut, asz0 ^ ax0 ^ ay1, asz0 ^ ax1 ^ ay1, bsz0 ^ bx0 ^ by1, bsz0 ^ bx1 ^ by1, xf0, xf1, yf1, zf0, xs), ys);
+    const f2 b = lerp2(grad_edge_lut2(lut, asz1 ^ ax0 ^ ay0, asz1 ^ ax1 ^ ay0, bsz1 ^ bx0 ^ by0, bsz1 ^ bx1 ^ by0, xf0, xf1, yf0, zf1, xs),
+                       grad_edge_lut2(lut, asz1 ^ ax0 ^ ay1, asz1 ^ ax1 ^ ay1, bsz1 ^ bx0 ^ by1, bsz1 ^ bx1 ^ by1, xf0, xf1, yf1, zf1, xs), ys);
+    return lerp2(a, b, zs);
+}
+
+template <class LUT>
+__device__ __forceinline__ f2 fbm_perlin2(LUT lut, const FbmField& F, f2 x, f2 y, f2 z) {
+    int seed = F.seed;
+    float amp = F.bounding * kPerlinScale;
+    const f2 lac = splat2(F.lacunarity);
+    f2 sum = mul2(perlin3_lut2(lut, seed, x, y, z), splat2(amp));
+    for (int i = 1; i < F.octaves; ++i) {
+        seed += 1;
+        amp *= F.gain;
+        x = mul2(x, lac); y = mul2(y, lac); z = mul2(z, lac);
+        sum = fma2(perlin3_lut2(lut, seed, x, y, z), splat2(amp), sum);
+    }
+    return sum;
+}
+
+__device__ __forceinline__ float fbm_edge(const FbmField& F, float ux, float uy, float uz) {
+    const float m = fmaxf(fmaxf(fabsf(ux - 0.5f), fabsf(uy - 0.5f)), fabsf(uz - 0.5f));
+    const float t = __saturatef((m - F.falloff0) * F.inv_falloff);
+    return 1.0f - t * t * (3.0f - 2.0f * t);
+}
+
+// density_fbm at two points; a point whose edge factor is <= 0 gets exactly 0 like the scalar early-out
+template <class LUT>
+__device__ __forceinline__ f2 density_fbm2(LUT lut, const FbmField& F, f2 ux, f2 uy, f2 uz) {
+    const float ea = fbm_edge(F, f2_a(ux), f2_a(uy), f2_a(uz)), eb = fbm_edge(F, f2_b(ux), f2_b(uy), f2_b(uz));
+    if (ea <= 0.0f && eb <= 0.0f) return make_f2(0.0f, 0.0f);
+    const f2 fr = splat2(F.frequency);
+    const f2 f = fbm_perlin2(lut, F, mul2(ux, fr), mul2(uy, fr), mul2(uz, fr));
+    const float fa = f2_a(f), fb = f2_b(f);
+    return make_f2(ea <= 0.0f ? 0.0f : fmaxf(0.0f, (0.5f * fa + 0.5f) - F.coverage) * ea,
+                   eb <= 0.0f ? 0.0f : fmaxf(0.0f, (0.5f * fb + 0.5f) - F.coverage) * eb);
+}
+
 // rho = max(0, .5 fbm + .5 - coverage) * (1 - smoothstep(f0, f1, maxabs(P - 1/2)))
-__device__ __forceinline__ float density_fbm(const GradLut* lut, const FbmField& F, float ux, float uy, float uz) {
+template <class LUT>
+__device__ __forceinline__ float density_fbm(LUT lut, const FbmField& F, float ux, float uy, float uz) {
     float m = fmaxf(fmaxf(fabsf(ux - 0.5f), fabsf(uy - 0.5f)), fabsf(uz - 0.5f));
     float t = __saturatef((m - F.falloff0) * F.inv_falloff);
     float edge = 1.0f - t * t * (3.0f - 2.0f * t);
