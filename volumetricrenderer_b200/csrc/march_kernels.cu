@@ -415,6 +415,15 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
         float T = 1.0f;
         cr = cg = cb = 0.0f;
         const f3 lv = {P.sun_dir[0] * P.light_step_len * 0.5f, P.sun_dir[1] * P.light_step_len * 0.5f, P.sun_dir[2] * P.light_step_len * 0.5f};
+        // fBm, optional: the densities of steps i and i+1 evaluated together on the packed FP32 instructions like the light
+        // samples, the second one waiting in rho_next for the next iteration.  Measured slower (C2 1.763 -> 1.781 ms, C3
+        // 17.18 -> 17.30): the value held across the light-march costs registers (126, 4 CTAs/SM).  Off by default.
+#ifndef VOLRT_FBM_PAIR_PRIMARY
+#define VOLRT_FBM_PAIR_PRIMARY 0
+#endif
+        constexpr bool PAIR_PRIMARY = (VARIANT == MARCH_FBM) && VOLRT_FBM_PAIRS && VOLRT_FBM_PAIR_PRIMARY && !STATS;
+        float rho_next = 0.0f;
+        bool have_next = false;
         for (int i = 0; i < n; ++i) {
             float rho = 0.0f;
             if (skip) {
@@ -428,7 +437,22 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
                     continue;           // transmittance unchanged: nothing to test for early termination
                 }
             }
-            rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
+            if constexpr (PAIR_PRIMARY) {
+                if (have_next) {
+                    rho = rho_next;
+                    have_next = false;
+                } else if (i + 1 < n) {
+                    const f3 q = add3(p, ray.step);
+                    const f2 r = density_fbm2(GradLutFixed{}, P.fbm, make_f2(p.x, q.x), make_f2(p.y, q.y), make_f2(p.z, q.z));
+                    rho = f2_a(r);
+                    rho_next = f2_b(r);
+                    have_next = true;
+                } else {
+                    rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
+                }
+            } else {
+                rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
+            }
             if (rho > 0.0f) {                       // rho == 0 contributes exactly nothing
                 float a = 1.0f - expf(-P.sigma_t * rho * step_size);
                 float S = 1.0f;
@@ -531,9 +555,12 @@ __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
 #ifndef VOLRT_CTA_WY
 #define VOLRT_CTA_WY 2          // warps per CTA along y (4 pixels each)
 #endif
+#ifndef VOLRT_DIRECT_MIN_CTAS
+#define VOLRT_DIRECT_MIN_CTAS 1     // register cap of the direct kernel (binds for the fBm variant only)
+#endif
 constexpr int kCtaWx = VOLRT_CTA_WX, kCtaWy = VOLRT_CTA_WY, kCtaThreads = 32 * kCtaWx * kCtaWy;
 template <int VARIANT, bool COMPOSITE, bool STATS>
-__global__ void __launch_bounds__(kCtaThreads) march_kernel(const __grid_constant__ MarchParams P) {
+__global__ void __launch_bounds__(kCtaThreads, VOLRT_DIRECT_MIN_CTAS) march_kernel(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     __shared__ MarchSmem<LINEAR> smem;
     float* const unorm = smem.unorm;

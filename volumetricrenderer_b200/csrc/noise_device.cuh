@@ -287,12 +287,37 @@ __device__ __forceinline__ f2 grad_edge_lut2(LUT lut, int tA0, int tA1, int tB0,
     return fma2(s, e, d0);
 }
 
+#ifndef VOLRT_FBM_FLOOR_MODE
+#define VOLRT_FBM_FLOOR_MODE 1
+#endif
 template <class LUT>
 __device__ __forceinline__ f2 perlin3_lut2(LUT lut, int seed, f2 x, f2 y, f2 z) {
+#if VOLRT_FBM_FLOOR_MODE == 0
     const float xsA = floorf(f2_a(x)), xsB = floorf(f2_b(x)), ysA = floorf(f2_a(y)), ysB = floorf(f2_b(y)), zsA = floorf(f2_a(z)), zsB = floorf(f2_b(z));
     f2 xs = make_f2(xsA, xsB), ys = make_f2(ysA, ysB), zs = make_f2(zsA, zsB);
     const int ax0 = __float2int_rn(xsA) * kPrimeX, ay0 = __float2int_rn(ysA) * kPrimeY, az0 = __float2int_rn(zsA) * kPrimeZ;
     const int bx0 = __float2int_rn(xsB) * kPrimeX, by0 = __float2int_rn(ysB) * kPrimeY, bz0 = __float2int_rn(zsB) * kPrimeZ;
+#else
+    // The lattice coordinate as an integer without F2I (an XU-pipe instruction, 4 lanes/clk per scheduler): for an integral
+    // |v| <= 2^22 the binary32 sum v + 1.5*2^23 is exact and its bit pattern is 0x4B400000 + v, so v * prime is one IMAD
+    // on those bits with the constant -0x4B400000 * prime as addend.  Coordinates beyond 2^22 have no fraction bits
+    // left for a noise lattice anyway.
+    const f2 magic = splat2(12582912.0f);
+#if VOLRT_FBM_FLOOR_MODE == 1
+    f2 xs = make_f2(floorf(f2_a(x)), floorf(f2_b(x))), ys = make_f2(floorf(f2_a(y)), floorf(f2_b(y))), zs = make_f2(floorf(f2_a(z)), floorf(f2_b(z)));
+    const f2 xt = add2(xs, magic), yt = add2(ys, magic), zt = add2(zs, magic);
+#else
+    // floor itself on the FMA pipe too: rint(v - 1/2) is floor(v) except that an integral v may land one cell lower with
+    // fraction exactly 1, where Perlin noise has the same value (the fade is 1 and the far corner's offset is 0)
+    const f2 mh = splat2(-0.5f);
+    const f2 xt = add2(add2(x, mh), magic), yt = add2(add2(y, mh), magic), zt = add2(add2(z, mh), magic);
+    f2 xs = sub2(xt, magic), ys = sub2(yt, magic), zs = sub2(zt, magic);
+#endif
+    constexpr unsigned int kBias = 0x4B400000u;
+    constexpr int kx = (int)(0u - kBias * (unsigned int)kPrimeX), ky = (int)(0u - kBias * (unsigned int)kPrimeY), kz = (int)(0u - kBias * (unsigned int)kPrimeZ);
+    const int ax0 = __float_as_int(f2_a(xt)) * kPrimeX + kx, ay0 = __float_as_int(f2_a(yt)) * kPrimeY + ky, az0 = __float_as_int(f2_a(zt)) * kPrimeZ + kz;
+    const int bx0 = __float_as_int(f2_b(xt)) * kPrimeX + kx, by0 = __float_as_int(f2_b(yt)) * kPrimeY + ky, bz0 = __float_as_int(f2_b(zt)) * kPrimeZ + kz;
+#endif
     const int ax1 = ax0 + kPrimeX, ay1 = ay0 + kPrimeY, az1 = az0 + kPrimeZ;
     const int bx1 = bx0 + kPrimeX, by1 = by0 + kPrimeY, bz1 = bz0 + kPrimeZ;
     const f2 xf0 = sub2(x, xs), yf0 = sub2(y, ys), zf0 = sub2(z, zs);
