@@ -333,11 +333,14 @@ VR_API vr_status vr_volume_pyramid(vr_context* ctx, float* out, size_t out_bytes
  * exports).  vr_noise_tree_compile decodes such a string on the host (no device needed) into a straight-line
  * program; vr_noise_tree_grid evaluates it on the device with GenUniformGrid3D semantics (Generator.inl:124-176):
  * out[z][y][x] = tree((x0+x)*frequency, (y0+y)*frequency, (z0+z)*frequency; seed), min/max returned like
- * FastNoise::OutputMinMax.  Built: Constant, White, SineWave, PositionOutput, DistanceToPoint, Value, Perlin, Simplex,
- * OpenSimplex2, CellularValue/Distance/Lookup, FractalFBm/Ridged/PingPong, DomainWarpGradient,
- * DomainWarpFractalProgressive/Independant, DomainScale/Offset/Rotate/AxisScale, SeedOffset, Remap, ConvertRGBA8, Terrace,
+ * FastNoise::OutputMinMax.  Built (40 of the reference's 42 node classes): Constant, White, Checkerboard, SineWave,
+ * PositionOutput, DistanceToPoint, Value, Perlin, Simplex, OpenSimplex2, OpenSimplex2S, CellularValue/Distance/Lookup,
+ * FractalFBm/Ridged/PingPong, DomainWarpGradient, DomainWarpFractalProgressive/Independant,
+ * DomainScale/Offset/Rotate/AxisScale, SeedOffset, Remap, ConvertRGBA8, Terrace,
  * Add/Subtract/Multiply/Divide/Min/Max/MinSmooth/MaxSmooth/Fade/PowFloat/PowInt, GeneratorCache; 3-D positions only.
- * Anything else (Checkerboard, OpenSimplex2S, Add/RemoveDimension) -> VR_ERR_UNSUPPORTED with the node's name in err. */
+ * AddDimension / RemoveDimension (they change the dimension count) -> VR_ERR_UNSUPPORTED with the node's name in err.
+ * Checkerboard divides by the size exactly; the reference multiplies by an approximate reciprocal, so a point exactly
+ * on a cell border may fall on the other side there. */
 VR_API vr_status vr_noise_tree_compile(const char* encoded_node_tree, vr_noise_tree** out, char* err, size_t err_cap);
 VR_API void vr_noise_tree_free(vr_noise_tree* tree);
 VR_API vr_status vr_noise_tree_info(const vr_noise_tree* tree, uint32_t* nodes, uint32_t* instructions, uint32_t* value_regs,

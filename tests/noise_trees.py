@@ -49,5 +49,13 @@ TREES = {
     "convert_rgba8": (N("ConvertRGBA8", Min=-0.8, Max=0.9, Source=N("Perlin")), 0.17, 69, (0, 0, 0)),
     "cloud_density": (N("Max", RHS=0.0, LHS=N("Subtract", RHS=0.45, LHS=N("Remap", FromMin=-1, FromMax=1, ToMin=0, ToMax=1,
                         Source=N("DomainWarpGradient", WarpFrequency=0.7, WarpAmplitude=0.6, Source=N("FractalFBm", Octaves=5, Source=N("Perlin")))))), 0.16, 1337, (0, 0, 0)),
+    # added after the first fixture: the smooth simplex variant, alone / under a looping fractal / under an unrolled one, and
+    # the checkerboard (size and frequency chosen so that no grid point sits on a cell border, where the reference's
+    # approximate reciprocal decides the side)
+    "opensimplex2s": (N("OpenSimplex2S"), 0.21, 9, (2, -9, 5)),
+    "fbm_opensimplex2s": (N("FractalFBm", Octaves=4, Lacunarity=2.1, Source=N("OpenSimplex2S"), Gain=0.55), 0.09, 78, (-3, 4, 1)),
+    "ridged_opensimplex2s_gain_node": (N("FractalRidged", Octaves=3, Source=N("OpenSimplex2S"), Gain=N("Remap", Source=N("Value"), FromMin=-1, FromMax=1, ToMin=0.4, ToMax=0.6)), 0.11, 79, (0, 0, 0)),
+    "checkerboard": (N("Checkerboard", Size=0.9), 0.07, 0, (-5, 3, 0)),
+    "checkerboard_blend": (N("Multiply", LHS=N("Perlin"), RHS=N("Checkerboard", Size=2.3)), 0.37, 70, (1, -6, 2)),
 }
 SHAPE = (9, 10, 12)        # (nz, ny, nx)

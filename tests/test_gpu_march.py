@@ -229,6 +229,26 @@ def test_procedural_fbm_cloud(oracle):
     assert psnr8(img, ref8) >= PSNR_MIN
 
 
+@pytest.mark.parametrize("light_steps", [6, 5, 1])
+def test_fbm_light_march_pairs_equal_the_scalar_loop(monkeypatch, light_steps):
+    """The fBm light-march evaluates its samples two at a time on packed FP32 (FFMA2); each half does the
+    scalar routine's operations in the same order, so one thread per ray must give the very same binary32 frame as
+    the counting build (VR_RENDER_STATS), which keeps the scalar loop — for even and odd sample counts."""
+    monkeypatch.setenv("VOLRT_RAY_SPLIT_COMPOSITE", "1")
+    W, H = 320, 180
+    ubo0, ubo1 = scene.default_scene(25.0, -15.0)
+    sun = np.array([1.0, 1.0, 2.0], np.float32)
+    sun /= np.linalg.norm(sun)
+    kw = dict(max_steps=48, sigma_t=8.0, light_steps=light_steps, light_step_len=2 * 4.0 / 48, ambient=0.15)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.set_params(ubo0, ubo1, density_mode=capi.DENSITY_FBM, sun_dir=sun, sun_color=[1.0, 0.95, 0.85], **kw)
+        packed = r.render()[0].copy()
+        scalar = r.render(flags=capi.RENDER_STATS)[0].copy()
+        s = r.stats()
+    assert s["light_samples"] > 0 and packed[..., :3].max() > 0.2
+    assert np.array_equal(packed.view(np.uint32), scalar.view(np.uint32))
+
+
 def test_known_answers_on_gpu():
     """closed forms that do not depend on the oracle: constant volume, axis-aligned centre ray."""
     W, H = 256, 256

@@ -12,7 +12,7 @@ from volumetricrenderer_b200.noisetree import N, CompiledTree
 from noise_trees import TREES, SHAPE
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-UNSUPPORTED = {"Checkerboard", "AddDimension", "RemoveDimension", "OpenSimplex2S"}
+UNSUPPORTED = {"AddDimension", "RemoveDimension"}
 
 
 def _metadata():

@@ -2,6 +2,8 @@
 // (SURVEY.md §8(f) rank 3).  Behaviour restated from vendor/noise/include/FastNoise/Generators/:
 //   white3, value3                BasicGenerators.inl:20-33, Value.inl:30-57, Utils.inl:300-308 (GetValueCoord)
 //   opensimplex2_3                Simplex.inl:309-372
+//   opensimplex2s_3               Simplex.inl:443-524
+//   checkerboard3                 BasicGenerators.inl:36-50
 //   cellular_*                    Cellular.inl:95-160 (value), :307-366 + :439-474 (distance, return types), :520-580 (lookup)
 //   calc_distance                 Utils.inl:329-372
 //   warp_gradient3                DomainWarp.inl:69-122
@@ -67,6 +69,54 @@ __device__ __forceinline__ float opensimplex2_3(int seed, float x, float y, floa
         seed = ~seed;
     }
     return 32.69428253173828125f * val;
+}
+
+// OpenSimplex2S ("smooth"): two half-offset cubic lattices; on each, the cell's base corner or its opposite (whichever side
+// of the plane x+y+z = 3/2 the point is on) plus, per axis, the corner across that axis or its mirror — four kernels of
+// radius^2 3/4 per lattice.  One vertex is (sign pattern sx,sy,sz in {+1,-1}): p = the plane test of the pattern,
+// chosen = p >= 0; an axis with sign +1 steps to the far corner when chosen, an axis with sign -1 when NOT chosen.
+__device__ __forceinline__ float os2s_vertex(int seed, int bx, int by, int bz, float x, float y, float z, float falloff_base, float p,
+                                             bool nx, bool ny, bool nz) {
+    const bool chosen = p >= 0.0f;
+    float t = fmaxf(chosen ? falloff_base + p : falloff_base, 0.0f);
+    t *= t; t *= t;
+    const bool fx = chosen != nx, fy = chosen != ny, fz = chosen != nz;       // far corner on this axis?
+    const int h = hash3(seed ^ (fz ? bz + kPrimeZ : bz), (fx ? bx + kPrimeX : bx) ^ (fy ? by + kPrimeY : by));
+    return t * grad_dot(h, fx ? x - 1.0f : x, fy ? y - 1.0f : y, fz ? z - 1.0f : z);
+}
+__device__ __forceinline__ float opensimplex2s_3(int seed, float x, float y, float z) {
+    const float f = (2.0f / 3.0f) * (x + y + z);
+    const float xr = f - x, yr = f - y, zr = f - z;
+    const float xb = floorf(xr), yb = floorf(yr), zb = floorf(zr);
+    float xi = xr - xb, yi = yr - yb, zi = zr - zb;
+    int bx = __float2int_rn(xb) * kPrimeX, by = __float2int_rn(yb) * kPrimeY, bz = __float2int_rn(zb) * kPrimeZ;
+    float val = 0.0f;
+#pragma unroll
+    for (int pass = 0; pass < 2; ++pass) {
+        float a = fmaf(-xi, xi, fmaf(-yi, yi, fmaf(-zi, zi, 0.75f))) * 0.5f;
+        val += os2s_vertex(seed, bx, by, bz, xi, yi, zi, a, zi + yi + xi - 1.5f, false, false, false);
+        a -= 0.5f;
+        val += os2s_vertex(seed, bx, by, bz, xi, yi, zi, a + xi, zi + yi - xi + -0.5f, true, false, false);
+        val += os2s_vertex(seed, bx, by, bz, xi, yi, zi, a + yi, xi + -0.5f + (zi - yi), false, true, false);
+        val += os2s_vertex(seed, bx, by, bz, xi, yi, zi, a + zi, xi + -0.5f - (zi - yi), false, false, true);
+        if (pass == 1) break;
+        const bool sx = xi >= 0.5f, sy = yi >= 0.5f, sz = zi >= 0.5f;       // the second lattice: shifted by half a cell
+        if (sx) bx += kPrimeX;
+        if (sy) by += kPrimeY;
+        if (sz) bz += kPrimeZ;
+        xi += sx ? -0.5f : 0.5f; yi += sy ? -0.5f : 0.5f; zi += sz ? -0.5f : 0.5f;
+        seed = ~seed;
+    }
+    return 144.736422163332608f * val;
+}
+
+// +1 / -1 by the parity of round(x/size) ^ round(y/size) ^ round(z/size) (round to nearest even, like cvtps2dq).  The
+// reference multiplies by an approximate reciprocal of the size (rcpps + one Newton step), so exactly on a cell border
+// (a half-integer quotient) the two may land on different sides; everywhere else they agree.
+__device__ __forceinline__ float checkerboard3(float size, float x, float y, float z) {
+    const float m = 1.0f / size;
+    const int v = __float2int_rn(x * m) ^ __float2int_rn(y * m) ^ __float2int_rn(z * m);
+    return (v & 1) ? -1.0f : 1.0f;
 }
 
 // DistanceFunction: 0 Euclidean, 1 EuclideanSquared, 2 Manhattan, 3 Hybrid, 4 MaxAxis

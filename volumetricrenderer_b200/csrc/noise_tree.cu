@@ -187,10 +187,16 @@ struct Compiler {
         const Node& n = t.nodes[ni];
         switch (n.id) {
             case 0: return constant(n.varf(0));
-            case 1: case 6: case 7: case 8: case 9: {
+            case 1: case 6: case 7: case 8: case 9: case 41: {
                 static const TreeOp ops[10] = {T_CONST, T_WHITE, T_CONST, T_CONST, T_CONST, T_CONST, T_VALUE, T_PERLIN, T_SIMPLEX, T_OPENSIMPLEX2};
                 const int r = new_value();
-                push(ops[n.id], r, pos, so);
+                push(n.id == 41 ? T_OPENSIMPLEX2S : ops[n.id], r, pos, so);
+                return r;
+            }
+            case 2: {
+                if (!(n.varf(0) != 0.0f)) unsupported(n, "size must not be 0");
+                const int r = new_value();
+                push(T_CHECKERBOARD, r, pos, so).f[0] = n.varf(0);
                 return r;
             }
             case 3: { const int r = new_value(); push(T_SINE, r, pos, so).f[0] = 1.0f / n.varf(0); return r; }
@@ -323,9 +329,7 @@ struct Compiler {
                 return emit(n.lookups[0], p, so);
             }
             case 40: return emit(n.lookups[0], pos, so);                                 // GeneratorCache: same value
-            case 2: unsupported(n, "depends on the reference's approximate reciprocal at cell borders; not built");
             case 38: case 39: unsupported(n, "changes the dimension count; libvolrt evaluates 3-D positions only");
-            case 41: unsupported(n, "OpenSimplex2S is not built");
             default: unsupported(n, "not built");
         }
     }
@@ -334,16 +338,16 @@ struct Compiler {
         const int octaves = n.vars[0];
         const float lac = n.varf(1);
         if (octaves < 1 || octaves > 16) unsupported(n, "octaves must be in 1..16");
-        // the usual case — constant gain and weighted strength over Value / Perlin / Simplex / OpenSimplex2 — is one
+        // the usual case — constant gain and weighted strength over Value / Perlin / Simplex / OpenSimplex2(S) — is one
         // instruction that loops over the octaves in registers (noise_tree_eval.cuh)
         const Node& src = t.nodes[n.lookups[0]];
-        const bool leaf = src.id >= 6 && src.id <= 9;
+        const bool leaf = (src.id >= 6 && src.id <= 9) || src.id == 41;
         const bool constants = n.hybrids[0].node < 0 && n.hybrids[1].node < 0 && (n.id != 14 || n.hybrids[2].node < 0);
         if (fuse && leaf && constants) {
             static const TreeOp gen[4] = {T_VALUE, T_PERLIN, T_SIMPLEX, T_OPENSIMPLEX2};
             const int r = new_value();
             TreeInstr& in = push(T_FRACTAL_LEAF, r, pos, so);
-            in.i0 = gen[src.id - 6]; in.i1 = octaves; in.i2 = n.id == 13 ? 0 : n.id == 15 ? 1 : 2;
+            in.i0 = src.id == 41 ? T_OPENSIMPLEX2S : gen[src.id - 6]; in.i1 = octaves; in.i2 = n.id == 13 ? 0 : n.id == 15 ? 1 : 2;
             in.f[0] = fractal_bounding(octaves, n.hybrids[0].value); in.f[1] = lac; in.f[2] = n.hybrids[0].value;
             in.f[3] = n.hybrids[1].value; in.f[4] = n.id == 14 ? n.hybrids[2].value : 0.0f;
             return r;

@@ -14,6 +14,7 @@ __device__ __forceinline__ float tree_leaf(int gen, const GradLut* lut, int s, f
         case T_VALUE: return value3(s, x, y, z);
         case T_SIMPLEX: return simplex3(s, x, y, z);
         case T_OPENSIMPLEX2: return opensimplex2_3(s, x, y, z);
+        case T_OPENSIMPLEX2S: return opensimplex2s_3(s, x, y, z);
         default: return perlin3_lut(lut, s, x, y, z) * kPerlinScale;
     }
 }
@@ -37,7 +38,7 @@ __device__ __forceinline__ float tree_eval(const TreeInstr* __restrict__ prog, i
             // T_*_FIRST / T_*_NEXT instructions below (Fractal.inl), so fused and unfused programs agree bit for bit.
             // i0 = generator, i1 = octaves, i2 = 0 fBm | 1 ridged | 2 ping-pong; f = bounding, lacunarity, gain, weighted
             // strength, ping-pong strength
-            case T_VALUE: case T_PERLIN: case T_SIMPLEX: case T_OPENSIMPLEX2: case T_FRACTAL_LEAF: {
+            case T_VALUE: case T_PERLIN: case T_SIMPLEX: case T_OPENSIMPLEX2: case T_OPENSIMPLEX2S: case T_FRACTAL_LEAF: {
                 const bool fr = in.op == T_FRACTAL_LEAF;
                 const int gen = fr ? in.i0 : (int)in.op, oct = fr ? in.i1 : 1, kind = fr ? in.i2 : 0;
                 const float lac = in.f[1], gain = in.f[2], ws = in.f[3], pps = in.f[4];
@@ -57,6 +58,7 @@ __device__ __forceinline__ float tree_eval(const TreeInstr* __restrict__ prog, i
                 V[in.dst] = sum;
                 break;
             }
+            case T_CHECKERBOARD: V[in.dst] = checkerboard3(in.f[0], px, py, pz); break;
             case T_SINE: V[in.dst] = (fs_sin(px * in.f[0]) * fs_sin(py * in.f[0])) * fs_sin(pz * in.f[0]); break;
             case T_POSITION_OUTPUT: V[in.dst] = ((px + in.f[3]) * in.f[0] + (py + in.f[4]) * in.f[1]) + (pz + in.f[5]) * in.f[2]; break;
             case T_DISTANCE_TO_POINT: V[in.dst] = calc_distance(in.i0, px - in.f[0], py - in.f[1], pz - in.f[2]); break;

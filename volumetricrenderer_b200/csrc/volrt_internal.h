@@ -137,6 +137,7 @@ enum TreeOp : uint16_t {
     T_FBM_FIRST, T_FBM_NEXT, T_RIDGED_FIRST, T_RIDGED_NEXT, T_PINGPONG_FIRST, T_PINGPONG_NEXT,
     T_POS_COPY, T_POS_SCALE, T_POS_AXIS_SCALE, T_POS_OFFSET, T_POS_ROTATE, T_POS_WARP, T_WARP_AMP_NEXT,
     T_FRACTAL_LEAF,
+    T_OPENSIMPLEX2S, T_CHECKERBOARD,
     T_OP_COUNT
 };
 struct TreeInstr {
