@@ -239,7 +239,8 @@ def run_volrt(args, rank, world, local):
     W, H, desc, kw = WORKLOADS[args.workload]
     K, Wm = args.steps, max(args.warmup, 3)
     ubo0, ubo1 = scene.default_scene()
-    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local)
+    # N > 1: GPU 0 holds two frames, so the gather of frame k+1 (peer stores) overlaps the D2H copy of frame k
+    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local, max_views=2 if world > 1 else 1)
     vol_bytes = setup_volume(r, args.workload, args.layout)
     r.set_params(ubo0, ubo1, **kw)
 
@@ -340,6 +341,35 @@ def run_volrt(args, rank, world, local):
     barrier()
     sync_s = (time.perf_counter() - t0) / K
     e2e_s = sync_s
+    e2e_check = None
+    if world > 1:
+        # two frames in flight across the GPUs: every rank marches frame i into frame slot i & 1 of GPU 0 (peer stores;
+        # rank 0 into its own memory), the barrier says the frame is whole, and rank 0 hands the slot to the copy
+        # stream; frame i+1 marches into the other slot meanwhile.  barrier() starts with vr_wait, which on rank 0 also
+        # completes the copy of frame i-1 — so a slot is never written while it is still being read.
+        own_ptr, _pitch, vstride = r.frame_info()
+        hosts2 = r.new_frame_buffer(views=2, pinned=True) if rank == 0 else None
+        base = mapped if mapped is not None else own_ptr
+
+        def e2e_step_mg(i):
+            slot = i & 1
+            r.set_params(ubo0, ubo1, **kw)
+            if rows[1] > rows[0]:
+                r.render_device(base + slot * vstride, rows=rows, flags=capi.RENDER_DIRECT | capi.RENDER_ASYNC)
+            barrier()
+            if rank == 0:
+                r.render(out=hosts2, views=(slot, slot + 1), flags=capi.RENDER_NO_MARCH | capi.RENDER_ASYNC)
+
+        for i in range(4):
+            e2e_step_mg(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(K):
+            e2e_step_mg(i)
+        barrier()                                          # every frame is in host memory
+        e2e_s = (time.perf_counter() - t0) / K
+        if rank == 0:                                      # both slots hold the frame the one-at-a-time path delivered
+            e2e_check = bool(np.array_equal(hosts2[0], hosts[0][0]) and np.array_equal(hosts2[1], hosts[0][0]))
     if world == 1:
         for i in range(3):
             e2e_step(i, capi.RENDER_ASYNC)
@@ -349,9 +379,10 @@ def run_volrt(args, rank, world, local):
             e2e_step(i, capi.RENDER_ASYNC)
         barrier()                                          # vr_wait: every frame is in host memory
         e2e_s = (time.perf_counter() - t0) / K
+        e2e_check = bool(np.array_equal(hosts[0], hosts[1]))
     e2e = {"value": W * H / e2e_s / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_s * 1e3,
-           "sync_ms_per_frame": sync_s * 1e3, "frames_in_flight": 2 if world == 1 else 1,
-           "h2d_bytes_per_step": 192 + 140, "d2h_bytes_per_step": W * H * 4}
+           "sync_ms_per_frame": sync_s * 1e3, "frames_in_flight": 2,
+           "h2d_bytes_per_step": 192 + 140, "d2h_bytes_per_step": W * H * 4, "frames_identical": e2e_check}
 
     if rank == 0:
         line = {

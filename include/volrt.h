@@ -109,7 +109,9 @@ enum {
                                       NVLink peer access / CUDA IPC) instead of the context frame */
     VR_RENDER_STATS = 1u << 2,     /* count covered rays / steps on the device (slower variant) */
     VR_RENDER_NO_MARCH = 1u << 3   /* launch nothing; only copy the context frame (e.g. the one the
-                                      peers have just gathered into) to dst                         */
+                                      peers have just gathered into) to dst.  The view range may name any of
+                                      the context's max_views frames; with VR_RENDER_ASYNC + VR_MEM_HOST the
+                                      copy runs on the copy stream and completes at vr_wait                 */
 };
 
 /* vr_create_info.flags: how pixels are handed to warps.  Default (0) = by cost of a step: cheap steps

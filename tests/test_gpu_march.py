@@ -229,6 +229,27 @@ def test_procedural_fbm_cloud(oracle):
     assert psnr8(img, ref8) >= PSNR_MIN
 
 
+def test_copy_only_async_of_a_second_frame(default_volume):
+    """What the multi-GPU gather pipelines on GPU 0: a march stores straight into frame slot 1 of the context
+    (VR_RENDER_DIRECT), then a copy-only asynchronous vr_render hands that slot to the copy stream; vr_wait completes it."""
+    W, H = 256, 144
+    ubo0, ubo1 = scene.default_scene(10.0, 5.0)
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, max_views=2) as r:
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        r.set_params(ubo0, ubo1)
+        ref = r.render()[0].copy()
+        ptr, pitch, vstride = r.frame_info()
+        assert vstride == pitch * H
+        host = r.new_frame_buffer(views=2, pinned=True)
+        host[:] = 7
+        r.render_device(ptr + vstride, rows=(0, H), flags=capi.RENDER_DIRECT | capi.RENDER_ASYNC)
+        got = r.render(out=host, views=(1, 2), flags=capi.RENDER_NO_MARCH | capi.RENDER_ASYNC)
+        r.wait()
+        assert np.array_equal(got[0], ref) and (host[0] == 7).all()
+        with pytest.raises(Exception):                       # a marching call may only name views that have parameters
+            r.render(out=host, views=(1, 2))
+
+
 @pytest.mark.parametrize("light_steps", [6, 5, 1])
 def test_fbm_light_march_pairs_equal_the_scalar_loop(monkeypatch, light_steps):
     """The fBm light-march evaluates its samples two at a time on packed FP32 (FFMA2); each half does the

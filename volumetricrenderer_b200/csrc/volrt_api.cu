@@ -960,9 +960,11 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
     uint32_t r0 = t->row_begin, r1 = t->row_end;
     if (r0 == 0 && r1 == 0) r1 = c->height;
     if (r0 > r1 || r1 > c->height) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: row band out of range");
+    const bool no_march = (t->flags & VR_RENDER_NO_MARCH) != 0;
     uint32_t v0 = t->view_begin, v1 = t->view_end;
     if (v0 == 0 && v1 == 0) v1 = c->view_count;
-    if (v0 > v1 || v1 > c->view_count) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: view range out of range");
+    // a copy-only call may name any frame the context holds (the multi-GPU gather double-buffers GPU 0's frames)
+    if (v0 > v1 || v1 > (no_march ? c->max_views : c->view_count)) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: view range out of range");
     const size_t pitch = t->row_pitch ? t->row_pitch : c->row_pitch;
     if (pitch < c->row_pitch) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_render: row_pitch smaller than a row");
 
@@ -981,7 +983,10 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
     }
     // asynchronous render into host memory: alternate between two device frames and hand the D2H copy to
     // the copy stream, so that the next frame's march overlaps it
-    const bool pipelined = (t->flags & VR_RENDER_ASYNC) && t->memory_kind == VR_MEM_HOST && !direct && !t->stream;
+    const bool pipelined = (t->flags & VR_RENDER_ASYNC) && t->memory_kind == VR_MEM_HOST && !direct && !t->stream && !no_march;
+    // copy-only + async: the frame(s) named by the view range leave on the copy stream, behind whatever the render
+    // stream holds now; the caller keeps the frame untouched until vr_wait (multi-GPU: the peers write the other frame)
+    const bool copy_async = (t->flags & VR_RENDER_ASYNC) && t->memory_kind == VR_MEM_HOST && !direct && !t->stream && no_march;
     char* frame = (char*)c->frame;
     int slot = 0;
     if (pipelined) {
@@ -992,7 +997,6 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
         if (c->copy_pending[slot]) VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_copy_done[slot], 0));   // frame slot is free again
         m.out = frame;
     }
-    const bool no_march = (t->flags & VR_RENDER_NO_MARCH) != 0;
     VR_CUDA(c, cudaEventRecord(c->ev0, s));
     if (variant == MARCH_SINGLE_BRICK && stats) variant = MARCH_SINGLE_LINEAR;     // device counters live in the generic kernel
     if (!no_march) {
@@ -1012,6 +1016,10 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
         if (pipelined) {
             VR_CUDA(c, cudaEventRecord(c->ev_render_done[slot], s));
             VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_render_done[slot], 0));
+            cs = c->copy_stream;
+        } else if (copy_async) {
+            VR_CUDA(c, cudaEventRecord(c->ev_render_done[0], s));
+            VR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_render_done[0], 0));
             cs = c->copy_stream;
         }
         for (uint32_t v = v0; v < v1; ++v) {
