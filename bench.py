@@ -343,22 +343,28 @@ def run_volrt(args, rank, world, local):
     e2e_s = sync_s
     e2e_check = None
     if world > 1:
-        # two frames in flight across the GPUs: every rank marches frame i into frame slot i & 1 of GPU 0 (peer stores;
-        # rank 0 into its own memory), the barrier says the frame is whole, and rank 0 hands the slot to the copy
-        # stream; frame i+1 marches into the other slot meanwhile.  barrier() starts with vr_wait, which on rank 0 also
-        # completes the copy of frame i-1 — so a slot is never written while it is still being read.
+        # two frames in flight across the GPUs, completed on the device (include/volrt.h: vr_gather_*): every rank marches
+        # frame i into frame slot i & 1 of GPU 0 (peer stores; rank 0 into its own memory) and bumps the slot's arrival
+        # counter behind its stores; GPU 0's copy stream waits for all the bands, copies the slot to the host and releases
+        # it; a rank's render stream waits for that release before it marches into the slot again.  No host barrier per
+        # frame: the hosts only enqueue, frame i+1 gathers while frame i leaves over PCIe.
         own_ptr, _pitch, vstride = r.frame_info()
         hosts2 = r.new_frame_buffer(views=2, pinned=True) if rank == 0 else None
         base = mapped if mapped is not None else own_ptr
+        frame0 = mapped                                    # None on rank 0
+        counter = [0]                                      # frames sent through the protocol so far (slot use = counter // 2)
 
-        def e2e_step_mg(i):
+        def e2e_step_mg(_i):
+            i = counter[0]
+            counter[0] += 1
             slot = i & 1
             r.set_params(ubo0, ubo1, **kw)
+            r.gather_acquire(frame0, 2, slot, i // 2)
             if rows[1] > rows[0]:
                 r.render_device(base + slot * vstride, rows=rows, flags=capi.RENDER_DIRECT | capi.RENDER_ASYNC)
-            barrier()
+            r.gather_signal(frame0, 2, slot)
             if rank == 0:
-                r.render(out=hosts2, views=(slot, slot + 1), flags=capi.RENDER_NO_MARCH | capi.RENDER_ASYNC)
+                r.gather_collect(slot, world * (i // 2 + 1), hosts2[slot])
 
         for i in range(4):
             e2e_step_mg(i)

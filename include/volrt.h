@@ -277,6 +277,20 @@ VR_API vr_status vr_split_rows(const float* cost, uint32_t height, uint32_t part
 VR_API vr_status vr_frame_export(vr_context* ctx, void* handle64);
 VR_API vr_status vr_frame_import(vr_context* ctx, const void* handle64, void** mapped);
 VR_API vr_status vr_frame_unmap(vr_context* ctx, void* mapped);
+/* Completion of that gather on the device, without a host barrier per frame.  GPU 0's context holds `frames`
+ * (= its max_views) frame slots followed by a mailbox of counters; frame0 = NULL on GPU 0 itself, the mapped pointer on the
+ * others (same width, height and format everywhere).  Per frame k into slot s, every rank (GPU 0 included) enqueues
+ *   vr_gather_acquire(ctx, frame0, frames, s, r)  r = how many earlier frames used slot s: the render stream waits until
+ *                                                 GPU 0 has copied that many out of it;
+ *   vr_render(VR_RENDER_DIRECT | VR_RENDER_ASYNC) into frame0 + s * view_stride;
+ *   vr_gather_signal(ctx, frame0, frames, s)      "my band of this frame has landed" (system-scope release);
+ * and GPU 0 alone
+ *   vr_gather_collect(ctx, s, ranks * (r + 1), dst_host, row_pitch)   its copy stream waits for all the bands, copies slot s
+ *                                                 to page-locked host memory and releases the slot.
+ * Nothing blocks the host; vr_wait on GPU 0 completes the copies.  A wait that is not satisfied within ~2 s traps. */
+VR_API vr_status vr_gather_acquire(vr_context* ctx, void* frame0, uint32_t frames, uint32_t slot, uint32_t releases);
+VR_API vr_status vr_gather_signal(vr_context* ctx, void* frame0, uint32_t frames, uint32_t slot);
+VR_API vr_status vr_gather_collect(vr_context* ctx, uint32_t slot, uint32_t arrivals, void* dst_host, size_t row_pitch);
 /* measurement helpers: evict the 126 MB L2 between timed frames (writes a 256 MiB scratch buffer on
  * the context's stream); page-locked host memory so that vr_render's D2H copy and
  * vr_upload_volume's H2D copy run at full PCIe rate (the reference maps its UBOs and stages

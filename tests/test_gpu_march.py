@@ -250,6 +250,33 @@ def test_copy_only_async_of_a_second_frame(default_volume):
             r.render(out=host, views=(1, 2))
 
 
+def test_device_side_gather_protocol_single_rank(default_volume):
+    """vr_gather_acquire / _signal / _collect with one rank: six frames through two slots with no host synchronisation in
+    between (slot reuse waits for the release on the device), every delivered frame equal to an ordinary render."""
+    W, H = 256, 144
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, max_views=2) as r:
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        ptr, pitch, vstride = r.frame_info()
+        host = r.new_frame_buffer(views=6, pinned=True)
+        refs = []
+        for i in range(6):
+            r.set_params(*scene.default_scene(10.0 * i, 5.0))
+            refs.append(r.render()[0].copy())
+        for i in range(6):
+            slot = i & 1
+            r.set_params(*scene.default_scene(10.0 * i, 5.0))
+            r.gather_acquire(None, 2, slot, i // 2)
+            r.render_device(ptr + slot * vstride, rows=(0, H // 2), flags=capi.RENDER_DIRECT | capi.RENDER_ASYNC)
+            r.render_device(ptr + slot * vstride, rows=(H // 2, H), flags=capi.RENDER_DIRECT | capi.RENDER_ASYNC)
+            r.gather_signal(None, 2, slot)
+            r.gather_collect(slot, i // 2 + 1, host[i])
+        r.wait()
+        for i in range(6):
+            assert np.array_equal(host[i], refs[i]), i
+        with pytest.raises(Exception):
+            r.gather_signal(None, 2, 2)                      # only two slots
+
+
 @pytest.mark.parametrize("light_steps", [6, 5, 1])
 def test_fbm_light_march_pairs_equal_the_scalar_loop(monkeypatch, light_steps):
     """The fBm light-march evaluates its samples two at a time on packed FP32 (FFMA2); each half does the

@@ -107,6 +107,9 @@ EXPORTS = {
     "vr_frame_export": (C.c_int32, [_VP, _VP]),
     "vr_frame_import": (C.c_int32, [_VP, _VP, C.POINTER(_VP)]),
     "vr_frame_unmap": (C.c_int32, [_VP, _VP]),
+    "vr_gather_acquire": (C.c_int32, [_VP, _VP, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "vr_gather_signal": (C.c_int32, [_VP, _VP, C.c_uint32, C.c_uint32]),
+    "vr_gather_collect": (C.c_int32, [_VP, C.c_uint32, C.c_uint32, _VP, C.c_size_t]),
     "vr_flush_l2": (C.c_int32, [_VP]),
     "vr_measure_peaks": (C.c_int32, [_VP, C.POINTER(C.c_float)]),
     "vr_host_alloc": (_VP, [C.c_size_t]),

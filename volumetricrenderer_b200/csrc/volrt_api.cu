@@ -185,7 +185,9 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
         if ((e = cudaEventCreateWithFlags(&c->ev_copy_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
     }
     if ((e = cudaEventCreateWithFlags(&c->ev_params, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
-    if ((e = cudaMalloc(&c->frame, c->view_stride * c->max_views)) != cudaSuccess) return bail("cudaMalloc(frame)", e);
+    // the frames, followed by the gather mailbox (kGatherMailboxBytes, zeroed): arrival / release counters per frame slot
+    if ((e = cudaMalloc(&c->frame, c->view_stride * c->max_views + kGatherMailboxBytes)) != cudaSuccess) return bail("cudaMalloc(frame)", e);
+    if ((e = cudaMemset((char*)c->frame + c->view_stride * c->max_views, 0, kGatherMailboxBytes)) != cudaSuccess) return bail("cudaMemset(mailbox)", e);
     c->view_capacity = c->max_views;
     if ((e = cudaMalloc(&c->d_views, sizeof(ViewConst) * c->view_capacity)) != cudaSuccess) return bail("cudaMalloc(views)", e);
     if ((e = cudaMallocHost(&c->h_views, sizeof(ViewConst) * c->view_capacity)) != cudaSuccess) return bail("cudaMallocHost(views)", e);
@@ -1146,6 +1148,75 @@ extern "C" vr_status vr_frame_unmap(vr_context* c, void* mapped) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
     VR_CUDA(c, cudaSetDevice(c->device));
     VR_CUDA(c, cudaIpcCloseMemHandle(mapped));
+    return VR_OK;
+}
+
+// ------------------------------------------------------------------ device-side completion of the gather
+// The peer stores fuse the gather into the march; what remained per frame was a host barrier (every band has landed)
+// before GPU 0 may copy the frame out, and another before a frame slot may be written again.  Both become counters in
+// GPU 0's memory, next to the frames (same IPC mapping):
+//   arrived[slot]   += 1 by every rank after its band of a frame (system-scope release behind the march's stores);
+//   released[slot]  += 1 by GPU 0 after the frame has left for the host.
+// GPU 0's copy stream spins on arrived[slot] (one thread), copies, releases; a rank's render stream spins on
+// released[slot] before it marches into that slot again.  The host only enqueues.  Spins are bounded (~2 s) and trap.
+namespace {
+struct GatherMailbox { unsigned int arrived[8]; unsigned int released[8]; };
+static_assert(sizeof(GatherMailbox) <= volrt::kGatherMailboxBytes, "mailbox size");
+constexpr uint32_t kGatherSlots = 8;
+
+__global__ void gather_bump_kernel(unsigned int* counter) {
+    __threadfence_system();
+    atomicAdd_system(counter, 1u);
+}
+__global__ void gather_wait_kernel(const unsigned int* counter, unsigned int target) {
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned int v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+        if ((int)(v - target) >= 0) return;
+        __nanosleep(100);
+        if (clock64() - t0 > 4000000000ll) __trap();         // a rank died or the protocol was misused: fail loudly
+    }
+}
+GatherMailbox* mailbox_of(vr_context* c, void* frame0, uint32_t frames) {
+    char* base = frame0 ? (char*)frame0 : (char*)c->frame;
+    return (GatherMailbox*)(base + c->view_stride * (frame0 ? frames : c->max_views));
+}
+}  // namespace
+
+extern "C" vr_status vr_gather_acquire(vr_context* c, void* frame0, uint32_t frames, uint32_t slot, uint32_t releases) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (slot >= kGatherSlots || (frame0 && (frames == 0 || slot >= frames)) || (!frame0 && slot >= c->max_views))
+        return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_gather_acquire: slot out of range");
+    if (releases == 0) return VR_OK;                          // first use of the slot: nothing to wait for
+    VR_CUDA(c, cudaSetDevice(c->device));
+    gather_wait_kernel<<<1, 1, 0, c->stream>>>(&mailbox_of(c, frame0, frames)->released[slot], releases);
+    VR_CUDA(c, cudaGetLastError());
+    return VR_OK;
+}
+extern "C" vr_status vr_gather_signal(vr_context* c, void* frame0, uint32_t frames, uint32_t slot) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (slot >= kGatherSlots || (frame0 && (frames == 0 || slot >= frames)) || (!frame0 && slot >= c->max_views))
+        return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_gather_signal: slot out of range");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    gather_bump_kernel<<<1, 1, 0, c->stream>>>(&mailbox_of(c, frame0, frames)->arrived[slot]);
+    VR_CUDA(c, cudaGetLastError());
+    return VR_OK;
+}
+extern "C" vr_status vr_gather_collect(vr_context* c, uint32_t slot, uint32_t arrivals, void* dst_host, size_t row_pitch) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (slot >= kGatherSlots || slot >= c->max_views) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_gather_collect: slot out of range");
+    if (!dst_host) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_gather_collect: dst is null");
+    const size_t pitch = row_pitch ? row_pitch : c->row_pitch;
+    if (pitch < c->row_pitch) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_gather_collect: row_pitch smaller than a row");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    GatherMailbox* mb = mailbox_of(c, nullptr, 0);
+    gather_wait_kernel<<<1, 1, 0, c->copy_stream>>>(&mb->arrived[slot], arrivals);
+    VR_CUDA(c, cudaGetLastError());
+    VR_CUDA(c, cudaMemcpy2DAsync(dst_host, pitch, (const char*)c->frame + (size_t)slot * c->view_stride, c->row_pitch, c->row_pitch,
+                                 c->height, cudaMemcpyDeviceToHost, c->copy_stream));
+    gather_bump_kernel<<<1, 1, 0, c->copy_stream>>>(&mb->released[slot]);
+    VR_CUDA(c, cudaGetLastError());
     return VR_OK;
 }
 

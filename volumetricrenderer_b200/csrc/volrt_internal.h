@@ -93,6 +93,8 @@ enum MarchVariant {
     MARCH_TREE = 6           // procedural density from a compiled FastNoise2 node tree (noise_tree_eval.cuh)
 };
 
+constexpr size_t kGatherMailboxBytes = 256;    // behind the context's frames: counters of the device-side gather protocol (volrt_api.cu)
+
 // launches one march over rows [row_begin,row_end) x views; returns cudaGetLastError()
 cudaError_t launch_march(const MarchParams& p, int variant, int n_views, bool stats, cudaStream_t stream);
 

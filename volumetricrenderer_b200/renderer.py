@@ -295,5 +295,19 @@ class Renderer:
         self._check(self._lib.vr_frame_import(self._ctx, C.cast(buf, C.c_void_p), C.byref(mapped)))
         return mapped.value
 
+    # ---- device-side completion of the multi-GPU gather (include/volrt.h: vr_gather_*)
+    def gather_acquire(self, frame0, frames, slot, releases):
+        self._check(self._lib.vr_gather_acquire(self._ctx, frame0, frames, slot, releases))
+
+    def gather_signal(self, frame0, frames, slot):
+        self._check(self._lib.vr_gather_signal(self._ctx, frame0, frames, slot))
+
+    def gather_collect(self, slot, arrivals, out):
+        """GPU 0: when `arrivals` bands have landed in frame slot `slot`, copy it to out (H, W, 4; page-locked) and release
+        the slot; returns at once, vr_wait completes it"""
+        if out.shape != (self.height, self.width, 4) or not out.flags.c_contiguous:
+            raise ValueError("out must be a contiguous (H, W, 4) array")
+        self._check(self._lib.vr_gather_collect(self._ctx, slot, arrivals, out.ctypes.data, 0))
+
     def frame_unmap(self, mapped):
         self._check(self._lib.vr_frame_unmap(self._ctx, mapped))
