@@ -357,14 +357,14 @@ def run_volrt(args, rank, world, local):
         def e2e_step_mg(_i):
             i = counter[0]
             counter[0] += 1
-            slot = i & 1
+            slot, releases, arrivals = multigpu.gather_ticket(i, world, 2)
             r.set_params(ubo0, ubo1, **kw)
-            r.gather_acquire(frame0, 2, slot, i // 2)
+            r.gather_acquire(frame0, 2, slot, releases)
             if rows[1] > rows[0]:
                 r.render_device(base + slot * vstride, rows=rows, flags=capi.RENDER_DIRECT | capi.RENDER_ASYNC)
             r.gather_signal(frame0, 2, slot)
             if rank == 0:
-                r.gather_collect(slot, world * (i // 2 + 1), hosts2[slot])
+                r.gather_collect(slot, arrivals, hosts2[slot])
 
         for i in range(4):
             e2e_step_mg(i)

@@ -5,6 +5,7 @@ import subprocess
 import sys
 
 import numpy as np
+import pytest
 
 from volumetricrenderer_b200 import multigpu
 
@@ -76,3 +77,18 @@ def test_world_size_2_gloo_band_gather(tmp_path):
     s = z["band_steps"].astype(np.float64)
     assert abs(s[0] - s[1]) / s.sum() < 0.08         # the two bands carry nearly equal work
     assert bool(z["views_ok"]) and int(z["n_views"]) == 5
+
+
+def test_gather_tickets_model_the_device_protocol():
+    """host arithmetic of vr_gather_*: replay the counters for 3 ranks and 7 frames through 2 slots — every frame finds its
+    slot released exactly as often as it was used before, and GPU 0's arrival target is reached by exactly this frame"""
+    world, slots = 3, 2
+    arrived, released = [0] * slots, [0] * slots
+    for i in range(7):
+        slot, releases, arrivals = multigpu.gather_ticket(i, world, slots)
+        assert slot == i % slots and released[slot] == releases          # acquire passes without waiting for a later frame
+        arrived[slot] += world                                            # every rank signals once
+        assert arrived[slot] == arrivals                                  # collect fires for this frame, not earlier
+        released[slot] += 1
+    with pytest.raises(ValueError):
+        multigpu.gather_ticket(-1, 2)

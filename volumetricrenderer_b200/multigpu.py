@@ -53,6 +53,17 @@ def rescale_and_split(row_cost, bounds, times):
     return split_rows(cost.astype(np.float32), len(times))
 
 
+def gather_ticket(frame_index, world, slots=2):
+    """Counters of the device-side gather (include/volrt.h: vr_gather_*) for the frame_index-th frame sent through it:
+    -> (slot, releases, arrivals): the frame goes into `slot`; a rank may write the slot once GPU 0 has released it
+    `releases` times (= earlier frames that used it); GPU 0 copies the slot out once `arrivals` bands have landed in it
+    over its whole life (every rank signals once per frame, empty bands included)."""
+    if frame_index < 0 or world < 1 or slots < 1:
+        raise ValueError("gather_ticket(%r, %r, %r)" % (frame_index, world, slots))
+    slot, uses = frame_index % slots, frame_index // slots
+    return slot, uses, world * (uses + 1)
+
+
 class BandGather:
     """Row-band partition of ONE frame over `world` ranks and its gather on rank 0.
 
