@@ -114,9 +114,9 @@ enum {
                                       copy runs on the copy stream and completes at vr_wait                 */
 };
 
-/* vr_create_info.flags: how pixels are handed to warps.  Default (0) = by cost of a step: cheap steps
- * (texture fetches) use one CTA per 16x8 tile; heavy steps (procedural density, light-march) use
- * persistent warps pulling 8x4 tiles off a device-side queue (one vr_render in flight per context). */
+/* vr_create_info.flags: how pixels are handed to warps.  Default (0) = one CTA per 16x8-pixel tile, tiles dispatched from
+ * the frame's centre outwards (measured fastest for every workload on B200).  PERSISTENT = warps pulling 8x4 tiles off a
+ * device-side queue (one vr_render in flight per context); kept for comparison. */
 enum {
     VR_CREATE_SCHEDULE_DIRECT = 1u << 0,
     VR_CREATE_SCHEDULE_PERSISTENT = 1u << 1

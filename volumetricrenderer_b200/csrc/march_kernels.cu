@@ -268,6 +268,20 @@ __device__ __forceinline__ int brick_distance(const MarchParams& P, f3 p) {
     int bz = min(max((int)(p.z * B.inv_brick[2]), 0), B.bz - 1);
     return (int)__ldg(B.dist + ((size_t)bz * B.by + by) * B.bx + bx);
 }
+// The same lookup without the three float->int conversions (XU pipe: 41 % busy in the C5 march): x*inv + (2^23 - 1/2)
+// rounds to an integer-valued float whose bit pattern is 0x4B000000 + round(x*inv - 1/2), i.e. the brick index except that a
+// coordinate exactly on a brick face may name the brick below — which shares that face, so its distance bounds the same
+// leap (the map is conservative on closed bricks).  Used by the hardware-filtered march only; the strict path and the
+// counting build keep the truncation, so their skipped-step counts equal the oracle's.
+__device__ __forceinline__ int brick_distance_fast(const MarchParams& P, f3 p) {
+    const BrickInfo& B = P.bricks;
+    constexpr float kM = 8388607.5f;
+    constexpr int kLo = 0x4B000000;
+    const int bx = min(max(__float_as_int(fmaf(p.x, B.inv_brick[0], kM)), kLo), kLo + B.bx - 1) - kLo;
+    const int by = min(max(__float_as_int(fmaf(p.y, B.inv_brick[1], kM)), kLo), kLo + B.by - 1) - kLo;
+    const int bz = min(max(__float_as_int(fmaf(p.z, B.inv_brick[2], kM)), kLo), kLo + B.bz - 1) - kLo;
+    return (int)__ldg(B.dist + (unsigned int)((bz * B.by + by) * B.bx + bx));
+}
 // Empty-space leaping.  From a sample in a brick of distance d >= 2, every sample whose coordinates have moved by less
 // than (d-1) bricks on every axis still lies in an empty brick, so m = floor(min_c((d-1)*brick_c - eps) / |step_c|)
 // further steps can be skipped without a lookup.  eps (1e-4 texture units) absorbs the rounding of the running add.
@@ -432,6 +446,9 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
         // Measured (tools/c5_probe.py, 16 views of C5, ms): batch 1 / 2 / 4 / 8 = 2.008 / 1.860 / 1.956 / 2.561 with
         // skipping + early termination, 4.57 / 4.58 / 5.89 / 6.24 with early termination alone: two in flight is all the
         // memory system rewards — deeper batches fetch past the terminating step and evict each other's lines.
+#ifndef VOLRT_FAST_BRICK
+#define VOLRT_FAST_BRICK 1
+#endif
 #ifndef VOLRT_COMPOSITE_BATCH
 #define VOLRT_COMPOSITE_BATCH 2
 #endif
@@ -443,7 +460,7 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
             int i = 0;
             while (i < n && !early) {
                 if (skip) {
-                    const int bd = brick_distance(P, p);
+                    const int bd = VOLRT_FAST_BRICK ? brick_distance_fast(P, p) : brick_distance(P, p);
                     if (bd) {
                         const float fm = (float)(leap_steps(leap, bd, n - 1 - i) + 1);
                         p = {fmaf(fm, ray.step.x, p.x), fmaf(fm, ray.step.y, p.y), fmaf(fm, ray.step.z, p.z)};
@@ -1072,7 +1089,6 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     bool composite = p.sigma_t > 0.0f;
     // schedule: 0 = direct tiles, 1 = persistent warps, -1 = auto
     bool persistent = p.schedule > 0;    // auto = direct: the queue did not pay off on B200 (measurements)
-    if (!p.queue) persistent = false;
     if (!p.queue) persistent = false;
     // ray split of the compositing integrator (any density source; not with device counters)
     if (composite && !stats && !persistent) {
