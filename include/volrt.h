@@ -287,7 +287,7 @@ VR_API vr_status vr_frame_unmap(vr_context* ctx, void* mapped);
  * and GPU 0 alone
  *   vr_gather_collect(ctx, s, ranks * (r + 1), dst_host, row_pitch)   its copy stream waits for all the bands, copies slot s
  *                                                 to page-locked host memory and releases the slot.
- * Nothing blocks the host; vr_wait on GPU 0 completes the copies.  A wait that is not satisfied within ~2 s traps. */
+ * Nothing blocks the host; vr_wait on GPU 0 completes the copies.  A wait that is not satisfied within ~10 s traps. */
 VR_API vr_status vr_gather_acquire(vr_context* ctx, void* frame0, uint32_t frames, uint32_t slot, uint32_t releases);
 VR_API vr_status vr_gather_signal(vr_context* ctx, void* frame0, uint32_t frames, uint32_t slot);
 VR_API vr_status vr_gather_collect(vr_context* ctx, uint32_t slot, uint32_t arrivals, void* dst_host, size_t row_pitch);

@@ -1158,7 +1158,7 @@ extern "C" vr_status vr_frame_unmap(vr_context* c, void* mapped) {
 //   arrived[slot]   += 1 by every rank after its band of a frame (system-scope release behind the march's stores);
 //   released[slot]  += 1 by GPU 0 after the frame has left for the host.
 // GPU 0's copy stream spins on arrived[slot] (one thread), copies, releases; a rank's render stream spins on
-// released[slot] before it marches into that slot again.  The host only enqueues.  Spins are bounded (~2 s) and trap.
+// released[slot] before it marches into that slot again.  The host only enqueues.  Spins are bounded (~10 s) and trap.
 namespace {
 struct GatherMailbox { unsigned int arrived[8]; unsigned int released[8]; };
 static_assert(sizeof(GatherMailbox) <= volrt::kGatherMailboxBytes, "mailbox size");
@@ -1175,7 +1175,7 @@ __global__ void gather_wait_kernel(const unsigned int* counter, unsigned int tar
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
         if ((int)(v - target) >= 0) return;
         __nanosleep(100);
-        if (clock64() - t0 > 4000000000ll) __trap();         // a rank died or the protocol was misused: fail loudly
+        if (clock64() - t0 > 20000000000ll) __trap();        // ~10 s: a rank died or the protocol was misused — fail loudly
     }
 }
 GatherMailbox* mailbox_of(vr_context* c, void* frame0, uint32_t frames) {
