@@ -766,11 +766,15 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
 // Lanes of a ray sit at neighbouring steps, so they mostly agree on "is there density here" and the
 // light-march branch stays coherent.  The sum and the products are re-associated and positions are
 // Pin + i*stepVec: parity is tolerance-based (as it already is for every compositing variant).
+#ifndef VOLRT_SPLIT_MIN_CTAS_OTHER
+#define VOLRT_SPLIT_MIN_CTAS_OTHER 7   // every other density source (node trees keep V[]/P[] in local memory anyway; grids need few registers)
+#endif
 #ifndef VOLRT_SPLIT_MIN_CTAS
 #define VOLRT_SPLIT_MIN_CTAS 5      // 96 registers: the two-point fBm light-march spills at 72 (7 CTAs/SM) — measured 4/5/6/7
 #endif
 template <int VARIANT, int S>
-__global__ void __launch_bounds__(128, VOLRT_SPLIT_MIN_CTAS) march_composite_split_kernel(const __grid_constant__ MarchParams P) {
+__global__ void __launch_bounds__(128, VARIANT == MARCH_FBM ? VOLRT_SPLIT_MIN_CTAS : VOLRT_SPLIT_MIN_CTAS_OTHER)
+march_composite_split_kernel(const __grid_constant__ MarchParams P) {
     constexpr int RAYS = 32 / S, RW = RAYS / 2;
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
@@ -1101,6 +1105,9 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
             const double warps = (double)p.width * rows * n_views * 0.25 / 32.0;
             const double waves = warps / (148.0 * 32.0);
             split = waves >= 3.0 ? 1 : waves >= 0.8 ? 2 : 4;
+            // a node-tree sample costs 167 registers with one thread per ray (3 CTAs/SM, issue 50 %): the split kernel's
+            // register cap serves it better until the frame is many waves deep (C2 frame: 4.8 ms -> see DESIGN 5c)
+            if (variant == MARCH_TREE) split = waves >= 10.0 ? 1 : waves >= 2.5 ? 2 : 4;
         }
         if (split == 2 || split == 4 || split == 8) {
             switch (variant) {
