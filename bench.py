@@ -666,12 +666,17 @@ def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, wo
                             "instructions share the issue ports and are not counted as flop: ncu shows the kernel 88 % issue-active "
                             "(profiles/)."})
     else:
-        fetches = steps * (4 if kw.get("density_mode", 0) == 0 else 1)
+        # frag.glsl fetches four channels per step; a channel of the resident volume that holds one value everywhere
+        # (the reference's default bake: G = 255, quirk Q1) is not fetched by the hardware-filtered march
+        const_ch = bin(int(r.stats().get("constant_channels", 0)) & 15).count("1") if args.layout == "texture" else 0
+        fetches = steps * ((4 - const_ch) if kw.get("density_mode", 0) == 0 else 1)
         peak = peaks["tex_gfetch"] * world
         out.update({"bound": "tex", "achieved": fetches / t / 1e9, "peak": peak, "unit": "Gfetch/s",
                     "peak_source": "trilinear-fetch micro-benchmark in this process (L1/L2-resident RGBA8, warp-coherent; nominal 581)",
-                    "fetches_per_frame": fetches,
-                    "note": "the volume is cache-resident or streamed once; compulsory HBM traffic is under 'hbm'"})
+                    "fetches_per_frame": fetches, "fetches_per_step_algorithmic": 4 if kw.get("density_mode", 0) == 0 else 1,
+                    "constant_channels_elided": const_ch if kw.get("density_mode", 0) == 0 else 0,
+                    "note": "the volume is cache-resident or streamed once; compulsory HBM traffic is under 'hbm'; achieved counts "
+                            "the fetches actually issued (a constant channel of the volume is not fetched)"})
     out["frac"] = out["achieved"] / out["peak"] if out["peak"] else None
     return out
 

@@ -248,6 +248,9 @@ typedef struct vr_stats {
     uint64_t light_samples;
     uint64_t skipped_steps;
     uint32_t kernel_launches;    /* kernels launched by the last vr_render                     */
+    uint32_t constant_channels;  /* bit k: channel k of the resident RGBA8 volume holds one value everywhere; the
+                                    hardware-filtered march does not fetch such a channel (the reference's default bake
+                                    leaves G constant, TestMain.cpp:59-60,76)                    */
 } vr_stats;
 
 VR_API uint32_t vr_version(void);

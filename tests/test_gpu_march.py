@@ -229,6 +229,31 @@ def test_procedural_fbm_cloud(oracle):
     assert psnr8(img, ref8) >= PSNR_MIN
 
 
+def test_constant_channels_are_not_fetched(oracle, default_volume):
+    """A channel that holds one value everywhere is replaced by that value in the hardware-filtered march.  The reference's own
+    bake has one (G = 255, TestMain.cpp:59-60,76); arbitrary constants (B = 230, A = 64) must reproduce the oracle as well."""
+    W, H = 320, 180
+    ubo0, ubo1 = scene.default_scene(20.0, -10.0)
+    rng = np.random.default_rng(3)
+    vol = rng.integers(0, 256, size=(24, 40, 32, 4), dtype=np.uint8)
+    vol[..., 2] = 230
+    vol[..., 3] = 64
+    p = oracle_params(oracle, ubo0, ubo1)
+    ovol, _keep = oracle.make_volume(vol, oracle.VOL_RGBA8)
+    ref8 = oracle.encode(oracle.render(ovol, p, W, H)[0], oracle.OUT_RGBA8_UNORM)
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM) as r:
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        assert r.stats()["constant_channels"] == 0b0010
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        assert r.stats()["constant_channels"] == 0b1100
+        r.set_params(ubo0, ubo1)
+        img = r.render()[0]
+        assert ref8[..., 0].max() > 15
+        assert max_abs8(img, ref8) <= TOL8 and psnr8(img, ref8) >= PSNR_MIN
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)        # the strict path fetches everything
+        assert r.stats()["constant_channels"] == 0
+
+
 def test_copy_only_async_of_a_second_frame(default_volume):
     """What the multi-GPU gather pipelines on GPU 0: a march stores straight into frame slot 1 of the context
     (VR_RENDER_DIRECT), then a copy-only asynchronous vr_render hands that slot to the copy stream; vr_wait completes it."""

@@ -81,7 +81,7 @@ class vr_target(C.Structure):
 class vr_stats(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("gpu_ms", C.c_float), ("rays", C.c_uint64), ("covered", C.c_uint64),
                 ("steps", C.c_uint64), ("early_terminated", C.c_uint64), ("light_samples", C.c_uint64),
-                ("skipped_steps", C.c_uint64), ("kernel_launches", C.c_uint32)]
+                ("skipped_steps", C.c_uint64), ("kernel_launches", C.c_uint32), ("constant_channels", C.c_uint32)]
 
 
 # every symbol include/volrt.h declares: name -> (restype, argtypes)

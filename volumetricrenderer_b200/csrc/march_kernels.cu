@@ -215,11 +215,15 @@ __device__ __forceinline__ float density_at(const MarchParams& P, const RayConst
         const float x4 = fmaf(p.x, P.coord_scale[3], rc.off3.x), y4 = fmaf(p.y, P.coord_scale[3], rc.off3.y), z4 = fmaf(p.z, P.coord_scale[3], rc.off3.z);
         float s1, s2, s3, s4;
         if (P.planar) {
-            // each fetch wants one channel: from a one-channel texture it moves a quarter of the bytes through L1/L2
-            s1 = tex3D<float>(P.tex_plane[0], x1, y1, z1);
-            s2 = tex3D<float>(P.tex_plane[1], x2, y2, z2);
-            s3 = tex3D<float>(P.tex_plane[2], x3, y3, z3);
-            s4 = tex3D<float>(P.tex_plane[3], x4, y4, z4);
+            // each fetch wants one channel: from a one-channel texture it moves a quarter of the bytes through L1/L2.
+            // A channel that holds one value everywhere needs no fetch at all (a filter of equal texels returns the
+            // texel): the reference's own bake leaves G at 255 throughout (TestMain.cpp:59-60,76 — SURVEY quirk Q1), so a
+            // quarter of frag.glsl's fetches read a constant.  The kernel is bound by the fetch rate; the mask is uniform.
+            const int cm = P.const_mask;
+            s1 = (cm & 1) ? P.const_val[0] : tex3D<float>(P.tex_plane[0], x1, y1, z1);
+            s2 = (cm & 2) ? P.const_val[1] : tex3D<float>(P.tex_plane[1], x2, y2, z2);
+            s3 = (cm & 4) ? P.const_val[2] : tex3D<float>(P.tex_plane[2], x3, y3, z3);
+            s4 = (cm & 8) ? P.const_val[3] : tex3D<float>(P.tex_plane[3], x4, y4, z4);
         } else {
             s1 = tex3D<float4>(P.tex, x1, y1, z1).x;
             s2 = tex3D<float4>(P.tex, x2, y2, z2).y;

@@ -360,6 +360,34 @@ __global__ void __launch_bounds__(256) deinterleave_rgba8_kernel(const uint4* __
             for (int c = 0; c < 4; ++c) planes[(size_t)c * voxels + i] = reinterpret_cast<const unsigned char*>(rgba)[i * 4 + c];
     }
 }
+// per-channel minimum and maximum of an RGBA8 volume: mm[0..3] = min, mm[4..7] = max (initialised to 255 / 0 by the caller).
+// Byte-wise SIMD min/max on the packed texel (VMNMX), one atomic pair per channel and warp.
+__global__ void __launch_bounds__(256) channel_range_rgba8_kernel(const unsigned int* __restrict__ rgba, size_t voxels, unsigned int* __restrict__ mm) {
+    unsigned int mn = 0xffffffffu, mx = 0u;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < voxels; i += (size_t)gridDim.x * blockDim.x) {
+        const unsigned int v = __ldg(rgba + i);
+        mn = __vminu4(mn, v);
+        mx = __vmaxu4(mx, v);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = __vminu4(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = __vmaxu4(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            atomicMin(mm + c, (mn >> (8 * c)) & 0xffu);
+            atomicMax(mm + 4 + c, (mx >> (8 * c)) & 0xffu);
+        }
+    }
+}
+cudaError_t launch_channel_range_rgba8(const uint8_t* rgba, size_t voxels, unsigned int* mm8, cudaStream_t s) {
+    const size_t want = (voxels + 256 * 16 - 1) / (256 * 16);
+    channel_range_rgba8_kernel<<<(unsigned)(want < 1 ? 1 : want > 148 * 8 ? 148 * 8 : want), 256, 0, s>>>((const unsigned int*)rgba, voxels, mm8);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, cudaStream_t s) {
     const size_t quads = (voxels + 3) / 4;
     deinterleave_rgba8_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, s>>>((const uint4*)rgba, planes4, voxels);

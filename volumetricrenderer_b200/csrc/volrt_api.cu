@@ -52,6 +52,9 @@ struct vr_context {
     cudaTextureObject_t plane_tex[4] = {};
     unsigned char* plane_lin = nullptr;    // de-interleave scratch (4 planes)
     bool planar = false;
+    uint32_t const_mask = 0;           // channels of the RGBA8 volume that hold a single value (bit k), and that value as the sampler returns it
+    float const_val[4] = {0, 0, 0, 0};
+    unsigned int* d_chan_mm = nullptr; // 8 words: per-channel min / max of the last RGBA8 volume
     uint8_t* occupied = nullptr;
     uint8_t* brick_dist = nullptr;         // 2 planes: the distance map and the scratch of its passes
     alignas(64) unsigned char tensor_map[128] = {};   // BRICK layout: CUtensorMap over `lin`
@@ -233,6 +236,7 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
     if (c->frame) cudaFree(c->frame);
     if (c->frame2) cudaFree(c->frame2);
+    if (c->d_chan_mm) cudaFree(c->d_chan_mm);
     for (int i = 0; i < 2; ++i) {
         if (c->ev_render_done[i]) cudaEventDestroy(c->ev_render_done[i]);
         if (c->ev_copy_done[i]) cudaEventDestroy(c->ev_copy_done[i]);
@@ -264,6 +268,8 @@ extern "C" void vr_destroy(vr_context* c) {
 // build the texture object (TEXTURE layout) and the occupancy grid from c->lin
 static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
     const uint32_t layout = d.layout == VR_LAYOUT_AUTO ? (uint32_t)VR_LAYOUT_TEXTURE : d.layout;
+    bool range_pending = false;
+    c->const_mask = 0;
     if (layout == VR_LAYOUT_TEXTURE) {
         cudaChannelFormatDesc cd;
         switch (d.format) {
@@ -297,6 +303,14 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
             const size_t vox = (size_t)d.width * d.height * d.depth;
             if (!c->plane_lin) VR_CUDA(c, cudaMalloc(&c->plane_lin, 4 * vox));
             VR_CUDA(c, launch_deinterleave_rgba8((const uint8_t*)c->lin, c->plane_lin, vox, c->stream));
+            static const bool want_const = [] { const char* e = getenv("VOLRT_CONST_CHANNELS"); return !e || atoi(e) != 0; }();
+            if (want_const) {
+                static const unsigned int init[8] = {255u, 255u, 255u, 255u, 0u, 0u, 0u, 0u};
+                if (!c->d_chan_mm) VR_CUDA(c, cudaMalloc(&c->d_chan_mm, sizeof init));
+                VR_CUDA(c, cudaMemcpyAsync(c->d_chan_mm, init, sizeof init, cudaMemcpyHostToDevice, c->stream));
+                VR_CUDA(c, launch_channel_range_rgba8((const uint8_t*)c->lin, vox, c->d_chan_mm, c->stream));
+                range_pending = true;
+            }
             const cudaChannelFormatDesc cd1 = cudaCreateChannelDesc<unsigned char>();
             for (int k = 0; k < 4; ++k) {
                 if (!c->plane_array[k]) VR_CUDA(c, cudaMalloc3DArray(&c->plane_array[k], &cd1, ext));
@@ -353,7 +367,13 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
     c->stats.kernel_launches = c->fill_launches + 4;       // + the occupancy kernel and the 3 distance passes
     c->fill_launches = 0;
     std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
+    unsigned int mm[8];
+    if (range_pending) VR_CUDA(c, cudaMemcpyAsync(mm, c->d_chan_mm, sizeof mm, cudaMemcpyDeviceToHost, c->stream));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (range_pending)
+        for (int k = 0; k < 4; ++k)
+            if (mm[k] == mm[4 + k]) { c->const_mask |= 1u << k; c->const_val[k] = (float)mm[k] / 255.0f; }
+    c->stats.constant_channels = c->const_mask;
     c->vdesc = d;
     c->vdesc.layout = layout;
     c->has_volume = true;
@@ -929,6 +949,8 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     const vr_volume_desc& d = c->vdesc;
     m.tex = c->tex; m.lin = c->lin;
     m.planar = c->planar ? 1 : 0;
+    m.const_mask = c->planar ? (int)c->const_mask : 0;
+    for (int k = 0; k < 4; ++k) m.const_val[k] = c->const_val[k];
     for (int k = 0; k < 4; ++k) m.tex_plane[k] = c->plane_tex[k];
     m.vw = (int)d.width; m.vh = (int)d.height; m.vd = (int)d.depth;
     m.vol_format = (int)d.format; m.address_mode = (int)d.address_mode;

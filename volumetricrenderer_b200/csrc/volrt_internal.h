@@ -65,6 +65,8 @@ struct MarchParams {
     cudaTextureObject_t tex;    // TEXTURE layout
     cudaTextureObject_t tex_plane[4];   // RGBA8 volume as four R8 textures (planar != 0)
     int planar;
+    int const_mask;             // bit k: channel k of the RGBA8 volume has one value everywhere -> no fetch, const_val[k]
+    float const_val[4];
     const void* lin;            // LINEAR layout (x fastest)
     int vw, vh, vd;
     int vol_format;             // vr_volume_format
@@ -115,6 +117,7 @@ cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_r
 cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s);
 cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int address_mode,
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
+cudaError_t launch_channel_range_rgba8(const uint8_t* rgba, size_t voxels, unsigned int* mm8, cudaStream_t s);
 cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, cudaStream_t s);
 cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_t* tmp, int bx, int by, int bz, cudaStream_t s);
 // ---- peak_kernels.cu: measured roofline denominators
