@@ -69,6 +69,8 @@ struct Ray {
 // returns false for pixels the rasteriser would not shade (they keep the clear colour)
 __device__ __forceinline__ bool setup_ray(const MarchParams& P, const ViewConst* __restrict__ V, int px, int py,
                                           float step_size, Ray& r) {
+    // outside the cube's screen rectangle (ViewConst::rect, from the projected corners): nothing to set up
+    if (px < V->rect[0] || py < V->rect[1] || px >= V->rect[2] || py >= V->rect[3]) return false;
     // pixel centre -> NDC (viewport (0,0,W,H), TestMain.cpp:198-205)
     float x = sub(mul(add((float)px, 0.5f), dvd(2.0f, (float)P.width)), 1.0f);
     float y = sub(mul(add((float)py, 0.5f), dvd(2.0f, (float)P.height)), 1.0f);

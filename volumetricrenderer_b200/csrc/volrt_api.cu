@@ -826,7 +826,7 @@ static bool inverse_d(const double* m, double* inv) {                      // co
 }
 
 // ubo0: ObjectShaderData (vert.glsl:4-9), ubo1: GlobalShaderData as std140 reads it (frag.glsl:9-14)
-static bool decode_view(const unsigned char* ubo0, uint32_t n0, const unsigned char* ubo1, uint32_t n1, ViewConst* v) {
+static bool decode_view(const unsigned char* ubo0, uint32_t n0, const unsigned char* ubo1, uint32_t n1, uint32_t W, uint32_t H, ViewConst* v) {
     float u0[48], u1[36];
     std::memset(u0, 0, sizeof u0); std::memset(u1, 0, sizeof u1);
     std::memcpy(u0, ubo0, n0 < 192u ? n0 : 192u);      // bytes past the descriptor range read as zero
@@ -841,6 +841,30 @@ static bool decode_view(const unsigned char* ubo0, uint32_t n0, const unsigned c
         v->model[i] = Model[i]; v->w2l[i] = u1[i];
     }
     for (int i = 0; i < 3; ++i) v->cam[i] = u1[16 + i];
+    // screen rectangle of the cube [-1,1]^3 (TestMain.cpp:94-112) under Projection * View * Model, in the pixel convention of
+    // setup_ray (centre of pixel px at NDC (px + 1/2) * 2/W - 1).  The silhouette of a convex body whose corners are all in
+    // front of the camera is the hull of the projected corners, so their bounding rectangle holds every covered pixel.
+    v->rect[0] = 0; v->rect[1] = 0; v->rect[2] = (int)W; v->rect[3] = (int)H;
+    {
+        double lo[2] = {1e300, 1e300}, hi[2] = {-1e300, -1e300};
+        bool all_front = true;
+        for (int k = 0; k < 8 && all_front; ++k) {
+            const double cx = (k & 1) ? 1.0 : -1.0, cy = (k & 2) ? 1.0 : -1.0, cz = (k & 4) ? 1.0 : -1.0;
+            double w4[4], c4[4];
+            for (int r = 0; r < 4; ++r) w4[r] = md[r] * cx + md[4 + r] * cy + md[8 + r] * cz + md[12 + r];
+            for (int r = 0; r < 4; ++r) c4[r] = pv[r] * w4[0] + pv[4 + r] * w4[1] + pv[8 + r] * w4[2] + pv[12 + r] * w4[3];
+            if (!(c4[3] > 1e-6) || !(w4[3] == w4[3])) { all_front = false; break; }
+            const double px = (c4[0] / c4[3] + 1.0) * 0.5 * (double)W - 0.5, py = (c4[1] / c4[3] + 1.0) * 0.5 * (double)H - 0.5;
+            if (!(px == px) || !(py == py)) { all_front = false; break; }
+            lo[0] = px < lo[0] ? px : lo[0]; hi[0] = px > hi[0] ? px : hi[0];
+            lo[1] = py < lo[1] ? py : lo[1]; hi[1] = py > hi[1] ? py : hi[1];
+        }
+        if (all_front) {
+            auto clampi = [](double x, int a, int b) { return x < (double)a ? a : x > (double)b ? b : (int)x; };
+            v->rect[0] = clampi(std::floor(lo[0]) - 2.0, 0, (int)W); v->rect[1] = clampi(std::floor(lo[1]) - 2.0, 0, (int)H);
+            v->rect[2] = clampi(std::ceil(hi[0]) + 3.0, 0, (int)W); v->rect[3] = clampi(std::ceil(hi[1]) + 3.0, 0, (int)H);
+        }
+    }
     const float* MS = u1 + 20;                          // std140: MediaScroll at byte 80
     for (int col = 0; col < 3; ++col) {
         v->scroll_y[col] = MS[col * 4 + 1];             // (MS[0].y, MS[1].y, MS[2].y)  frag.glsl:67
@@ -877,14 +901,14 @@ extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
     VR_CUDA(c, cudaSetDevice(c->device));
     if (views == 1 && !p->view_ubos) {
         // the reference's case: one view per frame.  Its constants travel in the kernel parameters.
-        if (!decode_view((const unsigned char*)p->ubo0, p->ubo0_size, (const unsigned char*)p->ubo1, p->ubo1_size, &c->view0))
+        if (!decode_view((const unsigned char*)p->ubo0, p->ubo0_size, (const unsigned char*)p->ubo1, p->ubo1_size, c->width, c->height, &c->view0))
             return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: Model or Projection*View is singular");
     } else {
         // the pinned staging block may still be in flight from the previous batch
         if (c->params_pending) { VR_CUDA(c, cudaEventSynchronize(c->ev_params)); c->params_pending = false; }
         for (uint32_t k = 0; k < views; ++k) {
             const unsigned char* b = (const unsigned char*)p->view_ubos + (size_t)k * 336;
-            if (!decode_view(b, 192, b + 192, 144, &c->h_views[k]))
+            if (!decode_view(b, 192, b + 192, 144, c->width, c->height, &c->h_views[k]))
                 return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_set_params: Model or Projection*View is singular");
         }
         // d_views may still be read by a march that was enqueued on a caller's stream

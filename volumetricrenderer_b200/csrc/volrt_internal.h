@@ -24,6 +24,10 @@ struct ViewConst {
     float scroll_y[3];      // (MS[0].y, MS[1].y, MS[2].y)           frag.glsl:67
     float scroll_z[3];      // (MS[0].z, ...)                        frag.glsl:68
     float scroll_w[3];      // (MS[0].w, ...)                        frag.glsl:69
+    // Pixels [x0,x1) x [y0,y1) that can see the cube: the bounding rectangle of its eight projected corners (+2 px), or
+    // the whole frame when a corner is not in front of the camera.  Four fifths of the reference's frame lie outside it
+    // and keep the clear colour without a ray set-up.
+    int rect[4];            // x0, y0, x1, y1
 };
 
 struct BrickInfo {          // min-max grid for empty-space skipping (8^3 voxel bricks)
