@@ -735,7 +735,10 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
         const GradLut* no_lut = nullptr;
         const int n = ray.n;
         int i = sub;
-        constexpr int BATCH = 2;
+#ifndef VOLRT_SPLIT_BATCH
+#define VOLRT_SPLIT_BATCH 2
+#endif
+        constexpr int BATCH = VOLRT_SPLIT_BATCH;
         for (; i + (BATCH - 1) * S < n; i += BATCH * S) {
             float d[BATCH];
 #pragma unroll
