@@ -89,9 +89,21 @@ __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
 #endif
 struct GradLutFixed {};     // tag type: "the table is at VOLRT_LUT_FIXED_ADDR"
 
+#ifndef VOLRT_HASH_SHIFT_ON_FMA
+#define VOLRT_HASH_SHIFT_ON_FMA 0
+#endif
 __device__ __forceinline__ unsigned int grad_lut_offset(int t) {
     const unsigned int h16 = (unsigned int)t * (0x27d4eb2du << 4);     // = h << 4 (mod 2^32)
+#if VOLRT_HASH_SHIFT_ON_FMA
+    // h16 >> 15 as the high word of h16 * 2^17: an IMAD.HI on the FMA pipe instead of a SHF on the (half-rate) ALU pipe.
+    // Measured on B200: slower (C2 1.769 -> 1.936 ms, C3 17.17 -> 18.95) — IMAD.HI costs more than the shift it replaces.
+    unsigned int k, sh;
+    asm("mov.u32 %0, 0x20000;" : "=r"(k));
+    asm("mul.hi.u32 %0, %1, %2;" : "=r"(sh) : "r"(h16), "r"(k));
+    return (h16 ^ sh) & 0xF0u;
+#else
     return (h16 ^ (h16 >> 15)) & 0xF0u;
+#endif
 }
 __device__ __forceinline__ float4 grad_lut_fetch(const GradLut* lut, int t) {
     return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + grad_lut_offset(t));
