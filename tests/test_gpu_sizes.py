@@ -212,3 +212,33 @@ def test_occupancy_grid_aprons(fmt, shape):
     if ch == 1:
         assert s["skipped_steps"] > 0
         assert np.array_equal(plain.view(np.uint32), skipped.view(np.uint32))
+
+
+def test_c5_machinery_properties_at_256():
+    """BASELINE config 5 at a size that runs in a second: a thresholded fp16 smoke grid, compositing with early termination,
+    several views.  Size-independent properties of the texture-filtered path: (1) empty-space skipping does not change the
+    frame; (2) the march with two steps' fetches in flight and the brick index taken from the float's bits equals the
+    counting build, which walks one step at a time with the truncating index; (3) early termination only ever removes
+    light, by less than its threshold per channel.  (1) and (2) hold to 3e-3 (under half of 2/255) rather than to the bit: a
+    leap, and the several-lanes-per-ray kernel that serves frames without early termination, place a sample with one FMA
+    where the plain loop adds step by step — an ulp the 8-bit filter weights may or may not see, amplified by sigma_t = 400."""
+    W, H, NV = 480, 270, 4
+    views = scene.orbit_views(64)[::16][:NV]
+    kw = dict(density_mode=1, max_steps=256, sample_scale=1.0, sigma_t=400.0, ambient=1.0, sun_color=[0.0, 0.0, 0.0])
+    with vr.Renderer(W, H, capi.OUT_RGBA32F, max_views=NV) as r:
+        r.generate_volume(size=256, format=capi.VOL_R16F, layout=capi.LAYOUT_TEXTURE, threshold=0.07)
+        frames = {}
+        for skip in (0, 1):
+            for eps in (0.0, 1.0 / 512):
+                r.set_params(view_ubos=views, skip_empty=skip, early_term_eps=eps, **kw)
+                fast = r.render().copy()
+                counted = r.render(flags=capi.RENDER_STATS).copy()
+                st = r.stats()
+                assert np.abs(fast - counted).max() <= 3e-3, (skip, eps)
+                assert st["covered"] > 0 and (st["skipped_steps"] > 0) == bool(skip)
+                assert (st["early_terminated"] > 0) == (eps > 0)
+                frames[(skip, eps)] = fast
+        for eps in (0.0, 1.0 / 512):
+            assert np.abs(frames[(0, eps)] - frames[(1, eps)]).max() <= 3e-3
+        full, cut = frames[(1, 0.0)][..., :3], frames[(1, 1.0 / 512)][..., :3]
+        assert (cut <= full + 1e-7).all() and (full - cut).max() <= 1.0 / 512 + 1e-6 and full.max() > 0.5
