@@ -229,6 +229,35 @@ def test_procedural_fbm_cloud(oracle):
     assert psnr8(img, ref8) >= PSNR_MIN
 
 
+@pytest.mark.parametrize("eye,center,fov", [((1.9, 1.7, 1.6), (0.0, 0.0, 0.0), 45.0),      # the cube overflows the frame
+                                            ((1.25, 0.3, 0.2), (0.0, 0.1, 0.0), 70.0),     # corners behind the near plane
+                                            ((6.0, -5.0, 4.0), (1.5, 0.0, 0.5), 30.0),     # small, off-centre, partly off-screen
+                                            ((0.4, 0.3, 0.2), (0.0, 0.0, 0.0), 45.0)])     # camera inside the cube: nothing drawn
+def test_screen_rectangle_is_conservative(oracle, eye, center, fov):
+    """The ray set-up is skipped outside the bounding rectangle of the cube's projected corners (whole frame when a corner
+    is not in front of the camera).  Cameras the reference's orbit never reaches: the strict path must still equal the
+    oracle bit for bit, i.e. no covered pixel was culled."""
+    W, H = 320, 200
+    rng = np.random.default_rng(11)
+    vol = rng.integers(0, 256, size=(16, 16, 16, 4), dtype=np.uint8)
+    ubo0, ubo1 = scene.default_scene(15.0, -20.0)
+    ubo0[16:32] = scene.look_at(eye, center, (0.0, 0.0, 1.0))
+    proj = scene.perspective(scene.radians(fov), np.float32(W) / np.float32(H), 0.1, 20.0)
+    proj[5] *= np.float32(-1.0)
+    ubo0[32:48] = proj
+    ubo1[16:19] = eye
+    p = oracle_params(oracle, ubo0, ubo1)
+    ref, st, _ = _oracle_frame(oracle, vol, oracle.VOL_RGBA8, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0, ubo1)
+        img = r.render(flags=capi.RENDER_STATS)[0]
+        s = r.stats()
+    assert s["covered"] == st["covered"] and s["steps"] == st["steps"]
+    assert (st["covered"] == 0) == (max(abs(c) for c in eye) < 1.0)
+    assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
+
+
 def test_constant_channels_are_not_fetched(oracle, default_volume):
     """A channel that holds one value everywhere is replaced by that value in the hardware-filtered march.  The reference's own
     bake has one (G = 255, TestMain.cpp:59-60,76); arbitrary constants (B = 230, A = 64) must reproduce the oracle as well."""
