@@ -530,13 +530,28 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
                 } else {
                     rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
                 }
+            } else if constexpr (VARIANT == MARCH_TREE && !STATS) {
+                rho = 0.0f;                         // evaluated below, in the light-march loop's iteration 0 (one interpreter call site)
             } else {
                 rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
+            }
+            float tree_sumL = 0.0f;
+            if constexpr (VARIANT == MARCH_TREE && !STATS) {
+                f3 q = p;
+                for (int j = 0; j <= P.light_steps; ++j) {
+                    const float d = density_at<VARIANT>(P, rc, unorm, &lut, q);
+                    if (j == 0) { rho = d; if (!(rho > 0.0f)) break; }
+                    else tree_sumL += d;
+                    q = {q.x + lv.x, q.y + lv.y, q.z + lv.z};
+                    if (!inside01(q)) break;
+                }
             }
             if (rho > 0.0f) {                       // rho == 0 contributes exactly nothing
                 float a = 1.0f - expf(-P.sigma_t * rho * step_size);
                 float S = 1.0f;
-                if (!STATS && P.light_steps > 0) {
+                if constexpr (VARIANT == MARCH_TREE && !STATS) {
+                    if (P.light_steps > 0) S = expf(-P.sigma_t * tree_sumL * P.light_step_len);
+                } else if (!STATS && P.light_steps > 0) {
                     S = expf(-P.sigma_t * light_sum<VARIANT>(P, rc, unorm, &lut, p, lv, skip) * P.light_step_len);
                 } else if (P.light_steps > 0) {
                     float sumL = 0.0f;
@@ -827,10 +842,28 @@ march_composite_split_kernel(const __grid_constant__ MarchParams P) {
             const float fi = (float)i;
             const f3 p = {fmaf(ray.step.x, fi, ray.pin.x), fmaf(ray.step.y, fi, ray.pin.y), fmaf(ray.step.z, fi, ray.pin.z)};
             float rho = 0.0f;
-            if (!(skip && !brick_occupied(P, p))) rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
-            if (rho > 0.0f) {
-                a = 1.0f - expf(-P.sigma_t * rho * step_size);
-                if (P.light_steps > 0) Sl = expf(-P.sigma_t * light_sum<VARIANT>(P, rc, unorm, &lut, p, lv, skip) * P.light_step_len);
+            if constexpr (VARIANT == MARCH_TREE) {
+                // one call site for the interpreter: the primary sample is iteration 0 of the light-march loop.  With two
+                // inlined copies the kernel outgrew the instruction cache (`no_instruction` 1.9 stalls per issue).
+                float sumL = 0.0f;
+                f3 q = p;
+                for (int j = 0; j <= P.light_steps; ++j) {
+                    const float d = density_at<VARIANT>(P, rc, unorm, &lut, q);
+                    if (j == 0) { rho = d; if (!(rho > 0.0f)) break; }
+                    else sumL += d;
+                    q = {q.x + lv.x, q.y + lv.y, q.z + lv.z};
+                    if (!inside01(q)) break;
+                }
+                if (rho > 0.0f) {
+                    a = 1.0f - expf(-P.sigma_t * rho * step_size);
+                    if (P.light_steps > 0) Sl = expf(-P.sigma_t * sumL * P.light_step_len);
+                }
+            } else {
+                if (!(skip && !brick_occupied(P, p))) rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
+                if (rho > 0.0f) {
+                    a = 1.0f - expf(-P.sigma_t * rho * step_size);
+                    if (P.light_steps > 0) Sl = expf(-P.sigma_t * light_sum<VARIANT>(P, rc, unorm, &lut, p, lv, skip) * P.light_step_len);
+                }
             }
         }
         // inclusive prefix product of (1 - a) over the S lanes of the ray
