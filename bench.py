@@ -663,8 +663,9 @@ def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, wo
                     "note": "achieved = primary steps x SURVEY 8(d) flop/step (every step owes 1+L noise samples of 5 octaves x 60 + 20 flop, "
                             "+26 for the integrator). The kernel evaluates fewer (achieved_executed): steps whose density is exactly 0 "
                             "owe no light-march and light samples outside the box are not taken. INT32 hash / LDS / conversion "
-                            "instructions share the issue ports and are not counted as flop: ncu shows the kernel 88 % issue-active "
-                            "(profiles/)."})
+                            "instructions share the issue ports and are not counted as flop: ncu shows the kernel 78 % issue-active on "
+                            "1.51 G warp instructions per C2 frame, the light-march's lattice arithmetic packed two samples per "
+                            "instruction (FFMA2) (profiles/r01_march_fbm_pairs.txt)."})
     else:
         # frag.glsl fetches four channels per step; a channel of the resident volume that holds one value everywhere
         # (the reference's default bake: G = 255, quirk Q1) is not fetched by the hardware-filtered march
