@@ -296,7 +296,7 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
         td.readMode = d.format == VR_VOL_R16F ? cudaReadModeElementType : cudaReadModeNormalizedFloat;
         td.normalizedCoords = 1;
         if (!c->tex) VR_CUDA(c, cudaCreateTextureObject(&c->tex, &rd, &td, nullptr));
-        // planar copies of an RGBA8 volume (decision 11); VOLRT_PLANAR=0 keeps the interleaved texture only
+        // planar copies of an RGBA8 volume (decision 10); VOLRT_PLANAR=0 keeps the interleaved texture only
         static const bool want_planar = [] { const char* e = getenv("VOLRT_PLANAR"); return !e || atoi(e) != 0; }();
         c->planar = false;
         if (d.format == VR_VOL_RGBA8_UNORM && want_planar) {
