@@ -344,11 +344,18 @@ cudaError_t launch_occupancy_from_pyramid(const float* level0, int channels, uin
     return cudaGetLastError();
 }
 
-// RGBA8 (x fastest) -> four tightly packed R8 planes; 4 voxels per thread so that every plane store is a 32-bit word
-__global__ void __launch_bounds__(256) deinterleave_rgba8_kernel(const uint4* __restrict__ rgba, unsigned char* __restrict__ planes, size_t voxels) {
+// RGBA8 (x fastest) -> four tightly packed R8 planes; 4 voxels per thread so that every plane store is a 32-bit word.
+// mm (may be null): per-channel min (mm[0..3], initialised >= 255) and max (mm[4..7], initialised 0) of the volume, folded in
+// here because this kernel reads every texel anyway (as a separate pass it cost the 128^3 bake 0.05 ms): byte-wise SIMD
+// min/max on the packed texels (VMNMX), one atomic pair per channel and CTA.
+__global__ void __launch_bounds__(256) deinterleave_rgba8_kernel(const uint4* __restrict__ rgba, unsigned char* __restrict__ planes, size_t voxels,
+                                                                 unsigned int* __restrict__ mm) {
     const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int mn = 0xffffffffu, mx = 0u;
     if (q * 4 + 3 < voxels) {
         const uint4 v = __ldg(rgba + q);
+        mn = __vminu4(__vminu4(v.x, v.y), __vminu4(v.z, v.w));
+        mx = __vmaxu4(__vmaxu4(v.x, v.y), __vmaxu4(v.z, v.w));
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             const unsigned sel = 0x0040u + 0x0011u * c;              // byte c of the first word, byte c of the second
@@ -356,41 +363,34 @@ __global__ void __launch_bounds__(256) deinterleave_rgba8_kernel(const uint4* __
             reinterpret_cast<unsigned*>(planes + (size_t)c * voxels)[q] = w;
         }
     } else {
-        for (size_t i = q * 4; i < voxels; ++i)
+        for (size_t i = q * 4; i < voxels; ++i) {
+            const unsigned int t = reinterpret_cast<const unsigned int*>(rgba)[i];
+            mn = __vminu4(mn, t);
+            mx = __vmaxu4(mx, t);
             for (int c = 0; c < 4; ++c) planes[(size_t)c * voxels + i] = reinterpret_cast<const unsigned char*>(rgba)[i * 4 + c];
+        }
     }
-}
-// per-channel minimum and maximum of an RGBA8 volume: mm[0..3] = min, mm[4..7] = max (initialised to 255 / 0 by the caller).
-// Byte-wise SIMD min/max on the packed texel (VMNMX), one atomic pair per channel and warp.
-__global__ void __launch_bounds__(256) channel_range_rgba8_kernel(const unsigned int* __restrict__ rgba, size_t voxels, unsigned int* __restrict__ mm) {
-    unsigned int mn = 0xffffffffu, mx = 0u;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < voxels; i += (size_t)gridDim.x * blockDim.x) {
-        const unsigned int v = __ldg(rgba + i);
-        mn = __vminu4(mn, v);
-        mx = __vmaxu4(mx, v);
-    }
+    if (mm) {
+        __shared__ unsigned int s_mn[8], s_mx[8];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        mn = __vminu4(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-        mx = __vmaxu4(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    }
-    if ((threadIdx.x & 31) == 0) {
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            atomicMin(mm + c, (mn >> (8 * c)) & 0xffu);
-            atomicMax(mm + 4 + c, (mx >> (8 * c)) & 0xffu);
+        for (int o = 16; o > 0; o >>= 1) {
+            mn = __vminu4(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+            mx = __vmaxu4(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        }
+        if ((threadIdx.x & 31) == 0) { s_mn[threadIdx.x >> 5] = mn; s_mx[threadIdx.x >> 5] = mx; }
+        __syncthreads();
+        if (threadIdx.x < 4) {
+            const int c = threadIdx.x;
+            unsigned int lo = 255u, hi = 0u;
+            for (int w = 0; w < 8; ++w) { lo = min(lo, (s_mn[w] >> (8 * c)) & 0xffu); hi = max(hi, (s_mx[w] >> (8 * c)) & 0xffu); }
+            atomicMin(mm + c, lo);
+            atomicMax(mm + 4 + c, hi);
         }
     }
 }
-cudaError_t launch_channel_range_rgba8(const uint8_t* rgba, size_t voxels, unsigned int* mm8, cudaStream_t s) {
-    const size_t want = (voxels + 256 * 16 - 1) / (256 * 16);
-    channel_range_rgba8_kernel<<<(unsigned)(want < 1 ? 1 : want > 148 * 8 ? 148 * 8 : want), 256, 0, s>>>((const unsigned int*)rgba, voxels, mm8);
-    return cudaGetLastError();
-}
-
-cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, cudaStream_t s) {
+cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, unsigned int* mm8, cudaStream_t s) {
     const size_t quads = (voxels + 3) / 4;
-    deinterleave_rgba8_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, s>>>((const uint4*)rgba, planes4, voxels);
+    deinterleave_rgba8_kernel<<<(unsigned)((quads + 255) / 256), 256, 0, s>>>((const uint4*)rgba, planes4, voxels, mm8);
     return cudaGetLastError();
 }
 

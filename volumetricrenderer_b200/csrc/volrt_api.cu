@@ -302,15 +302,15 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
         if (d.format == VR_VOL_RGBA8_UNORM && want_planar) {
             const size_t vox = (size_t)d.width * d.height * d.depth;
             if (!c->plane_lin) VR_CUDA(c, cudaMalloc(&c->plane_lin, 4 * vox));
-            VR_CUDA(c, launch_deinterleave_rgba8((const uint8_t*)c->lin, c->plane_lin, vox, c->stream));
             static const bool want_const = [] { const char* e = getenv("VOLRT_CONST_CHANNELS"); return !e || atoi(e) != 0; }();
             if (want_const) {
-                static const unsigned int init[8] = {255u, 255u, 255u, 255u, 0u, 0u, 0u, 0u};
-                if (!c->d_chan_mm) VR_CUDA(c, cudaMalloc(&c->d_chan_mm, sizeof init));
-                VR_CUDA(c, cudaMemcpyAsync(c->d_chan_mm, init, sizeof init, cudaMemcpyHostToDevice, c->stream));
-                VR_CUDA(c, launch_channel_range_rgba8((const uint8_t*)c->lin, vox, c->d_chan_mm, c->stream));
+                // min words start at 0xFFFFFFFF, max words at 0; the de-interleave kernel folds the texels' bytes into them
+                if (!c->d_chan_mm) VR_CUDA(c, cudaMalloc(&c->d_chan_mm, 8 * sizeof(unsigned int)));
+                VR_CUDA(c, cudaMemsetAsync(c->d_chan_mm, 0xFF, 4 * sizeof(unsigned int), c->stream));
+                VR_CUDA(c, cudaMemsetAsync(c->d_chan_mm + 4, 0, 4 * sizeof(unsigned int), c->stream));
                 range_pending = true;
             }
+            VR_CUDA(c, launch_deinterleave_rgba8((const uint8_t*)c->lin, c->plane_lin, vox, want_const ? c->d_chan_mm : nullptr, c->stream));
             const cudaChannelFormatDesc cd1 = cudaCreateChannelDesc<unsigned char>();
             for (int k = 0; k < 4; ++k) {
                 if (!c->plane_array[k]) VR_CUDA(c, cudaMalloc3DArray(&c->plane_array[k], &cd1, ext));

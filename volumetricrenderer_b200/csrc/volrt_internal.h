@@ -121,8 +121,7 @@ cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_r
 cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s);
 cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int address_mode,
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
-cudaError_t launch_channel_range_rgba8(const uint8_t* rgba, size_t voxels, unsigned int* mm8, cudaStream_t s);
-cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, cudaStream_t s);
+cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, unsigned int* mm8, cudaStream_t s);   // mm8 may be null
 cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_t* tmp, int bx, int by, int bz, cudaStream_t s);
 // ---- peak_kernels.cu: measured roofline denominators
 cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s);
