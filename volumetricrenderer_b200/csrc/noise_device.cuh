@@ -344,19 +344,32 @@ __device__ __forceinline__ f2 perlin3_lut2(LUT lut, int seed, f2 x, f2 y, f2 z) 
     return lerp2(a, b, zs);
 }
 
-template <class LUT>
-__device__ __forceinline__ f2 fbm_perlin2(LUT lut, const FbmField& F, f2 x, f2 y, f2 z) {
+// OCT > 0: the octave count as a compile-time constant — the loop is unrolled, so the independent octaves (their positions
+// are x * lacunarity^i) interleave in the instruction stream instead of each waiting for its own dependent chain.
+// Same operations on the same values in the same order per octave and in the sum: the result does not change.
+#ifndef VOLRT_FBM_UNROLL_OCTAVES
+#define VOLRT_FBM_UNROLL_OCTAVES 0
+#endif
+template <int OCT, class LUT>
+__device__ __forceinline__ f2 fbm_perlin2_n(LUT lut, const FbmField& F, f2 x, f2 y, f2 z) {
+    const int n = OCT > 0 ? OCT : F.octaves;
     int seed = F.seed;
     float amp = F.bounding * kPerlinScale;
     const f2 lac = splat2(F.lacunarity);
     f2 sum = mul2(perlin3_lut2(lut, seed, x, y, z), splat2(amp));
-    for (int i = 1; i < F.octaves; ++i) {
+#pragma unroll
+    for (int i = 1; i < n; ++i) {
         seed += 1;
         amp *= F.gain;
         x = mul2(x, lac); y = mul2(y, lac); z = mul2(z, lac);
         sum = fma2(perlin3_lut2(lut, seed, x, y, z), splat2(amp), sum);
     }
     return sum;
+}
+template <class LUT>
+__device__ __forceinline__ f2 fbm_perlin2(LUT lut, const FbmField& F, f2 x, f2 y, f2 z) {
+    if (VOLRT_FBM_UNROLL_OCTAVES > 0 && F.octaves == VOLRT_FBM_UNROLL_OCTAVES) return fbm_perlin2_n<VOLRT_FBM_UNROLL_OCTAVES>(lut, F, x, y, z);
+    return fbm_perlin2_n<0>(lut, F, x, y, z);
 }
 
 __device__ __forceinline__ float fbm_edge(const FbmField& F, float ux, float uy, float uz) {
