@@ -651,11 +651,12 @@ __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
 #define VOLRT_CTA_WY 2          // warps per CTA along y (4 pixels each)
 #endif
 #ifndef VOLRT_DIRECT_MIN_CTAS
-#define VOLRT_DIRECT_MIN_CTAS 1     // register cap of the direct kernel (binds for the fBm variant only)
-#endif
+#define VOLRT_DIRECT_MIN_CTAS 4     // register cap of the direct fBm kernel: 128.  With the octave loop unrolled (noise_device.cuh) ptxas
+#endif                              // would take 223 registers (2 CTAs/SM, C2 1.96 ms); measured 3 / 4 / 5 / 6 CTAs: 1.797 / 1.72 / 1.76 / 1.76 ms
+
 constexpr int kCtaWx = VOLRT_CTA_WX, kCtaWy = VOLRT_CTA_WY, kCtaThreads = 32 * kCtaWx * kCtaWy;
 template <int VARIANT, bool COMPOSITE, bool STATS>
-__global__ void __launch_bounds__(kCtaThreads, VOLRT_DIRECT_MIN_CTAS) march_kernel(const __grid_constant__ MarchParams P) {
+__global__ void __launch_bounds__(kCtaThreads, VARIANT == MARCH_FBM ? VOLRT_DIRECT_MIN_CTAS : 1) march_kernel(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     __shared__ MarchSmem<LINEAR> smem;
     float* const unorm = smem.unorm;
