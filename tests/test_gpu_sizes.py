@@ -47,6 +47,29 @@ def test_ragged_frames_every_mapping(oracle, W, H):
         assert np.abs(r.render()[0] - refc).max() <= 1e-4
 
 
+@pytest.mark.parametrize("shape", [(5, 5, 5), (27, 13, 10), (3, 3, 3), (1, 1, 1), (7, 1, 2)])
+def test_rgba8_texture_layout_with_a_voxel_count_not_divisible_by_four(oracle, shape):
+    """The planar copies of an RGBA8 volume are written as 32-bit words per plane; plane k starts at k * voxels bytes, which is
+    word aligned only when voxels % 4 == 0.  Odd volumes must take the byte path (a misaligned store is a sticky fault)."""
+    W, H = 96, 54
+    rng = np.random.default_rng(shape[0] * 100 + shape[1] * 10 + shape[2])
+    vol = rng.integers(0, 256, size=shape + (4,), dtype=np.uint8)
+    vol[..., 1] = 200                                   # a constant channel: exercises the per-channel min/max of the byte path
+    u0, u1 = scene.default_scene(11.0, 23.0)
+    p = oracle_params(oracle, u0, u1)
+    ov, _k = oracle.make_volume(vol, oracle.VOL_RGBA8)
+    ref, _ = oracle.render(ov, p, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        assert r.stats()["constant_channels"] & 2
+        r.set_params(u0, u1)
+        a = r.render()[0].copy()
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)     # same shape again: storage is reused
+        b = r.render()[0].copy()
+    assert np.abs(a - ref).max() <= 2.0 / 255.0
+    assert np.array_equal(a, b)
+
+
 def test_r8_volume_and_all_encodings_on_split_kernels(oracle):
     W, H = 200, 120
     rng = np.random.default_rng(3)

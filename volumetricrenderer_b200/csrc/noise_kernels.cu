@@ -352,7 +352,9 @@ __global__ void __launch_bounds__(256) deinterleave_rgba8_kernel(const uint4* __
                                                                  unsigned int* __restrict__ mm) {
     const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned int mn = 0xffffffffu, mx = 0u;
-    if (q * 4 + 3 < voxels) {
+    // the word stores below land on planes + c*voxels + 4q: 4-byte aligned for every plane only when voxels % 4 == 0
+    // (a 5^3 or 10x13x27 volume would raise a sticky misaligned-address fault); other volumes go texel by texel
+    if ((voxels & 3) == 0 && q * 4 + 3 < voxels) {
         const uint4 v = __ldg(rgba + q);
         mn = __vminu4(__vminu4(v.x, v.y), __vminu4(v.z, v.w));
         mx = __vmaxu4(__vmaxu4(v.x, v.y), __vmaxu4(v.z, v.w));
@@ -363,7 +365,8 @@ __global__ void __launch_bounds__(256) deinterleave_rgba8_kernel(const uint4* __
             reinterpret_cast<unsigned*>(planes + (size_t)c * voxels)[q] = w;
         }
     } else {
-        for (size_t i = q * 4; i < voxels; ++i) {
+        const size_t end = (voxels & 3) == 0 ? voxels : (q * 4 + 4 < voxels ? q * 4 + 4 : voxels);
+        for (size_t i = q * 4; i < end; ++i) {
             const unsigned int t = reinterpret_cast<const unsigned int*>(rgba)[i];
             mn = __vminu4(mn, t);
             mx = __vmaxu4(mx, t);
