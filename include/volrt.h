@@ -368,6 +368,22 @@ VR_API vr_status vr_noise_tree_info(const vr_noise_tree* tree, uint32_t* nodes, 
 VR_API vr_status vr_noise_tree_grid(vr_context* ctx, const vr_noise_tree* tree, int32_t x0, int32_t y0, int32_t z0, uint32_t nx,
                                     uint32_t ny, uint32_t nz, float frequency, int32_t seed, float* out_host, float minmax[2]);
 
+/* ---- allocation-free variant of vr_noise_tree_grid.  No counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same computation, same arguments and results as vr_noise_tree_grid, but it needs no context and calls no cudaMalloc /
+ * cudaFree / cudaMallocHost or any allocating library routine: the program upload buffer, the two min/max words and the output
+ * plane live in one file-scope device array of libvolrt.so (csrc/noalloc.cu, ~1.03 MiB, held by every GPU that loads the
+ * library until the process exits).  Limit: nx*ny*nz <= VR_STATIC_GRID_MAX_POINTS (64^3); larger grids are refused with
+ * VR_ERR_INVALID_ARGUMENT and a message naming the limit.  `device` = CUDA ordinal; `stream` = cudaStream_t, NULL = the default
+ * stream; the call returns after the results have reached out_host (may be NULL) and minmax.  All calls on a device share the
+ * array and it keeps the last call's contents (each call re-initialises what must start clean); calls are serialised by a
+ * mutex inside the library and complete before they return — work that overlapped on the GPU would race on the array.
+ * err (may be NULL) receives the message of a failure, as in vr_noise_tree_compile. */
+#define VR_STATIC_GRID_MAX_POINTS 262144u
+VR_API vr_status vr_noise_tree_grid_static(int32_t device, const vr_noise_tree* tree, int32_t x0, int32_t y0, int32_t z0, uint32_t nx,
+                                           uint32_t ny, uint32_t nz, float frequency, int32_t seed, float* out_host, float minmax[2],
+                                           void* stream, char* err, size_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

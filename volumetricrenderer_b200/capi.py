@@ -127,7 +127,10 @@ EXPORTS = {
     "vr_noise_tree_info": (C.c_int32, [_VP, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "vr_noise_tree_grid": (C.c_int32, [_VP, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_int32,
                                        C.POINTER(C.c_float), C.POINTER(C.c_float)]),
+    "vr_noise_tree_grid_static": (C.c_int32, [C.c_int32, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float,
+                                              C.c_int32, C.POINTER(C.c_float), C.POINTER(C.c_float), _VP, C.c_char_p, C.c_size_t]),
 }
+STATIC_GRID_MAX_POINTS = 262144
 
 _lib = None
 

@@ -139,3 +139,29 @@ class CompiledTree:
             self.close()
         except Exception:
             pass
+
+
+def grid_static(tree, shape, frequency, seed, start=(0, 0, 0), device=0, stream=None, want_grid=True):
+    """vr_noise_tree_grid_static: the allocation-free, context-free variant of Renderer.noise_tree_grid (include/volrt.h).
+    tree: encoded string, N or CompiledTree; shape = (nz, ny, nx) with nz*ny*nx <= capi.STATIC_GRID_MAX_POINTS."""
+    import numpy as np
+    lib = capi.load()
+    own = None
+    if isinstance(tree, N):
+        tree = tree.encode()
+    if not isinstance(tree, CompiledTree):
+        tree = own = CompiledTree(tree)
+    nz, ny, nx = shape
+    out = np.empty(shape, np.float32) if want_grid else None
+    mm = (C.c_float * 2)()
+    err = C.create_string_buffer(384)
+    try:
+        st = lib.vr_noise_tree_grid_static(device, tree.handle, start[0], start[1], start[2], nx, ny, nz, frequency, seed,
+                                           out.ctypes.data_as(C.POINTER(C.c_float)) if want_grid else None, mm, stream, err, len(err))
+    finally:
+        if own is not None:
+            own.close()
+    if st != capi.VR_OK:
+        from .renderer import VolrtError
+        raise VolrtError(st, err.value.decode())
+    return out, (mm[0], mm[1])
