@@ -70,6 +70,8 @@ def lib():
         L.vo_render_rows.argtypes = [C.POINTER(VoVolume), C.POINTER(VoParams), C.c_int, C.c_int, ip, C.c_int,
                                      fp, ip, C.POINTER(C.c_uint64), C.c_int]
         L.vo_render_rows.restype = C.c_int
+        L.vo_frag_positions.argtypes = [C.POINTER(VoParams), C.c_int, C.c_int, ip, C.c_int, fp, ip]
+        L.vo_frag_positions.restype = C.c_int
         L.vo_encode.argtypes = [fp, C.c_int64, C.c_int, C.c_void_p]
         L.vo_noise.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_float]
         L.vo_noise.restype = C.c_float
@@ -107,6 +109,16 @@ def ref():
         R.vref_bake_default.argtypes = [C.POINTER(C.c_uint8), C.c_int, C.c_int, fp]
         R.vref_tree_grid.argtypes = [C.c_char_p, C.c_int, fp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, fp]
         R.vref_metadata_dump.argtypes = [C.c_char_p, C.c_int]
+        if hasattr(R, "vref_frag"):          # the reference's shaders compiled as C++ (glsl_shim.h)
+            ip = C.POINTER(C.c_int32)
+            R.vref_frag.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_uint8), C.c_int, C.c_int, C.c_int, fp, ip, C.c_int64, fp, C.c_int]
+            R.vref_frag.restype = C.c_int
+            R.vref_frag_constants.argtypes = [fp]
+            R.vref_vert.argtypes = [C.c_void_p, C.c_uint32, fp, C.c_int, fp, fp]
+            R.vref_vert.restype = C.c_int
+            R.vref_draw.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint8), C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_int, fp, ip, fp, C.c_int]
+            R.vref_draw.restype = C.c_int
         _ref = R
     return _ref
 
@@ -214,6 +226,82 @@ def render_rows(vol, p, W, H, rows, threads=0):
     if rc != 0:
         raise ValueError("vo_render_rows rc=%d" % rc)
     return out, {"covered": int(st[0]), "steps": int(st[1]), "early": int(st[2]), "light_samples": int(st[3])}
+
+
+def frag_positions(p, W, H, rows=None):
+    """The fragment stage's inputs as the oracle generates them for the listed rows (default: all):
+    -> (fragPosition float32 (len(rows), W, 3), covered int32 (len(rows), W))"""
+    rows = np.arange(H, dtype=np.int32) if rows is None else np.ascontiguousarray(rows, np.int32)
+    xyz = np.zeros((len(rows), W, 3), np.float32)
+    cov = np.zeros((len(rows), W), np.int32)
+    ip = C.POINTER(C.c_int32)
+    rc = lib().vo_frag_positions(C.byref(p), W, H, rows.ctypes.data_as(ip), len(rows), _fp(xyz), cov.ctypes.data_as(ip))
+    if rc != 0:
+        raise ValueError("vo_frag_positions rc=%d" % rc)
+    return xyz, cov
+
+
+# ------------------------------------------------------------------ the reference's own shaders, compiled as C++ (oracle/_ref)
+def have_ref_glsl():
+    return have_ref() and hasattr(ref(), "vref_frag")
+
+
+def ref_frag(ubo1_raw, texels_rgba8, frag_pos, covered=None, threads=0):
+    """/root/reference/shaders/frag.glsl main(), one invocation per fragPosition.  ubo1_raw: the bytes the host
+    uploads for binding 1 (140 or 144; decoded with std140 offsets, bytes past the end read as zero); texels_rgba8:
+    uint8 (d, h, w, 4); frag_pos: float32 (..., 3); covered: int32 (...) or None (all).  -> outColor float32 (..., 4)"""
+    t = np.ascontiguousarray(texels_rgba8, np.uint8)
+    d, h, w = t.shape[:3]
+    fpos = np.ascontiguousarray(frag_pos, np.float32)
+    n = fpos.size // 3
+    cov = None if covered is None else np.ascontiguousarray(covered, np.int32)
+    out = np.zeros(fpos.shape[:-1] + (4,), np.float32)
+    raw = np.asarray(ubo1_raw, np.float32).tobytes() if not isinstance(ubo1_raw, (bytes, bytearray)) else bytes(ubo1_raw)
+    buf = (C.c_char * len(raw)).from_buffer_copy(raw)
+    rc = ref().vref_frag(C.cast(buf, C.c_void_p), len(raw), t.ctypes.data_as(C.POINTER(C.c_uint8)), w, h, d, _fp(fpos),
+                         cov.ctypes.data_as(C.POINTER(C.c_int32)) if cov is not None else None, n, _fp(out), threads)
+    if rc != 0:
+        raise ValueError("vref_frag rc=%d" % rc)
+    return out
+
+
+def ref_frag_constants():
+    """(density, maxSteps, boxMin.x, boxMax.x) as compiled from frag.glsl:29-32"""
+    out = np.zeros(4, np.float32)
+    ref().vref_frag_constants(_fp(out))
+    return out
+
+
+def ref_vert(ubo0, positions):
+    """/root/reference/shaders/vert.glsl main() per inPosition -> (gl_Position (n,4), fragPosition (n,3))"""
+    raw = np.asarray(ubo0, np.float32).tobytes()
+    buf = (C.c_char * len(raw)).from_buffer_copy(raw)
+    pos = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+    gl = np.zeros((len(pos), 4), np.float32)
+    fr = np.zeros((len(pos), 3), np.float32)
+    rc = ref().vref_vert(C.cast(buf, C.c_void_p), len(raw), _fp(pos), len(pos), _fp(gl), _fp(fr))
+    if rc != 0:
+        raise ValueError("vref_vert rc=%d" % rc)
+    return gl, fr
+
+
+def ref_draw(ubo0, ubo1_raw, texels_rgba8, W, H, threads=0):
+    """The reference's whole draw on the CPU: its vert.glsl -> fixed-function rasteriser (oracle/ref_raster.cpp) -> its
+    frag.glsl.  -> (rgba float32 (H,W,4), covered int32 (H,W), fragPosition float32 (H,W,3))"""
+    t = np.ascontiguousarray(texels_rgba8, np.uint8)
+    d, h, w = t.shape[:3]
+    r0 = np.asarray(ubo0, np.float32).tobytes()
+    r1 = np.asarray(ubo1_raw, np.float32).tobytes() if not isinstance(ubo1_raw, (bytes, bytearray)) else bytes(ubo1_raw)
+    b0 = (C.c_char * len(r0)).from_buffer_copy(r0)
+    b1 = (C.c_char * len(r1)).from_buffer_copy(r1)
+    out = np.zeros((H, W, 4), np.float32)
+    cov = np.zeros((H, W), np.int32)
+    fpos = np.zeros((H, W, 3), np.float32)
+    rc = ref().vref_draw(C.cast(b0, C.c_void_p), len(r0), C.cast(b1, C.c_void_p), len(r1), t.ctypes.data_as(C.POINTER(C.c_uint8)),
+                         w, h, d, W, H, _fp(out), cov.ctypes.data_as(C.POINTER(C.c_int32)), _fp(fpos), threads)
+    if rc != 0:
+        raise ValueError("vref_draw rc=%d" % rc)
+    return out, cov, fpos
 
 
 def encode(rgba, fmt):

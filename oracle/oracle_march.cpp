@@ -116,17 +116,12 @@ inline float density(const Ctx& c, vec3 Pin) {
 
 inline bool inside01(vec3 P) { return P.x >= 0.0f && P.x <= 1.0f && P.y >= 0.0f && P.y <= 1.0f && P.z >= 0.0f && P.z <= 1.0f; }
 
-// ---------------------------------------------------------------- one pixel
-// returns n (>= 0) for a covered pixel, -1 for the clear colour.
-int shade_pixel(const Ctx& c, const float* invPV, const float* invModel, int W, int H, int px, int py,
-                float out[4], uint64_t* early, uint64_t* light_samples) {
-    const vo_params* p = c.p;
+// ---------------------------------------------------------------- ray generation (A.2)
+// What vert.glsl:17-22 + the rasteriser hand the fragment stage: is the pixel covered by a front face of the cube
+// (cull back / depth LESS, VulkanPipeline.cpp:107-108,130-132), and the interpolated fragPosition = Model * (point of
+// the face under the pixel centre).  false = the pixel keeps the clear colour.
+bool ray_generate(const vo_params* p, const float* invPV, const float* invModel, int W, int H, int px, int py, vec3& fragPosition) {
     const float* Model = p->ubo0;
-    const float* WorldToLocal = p->ubo1;
-    const vec3 CameraPosition = {p->ubo1[16], p->ubo1[17], p->ubo1[18]};
-    out[0] = out[1] = out[2] = 0.0f; out[3] = 1.0f;            // VulkanRenderPass.cpp:17-19 clear colour
-
-    // --- A.2: ray generation (vert.glsl:17-22 + rasteriser, cull back / depth LESS)
     float x = ((float)px + 0.5f) * (2.0f / (float)W) - 1.0f;
     float y = ((float)py + 0.5f) * (2.0f / (float)H) - 1.0f;
     float pn[4], pf[4];
@@ -137,16 +132,30 @@ int shade_pixel(const Ctx& c, const float* invPV, const float* invModel, int W, 
     vec3 d_w = f_w - o_w;
     vec3 o_c = xform_point(invModel, o_w);
     vec3 d_c = xform_dir(invModel, d_w);
+    const vec3 boxMin = {-1, -1, -1}, boxMax = {1, 1, 1};      // the cube of TestMain.cpp:94-112
+    vec3 tMin = (boxMin - o_c) / d_c, tMax = (boxMax - o_c) / d_c;
+    vec3 t1 = vmin(tMin, tMax), t2 = vmax(tMin, tMax);
+    float t0 = std::fmax(std::fmax(t1.x, t1.y), t1.z), tF = std::fmin(std::fmin(t2.x, t2.y), t2.z);
+    if (!(t0 <= tF && t0 >= 0.0f && t0 <= 1.0f)) return false;
+    vec3 entry = o_c + d_c * t0;
+    // fragPosition = vec3(Model * vec4(inPosition, 1))          vert.glsl:20
+    fragPosition = xform_point(Model, entry);
+    return true;
+}
+
+// ---------------------------------------------------------------- one pixel
+// returns n (>= 0) for a covered pixel, -1 for the clear colour.
+int shade_pixel(const Ctx& c, const float* invPV, const float* invModel, int W, int H, int px, int py,
+                float out[4], uint64_t* early, uint64_t* light_samples) {
+    const vo_params* p = c.p;
+    const float* WorldToLocal = p->ubo1;
+    const vec3 CameraPosition = {p->ubo1[16], p->ubo1[17], p->ubo1[18]};
+    out[0] = out[1] = out[2] = 0.0f; out[3] = 1.0f;            // VulkanRenderPass.cpp:17-19 clear colour
+
+    vec3 fragPosition;
+    if (!ray_generate(p, invPV, invModel, W, H, px, py, fragPosition)) return -1;
     const vec3 boxMin = {-1, -1, -1}, boxMax = {1, 1, 1};      // frag.glsl:31-32
     {
-        vec3 tMin = (boxMin - o_c) / d_c, tMax = (boxMax - o_c) / d_c;
-        vec3 t1 = vmin(tMin, tMax), t2 = vmax(tMin, tMax);
-        float t0 = std::fmax(std::fmax(t1.x, t1.y), t1.z), tF = std::fmin(std::fmin(t2.x, t2.y), t2.z);
-        if (!(t0 <= tF && t0 >= 0.0f && t0 <= 1.0f)) return -1;
-        vec3 entry = o_c + d_c * t0;
-        // fragPosition = vec3(Model * vec4(inPosition, 1))          vert.glsl:20
-        vec3 fragPosition = xform_point(Model, entry);
-
         // --- frag.glsl:36-39
         vec3 cameraInBoxLocal = xform_point(WorldToLocal, CameraPosition);
         vec3 fragmentInBoxLocal = xform_point(WorldToLocal, fragPosition);
@@ -305,6 +314,30 @@ extern "C" int vo_render_rows(const vo_volume* v, const vo_params* p, int W, int
     if (stats) {
         for (int k = 0; k < 4; ++k) { stats[k] = 0; for (int t = 0; t < nt; ++t) stats[k] += acc[(size_t)t * 4 + k]; }
     }
+    return 0;
+}
+
+// what the fragment stage receives for the pixels of `rows`: covered[r*W + px] (0/1) and fragPosition (world space);
+// uncovered entries are zeroed.  Lets a test hand the very same inputs to the reference's frag.glsl compiled as C++
+// (oracle/_ref, glsl_shim.h) and project them back through its vert.glsl.
+extern "C" int vo_frag_positions(const vo_params* p, int W, int H, const int32_t* rows, int n_rows, float* out_xyz, int32_t* covered) {
+    if (!p || W <= 0 || H <= 0 || n_rows < 0 || (n_rows && !rows) || !out_xyz || !covered) return 1;
+    for (int r = 0; r < n_rows; ++r) if (rows[r] < 0 || rows[r] >= H) return 1;
+    double PV[16], PVi[16], Md[16], Mi[16];
+    mat_mul_d(p->ubo0 + 32, p->ubo0 + 16, PV);
+    inverse_d(PV, PVi);
+    for (int i = 0; i < 16; ++i) Md[i] = p->ubo0[i];
+    inverse_d(Md, Mi);
+    float invPV[16], invModel[16];
+    for (int i = 0; i < 16; ++i) { invPV[i] = (float)PVi[i]; invModel[i] = (float)Mi[i]; }
+    for (int r = 0; r < n_rows; ++r)
+        for (int px = 0; px < W; ++px) {
+            vec3 f = {0, 0, 0};
+            const bool c = ray_generate(p, invPV, invModel, W, H, px, rows[r], f);
+            const size_t i = (size_t)r * W + px;
+            covered[i] = c ? 1 : 0;
+            out_xyz[3 * i] = c ? f.x : 0.0f; out_xyz[3 * i + 1] = c ? f.y : 0.0f; out_xyz[3 * i + 2] = c ? f.z : 0.0f;
+        }
     return 0;
 }
 

@@ -17,14 +17,19 @@
  *   source/Etna/Core/Vulkan/VulkanTexture.cpp:111-156 RGBA8 UNORM, tight x-fastest layout
  *   vendor/noise/include/FastNoise/Generators/{Cellular,Perlin,Simplex,Fractal,Utils,Generator}.inl
  *
- * PARITY STATUS: "parity unpinned" for the ray-march — the reference holds no
- * golden vector, test or fixture for this path and its shader cannot be run on
- * this box (no graphics stack).  The march is pinned only by (i) this
- * near-verbatim transliteration, (ii) closed-form known-answer tests in
- * tests/test_oracle_*.py.  The NOISE restatement *is* pinned: it is checked
- * against the reference's own FastNoise2 compiled from /root/reference
- * (oracle/_ref, see oracle/Makefile) and against fixtures generated from it
- * (tests/golden/, made by tests/golden/make_golden.py).
+ * PARITY STATUS: pinned to the reference's own sources on both halves of the path.
+ *   Ray-march: /root/reference/shaders/frag.glsl and vert.glsl are compiled AS C++ (oracle/glsl_shim.h supplies
+ *   vec/mat types, the built-ins and the fixed-function sampler; oracle/Makefile `ref` pipes the shader text from
+ *   where it lies into g++) into oracle/_ref/libvolrt_ref.so.  tests/test_oracle_march.py holds oracle_march.cpp
+ *   to that build bit for bit on binary32 outColor (full config-1 frame + rotated / ragged / scrolled scenes), and
+ *   tests/golden/glsl_shaders_golden.npz (made by tests/golden/make_golden_glsl.py from the same build) does so
+ *   where /root/reference is absent.  Not executed: the reference's Vulkan pipeline itself (no graphics stack on
+ *   either box — unavailable); its fixed-function stages are restated in oracle/ref_raster.cpp from the pipeline
+ *   state the reference sets, and glm (a system include of the reference, not vendored) from its closed forms.
+ *   Noise / bake: the reference's FastNoise2 compiled from /root/reference/vendor/noise (same library file) and
+ *   fixtures generated from it (tests/golden/, made by tests/golden/make_golden.py).
+ *   The build-defined extensions (configs 2-5: light-march, fBm density, fp16 grids, skipping) have no reference
+ *   counterpart; their parity is GPU vs this oracle's statement of the build's own definition.
  */
 #ifndef VOLRT_ORACLE_H
 #define VOLRT_ORACLE_H
@@ -99,6 +104,10 @@ int vo_render(const vo_volume* v, const vo_params* p, int W, int H, int row0, in
 /* same for an arbitrary list of screen rows (the bounded, strided sample bench.py times) */
 int vo_render_rows(const vo_volume* v, const vo_params* p, int W, int H, const int32_t* rows, int n_rows,
                    float* out_rgba, int32_t* out_steps, uint64_t stats[4], int threads);
+
+/* the inputs of the fragment stage for the pixels of `rows` (SURVEY.md A.2 = vert.glsl:17-22 + rasteriser):
+ * covered[n_rows*W] and fragPosition xyz[n_rows*W*3] (world space; zero where not covered) */
+int vo_frag_positions(const vo_params* p, int W, int H, const int32_t* rows, int n_rows, float* out_xyz, int32_t* covered);
 
 /* ---- output conversion ---- */
 void vo_encode(const float* rgba, int64_t n_px, int fmt, void* out);

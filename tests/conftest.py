@@ -22,9 +22,16 @@ def oracle():
 
 @pytest.fixture(scope="session")
 def default_volume(oracle):
-    """The reference's start-up bake (TestMain.cpp:43-92) by the oracle's restatement, 128^3 RGBA8.
-    Cached on disk: it is ~10 s of scalar CPU work."""
-    path = "/tmp/volrt_default_volume_v1.npy"
+    """The reference's start-up bake (TestMain.cpp:43-92), 128^3 RGBA8.  Where oracle/_ref travelled along (the build
+    container and the GPU box) these are the bytes of the REFERENCE'S OWN FastNoise2 at the CPU's best SIMD level — what
+    the app itself would upload; elsewhere the oracle's restatement (~10 s of scalar work, cached on disk under a key
+    that changes whenever the oracle library does)."""
+    if oracle.have_ref():
+        return oracle.ref_bake_default(128)[0]
+    import hashlib
+    so = os.path.join(ROOT, "oracle", "libvolrt_oracle.so")
+    key = hashlib.sha256(open(so, "rb").read()).hexdigest()[:16]
+    path = "/tmp/volrt_default_volume_%s.npy" % key
     if os.path.exists(path):
         v = np.load(path)
         if v.shape == (128, 128, 128, 4):

@@ -39,6 +39,33 @@ def test_default_scene_linear_is_bit_exact(oracle, default_volume):
     assert np.array_equal(img.view(np.uint32), ref.view(np.uint32))
 
 
+def test_default_scene_against_the_reference_shaders_compiled_here(oracle, default_volume):
+    """config 1 against the REFERENCE ITSELF, no restatement in between: /root/reference/shaders/frag.glsl compiled as C++
+    (oracle/_ref, built by `make -C oracle ref`; oracle/glsl_shim.h) on the reference's own FastNoise2 bake.  LINEAR layout:
+    binary32 outColor bit for bit.  TEXTURE layout: north-star tolerance.  And the reference's whole draw (vert.glsl ->
+    rasteriser -> frag.glsl, oracle/ref_raster.cpp) within the tolerance too."""
+    if not oracle.have_ref_glsl():
+        pytest.skip("oracle/_ref with the compiled shaders did not travel to this box")
+    W, H = 1280, 720
+    ubo0, ubo1 = scene.default_scene()
+    p = oracle_params(oracle, ubo0, ubo1)
+    fpos, cov = oracle.frag_positions(p, W, H)
+    theirs = oracle.ref_frag(ubo1, default_volume, fpos, cov)                    # frag.glsl main() per covered pixel
+    drawn, dcov, _ = oracle.ref_draw(ubo0, ubo1, default_volume, W, H)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_LINEAR)
+        r.set_params(ubo0, ubo1)
+        strict = r.render()[0].copy()
+        r.upload_volume(default_volume, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        fast = r.render()[0].copy()
+    assert np.array_equal(strict.view(np.uint32), theirs.view(np.uint32))
+    e8 = lambda a: oracle.encode(a, oracle.OUT_RGBA8_UNORM)
+    assert max_abs8(e8(fast), e8(theirs)) <= TOL8 and psnr8(e8(fast), e8(theirs)) >= PSNR_MIN
+    assert (dcov != cov).sum() <= 4
+    assert max_abs8(e8(strict), e8(drawn)) <= TOL8 and psnr8(e8(strict), e8(drawn)) >= PSNR_MIN
+    assert max_abs8(e8(fast), e8(drawn)) <= TOL8 and psnr8(e8(fast), e8(drawn)) >= PSNR_MIN
+
+
 @pytest.mark.parametrize("fmt,ofmt", [(capi.OUT_RGBA8_UNORM, 0), (capi.OUT_RGBA8_SRGB, 1)])
 def test_default_scene_texture_within_tolerance(oracle, default_volume, fmt, ofmt):
     """config 1 through the texture unit (fixed-point trilinear weights), both target encodings (Q3)."""

@@ -1,8 +1,8 @@
-"""Known-answer tests that pin the CPU oracle's restatement of shaders/frag.glsl (oracle/oracle_march.cpp).
+"""Tests that pin the CPU oracle's restatement of shaders/frag.glsl (oracle/oracle_march.cpp).
 
-The reference holds no golden vector for the ray-march and its shader cannot be run here (no
-graphics stack; SURVEY.md §8(c): "parity unpinned"), so the oracle is pinned by closed forms derived
-from the shader text itself — none of these expectations comes out of the oracle:
+Two kinds.  (1) Closed forms derived from the shader text itself — none of these expectations comes out of the oracle.
+(2) At the end of the file: the oracle against the reference's own shaders COMPILED AS C++ (oracle/_ref), bit for bit.
+The reference holds no golden vector for the ray-march and its Vulkan pipeline cannot run here (no graphics stack).
   frag.glsl:42     stepSize = 4/128
   frag.glsl:46     n = min(128, int(|Pin-Pout| / stepSize))
   frag.glsl:66-71  rho = (s1*s2)*(s3+s4)*0.2
@@ -10,6 +10,8 @@ from the shader text itself — none of these expectations comes out of the orac
   VulkanCore.cpp:676-710   linear filter, mirrored repeat, texel centres at (i+0.5)/N
   VulkanRenderPass.cpp:17-19   clear colour (0,0,0,1)
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -215,3 +217,146 @@ def test_render_rows_is_a_slice_of_the_frame(oracle):
     assert np.array_equal(full[rows], some)
     empty, st0 = oracle.render(ov, p, 128, 72, rows=(10, 10))
     assert empty.shape == (0, 128, 4) and st0["covered"] == 0
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The oracle held to the REFERENCE'S OWN SHADER TEXT.  oracle/Makefile `ref` compiles /root/reference/shaders/frag.glsl and
+# vert.glsl — from where they lie, as C++ behind oracle/glsl_shim.h — into oracle/_ref/libvolrt_ref.so (it travels to the
+# GPU box; /root/reference does not).  tests/golden/glsl_shaders_golden.npz holds outputs of that build for machines
+# without it (script: tests/golden/make_golden_glsl.py).  Bit-exact on binary32 outColor: the oracle restates the same
+# operations in the same order, and both sides take GLSL's implementation-defined pieces (rounding per operator, mat*vec
+# order, exp, the fixed-function sampler) the same way — see the header of glsl_shim.h.
+GOLDEN_GLSL = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "glsl_shaders_golden.npz")
+CUBE = np.array([[1, -1, -1], [1, -1, 1], [-1, -1, 1], [-1, -1, -1], [1, 1, -1], [1, 1, 1], [-1, 1, 1], [-1, 1, -1]], np.float32)
+
+
+def _needs_compiled_shaders(oracle):
+    if not oracle.have_ref_glsl():
+        pytest.skip("oracle/_ref with the compiled shaders is not built (needs /root/reference: make -C oracle ref)")
+
+
+def _std140_with_scroll(u1_host, scroll_rows):
+    """144-byte std140 image of GlobalShaderData whose MediaScroll columns 0..2 carry the given .y / .z / .w"""
+    s = np.zeros(36, np.float32)
+    s[:19] = u1_host[:19]
+    for col in range(3):
+        for row, vals in zip((1, 2, 3), scroll_rows):
+            s[20 + 4 * col + row] = vals[col]
+    return s
+
+
+def test_compiled_shader_literals_are_the_oracle_defaults(oracle):
+    _needs_compiled_shaders(oracle)
+    density, max_steps, box_min, box_max = oracle.ref_frag_constants()          # frag.glsl:29-32 as compiled
+    p = oracle.params_default()
+    assert (density, max_steps, box_min, box_max) == (p.density, p.max_steps, -1.0, 1.0)
+    assert (p.step_scale, round(p.sample_scale, 6)) == (4.0, 0.2)
+
+
+def test_oracle_equals_compiled_frag_glsl(oracle):
+    """the full config-1 frame (1280x720, the reference's own bake) and five more scenes: binary32 outColor, bit for bit"""
+    _needs_compiled_shaders(oracle)
+    vol_default, _mm = oracle.ref_bake_default(128)                              # the reference's FastNoise2, TestMain.cpp:43-92
+    rng = np.random.default_rng(11)
+    scenes = [
+        # W, H, phi, theta, frame_time, volume, scroll (None = the host's 140-byte struct, quirk Q2)
+        (1280, 720, 0.0, 0.0, 0.0, vol_default, None),
+        (640, 360, 20.0, -10.0, 0.25, rng.integers(0, 256, size=(32, 32, 32, 4), dtype=np.uint8), None),
+        (640, 360, 77.0, 33.0, 3.0, rng.integers(0, 256, size=(9, 20, 12, 4), dtype=np.uint8), None),
+        (640, 360, -35.0, 12.0, 0.0, rng.integers(0, 256, size=(16, 16, 16, 4), dtype=np.uint8), [[0.3, -0.7, 1.9], [0.11, 0.5, -2.25], [4.0, 0.05, -0.6]]),
+        (333, 187, 181.0, -64.0, 0.0, vol_default[40:72, 8:40, 64:96].copy(), [[-1.5, 2.5, 0.25], [0.0, 0.0, 0.0], [9.0, -9.0, 0.5]]),
+        (200, 120, 45.0, 89.0, 7.0, rng.integers(0, 2, size=(5, 5, 5, 4), dtype=np.uint8) * 255, None),
+    ]
+    for W, H, phi, theta, ft, vol, scroll in scenes:
+        u0, u1 = oracle.scene_default(phi, theta, ft)
+        if scroll is not None:
+            u1 = _std140_with_scroll(u1, scroll)
+        p = oracle_params(oracle, u0, u1)
+        ov, _k = oracle.make_volume(vol, oracle.VOL_RGBA8)
+        mine, st, steps = oracle.render(ov, p, W, H, want_steps=True)
+        fpos, cov = oracle.frag_positions(p, W, H)
+        assert np.array_equal(cov == 1, steps >= 0) and st["covered"] == int(cov.sum()) > 0.1 * W * H
+        theirs = oracle.ref_frag(u1, vol, fpos, cov)
+        assert np.array_equal(mine.view(np.uint32), theirs.view(np.uint32)), (W, H, phi, theta)
+        assert theirs[..., 0].max() > 0.02                                         # not a frame of zeros
+
+
+def test_vert_glsl_projects_the_oracles_fragments_onto_their_pixel_centres(oracle):
+    """SURVEY A.2 (the oracle's ray generation) against the reference's vertex shader: the point of the cube the oracle
+    hands the fragment stage, pushed through vert.glsl, lands on the pixel centre it was generated for, and comes
+    back as the same fragPosition"""
+    _needs_compiled_shaders(oracle)
+    W, H = 320, 180
+    for phi, theta in ((0.0, 0.0), (20.0, -10.0), (123.0, 45.0)):
+        u0, u1 = oracle.scene_default(phi, theta)
+        p = oracle_params(oracle, u0, u1)
+        fpos, cov = oracle.frag_positions(p, W, H)
+        ys, xs = np.nonzero(cov)
+        inv_model = oracle.mat4_inverse(u0[:16]).reshape(4, 4).T.astype(np.float64)       # column-major -> rows
+        world = np.concatenate([fpos[ys, xs].astype(np.float64), np.ones((len(ys), 1))], axis=1)
+        local = (inv_model @ world.T).T[:, :3]
+        assert np.abs(np.abs(local).max(axis=1) - 1.0).max() < 2e-4                       # on a face of the cube [-1,1]^3
+        gl, fr = oracle.ref_vert(u0, local.astype(np.float32))
+        ndc = gl[:, :2] / gl[:, 3:4]
+        want = np.stack([(xs + 0.5) * 2.0 / W - 1.0, (ys + 0.5) * 2.0 / H - 1.0], axis=1)
+        assert np.abs(ndc - want).max() < 0.02 * 2.0 / W                                   # within 2 % of a pixel
+        assert np.abs(fr - fpos[ys, xs]).max() < 2e-4
+        depth = gl[:, 2] / gl[:, 3]
+        assert depth.min() > 0.0 and depth.max() < 1.0                                     # between the near and far planes
+
+
+def test_reference_draw_pipeline_vs_oracle(oracle):
+    """vert.glsl -> the fixed-function stages (oracle/ref_raster.cpp) -> frag.glsl, against the oracle's frame: the same
+    pixels are shaded (silhouette ties aside) and the frames agree within the north-star tolerance; they are not bit-equal
+    because the rasteriser interpolates fragPosition from the triangle's corners while the oracle un-projects the pixel"""
+    _needs_compiled_shaders(oracle)
+    W, H = 640, 360
+    rng = np.random.default_rng(5)
+    vol = rng.integers(0, 256, size=(24, 24, 24, 4), dtype=np.uint8)
+    for phi, theta in ((0.0, 0.0), (20.0, -10.0), (77.0, 33.0), (200.0, -80.0)):
+        u0, u1 = oracle.scene_default(phi, theta, 0.5)
+        p = oracle_params(oracle, u0, u1)
+        ov, _k = oracle.make_volume(vol, oracle.VOL_RGBA8)
+        mine, st = oracle.render(ov, p, W, H)
+        fpos, cov = oracle.frag_positions(p, W, H)
+        theirs, rcov, rfpos = oracle.ref_draw(u0, u1, vol, W, H)
+        differ = cov != rcov
+        assert differ.sum() <= 1e-4 * cov.sum() + 2
+        if differ.any():                                  # only on the silhouette: a neighbour is uncovered
+            ys, xs = np.nonzero(differ)
+            for y, x in zip(ys, xs):
+                assert (cov[max(y - 1, 0):y + 2, max(x - 1, 0):x + 2] == 0).any()
+        both = (cov == 1) & (rcov == 1)
+        assert np.abs(fpos[both] - rfpos[both]).max() < 3e-4
+        err = np.abs(mine - theirs).max(axis=-1)
+        assert err.max() <= 2.0 / 255.0
+        assert (err > 1e-5).mean() < 1e-3                 # a few rays whose truncated step count flips by one
+        a8, b8 = oracle.encode(mine, oracle.OUT_RGBA8_UNORM), oracle.encode(theirs, oracle.OUT_RGBA8_UNORM)
+        from util import psnr8
+        assert psnr8(a8, b8) >= 60.0
+
+
+def test_oracle_against_the_golden_outputs_of_the_compiled_shaders(oracle):
+    """runs everywhere: the committed outputs of the reference's compiled shaders (make_golden_glsl.py)"""
+    g = np.load(GOLDEN_GLSL)
+    W, H = (int(v) for v in g["size"])
+    names = sorted({k.split("/")[0] for k in g.files if "/" in k})
+    assert len(names) >= 4
+    p0 = oracle.params_default()
+    assert tuple(g["frag_constants"]) == (p0.density, p0.max_steps, -1.0, 1.0)
+    for name in names:
+        u0, u1, vol = g[name + "/ubo0"], g[name + "/ubo1"], g[name + "/volume"]
+        p = oracle_params(oracle, u0, u1)
+        ov, _k = oracle.make_volume(vol, oracle.VOL_RGBA8)
+        mine, st = oracle.render(ov, p, W, H)
+        fpos, cov = oracle.frag_positions(p, W, H)
+        assert np.array_equal(cov, g[name + "/covered"]) and np.array_equal(fpos.view(np.uint32), g[name + "/frag_position"].view(np.uint32))
+        assert np.array_equal(mine.view(np.uint32), g[name + "/out_color"].view(np.uint32)), name      # frag.glsl, bit for bit
+        # vert.glsl on the cube's corners against the oracle's own matrices (float64 product, rounded)
+        M, V, P = (u0[i:i + 16].reshape(4, 4).T.astype(np.float64) for i in (0, 16, 32))
+        corners = np.concatenate([CUBE.astype(np.float64), np.ones((8, 1))], axis=1)
+        assert np.abs((P @ V @ M @ corners.T).T - g[name + "/vert_gl_position"]).max() < 2e-5
+        assert np.abs((M @ corners.T).T[:, :3] - g[name + "/vert_frag_position"]).max() < 1e-6
+        # the whole draw
+        err = np.abs(mine - g[name + "/draw_rgba"]).max(axis=-1)
+        assert (cov != g[name + "/draw_covered"]).sum() <= 2 and err.max() <= 2.0 / 255.0 and (err > 1e-5).mean() < 2e-3
