@@ -378,6 +378,36 @@ def test_fbm_light_march_pairs_equal_the_scalar_loop(monkeypatch, light_steps):
     assert np.array_equal(packed.view(np.uint32), scalar.view(np.uint32))
 
 
+@pytest.mark.parametrize("octaves,freq,lac,falloff1,eligible", [
+    (5, 128 * 0.03, 2.0, 0.5, True),        # the C2 / C3 field
+    (3, 7.3, 1.7, 0.45, True),              # ragged lattice sizes, the three-octave loop
+    (8, 1.1, 2.0, 0.5, True),               # the most octaves the tables take (lattice up to 143^3)
+    (9, 0.5, 2.0, 0.5, False),              # too many octaves -> per-sample hash
+    (5, 128 * 0.03, 2.0, 0.6, False),       # fade reaches beyond the box -> per-sample hash
+    (2, 120.0, 2.0, 0.5, False),            # lattice larger than the float-encoded index allows -> per-sample hash
+])
+def test_fbm_cell_tables_equal_the_per_sample_hash(monkeypatch, octaves, freq, lac, falloff1, eligible):
+    """MARCH_FBM_CELLS reads, per lattice cell, the eight gradient-table offsets the hash would have produced; everything after
+    the hash is the same arithmetic, so the frame is bit-identical to the hash variant's — whichever of the two the field
+    is eligible for (ineligible fields must simply keep working)."""
+    W, H = 320, 180
+    u0, u1 = scene.default_scene(15.0, 25.0)
+    SUN = np.array([1.0, 1.0, 2.0], np.float32) / np.float32(np.sqrt(6.0))
+    kw = dict(density_mode=2, max_steps=64, sigma_t=8.0, light_steps=5, light_step_len=0.09, ambient=0.15, sun_dir=SUN,
+              sun_color=[1.0, 0.95, 0.85], fbm_octaves=octaves, fbm_frequency=freq, fbm_lacunarity=lac, fbm_falloff1=falloff1, fbm_seed=77)
+    frames = {}
+    for cells in ("1", "0"):
+        monkeypatch.setenv("VOLRT_FBM_CELLS", cells)
+        for split in (1, 2):                                  # one thread per ray, and two lanes per ray
+            monkeypatch.setenv("VOLRT_RAY_SPLIT_COMPOSITE", str(split))
+            with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+                r.set_params(u0, u1, **kw)
+                frames[cells, split] = r.render()[0].copy()
+    for split in (1, 2):
+        assert np.array_equal(frames["1", split].view(np.uint32), frames["0", split].view(np.uint32)), (split, eligible)
+    assert frames["1", 1][..., :3].max() > 0.05
+
+
 def test_known_answers_on_gpu():
     """closed forms that do not depend on the oracle: constant volume, axis-aligned centre ray."""
     W, H = 256, 256

@@ -254,10 +254,13 @@ __device__ __forceinline__ float density_at(const MarchParams& P, const RayConst
         const float edge = 1.0f - t * t * (3.0f - 2.0f * t);
         if (edge <= 0.0f) return 0.0f;
         return fmaxf(0.0f, tree_eval(P.tree_prog, P.tree_n, P.tree_result, lut, P.tree_seed, p.x * P.tree_freq, p.y * P.tree_freq, p.z * P.tree_freq)) * edge;
+    } else if (VARIANT == MARCH_FBM_CELLS) {
+        return density_fbm_cells(GradLutFixed{}, P.fbm, P.cells, p.x, p.y, p.z);
     } else {
         return density_fbm(GradLutFixed{}, P.fbm, p.x, p.y, p.z);     // the table's place is checked by stage_tables()
     }
 }
+__host__ __device__ constexpr bool is_fbm(int variant) { return variant == MARCH_FBM || variant == MARCH_FBM_CELLS; }
 
 __device__ __forceinline__ bool brick_occupied(const MarchParams& P, f3 p) {
     const BrickInfo& B = P.bricks;
@@ -325,17 +328,19 @@ __device__ __forceinline__ float light_sum(const MarchParams& P, const RayConst&
                                            const GradLut* lut, f3 p, f3 lv, bool skip) {
     float sumL = 0.0f;
     f3 pl = p;
-    if constexpr (VARIANT == MARCH_FBM && VOLRT_FBM_PAIRS) {
+    if constexpr (is_fbm(VARIANT) && VOLRT_FBM_PAIRS) {
         for (int j = 1; j <= P.light_steps; j += 2) {
             const f3 pa = {pl.x + lv.x, pl.y + lv.y, pl.z + lv.z};
             if (!inside01(pa)) break;
             const f3 pb = {pa.x + lv.x, pa.y + lv.y, pa.z + lv.z};
             if (j < P.light_steps && inside01(pb)) {
-                const f2 r = density_fbm2(GradLutFixed{}, P.fbm, make_f2(pa.x, pb.x), make_f2(pa.y, pb.y), make_f2(pa.z, pb.z));
+                f2 r;
+                if constexpr (VARIANT == MARCH_FBM_CELLS) r = density_fbm_cells2(GradLutFixed{}, P.fbm, P.cells, make_f2(pa.x, pb.x), make_f2(pa.y, pb.y), make_f2(pa.z, pb.z));
+                else r = density_fbm2(GradLutFixed{}, P.fbm, make_f2(pa.x, pb.x), make_f2(pa.y, pb.y), make_f2(pa.z, pb.z));
                 sumL += f2_a(r);
                 sumL += f2_b(r);
             } else {
-                sumL += density_fbm(GradLutFixed{}, P.fbm, pa.x, pa.y, pa.z);
+                sumL += density_at<VARIANT>(P, rc, unorm, lut, pa);
                 break;
             }
             pl = pb;
@@ -441,7 +446,7 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
 #ifndef VOLRT_FBM_PAIR_PRIMARY
 #define VOLRT_FBM_PAIR_PRIMARY 0
 #endif
-        constexpr bool PAIR_PRIMARY = (VARIANT == MARCH_FBM) && VOLRT_FBM_PAIRS && VOLRT_FBM_PAIR_PRIMARY && !STATS;
+        constexpr bool PAIR_PRIMARY = (VARIANT == MARCH_FBM) && VOLRT_FBM_PAIRS && VOLRT_FBM_PAIR_PRIMARY && !STATS;   // hash variant only
         float rho_next = 0.0f;
         bool have_next = false;
         // Texture-filtered grids: a step is one dependent chain brick byte -> fetch -> exp, and on a grid far larger than L2
@@ -631,12 +636,12 @@ template <int VARIANT>
 __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     if (LINEAR) for (int i = threadIdx.x; i < 256; i += blockDim.x) unorm[i] = dvd((float)i, 255.0f);
-    if (VARIANT == MARCH_FBM) {
+    if (is_fbm(VARIANT)) {
         // the fBm march fetches gradients at an immediate shared address (noise_device.cuh: GradLutFixed)
         if ((unsigned)__cvta_generic_to_shared(lut) != (unsigned)VOLRT_LUT_FIXED_ADDR) __trap();
     }
-    if (VARIANT == MARCH_FBM || VARIANT == MARCH_TREE) grad_lut_init(lut, threadIdx.x);
-    if (LINEAR || VARIANT == MARCH_FBM || VARIANT == MARCH_TREE) __syncthreads();
+    if (is_fbm(VARIANT) || VARIANT == MARCH_TREE) grad_lut_init(lut, threadIdx.x);
+    if (LINEAR || is_fbm(VARIANT) || VARIANT == MARCH_TREE) __syncthreads();
 }
 
 // (a) direct mapping: one CTA of 4 warps per 16x8-pixel tile, a warp per 8x4 sub-tile.  Used where a step
@@ -656,7 +661,7 @@ __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
 
 constexpr int kCtaWx = VOLRT_CTA_WX, kCtaWy = VOLRT_CTA_WY, kCtaThreads = 32 * kCtaWx * kCtaWy;
 template <int VARIANT, bool COMPOSITE, bool STATS>
-__global__ void __launch_bounds__(kCtaThreads, VARIANT == MARCH_FBM ? VOLRT_DIRECT_MIN_CTAS : 1) march_kernel(const __grid_constant__ MarchParams P) {
+__global__ void __launch_bounds__(kCtaThreads, is_fbm(VARIANT) ? VOLRT_DIRECT_MIN_CTAS : 1) march_kernel(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     __shared__ MarchSmem<LINEAR> smem;
     float* const unorm = smem.unorm;
@@ -798,7 +803,7 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
 #define VOLRT_SPLIT_MIN_CTAS 5      // 96 registers: the two-point fBm light-march spills at 72 (7 CTAs/SM) — measured 4/5/6/7
 #endif
 template <int VARIANT, int S>
-__global__ void __launch_bounds__(128, VARIANT == MARCH_FBM ? VOLRT_SPLIT_MIN_CTAS : VOLRT_SPLIT_MIN_CTAS_OTHER)
+__global__ void __launch_bounds__(128, is_fbm(VARIANT) ? VOLRT_SPLIT_MIN_CTAS : VOLRT_SPLIT_MIN_CTAS_OTHER)
 march_composite_split_kernel(const __grid_constant__ MarchParams P) {
     constexpr int RAYS = 32 / S, RW = RAYS / 2;
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
@@ -1159,6 +1164,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
                 case MARCH_SINGLE_TEX: return launch_composite_split<MARCH_SINGLE_TEX>(p, split, rows, n_views, stream);
                 case MARCH_SINGLE_LINEAR: return launch_composite_split<MARCH_SINGLE_LINEAR>(p, split, rows, n_views, stream);
                 case MARCH_FBM: return launch_composite_split<MARCH_FBM>(p, split, rows, n_views, stream);
+                case MARCH_FBM_CELLS: return launch_composite_split<MARCH_FBM_CELLS>(p, split, rows, n_views, stream);
                 case MARCH_TREE: return launch_composite_split<MARCH_TREE>(p, split, rows, n_views, stream);
             }
         }
@@ -1185,6 +1191,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
         case MARCH_SINGLE_TEX: return launch_v<MARCH_SINGLE_TEX>(p, grid, composite, stats, persistent, stream);
         case MARCH_SINGLE_LINEAR: return launch_v<MARCH_SINGLE_LINEAR>(p, grid, composite, stats, persistent, stream);
         case MARCH_FBM: return launch_v<MARCH_FBM>(p, grid, composite, stats, persistent, stream);
+        case MARCH_FBM_CELLS: return launch_v<MARCH_FBM_CELLS>(p, grid, composite, stats, persistent, stream);
         case MARCH_TREE: return launch_v<MARCH_TREE>(p, grid, composite, stats, false, stream);
     }
     return cudaErrorInvalidValue;

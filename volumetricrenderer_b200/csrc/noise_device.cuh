@@ -62,7 +62,12 @@ __device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
 // The table offset n*16 comes straight from the integer pipe of the FMA unit:
 //   h = t*C;  h16 = t*(C<<4) = h<<4;  off = (h16 ^ (h16 >> 15)) & 0xF0  ==  (((h >> 15) ^ h) & 15) * 16
 // (bits 4..7 of h16>>15 are bits 15..18 of h: the four bits the left shift drops are never looked at)
-struct __align__(16) GradLut { float4 g[16]; };
+// h[n] = the same gradient in 8 bytes for the cell-table march (perlin3_cells): .x = cx as float, .y = the upper halves of cy
+// and cz side by side (cy_bits & 0xffff0000 | cz_bits >> 16) — components are -1, 0 or +1, whose lower 16 mantissa bits are
+// zero, so one AND and one shift give the floats back exactly.  An LDS.64 costs the shared-memory pipe 2 wavefronts per
+// warp where the LDS.128 costs 4, and that pipe — not issue — bounds the march once the hashes are gone
+// (profiles/r02_march_fbm_cells_lds128.txt: 75 % of its peak at 68 % issue).
+struct __align__(16) GradLut { float4 g[16]; uint2 h[16]; };
 
 __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
     if (tid < 16) {
@@ -75,8 +80,11 @@ __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
         const float cy = (iu == 1 ? su : 0.0f) + (iv == 1 ? sv : 0.0f);
         const float cz = iv == 2 ? sv : 0.0f;
         lut->g[n] = make_float4(cx, cy, cz, 0.0f);
+        lut->h[n] = make_uint2(__float_as_uint(cx), (__float_as_uint(cy) & 0xffff0000u) | (__float_as_uint(cz) >> 16));
     }
 }
+// byte offset of h[n] from the start of the table for a lattice hash t (the cell tables store this, one byte per corner)
+__device__ __forceinline__ unsigned int grad_lut_offset8(int t);
 
 // A table the kernel guarantees to sit at shared-window address kLutFixedAddr (the first static __shared__ object of a
 // non-cluster launch on sm_100a: the window starts with 1 KiB the system keeps).  The table base then is an immediate
@@ -105,6 +113,9 @@ __device__ __forceinline__ unsigned int grad_lut_offset(int t) {
     return (h16 ^ (h16 >> 15)) & 0xF0u;
 #endif
 }
+__device__ __forceinline__ unsigned int grad_lut_offset8(int t) { return grad_lut_offset(t) >> 1; }
+// what a cell-table byte holds (grad_lut_at)
+__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t);
 __device__ __forceinline__ float4 grad_lut_fetch(const GradLut* lut, int t) {
     return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + grad_lut_offset(t));
 }
@@ -384,6 +395,172 @@ __device__ __forceinline__ f2 fbm_perlin2(LUT lut, const FbmField& F, f2 x, f2 y
     return fbm_perlin2_n<0>(lut, F, x, y, z);
 }
 
+// ---- the same fBm with the lattice hashes read from per-cell tables (volrt_internal.h: FbmCells) ------------------------
+// profiles/r01_march_fbm_pairs_unrolled.txt: the march is bound by instruction count, and of the ~100 instructions per
+// octave and point 40 are the lattice hash: three IMADs by the primes, three adds, two seed XORs and per corner a
+// three-input XOR, an IMAD, a shift and a mask.  None of it depends on anything but the integer cell coordinates, the
+// octave and the seed — and the box holds only (frequency * lacunarity^o + 1)^3 cells per octave (C2: 5^3 ... 63^3).
+// So vr_set_params evaluates the hashes once per cell (fbm_cell_table_kernel: 8 bytes per cell = the eight corners'
+// gradient-table offsets, 2.4 MB for the five octaves of C2/C3, L1/L2 resident) and a sample fetches them with ONE
+// 64-bit load: cell index in float (exact below 2^24: fma(zs, n^2, fma(ys, n, xs + K)), K = 1.5*2^23 + the index of
+// cell (0,0,0)), whose bit pattern is 0x4B400000 + index, so the address is one IMAD.WIDE with an adjusted base.
+// Everything after the hash — fractions, fades, gradient dot products, lerps, in the same order — is unchanged, and the
+// table holds exactly what the hash would have produced: the value is bit-identical to perlin3_lut / perlin3_lut2.
+__device__ __forceinline__ uint2 fbm_cell_fetch(const FbmCellOctave& C, float xs, float ys, float zs) {
+    const float t = fmaf(zs, C.n2f, fmaf(ys, C.nf, xs + C.kf));
+    return __ldg(reinterpret_cast<const uint2*>(C.base_adj + (unsigned long long)__float_as_uint(t) * 8ull));
+}
+// floor() of a lattice coordinate on the FMA pipe instead of FRND (an XU-pipe instruction: 8 issue cycles per warp, three per
+// octave and point).  Coordinates are in [0, 2^22) here (inside the unit box, times frequency * lacunarity^o), so
+// x + (2^23 - 1/2) rounds — once, to nearest — to 2^23 + rint(x - 1/2), which is 2^23 + floor(x) except that an integral x
+// may land one cell lower with fraction exactly 1, where Perlin noise has the same value (fade 1, far corner's offset 0;
+// the tables keep a guard cell at -1).
+#ifndef VOLRT_CELLS_FLOOR_MAGIC
+#define VOLRT_CELLS_FLOOR_MAGIC 0
+#endif
+__device__ __forceinline__ float cell_floor(float x) {
+#if VOLRT_CELLS_FLOOR_MAGIC
+    return (x + 8388607.5f) - 8388608.0f;
+#else
+    return floorf(x);
+#endif
+}
+__device__ __forceinline__ f2 cell_floor2(f2 x) {
+#if VOLRT_CELLS_FLOOR_MAGIC
+    return sub2(add2(x, splat2(8388607.5f)), splat2(8388608.0f));
+#else
+    return make_f2(floorf(f2_a(x)), floorf(f2_b(x)));
+#endif
+}
+__device__ __forceinline__ unsigned int cell_corner(unsigned int w, int k) { return __byte_perm(w, 0u, 0x4440u + (unsigned)k); }
+// off = the byte a cell-table entry holds for the corner: n * 16 into g[], or (VOLRT_CELLS_LDS64) n * 8 into h[].
+// Measured on B200, C2: the 8-byte entries halve the shared-memory wavefronts (306 M -> 146 M per frame) but their two
+// decode instructions per corner cost more than that buys — 1.104 G -> 1.296 G warp instructions, 1.478 -> 1.553 ms
+// (profiles/r02_march_fbm_cells_lds128.txt / _lds64.txt).  The march is issue-bound before it is LDS-bound.
+#ifndef VOLRT_CELLS_LDS64
+#define VOLRT_CELLS_LDS64 0
+#endif
+__device__ __forceinline__ float4 grad_lut_at(GradLutFixed, unsigned int off) {
+#if VOLRT_CELLS_LDS64
+    unsigned int a, b;
+    asm("ld.shared.v2.u32 {%0, %1}, [%2 + %3];" : "=r"(a), "=r"(b) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR + 256));
+    return make_float4(__uint_as_float(a), __uint_as_float(b & 0xffff0000u), __uint_as_float(b << 16), 0.0f);
+#else
+    float4 g;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4 + %5];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR));
+    return g;
+#endif
+}
+__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t) { return VOLRT_CELLS_LDS64 ? grad_lut_offset8(t) : grad_lut_offset(t); }
+__device__ __forceinline__ float4 grad_lut_at(const GradLut* lut, unsigned int off) {
+#if VOLRT_CELLS_LDS64
+    const uint2 v = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(lut->h) + off);
+    return make_float4(__uint_as_float(v.x), __uint_as_float(v.y & 0xffff0000u), __uint_as_float(v.y << 16), 0.0f);
+#else
+    return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
+#endif
+}
+template <class LUT>
+__device__ __forceinline__ float grad_edge_at(LUT lut, unsigned int o0, unsigned int o1, float fx0, float fx1, float fy, float fz, float s) {
+    const float4 g0 = grad_lut_at(lut, o0), g1 = grad_lut_at(lut, o1);
+    const float d0 = fmaf(fz, g0.z, fmaf(fy, g0.y, fx0 * g0.x));
+    const float e = fmaf(fz, g1.z, fmaf(fy, g1.y, fmaf(fx1, g1.x, -d0)));
+    return fmaf(s, e, d0);
+}
+template <class LUT>
+__device__ __forceinline__ float perlin3_cells(LUT lut, const FbmCellOctave& C, float x, float y, float z) {
+    float xs = cell_floor(x), ys = cell_floor(y), zs = cell_floor(z);
+    const uint2 w = fbm_cell_fetch(C, xs, ys, zs);
+    float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
+    float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
+    xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
+    float a = lerpf(grad_edge_at(lut, cell_corner(w.x, 0), cell_corner(w.x, 1), xf0, xf1, yf0, zf0, xs),
+                    grad_edge_at(lut, cell_corner(w.x, 2), cell_corner(w.x, 3), xf0, xf1, yf1, zf0, xs), ys);
+    float b = lerpf(grad_edge_at(lut, cell_corner(w.y, 0), cell_corner(w.y, 1), xf0, xf1, yf0, zf1, xs),
+                    grad_edge_at(lut, cell_corner(w.y, 2), cell_corner(w.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    return lerpf(a, b, zs);
+}
+template <class LUT>
+__device__ __forceinline__ f2 grad_edge_at2(LUT lut, unsigned int oA0, unsigned int oA1, unsigned int oB0, unsigned int oB1,
+                                            f2 fx0, f2 fx1, f2 fy, f2 fz, f2 s) {
+    const float4 a0 = grad_lut_at(lut, oA0), a1 = grad_lut_at(lut, oA1);
+    const float4 b0 = grad_lut_at(lut, oB0), b1 = grad_lut_at(lut, oB1);
+    const float fyA = f2_a(fy), fyB = f2_b(fy), fzA = f2_a(fz), fzB = f2_b(fz);
+    const float d0A = fmaf(fzA, a0.z, fmaf(fyA, a0.y, f2_a(fx0) * a0.x));
+    const float d0B = fmaf(fzB, b0.z, fmaf(fyB, b0.y, f2_b(fx0) * b0.x));
+    const float eA = fmaf(fzA, a1.z, fmaf(fyA, a1.y, fmaf(f2_a(fx1), a1.x, -d0A)));
+    const float eB = fmaf(fzB, b1.z, fmaf(fyB, b1.y, fmaf(f2_b(fx1), b1.x, -d0B)));
+    return fma2(s, make_f2(eA, eB), make_f2(d0A, d0B));
+}
+template <class LUT>
+__device__ __forceinline__ f2 perlin3_cells2(LUT lut, const FbmCellOctave& C, f2 x, f2 y, f2 z) {
+    f2 xs = cell_floor2(x), ys = cell_floor2(y), zs = cell_floor2(z);
+    const uint2 wA = fbm_cell_fetch(C, f2_a(xs), f2_a(ys), f2_a(zs));
+    const uint2 wB = fbm_cell_fetch(C, f2_b(xs), f2_b(ys), f2_b(zs));
+    const f2 xf0 = sub2(x, xs), yf0 = sub2(y, ys), zf0 = sub2(z, zs);
+    const f2 m1 = splat2(-1.0f);
+    const f2 xf1 = add2(xf0, m1), yf1 = add2(yf0, m1), zf1 = add2(zf0, m1);
+    xs = quintic2(xf0); ys = quintic2(yf0); zs = quintic2(zf0);
+    const f2 a = lerp2(grad_edge_at2(lut, cell_corner(wA.x, 0), cell_corner(wA.x, 1), cell_corner(wB.x, 0), cell_corner(wB.x, 1), xf0, xf1, yf0, zf0, xs),
+                       grad_edge_at2(lut, cell_corner(wA.x, 2), cell_corner(wA.x, 3), cell_corner(wB.x, 2), cell_corner(wB.x, 3), xf0, xf1, yf1, zf0, xs), ys);
+    const f2 b = lerp2(grad_edge_at2(lut, cell_corner(wA.y, 0), cell_corner(wA.y, 1), cell_corner(wB.y, 0), cell_corner(wB.y, 1), xf0, xf1, yf0, zf1, xs),
+                       grad_edge_at2(lut, cell_corner(wA.y, 2), cell_corner(wA.y, 3), cell_corner(wB.y, 2), cell_corner(wB.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    return lerp2(a, b, zs);
+}
+// the compile-time octave count (C2 / C3: 5), octave by octave
+template <int I, int OCT, class LUT>
+__device__ __forceinline__ float fbm_cells_unrolled(LUT lut, const FbmField& F, const FbmCells& T, float x, float y, float z, float amp, float sum) {
+    if constexpr (I >= OCT) return sum;
+    else {
+        const float p = perlin3_cells(lut, T.oct[I], x, y, z);
+        sum = I == 0 ? p * amp : fmaf(p, amp, sum);
+        return fbm_cells_unrolled<I + 1, OCT>(lut, F, T, x * F.lacunarity, y * F.lacunarity, z * F.lacunarity, amp * F.gain, sum);
+    }
+}
+template <int I, int OCT, class LUT>
+__device__ __forceinline__ f2 fbm_cells_unrolled2(LUT lut, const FbmField& F, const FbmCells& T, f2 x, f2 y, f2 z, f2 lac, float amp, f2 sum) {
+    if constexpr (I >= OCT) return sum;
+    else {
+        const f2 p = perlin3_cells2(lut, T.oct[I], x, y, z);
+        sum = I == 0 ? mul2(p, splat2(amp)) : fma2(p, splat2(amp), sum);
+        return fbm_cells_unrolled2<I + 1, OCT>(lut, F, T, mul2(x, lac), mul2(y, lac), mul2(z, lac), lac, amp * F.gain, sum);
+    }
+}
+
+template <int OCT, class LUT>
+__device__ __forceinline__ float fbm_perlin_cells_n(LUT lut, const FbmField& F, const FbmCells& T, float x, float y, float z) {
+    const int n = OCT > 0 ? OCT : F.octaves;
+    float amp = F.bounding * kPerlinScale;
+    if constexpr (OCT > 0) return fbm_cells_unrolled<0, OCT>(lut, F, T, x, y, z, amp, 0.0f);
+    float sum = perlin3_cells(lut, T.oct[0], x, y, z) * amp;
+#pragma unroll
+    for (int i = 1; i < n; ++i) {
+        amp *= F.gain;
+        x *= F.lacunarity; y *= F.lacunarity; z *= F.lacunarity;
+        sum = fmaf(perlin3_cells(lut, T.oct[i], x, y, z), amp, sum);
+    }
+    return sum;
+}
+template <int OCT, class LUT>
+__device__ __forceinline__ f2 fbm_perlin_cells2_n(LUT lut, const FbmField& F, const FbmCells& T, f2 x, f2 y, f2 z) {
+    const int n = OCT > 0 ? OCT : F.octaves;
+    float amp = F.bounding * kPerlinScale;
+    const f2 lac = splat2(F.lacunarity);
+    if constexpr (OCT > 0) return fbm_cells_unrolled2<0, OCT>(lut, F, T, x, y, z, lac, amp, make_f2(0.0f, 0.0f));
+    f2 sum = mul2(perlin3_cells2(lut, T.oct[0], x, y, z), splat2(amp));
+#pragma unroll
+    for (int i = 1; i < n; ++i) {
+        amp *= F.gain;
+        x = mul2(x, lac); y = mul2(y, lac); z = mul2(z, lac);
+        sum = fma2(perlin3_cells2(lut, T.oct[i], x, y, z), splat2(amp), sum);
+    }
+    return sum;
+}
+// the one-point routine (the primary sample) unrolled too: C2 1.468 -> 1.441 ms on B200 (the hash variant lost by it: spills)
+#ifndef VOLRT_FBM_CELLS_UNROLL_SCALAR
+#define VOLRT_FBM_CELLS_UNROLL_SCALAR 5
+#endif
+
 __device__ __forceinline__ float fbm_edge(const FbmField& F, float ux, float uy, float uz) {
     const float m = fmaxf(fmaxf(fabsf(ux - 0.5f), fabsf(uy - 0.5f)), fabsf(uz - 0.5f));
     const float t = __saturatef((m - F.falloff0) * F.inv_falloff);
@@ -410,6 +587,43 @@ __device__ __forceinline__ float density_fbm(LUT lut, const FbmField& F, float u
     float edge = 1.0f - t * t * (3.0f - 2.0f * t);
     if (edge <= 0.0f) return 0.0f;
     float f = fbm_perlin(lut, F, ux * F.frequency, uy * F.frequency, uz * F.frequency);
+    return fmaxf(0.0f, (0.5f * f + 0.5f) - F.coverage) * edge;
+}
+
+// The cell tables cover the unit box only.  vr_set_params enables them when falloff1 <= 1/2, so a positive edge fade
+// already means maxabs(P - 1/2) < 1/2; what is left to keep out is a NaN coordinate (fmaxf drops NaNs, the fade of a NaN
+// saturates to 0 and the edge would read 1): the maximum is taken NaN-propagating and anything not below 3/4 gets edge 0.
+__device__ __forceinline__ float max_nan(float a, float b) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float fbm_edge_in_box(const FbmField& F, float ux, float uy, float uz) {
+    const float m = max_nan(max_nan(fabsf(ux - 0.5f), fabsf(uy - 0.5f)), fabsf(uz - 0.5f));
+    const float t = __saturatef((m - F.falloff0) * F.inv_falloff);
+    const float e = 1.0f - t * t * (3.0f - 2.0f * t);
+    return m < 0.75f ? e : 0.0f;
+}
+// both points must be inside the unit box (the light-march checks inside01 before it pairs two samples)
+template <class LUT>
+__device__ __forceinline__ f2 density_fbm_cells2(LUT lut, const FbmField& F, const FbmCells& T, f2 ux, f2 uy, f2 uz) {
+    const float ea = fbm_edge(F, f2_a(ux), f2_a(uy), f2_a(uz)), eb = fbm_edge(F, f2_b(ux), f2_b(uy), f2_b(uz));
+    if (ea <= 0.0f && eb <= 0.0f) return make_f2(0.0f, 0.0f);
+    const f2 fr = splat2(F.frequency);
+    const f2 x = mul2(ux, fr), y = mul2(uy, fr), z = mul2(uz, fr);
+    const f2 f = (VOLRT_FBM_UNROLL_OCTAVES > 0 && F.octaves == VOLRT_FBM_UNROLL_OCTAVES) ? fbm_perlin_cells2_n<VOLRT_FBM_UNROLL_OCTAVES>(lut, F, T, x, y, z)
+                                                                                         : fbm_perlin_cells2_n<0>(lut, F, T, x, y, z);
+    const float fa = f2_a(f), fb = f2_b(f);
+    return make_f2(ea <= 0.0f ? 0.0f : fmaxf(0.0f, (0.5f * fa + 0.5f) - F.coverage) * ea,
+                   eb <= 0.0f ? 0.0f : fmaxf(0.0f, (0.5f * fb + 0.5f) - F.coverage) * eb);
+}
+template <class LUT>
+__device__ __forceinline__ float density_fbm_cells(LUT lut, const FbmField& F, const FbmCells& T, float ux, float uy, float uz) {
+    const float edge = fbm_edge_in_box(F, ux, uy, uz);
+    if (edge <= 0.0f) return 0.0f;
+    const float x = ux * F.frequency, y = uy * F.frequency, z = uz * F.frequency;
+    const float f = (VOLRT_FBM_CELLS_UNROLL_SCALAR > 0 && F.octaves == VOLRT_FBM_CELLS_UNROLL_SCALAR) ? fbm_perlin_cells_n<VOLRT_FBM_CELLS_UNROLL_SCALAR>(lut, F, T, x, y, z)
+                                                                                                       : fbm_perlin_cells_n<0>(lut, F, T, x, y, z);
     return fmaxf(0.0f, (0.5f * f + 0.5f) - F.coverage) * edge;
 }
 

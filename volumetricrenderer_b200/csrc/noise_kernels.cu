@@ -142,6 +142,27 @@ cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_
     return cudaGetLastError();
 }
 
+// fBm lattice-cell table of one octave (volrt_internal.h: FbmCells; noise_device.cuh: perlin3_cells): entry (ix,iy,iz), stored at
+// ((iz+1)*n + iy+1)*n + ix+1 for lattice coordinates -1 .. n-2, holds the gradient-table offsets of the cell's eight corners —
+// what perlin3_lut derives per sample from HashPrimes (Utils.inl:295-302) — as bytes x0y0, x1y0, x0y1, x1y1 at z0 (.x) and z1 (.y).
+__global__ void __launch_bounds__(256) fbm_cell_table_kernel(int seed, int n, uint2* __restrict__ entries) {
+    const int total = n * n * n, idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int ix = idx % n - 1, iy = (idx / n) % n - 1, iz = idx / (n * n) - 1;
+    const int x0 = ix * kPrimeX, y0 = iy * kPrimeY, z0 = iz * kPrimeZ;
+    const int x1 = x0 + kPrimeX, y1 = y0 + kPrimeY, z1 = z0 + kPrimeZ;
+    const int sz0 = seed ^ z0, sz1 = seed ^ z1;
+    uint2 e;
+    e.x = grad_lut_cell_byte(sz0 ^ x0 ^ y0) | grad_lut_cell_byte(sz0 ^ x1 ^ y0) << 8 | grad_lut_cell_byte(sz0 ^ x0 ^ y1) << 16 | grad_lut_cell_byte(sz0 ^ x1 ^ y1) << 24;
+    e.y = grad_lut_cell_byte(sz1 ^ x0 ^ y0) | grad_lut_cell_byte(sz1 ^ x1 ^ y0) << 8 | grad_lut_cell_byte(sz1 ^ x0 ^ y1) << 16 | grad_lut_cell_byte(sz1 ^ x1 ^ y1) << 24;
+    entries[idx] = e;
+}
+cudaError_t launch_fbm_cell_table(int seed, int n, uint2* entries, cudaStream_t s) {
+    const int total = n * n * n;
+    fbm_cell_table_kernel<<<(total + 255) / 256, 256, 0, s>>>(seed, n, entries);
+    return cudaGetLastError();
+}
+
 // Occupancy of 8^3-voxel bricks: a trilinear fetch at a position inside brick b touches texels
 // 8b-1 .. 8b+8 per axis, so the brick is "empty" iff all of those are exactly zero.  Index -1
 // and N wrap to 0 and N-1 in both addressing modes, so clamping the apron is exact.

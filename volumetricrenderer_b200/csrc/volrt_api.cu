@@ -74,6 +74,13 @@ struct vr_context {
     TreeInstr* d_tree_prog = nullptr;       // vr_noise_tree_grid: program upload buffer and a grow-only output plane
     float* d_tree_out = nullptr;
     size_t tree_out_bytes = 0;
+    // fBm lattice-cell tables (volrt_internal.h: FbmCells), rebuilt by vr_set_params when the field's lattice changes
+    uint2* d_fbm_cells = nullptr;          // the tables of every octave, back to back
+    size_t fbm_cells_bytes = 0;
+    FbmCells fbm_cells{};
+    bool fbm_cells_ok = false;
+    int fbm_cells_key_oct = 0, fbm_cells_key_seed = 0;
+    float fbm_cells_key_freq = 0.0f, fbm_cells_key_lac = 0.0f;
     const float* trusted_level0 = nullptr; // device copy of a file's pyramid level 0 (VR_FILE_TRUST_PYRAMID), for one finish_volume
     uint32_t fill_launches = 0;            // kernels the current upload / bake has launched so far
     // params
@@ -252,6 +259,7 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->d_tree_prog) cudaFree(c->d_tree_prog);
     if (c->d_march_tree) cudaFree(c->d_march_tree);
     if (c->d_tree_out) cudaFree(c->d_tree_out);
+    if (c->d_fbm_cells) cudaFree(c->d_fbm_cells);
     for (int i = 0; i < vr_context::kFileRing; ++i) {
         if (c->file_stage[i]) cudaFreeHost(c->file_stage[i]);
         if (c->file_done[i]) cudaEventDestroy(c->file_done[i]);
@@ -874,6 +882,58 @@ static bool decode_view(const unsigned char* ubo0, uint32_t n0, const unsigned c
     return true;
 }
 
+// The fBm field's lattice hashes, once per cell (noise_device.cuh: perlin3_cells).  Eligible when every octave's lattice
+// over the unit box is small enough for the float-encoded cell index (n^3 + 1.5*2^23 < 2^24) and the tables fit a budget;
+// anything else marches with the per-sample hash (MARCH_FBM).  Rebuilt only when octaves / seed / frequency / lacunarity change.
+static vr_status prepare_fbm_cells(vr_context* c, const vr_params* p) {
+    const char* env = std::getenv("VOLRT_FBM_CELLS");        // 0 = march with the per-sample hash (A/B runs, tests)
+    const bool want = !env || std::atoi(env) != 0;
+    c->fbm_cells_ok = false;
+    if (!want || p->fbm_octaves < 1 || p->fbm_octaves > kFbmCellMaxOctaves) return VR_OK;
+    if (!(p->fbm_frequency > 0.0f) || !(p->fbm_lacunarity > 0.0f) || !(p->fbm_frequency < 1e6f) || !(p->fbm_lacunarity < 1e3f)) return VR_OK;
+    // the noise is only evaluated where the edge fade is positive, i.e. maxabs(P - 1/2) < falloff1: inside the unit box
+    if (!(p->fbm_falloff1 <= 0.5f) || !(p->fbm_falloff1 > p->fbm_falloff0)) return VR_OK;
+    int n[kFbmCellMaxOctaves];
+    size_t total = 0;
+    double top = (double)p->fbm_frequency * (1.0 + 1e-5);
+    for (int o = 0; o < p->fbm_octaves; ++o) {
+        const double cells = std::floor(top) + 3.0;                 // lattice coordinates -1 .. floor(top) + 1
+        if (cells > 160.0) return VR_OK;                            // 160^3 + 1.5*2^23 < 2^24
+        n[o] = (int)cells;
+        total += (size_t)n[o] * n[o] * n[o];
+        top *= (double)p->fbm_lacunarity * (1.0 + 1e-5);
+    }
+    if (total * sizeof(uint2) > ((size_t)64 << 20)) return VR_OK;
+    const size_t need = total * sizeof(uint2);
+    const bool same = c->d_fbm_cells && c->fbm_cells_key_oct == p->fbm_octaves && c->fbm_cells_key_seed == p->fbm_seed &&
+                      c->fbm_cells_key_freq == p->fbm_frequency && c->fbm_cells_key_lac == p->fbm_lacunarity;
+    if (!same) {
+        if (c->foreign_stream_pending) { VR_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev1, 0)); c->foreign_stream_pending = false; }
+        if (c->fbm_cells_bytes < need) {
+            VR_CUDA(c, cudaStreamSynchronize(c->stream));
+            if (c->d_fbm_cells) { cudaFree(c->d_fbm_cells); c->d_fbm_cells = nullptr; c->fbm_cells_bytes = 0; }
+            VR_CUDA(c, cudaMalloc(&c->d_fbm_cells, need));
+            c->fbm_cells_bytes = need;
+        }
+        uint2* at = c->d_fbm_cells;
+        for (int o = 0; o < p->fbm_octaves; ++o) {
+            VR_CUDA(c, launch_fbm_cell_table(p->fbm_seed + o, n[o], at, c->stream));     // Fractal.inl: seed + octave index
+            FbmCellOctave& C = c->fbm_cells.oct[o];
+            C.base_adj = (unsigned long long)(uintptr_t)at - 8ull * 0x4B400000ull;
+            C.nf = (float)n[o];
+            C.n2f = (float)(n[o] * n[o]);
+            C.kf = 12582912.0f + (float)(n[o] * n[o] + n[o] + 1);
+            C.pad = 0.0f;
+            at += (size_t)n[o] * n[o] * n[o];
+        }
+        VR_CUDA(c, cudaEventRecord(c->ev_params, c->stream));      // a render on a caller's stream waits for the tables
+        c->fbm_cells_key_oct = p->fbm_octaves; c->fbm_cells_key_seed = p->fbm_seed;
+        c->fbm_cells_key_freq = p->fbm_frequency; c->fbm_cells_key_lac = p->fbm_lacunarity;
+    }
+    c->fbm_cells_ok = true;
+    return VR_OK;
+}
+
 extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
     // a caller built before the VR_DENSITY_TREE fields were appended passes the shorter struct
@@ -928,6 +988,10 @@ extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
         c->march_tree_n = (int)t->prog.size();
         c->march_tree_result = t->result_reg;
     }
+    if (p->density_mode == VR_DENSITY_FBM) {
+        vr_status st = prepare_fbm_cells(c, p);
+        if (st != VR_OK) return st;
+    }
     c->views_on_device = !(views == 1 && !p->view_ubos);
     c->params = *p;
     c->params.density_tree = nullptr;
@@ -961,7 +1025,11 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.queue_chunk = c->queue_chunk;
     m.ray_split = c->ray_split;
     m.ray_split_composite = c->ray_split_composite;
-    if (p.density_mode == VR_DENSITY_FBM) { variant = MARCH_FBM; return VR_OK; }
+    if (p.density_mode == VR_DENSITY_FBM) {
+        variant = MARCH_FBM;
+        if (c->fbm_cells_ok) { m.cells = c->fbm_cells; variant = MARCH_FBM_CELLS; }
+        return VR_OK;
+    }
     if (p.density_mode == VR_DENSITY_TREE) {
         m.tree_prog = c->d_march_tree; m.tree_n = c->march_tree_n; m.tree_result = c->march_tree_result;
         m.tree_seed = p.tree_seed; m.tree_freq = p.tree_frequency;
@@ -1026,7 +1094,7 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
     if (direct) { m.out = t->dst; m.row_pitch = pitch; m.view_stride = pitch * c->height; }
     const bool stats = (t->flags & VR_RENDER_STATS) != 0;
     if (stats) VR_CUDA(c, cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), s));
-    if (t->stream && c->views_on_device) {   // the view block was uploaded on the context stream
+    if (t->stream && (c->views_on_device || variant == MARCH_FBM_CELLS)) {   // the view block / the fBm cell tables were written on the context stream
         VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_params, 0));
     }
     // asynchronous render into host memory: alternate between two device frames and hand the D2H copy to

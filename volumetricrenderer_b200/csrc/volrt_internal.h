@@ -45,6 +45,20 @@ struct FbmField {
     float inv_falloff;      // 1 / (falloff1 - falloff0): a multiply per sample instead of a divide
 };
 
+// Lattice-cell tables of the fBm field (noise_device.cuh: perlin3_cells).  Per octave, one uint2 per lattice CELL of the
+// box: the eight corners' offsets into the gradient table (bytes: x0y0, x1y0, x0y1, x1y1 at z0 in .x, at z1 in .y), i.e.
+// FastNoise2's HashPrimes + the low nibble GetGradientDot looks at (Utils.inl:229-247,295-302), evaluated once per cell
+// at vr_set_params instead of eight times per sample per octave.  Cells cover lattice coordinates -1 .. n-2 per axis.
+constexpr int kFbmCellMaxOctaves = 8;
+struct FbmCellOctave {
+    unsigned long long base_adj;   // device address of cell (-1,-1,-1)'s entry, minus 8 * 0x4B400000 (the index arrives as float bits)
+    float nf, n2f, kf;             // n, n*n, and 1.5*2^23 + n*n + n + 1 (magic + the offset of lattice coordinate (0,0,0))
+    float pad;
+};
+struct FbmCells {
+    FbmCellOctave oct[kFbmCellMaxOctaves];
+};
+
 struct MarchParams {
     // target
     int width, height;
@@ -81,6 +95,7 @@ struct MarchParams {
     int skip_empty;
     BrickInfo bricks;
     FbmField fbm;
+    FbmCells cells;             // MARCH_FBM_CELLS only
     // VR_DENSITY_TREE: the compiled program (device copy owned by the context), evaluated at P * tree_freq
     const TreeInstr* tree_prog;
     int tree_n, tree_result, tree_seed;
@@ -96,7 +111,8 @@ enum MarchVariant {
     MARCH_SINGLE_LINEAR = 3,
     MARCH_FBM = 4,           // procedural density
     MARCH_SINGLE_BRICK = 5,  // one-channel fp16 grid, boxes staged to shared memory by TMA
-    MARCH_TREE = 6           // procedural density from a compiled FastNoise2 node tree (noise_tree_eval.cuh)
+    MARCH_TREE = 6,          // procedural density from a compiled FastNoise2 node tree (noise_tree_eval.cuh)
+    MARCH_FBM_CELLS = 7      // MARCH_FBM with the lattice hashes read from per-cell tables (MarchParams::cells)
 };
 
 constexpr size_t kGatherMailboxBytes = 256;    // behind the context's frames: counters of the device-side gather protocol (volrt_api.cu)
@@ -119,6 +135,8 @@ cudaError_t launch_noise_minmax_only(const NoiseField& f, int n, unsigned int* m
 struct PackChannel { const float* field; float mn, mx; uint32_t power; };
 cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_rgba8, cudaStream_t s);
 cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s);
+// fBm lattice-cell tables: entries[n^3] for one octave (seed already offset by the octave index), cells -1 .. n-2 per axis
+cudaError_t launch_fbm_cell_table(int seed, int n, uint2* entries, cudaStream_t s);
 cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int address_mode,
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
 cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, unsigned int* mm8, cudaStream_t s);   // mm8 may be null
