@@ -440,15 +440,6 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
         float T = 1.0f;
         cr = cg = cb = 0.0f;
         const f3 lv = {P.sun_dir[0] * P.light_step_len * 0.5f, P.sun_dir[1] * P.light_step_len * 0.5f, P.sun_dir[2] * P.light_step_len * 0.5f};
-        // fBm, optional: the densities of steps i and i+1 evaluated together on the packed FP32 instructions like the light
-        // samples, the second one waiting in rho_next for the next iteration.  Measured slower (C2 1.763 -> 1.781 ms, C3
-        // 17.18 -> 17.30): the value held across the light-march costs registers (126, 4 CTAs/SM).  Off by default.
-#ifndef VOLRT_FBM_PAIR_PRIMARY
-#define VOLRT_FBM_PAIR_PRIMARY 0
-#endif
-        constexpr bool PAIR_PRIMARY = (VARIANT == MARCH_FBM) && VOLRT_FBM_PAIRS && VOLRT_FBM_PAIR_PRIMARY && !STATS;   // hash variant only
-        float rho_next = 0.0f;
-        bool have_next = false;
         // Texture-filtered grids: a step is one dependent chain brick byte -> fetch -> exp, and on a grid far larger than L2
         // (C5: 2 GiB) a warp with ONE fetch in flight leaves the memory system idle (long_scoreboard 7 per issue, DRAM 45 %).
         // So the fetches of the next COMPOSITE_BATCH steps are issued together and consumed in order.  The brick map is
@@ -522,20 +513,7 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
                     continue;           // transmittance unchanged: nothing to test for early termination
                 }
             }
-            if constexpr (PAIR_PRIMARY) {
-                if (have_next) {
-                    rho = rho_next;
-                    have_next = false;
-                } else if (i + 1 < n) {
-                    const f3 q = add3(p, ray.step);
-                    const f2 r = density_fbm2(GradLutFixed{}, P.fbm, make_f2(p.x, q.x), make_f2(p.y, q.y), make_f2(p.z, q.z));
-                    rho = f2_a(r);
-                    rho_next = f2_b(r);
-                    have_next = true;
-                } else {
-                    rho = density_at<VARIANT>(P, rc, unorm, &lut, p);
-                }
-            } else if constexpr (VARIANT == MARCH_TREE && !STATS) {
+            if constexpr (VARIANT == MARCH_TREE && !STATS) {
                 rho = 0.0f;                         // evaluated below, in the light-march loop's iteration 0 (one interpreter call site)
             } else {
                 rho = density_at<VARIANT>(P, rc, unorm, &lut, p);

@@ -460,27 +460,27 @@ __device__ __forceinline__ float4 grad_lut_at(const GradLut* lut, unsigned int o
     return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
 #endif
 }
-template <class LUT>
+template <int I = -1, class LUT>
 __device__ __forceinline__ float grad_edge_at(LUT lut, unsigned int o0, unsigned int o1, float fx0, float fx1, float fy, float fz, float s) {
     const float4 g0 = grad_lut_at(lut, o0), g1 = grad_lut_at(lut, o1);
     const float d0 = fmaf(fz, g0.z, fmaf(fy, g0.y, fx0 * g0.x));
     const float e = fmaf(fz, g1.z, fmaf(fy, g1.y, fmaf(fx1, g1.x, -d0)));
     return fmaf(s, e, d0);
 }
-template <class LUT>
+template <int I = -1, class LUT>
 __device__ __forceinline__ float perlin3_cells(LUT lut, const FbmCellOctave& C, float x, float y, float z) {
     float xs = cell_floor(x), ys = cell_floor(y), zs = cell_floor(z);
     const uint2 w = fbm_cell_fetch(C, xs, ys, zs);
     float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
     float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
     xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
-    float a = lerpf(grad_edge_at(lut, cell_corner(w.x, 0), cell_corner(w.x, 1), xf0, xf1, yf0, zf0, xs),
-                    grad_edge_at(lut, cell_corner(w.x, 2), cell_corner(w.x, 3), xf0, xf1, yf1, zf0, xs), ys);
-    float b = lerpf(grad_edge_at(lut, cell_corner(w.y, 0), cell_corner(w.y, 1), xf0, xf1, yf0, zf1, xs),
-                    grad_edge_at(lut, cell_corner(w.y, 2), cell_corner(w.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    float a = lerpf(grad_edge_at<I>(lut, cell_corner(w.x, 0), cell_corner(w.x, 1), xf0, xf1, yf0, zf0, xs),
+                    grad_edge_at<I>(lut, cell_corner(w.x, 2), cell_corner(w.x, 3), xf0, xf1, yf1, zf0, xs), ys);
+    float b = lerpf(grad_edge_at<I>(lut, cell_corner(w.y, 0), cell_corner(w.y, 1), xf0, xf1, yf0, zf1, xs),
+                    grad_edge_at<I>(lut, cell_corner(w.y, 2), cell_corner(w.y, 3), xf0, xf1, yf1, zf1, xs), ys);
     return lerpf(a, b, zs);
 }
-template <class LUT>
+template <int I = -1, class LUT>
 __device__ __forceinline__ f2 grad_edge_at2(LUT lut, unsigned int oA0, unsigned int oA1, unsigned int oB0, unsigned int oB1,
                                             f2 fx0, f2 fx1, f2 fy, f2 fz, f2 s) {
     const float4 a0 = grad_lut_at(lut, oA0), a1 = grad_lut_at(lut, oA1);
@@ -492,7 +492,7 @@ __device__ __forceinline__ f2 grad_edge_at2(LUT lut, unsigned int oA0, unsigned 
     const float eB = fmaf(fzB, b1.z, fmaf(fyB, b1.y, fmaf(f2_b(fx1), b1.x, -d0B)));
     return fma2(s, make_f2(eA, eB), make_f2(d0A, d0B));
 }
-template <class LUT>
+template <int I = -1, class LUT>
 __device__ __forceinline__ f2 perlin3_cells2(LUT lut, const FbmCellOctave& C, f2 x, f2 y, f2 z) {
     f2 xs = cell_floor2(x), ys = cell_floor2(y), zs = cell_floor2(z);
     const uint2 wA = fbm_cell_fetch(C, f2_a(xs), f2_a(ys), f2_a(zs));
@@ -501,10 +501,10 @@ __device__ __forceinline__ f2 perlin3_cells2(LUT lut, const FbmCellOctave& C, f2
     const f2 m1 = splat2(-1.0f);
     const f2 xf1 = add2(xf0, m1), yf1 = add2(yf0, m1), zf1 = add2(zf0, m1);
     xs = quintic2(xf0); ys = quintic2(yf0); zs = quintic2(zf0);
-    const f2 a = lerp2(grad_edge_at2(lut, cell_corner(wA.x, 0), cell_corner(wA.x, 1), cell_corner(wB.x, 0), cell_corner(wB.x, 1), xf0, xf1, yf0, zf0, xs),
-                       grad_edge_at2(lut, cell_corner(wA.x, 2), cell_corner(wA.x, 3), cell_corner(wB.x, 2), cell_corner(wB.x, 3), xf0, xf1, yf1, zf0, xs), ys);
-    const f2 b = lerp2(grad_edge_at2(lut, cell_corner(wA.y, 0), cell_corner(wA.y, 1), cell_corner(wB.y, 0), cell_corner(wB.y, 1), xf0, xf1, yf0, zf1, xs),
-                       grad_edge_at2(lut, cell_corner(wA.y, 2), cell_corner(wA.y, 3), cell_corner(wB.y, 2), cell_corner(wB.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    const f2 a = lerp2(grad_edge_at2<I>(lut, cell_corner(wA.x, 0), cell_corner(wA.x, 1), cell_corner(wB.x, 0), cell_corner(wB.x, 1), xf0, xf1, yf0, zf0, xs),
+                       grad_edge_at2<I>(lut, cell_corner(wA.x, 2), cell_corner(wA.x, 3), cell_corner(wB.x, 2), cell_corner(wB.x, 3), xf0, xf1, yf1, zf0, xs), ys);
+    const f2 b = lerp2(grad_edge_at2<I>(lut, cell_corner(wA.y, 0), cell_corner(wA.y, 1), cell_corner(wB.y, 0), cell_corner(wB.y, 1), xf0, xf1, yf0, zf1, xs),
+                       grad_edge_at2<I>(lut, cell_corner(wA.y, 2), cell_corner(wA.y, 3), cell_corner(wB.y, 2), cell_corner(wB.y, 3), xf0, xf1, yf1, zf1, xs), ys);
     return lerp2(a, b, zs);
 }
 // the compile-time octave count (C2 / C3: 5), octave by octave
@@ -512,7 +512,7 @@ template <int I, int OCT, class LUT>
 __device__ __forceinline__ float fbm_cells_unrolled(LUT lut, const FbmField& F, const FbmCells& T, float x, float y, float z, float amp, float sum) {
     if constexpr (I >= OCT) return sum;
     else {
-        const float p = perlin3_cells(lut, T.oct[I], x, y, z);
+        const float p = perlin3_cells<I>(lut, T.oct[I], x, y, z);
         sum = I == 0 ? p * amp : fmaf(p, amp, sum);
         return fbm_cells_unrolled<I + 1, OCT>(lut, F, T, x * F.lacunarity, y * F.lacunarity, z * F.lacunarity, amp * F.gain, sum);
     }
@@ -521,7 +521,7 @@ template <int I, int OCT, class LUT>
 __device__ __forceinline__ f2 fbm_cells_unrolled2(LUT lut, const FbmField& F, const FbmCells& T, f2 x, f2 y, f2 z, f2 lac, float amp, f2 sum) {
     if constexpr (I >= OCT) return sum;
     else {
-        const f2 p = perlin3_cells2(lut, T.oct[I], x, y, z);
+        const f2 p = perlin3_cells2<I>(lut, T.oct[I], x, y, z);
         sum = I == 0 ? mul2(p, splat2(amp)) : fma2(p, splat2(amp), sum);
         return fbm_cells_unrolled2<I + 1, OCT>(lut, F, T, mul2(x, lac), mul2(y, lac), mul2(z, lac), lac, amp * F.gain, sum);
     }
