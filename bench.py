@@ -64,6 +64,27 @@ BAKE_FLOP_PER_VOXEL = 2 * 27 * 14.0 + 60.0 + 80.0
 FLOP_PER_OCTAVE, FLOP_PER_SAMPLE, FLOP_PER_STEP = 60.0, 20.0, 26.0
 
 
+def config_for(workload, world, layout, has_volume):
+    """`config` of a bench line; the product arm and the reference arm print the very same dict for the same command"""
+    W, H, desc, _ = WORKLOADS[workload]
+    return {"workload": "%s: %s" % (workload, desc), "width": W, "height": H,
+            "l2": "flushed between frames (256 MiB write); the procedural workloads read no input",
+            "partition": "cost-balanced row bands, peer stores into GPU0's frame over NVLink (CUDA IPC)" if world > 1 else "single GPU",
+            "volume_layout": layout if has_volume else None}
+
+
+def kernel_source_sha16():
+    """identity of the kernels' source: roofline.traffic is only reported when the committed ncu capture was taken on this source"""
+    import glob
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "volumetricrenderer_b200", "csrc", "*.cu*")) +
+                    glob.glob(os.path.join(ROOT, "volumetricrenderer_b200", "csrc", "*.h"))):
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -74,6 +95,7 @@ def parse_args():
     ap.add_argument("--layout", default="texture", choices=["texture", "linear", "brick"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the oracle sample")
+    ap.add_argument("--no-extra", action="store_true", help="c2 only: skip the extra.c3 measurement")
     return ap.parse_args()
 
 
@@ -203,8 +225,8 @@ def run_reference(args, rank, world):
         "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": W * H / (mrays * 1e6) * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "%s: %s" % (args.workload, desc), "width": W, "height": H,
-                   "note": "ms_per_step = full-frame time extrapolated from the timed row sample"},
+        "config": config_for(args.workload, max(1, args.gpus), args.layout, args.workload == "c1" or args.workload.startswith("c4")),
+        "note": "ms_per_step = full-frame time extrapolated from the timed row sample; the CPU arm runs on rank 0's host cores whatever --gpus says",
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": last["cores"], "kind": "port", "sample": last["sample"]},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "sample_seconds": secs,
@@ -227,21 +249,35 @@ def setup_volume(r, workload, layout):
 
 
 def run_volrt(args, rank, world, local):
-    import volumetricrenderer_b200 as vr
-    from volumetricrenderer_b200 import capi, scene
     dist = None
     if world > 1:
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    line = measure_workload(args, args.workload, rank, world, local, dist, args.steps, full=True)
+    if args.workload == "c2" and not args.no_extra:
+        # BASELINE.json configs[2] (4K, 256 + 8) on the same record, at every N: the configuration north_star wants
+        # "near-linear" on.  Fewer frames (a 4K frame is ~10x the work), same timing rules.
+        extra = measure_workload(args, "c3", rank, world, local, dist, max(5, args.steps // 3), full=False)
+        if rank == 0:
+            line["extra"] = {"c3": extra}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
 
-    W, H, desc, kw = WORKLOADS[args.workload]
-    K, Wm = args.steps, max(args.warmup, 3)
+
+def measure_workload(args, workload, rank, world, local, dist, K, full):
+    """one workload on `world` ranks -> the bench line (rank 0; None elsewhere).  full: with roofline notes, cpu_baseline"""
+    import volumetricrenderer_b200 as vr
+    from volumetricrenderer_b200 import capi, scene
+    W, H, desc, kw = WORKLOADS[workload]
+    Wm = max(args.warmup, 3)
     ubo0, ubo1 = scene.default_scene()
     # N > 1: GPU 0 holds two frames, so the gather of frame k+1 (peer stores) overlaps the D2H copy of frame k
     r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local, max_views=2 if world > 1 else 1)
-    vol_bytes = setup_volume(r, args.workload, args.layout)
+    vol_bytes = setup_volume(r, workload, args.layout)
     r.set_params(ubo0, ubo1, **kw)
 
     # ---- partition: cost-balanced row bands, peer-mapped frame of rank 0
@@ -313,6 +349,20 @@ def run_volrt(args, rank, world, local):
         dev_ms = float(t.item())
     ms_per_step = dev_ms / K
     value = W * H / (ms_per_step * 1e-3) / 1e6
+
+    # ---- N > 1: is the gathered frame the right frame?  Rank 0 renders the whole frame alone and compares it with
+    # the frame its peers have just stored their bands into (a band may take another lanes-per-ray / depth-segment mapping
+    # than the full frame: re-association only, so the bar is 1/255)
+    gather_check = None
+    if world > 1:
+        march(); barrier()
+        if rank == 0:
+            gathered = r.render(flags=capi.RENDER_NO_MARCH)[0].copy()
+            alone = r.render()[0].copy()
+            d = np.abs(gathered.astype(np.int16) - alone.astype(np.int16))
+            gather_check = {"max_abs8": int(d.max()), "pixels_differing": int((d.max(axis=-1) > 0).sum()),
+                            "nonzero_pixels": int((alone[..., :3].max(axis=-1) > 0).sum()), "vs": "the same frame rendered by GPU 0 alone"}
+        barrier()
 
     # ---- end to end through the public API with host buffers
     # every step: vr_set_params (the UBO bytes the reference host writes) + vr_render into page-locked
@@ -390,34 +440,33 @@ def run_volrt(args, rank, world, local):
            "sync_ms_per_frame": sync_s * 1e3, "frames_in_flight": 2,
            "h2d_bytes_per_step": 192 + 140, "d2h_bytes_per_step": W * H * 4, "frames_identical": e2e_check}
 
+    line = None
     if rank == 0:
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "%s: %s" % (args.workload, desc), "width": W, "height": H,
-                       "l2": "flushed between frames (256 MiB write); the procedural workloads read no input",
-                       "partition": "cost-balanced row bands, peer stores into GPU0's frame over NVLink (CUDA IPC)" if world > 1 else "single GPU",
-                       "volume_layout": args.layout if vol_bytes else None},
+            "config": config_for(workload, world, args.layout, bool(vol_bytes)),
             "e2e": e2e, "gpu_launches": K * (1 if rows[1] > rows[0] else 0),
             "clocks": clocks, "wall_ms_per_step_incl_flush": wall / K * 1e3,
             "covered_rays": covered, "steps_per_frame": steps, "light_samples_per_frame": light_samples,
             "msamples_per_s": (steps + light_samples) / (ms_per_step * 1e-3) / 1e6,
         }
-        line["roofline"] = roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world)
+        line["covered_mrays_per_s"] = covered / (ms_per_step * 1e-3) / 1e6      # rays that actually march (the rest are cleared)
+        if gather_check is not None:
+            line["gather_check"] = gather_check
+        line["roofline"] = roofline(r, args, workload, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world)
         line["ray_split"] = os.environ.get("VOLRT_RAY_SPLIT_COMPOSITE", "auto")
-        if not args.no_cpu_baseline and world == 1:
+        if full and not args.no_cpu_baseline and world == 1:
             try:
-                cb = time_oracle(args.workload, args.cpu_seconds)
+                cb = time_oracle(workload, args.cpu_seconds)
                 line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
             except Exception as e:                          # the baseline is a report, not the product
                 line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "port", "sample": "failed: %r" % e}
-        print(json.dumps(line), flush=True)
     bg.disconnect_peer(r)
     barrier()
     r.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    return line
 
 
 def run_views(args, rank, world, local):
@@ -625,7 +674,7 @@ def run_bake(args, rank, world, local):
         dist.destroy_process_group()
 
 
-def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world):
+def roofline(r, args, workload, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world):
     """Dominant kernel = the march (the only kernel in the timed region).  Neither HBM nor the tensor cores bound
     this path: the procedural workloads read no input and the grid workloads' volumes are L2- or
     TEX-bound, so `bound` is "fp32" (algorithmic flop of SURVEY.md §8(d) / the FP32-FMA peak measured in this
@@ -640,15 +689,20 @@ def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, wo
         pass
     hbm_peak = measured.get("hbm_gbs", 6650.0)
     compulsory = vol_bytes + W * H * 4
-    traffic = None
-    try:                                                    # dram bytes per launch from the committed ncu capture
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(args.workload)
+    # dram bytes per launch from the committed ncu capture — only if that capture was taken on the kernels' current source
+    # (profiles/traffic.json records the source hash; tools/update_traffic.py writes it); otherwise null, never a stale number
+    traffic, traffic_note = None, "no ncu capture of this workload on the current kernel source"
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if tj.get("source_sha16") == kernel_source_sha16():
+            traffic = tj.get(workload)
+            traffic_note = "dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu capture %s" % tj.get("captures", {}).get(workload, "?")
     except Exception:
         pass
     out = {"hbm": {"algorithmic_bytes": compulsory, "achieved": compulsory / t / 1e9, "peak": hbm_peak * world, "unit": "GB/s",
                    "frac": compulsory / t / 1e9 / (hbm_peak * world),
                    "peak_source": "of measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in measured else "of fallback (6650 GB/s)"},
-           "traffic": traffic, "peaks_measured_here": peaks}
+           "traffic": traffic, "traffic_note": traffic_note, "peaks_measured_here": peaks}
     if kw.get("density_mode") == 2:
         octaves, L = 5, kw.get("light_steps", 0)
         per_sample = octaves * FLOP_PER_OCTAVE + FLOP_PER_SAMPLE
@@ -662,10 +716,10 @@ def roofline(r, args, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, wo
                     "achieved_executed": executed / t / 1e12, "frac_executed": executed / t / 1e12 / peak if peak else None,
                     "note": "achieved = primary steps x SURVEY 8(d) flop/step (every step owes 1+L noise samples of 5 octaves x 60 + 20 flop, "
                             "+26 for the integrator). The kernel evaluates fewer (achieved_executed): steps whose density is exactly 0 "
-                            "owe no light-march and light samples outside the box are not taken. INT32 hash / LDS / conversion "
-                            "instructions share the issue ports and are not counted as flop: ncu shows the kernel 78 % issue-active on "
-                            "1.51 G warp instructions per C2 frame, the light-march's lattice arithmetic packed two samples per "
-                            "instruction (FFMA2) (profiles/r01_march_fbm_pairs.txt)."})
+                            "owe no light-march and light samples outside the box are not taken. Table fetches, byte extraction and "
+                            "conversions share the issue ports and are not counted as flop: ncu shows the kernel 68 % issue-active and the "
+                            "shared-memory pipe 75 % busy on 1.10 G warp instructions per C2 frame; the lattice hashes come from per-cell "
+                            "tables built at vr_set_params (profiles/r02_march_fbm_cells_lds128.txt)."})
     else:
         # frag.glsl fetches four channels per step; a channel of the resident volume that holds one value everywhere
         # (the reference's default bake: G = 255, quirk Q1) is not fetched by the hardware-filtered march
