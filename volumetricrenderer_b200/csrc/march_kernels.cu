@@ -358,9 +358,19 @@ __device__ __forceinline__ float light_sum(const MarchParams& P, const RayConst&
 
 // ------------------------------------------------------------------ the march
 // one pixel: ray set-up, step loop, resolve, store  (frag.glsl:34-81 + A.6 extensions)
+// seg: this thread's depth segment of the ray (0 when the launch has none).  A thick ray of the procedural cloud is a
+// dependent chain of 128-256 steps x 7-9 fBm samples on one thread, and a 1/8 row band on one of eight GPUs holds a third of a
+// wave of such rays: too few warps to keep an SM's schedulers fed.  Front-to-back compositing is associative —
+// (C_a, T_a) then (C_b, T_b) is (C_a + T_a C_b, T_a T_b) — so a ray's step range is cut into P.segments contiguous pieces
+// marched independently from T = 1 by different CTAs, and the last piece to finish composes them in order and stores the pixel.
+// Unlike the lanes-per-ray split (march_composite_split_kernel: +22 % instructions at four lanes) a piece costs one extra ray
+// set-up and nothing per step.  Grid x = tiles x pieces (tile_of_cta).  Not with early termination (a later piece cannot know
+// the transmittance in front of it) and not in the counting build.  Measured on B200 (profiles/r02_depth_segments.txt): a
+// 1/8 band of C2 0.267 -> 0.230 ms with 8 pieces, of C3 2.00 -> 1.86 ms with 4; whole frames lose ~2 % per doubling, so the
+// automatic choice (march_pick_segments) only cuts launches that are less than two waves deep.
 template <int VARIANT, bool COMPOSITE, bool STATS>
 __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* __restrict__ unorm, const GradLut& lut,
-                                            int px, int py, int view) {
+                                            int px, int py, int view, int seg = 0) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     constexpr bool STRICT = LINEAR;                       // bit-for-bit with the oracle
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
@@ -370,7 +380,7 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
     const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);          // frag.glsl:42
     Ray ray;
     if (!setup_ray(P, V, px, py, step_size, ray)) {
-        store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);                          // VulkanRenderPass.cpp:17-19
+        if (seg == 0) store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);            // VulkanRenderPass.cpp:17-19
         return;
     }
     RayConst rc;
@@ -379,13 +389,23 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
     rc.off3 = {mul(V->scroll_w[0], P.scroll_weight[3]), mul(V->scroll_w[1], P.scroll_weight[3]), mul(V->scroll_w[2], P.scroll_weight[3])};
 
     f3 p = ray.pin;
-    const int n = ray.n;
+    int n = ray.n;
+    const bool segmented = COMPOSITE && !STATS && P.segments > 1;
+    if (segmented) {
+        // this piece: steps [n*seg/K, n*(seg+1)/K), first position Pin + i*stepVec (like the lanes-per-ray kernels).  The loops
+        // below count from 0 to the piece's length, so the lanes of a warp start together whatever their rays' lengths
+        const int seg_begin = (int)(((long long)n * seg) / P.segments);
+        n = (int)(((long long)n * (seg + 1)) / P.segments) - seg_begin;
+        const float fi = (float)seg_begin;
+        p = {fmaf(ray.step.x, fi, p.x), fmaf(ray.step.y, fi, p.y), fmaf(ray.step.z, fi, p.z)};
+    }
     const bool skip = CAN_SKIP && P.skip_empty;
     Leap leap = {0.0f, 0.0f};
     if (skip) leap = leap_setup(P, ray.step);
     unsigned long long n_light = 0, n_skipped = 0;
     bool early = false;
     float cr, cg, cb;
+    float T_piece = 1.0f;       // transmittance of this thread's piece of the ray (compositing march)
 
     if (!COMPOSITE) {
         // reference integrator, frag.glsl:55-80
@@ -557,6 +577,25 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
             p = add3(p, ray.step);
             if (P.early_term_eps > 0.0f && T < P.early_term_eps) { early = true; break; }
         }
+        T_piece = T;
+    }
+    if (segmented) {
+        // hand the piece over; whoever arrives last composes the ray front to back and stores the pixel
+        const size_t band_px = (size_t)(P.row_end - P.row_begin) * P.width;
+        const size_t pix = (size_t)(py - P.row_begin) * P.width + px, v = (size_t)(view - P.view_begin);
+        __stcg(P.seg_partials + (v * P.segments + seg) * band_px + pix, make_float4(cr, cg, cb, T_piece));
+        __threadfence();
+        unsigned int* arrived = P.seg_arrived + v * band_px + pix;
+        if (atomicAdd(arrived, 1u) != (unsigned)(P.segments - 1)) return;
+        __threadfence();
+        *arrived = 0u;                                                                 // ready for the next launch
+        float Tacc = 1.0f;
+        cr = cg = cb = 0.0f;
+        for (int k = 0; k < P.segments; ++k) {
+            const float4 q = __ldcg(P.seg_partials + (v * P.segments + k) * band_px + pix);
+            cr = fmaf(Tacc, q.x, cr); cg = fmaf(Tacc, q.y, cg); cb = fmaf(Tacc, q.z, cb);
+            Tacc *= q.w;
+        }
     }
     store_pixel(P, view, px, py, cr, cg, cb, 1.0f);                                    // :80
     if (STATS) {
@@ -590,9 +629,18 @@ __device__ __forceinline__ int outward_from(int k, int n, int c) {
 // hundreds of columns) that is column by column from the middle, each column starting at the tile row nearest the frame's
 // centre row (which for most bands is an edge of the band, not its middle).  With x always fastest and the band's own
 // middle first, a third of the SM time of a 1/8 band was idle (profiles/r01_band8_before.txt).
-__device__ __forceinline__ void tile_of_cta(const MarchParams& P, int tile_h, int& tx, int& ty) {
-    const int gx = (int)gridDim.x, gy = (int)gridDim.y;
+// segs > 1 (depth segments, march_pixel): the grid's x extent is tiles x segs and the pieces of one tile are NEIGHBOURS in dispatch
+// order (piece index fastest) — as separate z slices the pieces of a frame would be dispatched one whole frame after the other
+__device__ __forceinline__ void tile_of_cta(const MarchParams& P, int tile_h, int& tx, int& ty, int segs = 1, int* seg = nullptr) {
+    const int gx = (int)gridDim.x / segs, gy = (int)gridDim.y;
     int kx = (int)blockIdx.x, ky = (int)blockIdx.y;
+    if (segs > 1) {
+        int lin = kx + (int)gridDim.x * ky;
+        *seg = lin % segs;
+        lin /= segs;
+        ky = lin / gx;
+        kx = lin - ky * gx;
+    }
     if (gy < gx) {
         const int lin = kx + gx * ky;
         kx = lin / gy;
@@ -645,14 +693,15 @@ __global__ void __launch_bounds__(kCtaThreads, is_fbm(VARIANT) ? VOLRT_DIRECT_MI
     float* const unorm = smem.unorm;
     GradLut& lut = smem.lut;
     stage_tables<VARIANT>(unorm, &lut);
-    int tx, ty;
-    tile_of_cta(P, 4 * kCtaWy, tx, ty);
+    int tx, ty, seg = 0;
+    if (COMPOSITE && !STATS && P.segments > 1) tile_of_cta(P, 4 * kCtaWy, tx, ty, P.segments, &seg);     // grid x = tiles x depth segments
+    else tile_of_cta(P, 4 * kCtaWy, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = tx * (8 * kCtaWx) + (warp % kCtaWx) * 8 + (lane & 7);
     const int py = P.row_begin + ty * (4 * kCtaWy) + (warp / kCtaWx) * 4 + (lane >> 3);
     const int view = P.view_begin + blockIdx.z;
     if (px >= P.width || py >= P.row_end) return;
-    march_pixel<VARIANT, COMPOSITE, STATS>(P, unorm, lut, px, py, view);
+    march_pixel<VARIANT, COMPOSITE, STATS>(P, unorm, lut, px, py, view, seg);
 }
 
 // (b) persistent warps: the grid is sized to the machine (SMs x resident CTAs) and every WARP pulls 8x4-pixel
@@ -1110,6 +1159,31 @@ static cudaError_t launch_v(const MarchParams& p, dim3 grid, bool composite, boo
     return stats ? launch_one<VARIANT, false, true>(p, grid, persistent, s) : launch_one<VARIANT, false, false>(p, grid, persistent, s);
 }
 
+// waves of the machine the covered rays of a launch make at one thread per ray: about a quarter of the pixels are covered
+// (the reference's cube fills 21 % of its frame), an SM holds 32 warps of the cheap marches
+static double launch_waves(const MarchParams& p, int rows, int n_views) {
+    const double warps = (double)p.width * rows * n_views * 0.25 / 32.0;
+    return warps / ((double)(p.sm_count > 0 ? p.sm_count : 148) * 32.0);
+}
+
+int march_pick_segments(const MarchParams& p, int variant, int n_views, bool stats) {
+    const int rows = p.row_end - p.row_begin;
+    if (rows <= 0 || n_views <= 0 || stats || !(p.sigma_t > 0.0f) || p.early_term_eps > 0.0f) return 1;
+    if (p.schedule > 0 && p.queue) return 1;                     // persistent warps
+    if (variant == MARCH_SINGLE_BRICK) return 1;
+    int k = p.ray_segments;
+    if (k < 0) {
+        // auto: only where a step is expensive (procedural density: hundreds to thousands of instructions per step) and the
+        // launch is too shallow for whole rays to fill the machine.  Measured (profiles/r02_depth_segments.txt): see march_pixel
+        if (!(is_fbm(variant) || variant == MARCH_TREE)) return 1;
+        const double waves = launch_waves(p, rows, n_views);
+        k = waves >= 2.0 ? 1 : waves >= 1.0 ? 2 : waves >= 0.5 ? 4 : 8;
+    }
+    if (k > kMaxRaySegments) k = kMaxRaySegments;
+    if (k > p.max_steps) k = p.max_steps;
+    return k < 1 ? 1 : k;
+}
+
 cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool stats, cudaStream_t stream) {
     int rows = p_in.row_end - p_in.row_begin;
     if (rows <= 0 || n_views <= 0) return cudaSuccess;
@@ -1117,6 +1191,23 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     p.n_views = n_views;
     dim3 grid((p.width + 8 * kCtaWx - 1) / (8 * kCtaWx), (rows + 4 * kCtaWy - 1) / (4 * kCtaWy), n_views);
     bool composite = p.sigma_t > 0.0f;
+    // depth segments (march_pixel): one thread per ray and piece, grid x = tiles x pieces
+    if (p.segments > 1) {
+        if (!composite || stats || !p.seg_partials || !p.seg_arrived ||
+            (size_t)rows * p.width * n_views * p.segments > p.seg_capacity) return cudaErrorInvalidValue;
+        grid.x *= p.segments;
+        switch (variant) {
+            case MARCH_RGBA_TEX: return launch_one<MARCH_RGBA_TEX, true, false>(p, grid, false, stream);
+            case MARCH_RGBA_LINEAR: return launch_one<MARCH_RGBA_LINEAR, true, false>(p, grid, false, stream);
+            case MARCH_SINGLE_TEX: return launch_one<MARCH_SINGLE_TEX, true, false>(p, grid, false, stream);
+            case MARCH_SINGLE_LINEAR: return launch_one<MARCH_SINGLE_LINEAR, true, false>(p, grid, false, stream);
+            case MARCH_FBM: return launch_one<MARCH_FBM, true, false>(p, grid, false, stream);
+            case MARCH_FBM_CELLS: return launch_one<MARCH_FBM_CELLS, true, false>(p, grid, false, stream);
+            case MARCH_TREE: return launch_one<MARCH_TREE, true, false>(p, grid, false, stream);
+        }
+        return cudaErrorInvalidValue;
+    }
+    p.segments = 1;
     // schedule: 0 = direct tiles, 1 = persistent warps, -1 = auto
     bool persistent = p.schedule > 0;    // auto = direct: the queue did not pay off on B200 (measurements)
     if (!p.queue) persistent = false;
@@ -1128,8 +1219,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
             // Measured on B200 with the two-point fBm light-march (ms, 1 / 2 / 4 lanes per ray): 1080p frame (3.4 waves)
             // 1.776 / 1.799 / 1.99; its half (1.7 waves) 0.97 / 0.935 / 1.0; its quarter 0.68 / 0.51 / 0.52; its eighth
             // 0.48 / 0.33 / 0.28; 4K frame 17.0 / 17.4 / -; its eighth (1.7 waves) 2.44 / 2.26 / -.
-            const double warps = (double)p.width * rows * n_views * 0.25 / 32.0;
-            const double waves = warps / (148.0 * 32.0);
+            const double waves = launch_waves(p, rows, n_views);
             split = waves >= 3.0 ? 1 : waves >= 0.8 ? 2 : 4;
             // a node-tree sample costs 167 registers with one thread per ray (3 CTAs/SM, issue 50 %): the split kernel's
             // register cap serves it better until the frame is many waves deep (C2 frame: 4.8 ms -> see DESIGN 5c)
@@ -1155,9 +1245,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
             // auto: two lanes per ray while the covered rays (about a quarter of the pixels) would not fill two
             // waves of the machine; measured on B200 at 1280x720: 1 -> 0.099 ms, 2 -> 0.095, 4 -> 0.138, 8 -> 0.171
             // (more lanes per ray spread a warp's footprint along the ray and cost L1 data-stage wavefronts)
-            const double warps = (double)p.width * rows * n_views * 0.25 / 32.0;
-            const double slots = 148.0 * 40.0;
-            split = warps >= 2.0 * slots ? 1 : 2;
+            split = launch_waves(p, rows, n_views) >= 2.5 ? 1 : 2;     // 2.5 waves of 32 warps = two waves of the 40 the texture march fits
         }
         if (split == 2 || split == 4 || split == 8)
             return variant == MARCH_RGBA_TEX ? launch_split<MARCH_RGBA_TEX>(p, split, rows, n_views, stream)

@@ -97,6 +97,11 @@ struct vr_context {
     int queue_chunk = 1;
     int ray_split = -1;                // lanes per ray (texture march): -1 auto
     int ray_split_composite = -1;      // lanes per ray (compositing march): -1 auto
+    int ray_segments = -1;             // depth segments per ray (compositing march): -1 auto
+    int sm_count = 0;
+    float4* d_seg_partials = nullptr;  // depth-segment scratch (MarchParams::seg_partials), grow-only
+    unsigned int* d_seg_arrived = nullptr;
+    size_t seg_capacity = 0, seg_arrived_px = 0;
     void* flush_buf = nullptr;      // 256 MiB scratch, allocated by the first vr_flush_l2
     vr_stats stats{};
     std::string err;
@@ -214,6 +219,8 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
     }
     if (const char* ev = std::getenv("VOLRT_RAY_SPLIT")) c->ray_split = std::atoi(ev);
     if (const char* ev = std::getenv("VOLRT_RAY_SPLIT_COMPOSITE")) c->ray_split_composite = std::atoi(ev);
+    if (const char* ev = std::getenv("VOLRT_RAY_SEGMENTS")) c->ray_segments = std::atoi(ev);
+    cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, c->device);
     if (const char* ev = std::getenv("VOLRT_QUEUE_CHUNK")) { int v = std::atoi(ev); if (v > 0 && v <= 1024) c->queue_chunk = v; }
     *out = c;
     return VR_OK;
@@ -260,6 +267,8 @@ extern "C" void vr_destroy(vr_context* c) {
     if (c->d_march_tree) cudaFree(c->d_march_tree);
     if (c->d_tree_out) cudaFree(c->d_tree_out);
     if (c->d_fbm_cells) cudaFree(c->d_fbm_cells);
+    if (c->d_seg_partials) cudaFree(c->d_seg_partials);
+    if (c->d_seg_arrived) cudaFree(c->d_seg_arrived);
     for (int i = 0; i < vr_context::kFileRing; ++i) {
         if (c->file_stage[i]) cudaFreeHost(c->file_stage[i]);
         if (c->file_done[i]) cudaEventDestroy(c->file_done[i]);
@@ -1025,6 +1034,8 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.queue_chunk = c->queue_chunk;
     m.ray_split = c->ray_split;
     m.ray_split_composite = c->ray_split_composite;
+    m.ray_segments = c->ray_segments;
+    m.sm_count = c->sm_count;
     if (p.density_mode == VR_DENSITY_FBM) {
         variant = MARCH_FBM;
         if (c->fbm_cells_ok) { m.cells = c->fbm_cells; variant = MARCH_FBM_CELLS; }
@@ -1113,8 +1124,29 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
         if (c->copy_pending[slot]) VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_copy_done[slot], 0));   // frame slot is free again
         m.out = frame;
     }
-    VR_CUDA(c, cudaEventRecord(c->ev0, s));
     if (variant == MARCH_SINGLE_BRICK && stats) variant = MARCH_SINGLE_LINEAR;     // device counters live in the generic kernel
+    if (!no_march && r1 > r0 && v1 > v0) {
+        // depth segments: the scratch (one float4 per pixel and piece, one arrival counter per pixel) is grown here, once
+        int segs = march_pick_segments(m, variant, (int)(v1 - v0), stats);
+        const size_t px = (size_t)(r1 - r0) * c->width * (v1 - v0);
+        while (segs > 1 && px * segs * sizeof(float4) > ((size_t)2 << 30)) --segs;
+        if (segs > 1) {
+            if (c->seg_capacity < px * segs || c->seg_arrived_px < px) {
+                VR_CUDA(c, cudaStreamSynchronize(c->stream));
+                if (c->foreign_stream_pending) { VR_CUDA(c, cudaEventSynchronize(c->ev1)); c->foreign_stream_pending = false; }
+                if (c->d_seg_partials) { cudaFree(c->d_seg_partials); c->d_seg_partials = nullptr; c->seg_capacity = 0; }
+                if (c->d_seg_arrived) { cudaFree(c->d_seg_arrived); c->d_seg_arrived = nullptr; c->seg_arrived_px = 0; }
+                VR_CUDA(c, cudaMalloc(&c->d_seg_partials, px * segs * sizeof(float4)));
+                c->seg_capacity = px * segs;
+                VR_CUDA(c, cudaMalloc(&c->d_seg_arrived, px * sizeof(unsigned int)));
+                VR_CUDA(c, cudaMemsetAsync(c->d_seg_arrived, 0, px * sizeof(unsigned int), s));
+                c->seg_arrived_px = px;
+            }
+            m.segments = segs;
+            m.seg_partials = c->d_seg_partials; m.seg_arrived = c->d_seg_arrived; m.seg_capacity = c->seg_capacity;
+        }
+    }
+    VR_CUDA(c, cudaEventRecord(c->ev0, s));
     if (!no_march) {
         if (variant == MARCH_SINGLE_BRICK) VR_CUDA(c, launch_march_brick(m, c->tensor_map, (int)(v1 - v0), s));
         else VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));

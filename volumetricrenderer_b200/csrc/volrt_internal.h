@@ -102,7 +102,17 @@ struct MarchParams {
     float tree_freq;
     // device counters (VR_RENDER_STATS): covered, steps, early, light samples, skipped
     unsigned long long* counters;
+    int sm_count;               // multiprocessors of the context's device (launch heuristics)
+    // depth segments of the compositing march (march_kernels.cu: march_pixel): a ray's steps are cut into `segments`
+    // contiguous pieces marched by different CTAs (grid x = tiles x segments); each writes its (colour, transmittance) to
+    // seg_partials and the last one to arrive composes them front to back and stores the pixel.  segments <= 1: off.
+    int segments;               // set by the caller from march_pick_segments (0 / 1 = off)
+    int ray_segments;           // request: -1 auto, 1 off, 2..8
+    float4* seg_partials;       // [view][segment][row - row_begin][x], context scratch
+    unsigned int* seg_arrived;  // [view][row - row_begin][x], zero between launches (the composing thread resets it)
+    size_t seg_capacity;        // pixel-segments the scratch holds
 };
+constexpr int kMaxRaySegments = 8;
 
 enum MarchVariant {
     MARCH_RGBA_TEX = 0,      // reference integrator, 4 HW-filtered fetches/step
@@ -119,6 +129,9 @@ constexpr size_t kGatherMailboxBytes = 256;    // behind the context's frames: c
 
 // launches one march over rows [row_begin,row_end) x views; returns cudaGetLastError()
 cudaError_t launch_march(const MarchParams& p, int variant, int n_views, bool stats, cudaStream_t stream);
+// how many depth segments (MarchParams::segments) this launch should use: 1 = none.  The caller sizes seg_partials / seg_arrived
+// for rows x width x views x segments before it launches.
+int march_pick_segments(const MarchParams& p, int variant, int n_views, bool stats);
 
 // TMA-staged brick march (VR_LAYOUT_BRICK): tensor_map = 128-byte CUtensorMap over the x-fastest fp16 volume
 cudaError_t launch_march_brick(const MarchParams& p, const void* tensor_map, int n_views, cudaStream_t stream);
