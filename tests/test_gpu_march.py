@@ -364,6 +364,7 @@ def test_fbm_light_march_pairs_equal_the_scalar_loop(monkeypatch, light_steps):
     scalar routine's operations in the same order, so one thread per ray must give the very same binary32 frame as
     the counting build (VR_RENDER_STATS), which keeps the scalar loop — for even and odd sample counts."""
     monkeypatch.setenv("VOLRT_RAY_SPLIT_COMPOSITE", "1")
+    monkeypatch.setenv("VOLRT_RAY_SEGMENTS", "1")          # one thread per WHOLE ray: depth pieces re-associate the compositing
     W, H = 320, 180
     ubo0, ubo1 = scene.default_scene(25.0, -15.0)
     sun = np.array([1.0, 1.0, 2.0], np.float32)
@@ -406,6 +407,46 @@ def test_fbm_cell_tables_equal_the_per_sample_hash(monkeypatch, octaves, freq, l
     for split in (1, 2):
         assert np.array_equal(frames["1", split].view(np.uint32), frames["0", split].view(np.uint32)), (split, eligible)
     assert frames["1", 1][..., :3].max() > 0.05
+
+
+@pytest.mark.parametrize("mode", ["fbm", "grid"])
+def test_depth_segments_compose_to_the_whole_ray(monkeypatch, oracle, mode):
+    """The compositing march may cut a ray's steps into K contiguous pieces marched by different CTAs and compose them with
+    (C_a + T_a C_b, T_a T_b).  Every K gives the frame of K = 1 up to re-association and the pieces' first positions being
+    Pin + i*stepVec rather than a running sum (1e-4 in float, 1/80 of the 2/255 bar), which in turn is the
+    oracle's frame; a second frame through the same context reuses the arrival counters the first one reset."""
+    W, H = 333, 187
+    u0, u1 = scene.default_scene(35.0, -20.0)
+    sun = np.array([1.0, 1.0, 2.0], np.float32) / np.float32(np.sqrt(6.0))
+    kw = dict(max_steps=96, sigma_t=8.0, light_steps=3, light_step_len=0.08, ambient=0.15, sun_dir=sun, sun_color=[1.0, 0.95, 0.85])
+    if mode == "fbm":
+        kw.update(density_mode=capi.DENSITY_FBM)
+        vol, ovol = None, None
+    else:
+        kw.update(density_mode=capi.DENSITY_SINGLE, sample_scale=1.0)
+        vol = smoke_volume(24, 3)
+        ovol, _k = oracle.make_volume(vol.view(np.uint16), oracle.VOL_R16F)
+    scal = {k: v for k, v in kw.items() if not hasattr(v, "__len__")}
+    p = oracle_params(oracle, u0, u1, **scal)
+    oracle.set_params(p, sun_dir=sun, sun_color=[1.0, 0.95, 0.85])
+    ref, _ = oracle.render(ovol, p, W, H)
+    monkeypatch.setenv("VOLRT_RAY_SPLIT_COMPOSITE", "1")
+    frames = {}
+    for k in (1, 2, 3, 8):
+        monkeypatch.setenv("VOLRT_RAY_SEGMENTS", str(k))
+        with vr.Renderer(W, H, capi.OUT_RGBA32F) as r:
+            if vol is not None:
+                r.upload_volume(vol, capi.VOL_R16F, capi.LAYOUT_LINEAR)
+            r.set_params(u0, u1, **kw)
+            a = r.render()[0].copy()
+            b = r.render(rows=(40, 131))[0].copy()                 # a band: other scratch shape, counters must be clean
+            c = r.render()[0].copy()
+        assert np.array_equal(a, c) and np.array_equal(a[40:131], b)
+        frames[k] = a
+    assert frames[1][..., :3].max() > 0.1
+    for k in (2, 3, 8):
+        assert np.abs(frames[k] - frames[1]).max() <= 1e-4, k
+    assert np.abs(frames[8] - ref).max() <= (2e-4 if mode == "grid" else 2.0 / 255.0)
 
 
 def test_known_answers_on_gpu():

@@ -1177,7 +1177,7 @@ int march_pick_segments(const MarchParams& p, int variant, int n_views, bool sta
         // launch is too shallow for whole rays to fill the machine.  Measured (profiles/r02_depth_segments.txt): see march_pixel
         if (!(is_fbm(variant) || variant == MARCH_TREE)) return 1;
         const double waves = launch_waves(p, rows, n_views);
-        k = waves >= 2.0 ? 1 : waves >= 1.0 ? 2 : waves >= 0.5 ? 4 : 8;
+        k = waves >= 2.0 ? 1 : waves >= 0.8 ? 2 : waves >= 0.25 ? 4 : 8;
     }
     if (k > kMaxRaySegments) k = kMaxRaySegments;
     if (k > p.max_steps) k = p.max_steps;
