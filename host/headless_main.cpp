@@ -4,6 +4,7 @@
 // without a window").  Everything heavy happens in libvolrt (CUDA); this file is host logic only.
 //
 //   volrt_headless [--frames N] [--keys "D*60,W*30,A*20"] [--out DIR] [--every K] [--size WxH]
+//                  [--gpus N]      CUDA devices 0..N-1 behind the one context (row bands, peer stores into device 0's frame)
 //                  [--std140]      send GlobalShaderData in the shader's std140 layout (quirk Q2 "fixed": the medium scrolls)
 //                  [--dt SECONDS]  frameTime advances by this much per frame instead of following the wall clock
 //                  [--scroll-yzw]  also write -frameTime into MediaScroll[0].y/.z/.w — the only element the reference writes,
@@ -72,7 +73,7 @@ static void write_ppm(const std::string& path, const unsigned char* rgba, uint32
 }
 
 int main(int argc, char** argv) {
-    int frames = 120, every = 0;
+    int frames = 120, every = 0, gpus = 1;
     bool std140 = false, scroll_yzw = false;
     float scripted_dt = -1.0f;
     uint32_t W = 1280, H = 720;                         // VulkanContext.cpp:24
@@ -87,11 +88,12 @@ int main(int argc, char** argv) {
         else if (a == "--scroll-yzw") scroll_yzw = true;
         else if (a == "--dt" && i + 1 < argc) scripted_dt = (float)std::atof(argv[++i]);
         else if (a == "--size" && i + 1 < argc) { if (std::sscanf(argv[++i], "%ux%u", &W, &H) != 2) return 2; }
+        else if (a == "--gpus" && i + 1 < argc) gpus = std::atoi(argv[++i]);
         else { std::fprintf(stderr, "unknown argument %s\n", a.c_str()); return 2; }
     }
     try {
         vkc::Renderer renderer;
-        renderer.Init(W, H, VR_OUT_RGBA8_UNORM);                                  // TestMain.cpp:121
+        renderer.Init(W, H, VR_OUT_RGBA8_UNORM, 0, gpus);                         // TestMain.cpp:121; --gpus N: one context, N devices
         // TestMain.cpp:43-92 + :128 — the 128^3 RGBA8 noise volume, baked on the device (incl. quirk Q1)
         vkc::Texture3D texture = vkc::Texture3D::Bake();
 

@@ -116,8 +116,15 @@ class Renderer {
 public:
     static constexpr uint32_t MaxFramesInFlight = 2;            // VulkanRenderer.cpp:13
 
-    void Init(uint32_t width = 1280, uint32_t height = 720, vr_output_format fmt = VR_OUT_RGBA8_UNORM, int device = 0) {
-        vr_create_info ci = {sizeof(vr_create_info), device, width, height, (uint32_t)fmt, 1, 0};
+    // gpus > 1: CUDA devices 0 .. gpus-1 behind the one context (vr_create_info.device_count); the frame lives on device 0
+    void Init(uint32_t width = 1280, uint32_t height = 720, vr_output_format fmt = VR_OUT_RGBA8_UNORM, int device = 0, int gpus = 1) {
+        vr_create_info ci = {};
+        ci.struct_size = sizeof(vr_create_info);
+        ci.device = device; ci.width = width; ci.height = height; ci.format = (uint32_t)fmt; ci.max_views = 1;
+        if (gpus > 1) {
+            ci.device_count = (uint32_t)(gpus > VR_MAX_DEVICES ? VR_MAX_DEVICES : gpus);
+            for (uint32_t k = 0; k < ci.device_count; ++k) ci.devices[k] = (int32_t)k;
+        }
         vr_context* ctx = nullptr;
         vr_status st = vr_create(&ci, &ctx);
         if (st != VR_OK) VOLRT_HOST_ERROR(std::string("Renderer::Init: ") + vr_last_error(nullptr));

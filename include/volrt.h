@@ -35,7 +35,7 @@ extern "C" {
 #endif
 
 #define VR_VERSION_MAJOR 0
-#define VR_VERSION_MINOR 1
+#define VR_VERSION_MINOR 2
 #define VR_MAX_DEVICES 8
 
 typedef struct vr_context vr_context;
@@ -126,11 +126,20 @@ enum {
  * source/Etna/TestMain.cpp:121-122,156-166; Core/Vulkan/VulkanRenderer.cpp:17-118,232-256 */
 typedef struct vr_create_info {
     uint32_t struct_size;
-    int32_t device;              /* CUDA ordinal of this context's GPU                       */
+    int32_t device;              /* CUDA ordinal of this context's GPU (device_count <= 1)   */
     uint32_t width, height;      /* reference: 1280 x 720 (VulkanContext.cpp:24)             */
     uint32_t format;             /* vr_output_format                                         */
     uint32_t max_views;          /* frames held by the context (0 -> 1)                      */
     uint32_t flags;
+    /* ---- several GPUs behind ONE context, in ONE process (read only when struct_size covers them; a caller compiled
+     * against the 28-byte struct of version 0.1 keeps working).  The reference host is one process, one thread, one main()
+     * (source/Etna/TestMain.cpp:41,173-256) and picks one physical device (Core/Vulkan/VulkanDevice.cpp:42-49); with
+     * device_count = N > 1 the same five calls drive N GPUs of one box: the frame lives on devices[0], the volume is
+     * replicated over NVLink at upload, and vr_render cuts the frame into cost-balanced row bands (or a view batch into view
+     * shards), one per GPU, whose march kernels store their pixels straight into devices[0]'s frame through peer access;
+     * the cut follows the measured band times from frame to frame.  Needs peer access between devices[0] and the others. */
+    uint32_t device_count;       /* 0 / 1: the single `device` above                          */
+    int32_t devices[VR_MAX_DEVICES];
 } vr_create_info;
 
 /* replaces vkc::Texture3D texture(pixelData.data(), VkExtent3D(size,size,size)):

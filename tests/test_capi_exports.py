@@ -23,12 +23,12 @@ def test_library_exports_every_declared_symbol():
     lib = capi.load()
     for name in _declared():
         assert hasattr(lib, name), name
-    assert lib.vr_version() == (0 << 16) | 1
+    assert lib.vr_version() == (0 << 16) | 2
 
 
 def test_struct_sizes_match_the_header_layout():
     # natural alignment, as a C compiler lays the structs of include/volrt.h out
-    assert C.sizeof(capi.vr_create_info) == 28
+    assert C.sizeof(capi.vr_create_info) == 28 + 4 + 4 * capi.MAX_DEVICES      # the 28-byte struct of version 0.1 + the device group
     assert C.sizeof(capi.vr_volume_desc) == 28
     assert C.sizeof(capi.vr_noise_channel) == 28
     assert C.sizeof(capi.vr_noise_desc) == 24 + 4 * 28 + 4 * 8          # channel recipes + the per-channel node-tree pointers
@@ -61,6 +61,9 @@ def test_no_cpu_fallback_without_a_device():
     ctx = C.c_void_p()
     info = capi.vr_create_info(C.sizeof(capi.vr_create_info), 0, 64, 64, 0, 1, 0)
     st = lib.vr_create(C.byref(info), C.byref(ctx))
+    if st != capi.VR_OK:                      # a caller compiled against version 0.1's 28-byte struct gets the same answer
+        old = capi.vr_create_info(28, 0, 64, 64, 0, 1, 0)
+        assert lib.vr_create(C.byref(old), C.byref(ctx)) == st
     if st == capi.VR_OK:                      # a GPU is present: fine, clean up
         lib.vr_destroy(ctx)
         pytest.skip("CUDA device present")

@@ -26,9 +26,13 @@ NOISE_CELLULAR_DISTANCE, NOISE_PERLIN, NOISE_SIMPLEX, NOISE_ZERO, NOISE_SAME = 0
 NOISE_TREE = 4
 
 
+MAX_DEVICES = 8
+
+
 class vr_create_info(C.Structure):
     _fields_ = [("struct_size", C.c_uint32), ("device", C.c_int32), ("width", C.c_uint32), ("height", C.c_uint32),
-                ("format", C.c_uint32), ("max_views", C.c_uint32), ("flags", C.c_uint32)]
+                ("format", C.c_uint32), ("max_views", C.c_uint32), ("flags", C.c_uint32),
+                ("device_count", C.c_uint32), ("devices", C.c_int32 * MAX_DEVICES)]
 
 
 class vr_volume_desc(C.Structure):

@@ -105,6 +105,18 @@ struct vr_context {
     void* flush_buf = nullptr;      // 256 MiB scratch, allocated by the first vr_flush_l2
     vr_stats stats{};
     std::string err;
+    // ---- several GPUs behind this context (vr_create_info.device_count > 1): sub-contexts of devices[1..]; the frame,
+    // the band plan and everything the caller sees live here, on devices[0]
+    std::vector<vr_context*> peers;
+    vr_context* leader = nullptr;            // set in a sub-context
+    vr_params plan_params{};                 // the parameters the plan was made for
+    std::vector<float> plan_cost;            // analytic per-row cost (vr_row_cost) the bands are cut from
+    std::vector<uint32_t> plan_bounds;       // row bands of the last single-view frame, one per device
+    std::vector<uint32_t> plan_views;        // view shards of the last view batch
+    uint32_t plan_age = 0;                   // frames since plan_cost was computed
+    bool plan_valid = false;
+    bool group_timed = false;                // the last vr_render went through the group path (stats: max over the devices)
+    cudaEvent_t ev_consumed = nullptr;       // the frame of the last group render has been copied out / handed over
 };
 
 static thread_local std::string g_create_error;
@@ -166,7 +178,7 @@ extern "C" vr_status vr_params_default(vr_params* p) {
 }
 
 extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
-    if (!info || !out || info->struct_size < sizeof(vr_create_info))
+    if (!info || !out || info->struct_size < offsetof(vr_create_info, device_count))      // the 28-byte struct of version 0.1 is accepted
         return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: null argument or struct_size too small");
     if (info->width == 0 || info->height == 0 || info->width > 32768 || info->height > 32768)
         return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: width/height out of range");
@@ -175,11 +187,21 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0)
         return fail(nullptr, VR_ERR_CUDA, "vr_create: no CUDA device (libvolrt has no CPU path)", e);
-    if (info->device < 0 || info->device >= ndev) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: device ordinal out of range");
-    VR_CUDA(nullptr, cudaSetDevice(info->device));
+    int device0 = info->device;
+    if (info->struct_size >= offsetof(vr_create_info, devices) + sizeof(info->devices) && info->device_count > 1) {
+        if (info->device_count > VR_MAX_DEVICES) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: device_count exceeds VR_MAX_DEVICES");
+        for (uint32_t a = 0; a < info->device_count; ++a) {
+            if (info->devices[a] < 0 || info->devices[a] >= ndev) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: devices[] ordinal out of range");
+            for (uint32_t b = 0; b < a; ++b)
+                if (info->devices[a] == info->devices[b]) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: devices[] names a device twice");
+        }
+        device0 = info->devices[0];
+    }
+    if (device0 < 0 || device0 >= ndev) return fail(nullptr, VR_ERR_INVALID_ARGUMENT, "vr_create: device ordinal out of range");
+    VR_CUDA(nullptr, cudaSetDevice(device0));
     vr_context* c = new (std::nothrow) vr_context();
     if (!c) return fail(nullptr, VR_ERR_OUT_OF_MEMORY, "vr_create: host allocation failed");
-    c->device = info->device;
+    c->device = device0;
     c->width = info->width; c->height = info->height; c->format = info->format;
     c->max_views = info->max_views ? info->max_views : 1;
     c->px_bytes = out_px_bytes(info->format);
@@ -222,9 +244,39 @@ extern "C" vr_status vr_create(const vr_create_info* info, vr_context** out) {
     if (const char* ev = std::getenv("VOLRT_RAY_SEGMENTS")) c->ray_segments = std::atoi(ev);
     cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, c->device);
     if (const char* ev = std::getenv("VOLRT_QUEUE_CHUNK")) { int v = std::atoi(ev); if (v > 0 && v <= 1024) c->queue_chunk = v; }
+    // several GPUs behind this context: one sub-context per further device, peer access both ways with devices[0]
+    const bool has_group = info->struct_size >= offsetof(vr_create_info, devices) + sizeof(info->devices) && info->device_count > 1;
+    if (has_group) {
+        if ((e = cudaEventCreateWithFlags(&c->ev_consumed, cudaEventDisableTiming)) != cudaSuccess) return bail("cudaEventCreate", e);
+        for (uint32_t k = 1; k < info->device_count; ++k) {
+            vr_create_info sub = {};
+            sub.struct_size = (uint32_t)offsetof(vr_create_info, device_count);
+            sub.device = info->devices[k]; sub.width = info->width; sub.height = info->height; sub.format = info->format;
+            sub.max_views = 1; sub.flags = info->flags;
+            vr_context* pc = nullptr;
+            const vr_status st = vr_create(&sub, &pc);
+            if (st != VR_OK) { vr_destroy(c); return st; }           // the message is in g_create_error already
+            pc->leader = c;
+            c->peers.push_back(pc);
+            int can = 0, can_back = 0;
+            cudaDeviceCanAccessPeer(&can, pc->device, c->device);
+            cudaDeviceCanAccessPeer(&can_back, c->device, pc->device);
+            if (!can || !can_back) { vr_destroy(c); return fail(nullptr, VR_ERR_UNSUPPORTED, "vr_create: no peer access between devices[0] and another device of the group"); }
+            cudaSetDevice(pc->device);
+            e = cudaDeviceEnablePeerAccess(c->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return bail("cudaDeviceEnablePeerAccess", e);
+            cudaSetDevice(c->device);
+            e = cudaDeviceEnablePeerAccess(pc->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return bail("cudaDeviceEnablePeerAccess", e);
+            cudaGetLastError();
+        }
+        cudaSetDevice(c->device);
+    }
     *out = c;
     return VR_OK;
 }
+
+static vr_status replicate_volume(vr_context* c);      // group contexts: copy the leader's volume to the other devices
 
 static void release_volume(vr_context* c) {
     if (c->tex) { cudaDestroyTextureObject(c->tex); c->tex = 0; }
@@ -244,7 +296,11 @@ static void release_volume(vr_context* c) {
 
 extern "C" void vr_destroy(vr_context* c) {
     if (!c) return;
+    for (vr_context* pc : c->peers) { if (pc->stream) { cudaSetDevice(pc->device); cudaStreamSynchronize(pc->stream); } }
+    for (vr_context* pc : c->peers) vr_destroy(pc);
+    c->peers.clear();
     cudaSetDevice(c->device);
+    if (c->ev_consumed) cudaEventDestroy(c->ev_consumed);
     if (c->stream) cudaStreamSynchronize(c->stream);
     release_volume(c);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
@@ -439,8 +495,31 @@ extern "C" vr_status vr_upload_volume(vr_context* c, const vr_volume_desc* d, co
     // synchronous like the reference's staging copy + vkQueueWaitIdle (VulkanCore.cpp:529-541)
     VR_CUDA(c, cudaMemcpyAsync(c->lin, texels, c->lin_bytes, cudaMemcpyHostToDevice, c->stream));
     st = finish_volume(c, *d);
-    if (st != VR_OK) release_volume(c);
-    return st;
+    if (st != VR_OK) { release_volume(c); return st; }
+    return replicate_volume(c);
+}
+
+// group context: the leader's resident volume, copied to every other device over NVLink (peer copy of the x-fastest texels), where
+// the texture objects, the occupancy grid and the distance map are built like after an upload
+static vr_status replicate_volume(vr_context* c) {
+    if (c->peers.empty() || !c->has_volume) return VR_OK;
+    vr_volume_desc d = c->vdesc;
+    d.struct_size = sizeof d;
+    vr_status st = VR_OK;
+    for (vr_context* pc : c->peers) {
+        cudaError_t e = cudaSetDevice(pc->device);
+        if (e == cudaSuccess) st = prepare_volume(pc, d);
+        if (e == cudaSuccess && st == VR_OK) e = cudaMemcpyPeerAsync(pc->lin, pc->device, c->lin, c->device, c->lin_bytes, pc->stream);
+        if (e == cudaSuccess && st == VR_OK) st = finish_volume(pc, d);
+        if (e != cudaSuccess || st != VR_OK) {
+            release_volume(pc);
+            cudaSetDevice(c->device);
+            if (e != cudaSuccess) return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, "replicating the volume to a device of the group", e);
+            return fail(c, st, ("replicating the volume to a device of the group: " + pc->err).c_str());
+        }
+    }
+    VR_CUDA(c, cudaSetDevice(c->device));
+    return VR_OK;
 }
 
 extern "C" vr_status vr_download_volume(vr_context* c, void* texels, size_t bytes) {
@@ -635,8 +714,8 @@ extern "C" vr_status vr_upload_volume_file(vr_context* c, const char* path, uint
     if (d_level0) cudaFree(d_level0);
     if (what) { release_volume(c); return fail(c, VR_ERR_IO, (std::string("vr_upload_volume_file: ") + what).c_str()); }
     if (e != cudaSuccess) { release_volume(c); return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, "vr_upload_volume_file", e); }
-    if (st != VR_OK) release_volume(c);
-    return st;
+    if (st != VR_OK) { release_volume(c); return st; }
+    return replicate_volume(c);
 }
 
 // ------------------------------------------------------------------ volume bake on the device
@@ -767,8 +846,8 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
         if (e != cudaSuccess) { release_volume(c); return fail(c, e == cudaErrorMemoryAllocation ? VR_ERR_OUT_OF_MEMORY : VR_ERR_CUDA, "vr_generate_volume", e); }
     }
     st = finish_volume(c, vd);
-    if (st != VR_OK) release_volume(c);
-    return st;
+    if (st != VR_OK) { release_volume(c); return st; }
+    return replicate_volume(c);
 }
 
 // ------------------------------------------------------------------ FastNoise2 node trees on the device
@@ -943,6 +1022,23 @@ static vr_status prepare_fbm_cells(vr_context* c, const vr_params* p) {
     return VR_OK;
 }
 
+// a sub-context of a group needs max_views >= the batch: its view block is grown on demand
+static vr_status vr_set_params_peer(vr_context* pc, const vr_params* p) {
+    const uint32_t views = p->view_count ? p->view_count : 1;
+    if (views > pc->max_views) {
+        cudaError_t e = cudaSetDevice(pc->device);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(pc->stream);
+        if (e != cudaSuccess) return fail(pc, VR_ERR_CUDA, "vr_set_params (group)", e);
+        if (pc->d_views) { cudaFree(pc->d_views); pc->d_views = nullptr; }
+        if (pc->h_views) { cudaFreeHost(pc->h_views); pc->h_views = nullptr; }
+        if ((e = cudaMalloc(&pc->d_views, sizeof(ViewConst) * views)) != cudaSuccess) return fail(pc, VR_ERR_OUT_OF_MEMORY, "cudaMalloc(views)", e);
+        if ((e = cudaMallocHost(&pc->h_views, sizeof(ViewConst) * views)) != cudaSuccess) return fail(pc, VR_ERR_OUT_OF_MEMORY, "cudaMallocHost(views)", e);
+        pc->view_capacity = views;
+        pc->max_views = views;             // its own frames are never used (it stores into the leader's), only the view block is
+    }
+    return vr_set_params(pc, p);
+}
+
 extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
     // a caller built before the VR_DENSITY_TREE fields were appended passes the shorter struct
@@ -1007,6 +1103,22 @@ extern "C" vr_status vr_set_params(vr_context* c, const vr_params* p) {
     c->params.ubo0 = c->params.ubo1 = c->params.view_ubos = nullptr;   // bytes were copied; do not keep caller pointers
     c->view_count = views;
     c->has_params = true;
+    // group context: every device decodes the same bytes (and builds its own fBm cell tables / tree copy); a peer holds one
+    // view's constants at a time, so view batches keep their whole view block (sharded at vr_render)
+    for (vr_context* pc : c->peers) {
+        vr_params q = *p;
+        q.struct_size = sizeof q;
+        const vr_status st = vr_set_params_peer(pc, &q);
+        if (st != VR_OK) { cudaSetDevice(c->device); return fail(c, st, ("vr_set_params on a device of the group: " + pc->err).c_str()); }
+    }
+    if (!c->peers.empty()) {
+        VR_CUDA(c, cudaSetDevice(c->device));
+        // a new camera keeps the band plan (the cut then follows the measured times); other changes start it over
+        const vr_params& o = c->plan_params;
+        if (!c->plan_valid || o.max_steps != p->max_steps || o.density_mode != p->density_mode || o.light_steps != p->light_steps ||
+            o.sigma_t != p->sigma_t || o.step_scale != p->step_scale || o.view_count != p->view_count) c->plan_valid = false;
+        c->plan_params = c->params;
+    }
     return VR_OK;
 }
 
@@ -1073,6 +1185,130 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     return VR_OK;
 }
 
+// the march of rows [r0,r1) x views [v0,v1) with m (already pointing at its destination) on stream s of context c's device:
+// depth-segment scratch, events around the launch
+static vr_status enqueue_march(vr_context* c, MarchParams& m, int variant, uint32_t r0, uint32_t r1, uint32_t v0, uint32_t v1, bool stats,
+                               bool no_march, cudaStream_t s, int* n_launches) {
+    if (variant == MARCH_SINGLE_BRICK && stats) variant = MARCH_SINGLE_LINEAR;     // device counters live in the generic kernel
+    if (!no_march && r1 > r0 && v1 > v0) {
+        // depth segments: the scratch (one float4 per pixel and piece, one arrival counter per pixel) is grown here, once
+        int segs = march_pick_segments(m, variant, (int)(v1 - v0), stats);
+        const size_t px = (size_t)(r1 - r0) * c->width * (v1 - v0);
+        while (segs > 1 && px * segs * sizeof(float4) > ((size_t)2 << 30)) --segs;
+        if (segs > 1) {
+            if (c->seg_capacity < px * segs || c->seg_arrived_px < px) {
+                VR_CUDA(c, cudaStreamSynchronize(c->stream));
+                if (c->foreign_stream_pending) { VR_CUDA(c, cudaEventSynchronize(c->ev1)); c->foreign_stream_pending = false; }
+                if (c->d_seg_partials) { cudaFree(c->d_seg_partials); c->d_seg_partials = nullptr; c->seg_capacity = 0; }
+                if (c->d_seg_arrived) { cudaFree(c->d_seg_arrived); c->d_seg_arrived = nullptr; c->seg_arrived_px = 0; }
+                // room for a taller band of the same frame: the cut of a group moves from frame to frame
+                const size_t want_px = px + px / 4;
+                VR_CUDA(c, cudaMalloc(&c->d_seg_partials, want_px * segs * sizeof(float4)));
+                c->seg_capacity = want_px * segs;
+                VR_CUDA(c, cudaMalloc(&c->d_seg_arrived, want_px * sizeof(unsigned int)));
+                VR_CUDA(c, cudaMemsetAsync(c->d_seg_arrived, 0, want_px * sizeof(unsigned int), s));
+                c->seg_arrived_px = want_px;
+            }
+            m.segments = segs;
+            m.seg_partials = c->d_seg_partials; m.seg_arrived = c->d_seg_arrived; m.seg_capacity = c->seg_capacity;
+        }
+    }
+    VR_CUDA(c, cudaEventRecord(c->ev0, s));
+    if (!no_march) {
+        if (variant == MARCH_SINGLE_BRICK) VR_CUDA(c, launch_march_brick(m, c->tensor_map, (int)(v1 - v0), s));
+        else VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
+        if (r1 > r0 && v1 > v0) ++*n_launches;
+    }
+    VR_CUDA(c, cudaEventRecord(c->ev1, s));
+    return VR_OK;
+}
+
+// ---- the frame of a group context (vr_create_info.device_count > 1), cut over its devices.
+// One view: contiguous row bands of equal estimated cost.  The analytic cost (row_cost_kernel: primary steps per row) does
+// not know how many steps carry a light-march, so from the second frame on every band's model cost is rescaled by the device
+// time its GPU measured for it and the rows are cut again — the cut follows the scene from frame to frame.  A view batch:
+// contiguous view shards.  Every device marches on its own stream straight into `frame` on devices[0] (peer access); the
+// leader's stream waits for their completion events, so whatever follows on it (the copy to the caller) sees the whole frame.
+static vr_status render_group(vr_context* c, char* frame, int slot, bool pipelined, cudaStream_t s, int* n_launches) {
+    const uint32_t n = (uint32_t)c->peers.size() + 1, H = c->height;
+    auto ctx_of = [&](uint32_t d) { return d == 0 ? c : c->peers[d - 1]; };
+    std::vector<uint32_t> lo(n, 0), hi(n, 0);
+    const bool by_views = c->view_count > 1;
+    if (by_views) {
+        const uint32_t base = c->view_count / n, extra = c->view_count % n;
+        uint32_t b = 0;
+        for (uint32_t d = 0; d < n; ++d) { lo[d] = b; b += base + (d < extra ? 1 : 0); hi[d] = b; }
+    } else {
+        if (!c->plan_valid || c->plan_cost.size() != H || c->plan_bounds.size() != n + 1 || c->plan_age >= 256) {
+            c->plan_cost.assign(H, 0.0f);
+            vr_status st = vr_row_cost(c, c->plan_cost.data());
+            if (st != VR_OK) return st;
+            c->plan_bounds.assign(n + 1, 0);
+            st = vr_split_rows(c->plan_cost.data(), H, n, c->plan_bounds.data());
+            if (st != VR_OK) return fail(c, st, "vr_render: cutting the row bands");
+            c->plan_valid = true;
+            c->plan_age = 0;
+        } else {
+            // feedback: the device times of the previous frame's bands, if they are all in
+            std::vector<float> ms(n, 0.0f);
+            bool all = true;
+            for (uint32_t d = 0; d < n && all; ++d) {
+                vr_context* x = ctx_of(d);
+                if (c->plan_bounds[d + 1] <= c->plan_bounds[d]) continue;
+                cudaSetDevice(x->device);
+                if (!x->timed || cudaEventQuery(x->ev1) != cudaSuccess || cudaEventElapsedTime(&ms[d], x->ev0, x->ev1) != cudaSuccess) all = false;
+            }
+            cudaGetLastError();
+            cudaSetDevice(c->device);
+            if (all) {
+                float mx = 0.0f, mn = 1e30f;
+                for (uint32_t d = 0; d < n; ++d) if (ms[d] > 0.0f) { mx = std::fmax(mx, ms[d]); mn = std::fmin(mn, ms[d]); }
+                if (mx > 1.03f * mn) {
+                    std::vector<float> cost(c->plan_cost);
+                    for (uint32_t d = 0; d < n; ++d) {
+                        double sum = 0.0;
+                        for (uint32_t y = c->plan_bounds[d]; y < c->plan_bounds[d + 1]; ++y) sum += cost[y];
+                        if (sum > 0.0 && ms[d] > 0.0f)
+                            for (uint32_t y = c->plan_bounds[d]; y < c->plan_bounds[d + 1]; ++y) cost[y] = (float)(cost[y] * ms[d] / sum);
+                    }
+                    std::vector<uint32_t> nb(n + 1, 0);
+                    if (vr_split_rows(cost.data(), H, n, nb.data()) == VR_OK) { c->plan_bounds = nb; c->plan_cost = cost; }
+                }
+            }
+            ++c->plan_age;
+        }
+        for (uint32_t d = 0; d < n; ++d) { lo[d] = c->plan_bounds[d]; hi[d] = c->plan_bounds[d + 1]; }
+    }
+    for (uint32_t d = 0; d < n; ++d) {
+        vr_context* x = ctx_of(d);
+        x->timed = false;
+        if (hi[d] <= lo[d]) continue;
+        VR_CUDA(c, cudaSetDevice(x->device));
+        cudaStream_t xs = d == 0 ? s : x->stream;
+        MarchParams m;
+        int variant = 0;
+        vr_status st = fill_march_params(x, m, variant);
+        if (st != VR_OK) { cudaSetDevice(c->device); return d == 0 ? st : fail(c, st, ("vr_render on a device of the group: " + x->err).c_str()); }
+        m.out = frame; m.row_pitch = c->row_pitch; m.view_stride = c->view_stride;
+        uint32_t r0 = 0, r1 = H, v0 = 0, v1 = 1;
+        if (by_views) { v0 = lo[d]; v1 = hi[d]; } else { r0 = lo[d]; r1 = hi[d]; }
+        m.row_begin = (int)r0; m.row_end = (int)r1; m.view_begin = (int)v0;
+        if (d > 0) {
+            // the frame slot must have left for the caller (copy stream / the leader's stream) before a peer writes it again
+            if (pipelined) { if (c->copy_pending[slot]) VR_CUDA(c, cudaStreamWaitEvent(xs, c->ev_copy_done[slot], 0)); }
+            else VR_CUDA(c, cudaStreamWaitEvent(xs, c->ev_consumed, 0));
+        }
+        st = enqueue_march(x, m, variant, r0, r1, v0, v1, false, false, xs, n_launches);
+        if (st != VR_OK) { cudaSetDevice(c->device); return d == 0 ? st : fail(c, st, ("vr_render on a device of the group: " + x->err).c_str()); }
+        x->timed = true;
+    }
+    VR_CUDA(c, cudaSetDevice(c->device));
+    for (vr_context* pc : c->peers) if (pc->timed) VR_CUDA(c, cudaStreamWaitEvent(s, pc->ev1, 0));
+    if (!c->timed) { VR_CUDA(c, cudaEventRecord(c->ev0, s)); VR_CUDA(c, cudaEventRecord(c->ev1, s)); }   // the leader's band was empty
+    c->group_timed = true;
+    return VR_OK;
+}
+
 extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
     if (!c->has_params) return fail(c, VR_ERR_BAD_STATE, "vr_render: vr_set_params has not been called");
@@ -1124,37 +1360,21 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
         if (c->copy_pending[slot]) VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_copy_done[slot], 0));   // frame slot is free again
         m.out = frame;
     }
-    if (variant == MARCH_SINGLE_BRICK && stats) variant = MARCH_SINGLE_LINEAR;     // device counters live in the generic kernel
-    if (!no_march && r1 > r0 && v1 > v0) {
-        // depth segments: the scratch (one float4 per pixel and piece, one arrival counter per pixel) is grown here, once
-        int segs = march_pick_segments(m, variant, (int)(v1 - v0), stats);
-        const size_t px = (size_t)(r1 - r0) * c->width * (v1 - v0);
-        while (segs > 1 && px * segs * sizeof(float4) > ((size_t)2 << 30)) --segs;
-        if (segs > 1) {
-            if (c->seg_capacity < px * segs || c->seg_arrived_px < px) {
-                VR_CUDA(c, cudaStreamSynchronize(c->stream));
-                if (c->foreign_stream_pending) { VR_CUDA(c, cudaEventSynchronize(c->ev1)); c->foreign_stream_pending = false; }
-                if (c->d_seg_partials) { cudaFree(c->d_seg_partials); c->d_seg_partials = nullptr; c->seg_capacity = 0; }
-                if (c->d_seg_arrived) { cudaFree(c->d_seg_arrived); c->d_seg_arrived = nullptr; c->seg_arrived_px = 0; }
-                VR_CUDA(c, cudaMalloc(&c->d_seg_partials, px * segs * sizeof(float4)));
-                c->seg_capacity = px * segs;
-                VR_CUDA(c, cudaMalloc(&c->d_seg_arrived, px * sizeof(unsigned int)));
-                VR_CUDA(c, cudaMemsetAsync(c->d_seg_arrived, 0, px * sizeof(unsigned int), s));
-                c->seg_arrived_px = px;
-            }
-            m.segments = segs;
-            m.seg_partials = c->d_seg_partials; m.seg_arrived = c->d_seg_arrived; m.seg_capacity = c->seg_capacity;
-        }
+    c->group_timed = false;
+    // several GPUs behind this context: whole-frame renders into the context's own frame are cut over the devices
+    const bool group = !c->peers.empty() && !no_march && !direct && !t->stream && !stats && r0 == 0 && r1 == c->height && v0 == 0 &&
+                       v1 == c->view_count;
+    int n_launches = 0;
+    if (group) {
+        st = render_group(c, frame, slot, pipelined, s, &n_launches);
+        if (st != VR_OK) return st;
+    } else {
+        st = enqueue_march(c, m, variant, r0, r1, v0, v1, stats, no_march, s, &n_launches);
+        if (st != VR_OK) return st;
     }
-    VR_CUDA(c, cudaEventRecord(c->ev0, s));
-    if (!no_march) {
-        if (variant == MARCH_SINGLE_BRICK) VR_CUDA(c, launch_march_brick(m, c->tensor_map, (int)(v1 - v0), s));
-        else VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
-    }
-    VR_CUDA(c, cudaEventRecord(c->ev1, s));
     c->timed = true;
     c->foreign_stream_pending = t->stream != nullptr;
-    c->stats.kernel_launches = (!no_march && r1 > r0 && v1 > v0) ? 1 : 0;
+    c->stats.kernel_launches = (uint32_t)n_launches;
     c->stats.rays = (uint64_t)(r1 - r0) * c->width * (v1 - v0);
     if (stats) VR_CUDA(c, cudaMemcpyAsync(c->h_counters, c->d_counters, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
     else std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
@@ -1177,6 +1397,7 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
                                          t->memory_kind == VR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, cs));
         }
         if (pipelined) { VR_CUDA(c, cudaEventRecord(c->ev_copy_done[slot], c->copy_stream)); c->copy_pending[slot] = true; }
+        if (c->ev_consumed && !pipelined) VR_CUDA(c, cudaEventRecord(c->ev_consumed, cs));   // the peers may write this frame again after it
     }
     if (!(t->flags & VR_RENDER_ASYNC)) VR_CUDA(c, cudaStreamSynchronize(s));
     return VR_OK;
@@ -1184,6 +1405,10 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
 
 extern "C" vr_status vr_wait(vr_context* c) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
+    for (vr_context* pc : c->peers) {
+        VR_CUDA(c, cudaSetDevice(pc->device));
+        VR_CUDA(c, cudaStreamSynchronize(pc->stream));
+    }
     VR_CUDA(c, cudaSetDevice(c->device));
     if (c->timed) VR_CUDA(c, cudaEventSynchronize(c->ev1));
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -1199,6 +1424,17 @@ extern "C" vr_status vr_get_stats(vr_context* c, vr_stats* out) {
     if (c->timed) {
         VR_CUDA(c, cudaEventSynchronize(c->ev1));
         VR_CUDA(c, cudaEventElapsedTime(&c->stats.gpu_ms, c->ev0, c->ev1));
+    }
+    if (c->group_timed) {          // a frame cut over the group's devices: the slowest band is the frame's device time
+        for (vr_context* pc : c->peers) {
+            if (!pc->timed) continue;
+            float ms = 0.0f;
+            VR_CUDA(c, cudaSetDevice(pc->device));
+            VR_CUDA(c, cudaEventSynchronize(pc->ev1));
+            VR_CUDA(c, cudaEventElapsedTime(&ms, pc->ev0, pc->ev1));
+            if (ms > c->stats.gpu_ms) c->stats.gpu_ms = ms;
+        }
+        VR_CUDA(c, cudaSetDevice(c->device));
     }
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
     c->stats.covered = c->h_counters[0];

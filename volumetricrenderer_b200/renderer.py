@@ -55,11 +55,18 @@ class PinnedArray:
 
 
 class Renderer:
-    def __init__(self, width=1280, height=720, fmt=capi.OUT_RGBA8_UNORM, device=0, max_views=1):
+    def __init__(self, width=1280, height=720, fmt=capi.OUT_RGBA8_UNORM, device=0, max_views=1, devices=None):
+        """devices: CUDA ordinals of several GPUs behind this ONE context (vr_create_info.device_count): the frame lives on
+        devices[0], vr_render cuts it into row bands (or a view batch into view shards) over all of them."""
         self._lib = capi.load()
         self._ctx = C.c_void_p()
         self.width, self.height, self.format, self.max_views = width, height, fmt, max_views
         info = capi.vr_create_info(C.sizeof(capi.vr_create_info), device, width, height, fmt, max_views, 0)
+        if devices is not None and len(devices) > 1:
+            info.device_count = len(devices)
+            for i, d in enumerate(devices):
+                info.devices[i] = d
+            info.device = devices[0]
         st = self._lib.vr_create(C.byref(info), C.byref(self._ctx))
         if st != capi.VR_OK:
             msg = self._lib.vr_last_error(None)
