@@ -64,13 +64,16 @@ BAKE_FLOP_PER_VOXEL = 2 * 27 * 14.0 + 60.0 + 80.0
 FLOP_PER_OCTAVE, FLOP_PER_SAMPLE, FLOP_PER_STEP = 60.0, 20.0, 26.0
 
 
-def config_for(workload, world, layout, has_volume):
+def config_for(workload, world, layout, has_volume, single_process=False):
     """`config` of a bench line; the product arm and the reference arm print the very same dict for the same command"""
     W, H, desc, _ = WORKLOADS[workload]
+    part = "single GPU"
+    if world > 1:
+        part = ("cost-balanced row bands, peer stores into GPU0's frame over NVLink; one process, one context over all devices"
+                if single_process else "cost-balanced row bands, peer stores into GPU0's frame over NVLink (CUDA IPC)")
     return {"workload": "%s: %s" % (workload, desc), "width": W, "height": H,
             "l2": "flushed between frames (256 MiB write); the procedural workloads read no input",
-            "partition": "cost-balanced row bands, peer stores into GPU0's frame over NVLink (CUDA IPC)" if world > 1 else "single GPU",
-            "volume_layout": layout if has_volume else None}
+            "partition": part, "volume_layout": layout if has_volume else None}
 
 
 def kernel_source_sha16():
@@ -96,6 +99,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the oracle sample")
     ap.add_argument("--no-extra", action="store_true", help="c2 only: skip the extra.c3 measurement")
+    ap.add_argument("--single-process", action="store_true",
+                    help="--gpus N without torchrun: ONE process, ONE context over N devices (vr_create_info.device_count)")
     return ap.parse_args()
 
 
@@ -225,7 +230,8 @@ def run_reference(args, rank, world):
         "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": W * H / (mrays * 1e6) * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config_for(args.workload, max(1, args.gpus), args.layout, args.workload == "c1" or args.workload.startswith("c4")),
+        "config": config_for(args.workload, max(1, args.gpus), args.layout, args.workload == "c1" or args.workload.startswith("c4"),
+                             args.single_process),
         "note": "ms_per_step = full-frame time extrapolated from the timed row sample; the CPU arm runs on rank 0's host cores whatever --gpus says",
         "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": last["cores"], "kind": "port", "sample": last["sample"]},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -275,8 +281,11 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
     W, H, desc, kw = WORKLOADS[workload]
     Wm = max(args.warmup, 3)
     ubo0, ubo1 = scene.default_scene()
+    group = args.single_process and args.gpus > 1 and world == 1      # one process, one context over args.gpus devices
+    n_gpus = args.gpus if group else world
     # N > 1: GPU 0 holds two frames, so the gather of frame k+1 (peer stores) overlaps the D2H copy of frame k
-    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local, max_views=2 if world > 1 else 1)
+    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local, max_views=2 if world > 1 else 1,
+                    devices=list(range(args.gpus)) if group else None)
     vol_bytes = setup_volume(r, workload, args.layout)
     r.set_params(ubo0, ubo1, **kw)
 
@@ -304,7 +313,7 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
             dist.barrier(device_ids=[local])
             torch.cuda.synchronize()
 
-    # ---- one counted pass (device counters): work actually done per frame
+    # ---- one counted pass (device counters): work actually done per frame (a counted pass runs on one device)
     march(capi.RENDER_STATS)
     st = r.stats()
     counts = np.array([st["covered"], st["steps"], st["light_samples"], st["early_terminated"]], np.float64)
@@ -316,7 +325,7 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
     covered, steps, light_samples = int(counts[0]), int(counts[1]), int(counts[2])
 
     # ---- device-timed region: K frames, L2 flushed between frames, CUDA events on the launching stream
-    for _ in range(Wm):
+    for _ in range(Wm + (6 if group else 0)):          # a group context re-cuts its bands from the measured times as it goes
         r.flush_l2(); march(); r.wait()
     if world > 1:
         # feedback re-cut of the bands from measured band times (a renderer does this every frame; here: during
@@ -329,11 +338,13 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
     barrier()
     sampler.start()
     wall0 = time.perf_counter()
-    ms = []
+    ms, launches = [], 0
     for _ in range(K):
         r.flush_l2()
         march()
-        ms.append(r.stats()["gpu_ms"] if rows[1] > rows[0] else 0.0)
+        st_k = r.stats() if rows[1] > rows[0] else {"gpu_ms": 0.0, "kernel_launches": 0}
+        ms.append(st_k["gpu_ms"])
+        launches += st_k["kernel_launches"]       # one march per device that had rows to render
     barrier()
     wall = time.perf_counter() - wall0
     clocks = sampler.stop()
@@ -354,6 +365,15 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
     # the frame its peers have just stored their bands into (a band may take another lanes-per-ray / depth-segment mapping
     # than the full frame: re-association only, so the bar is 1/255)
     gather_check = None
+    if group:
+        gathered = r.render()[0].copy()
+        with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=0) as solo:
+            setup_volume(solo, workload, args.layout)
+            solo.set_params(ubo0, ubo1, **kw)
+            alone = solo.render()[0].copy()
+        d = np.abs(gathered.astype(np.int16) - alone.astype(np.int16))
+        gather_check = {"max_abs8": int(d.max()), "pixels_differing": int((d.max(axis=-1) > 0).sum()),
+                        "nonzero_pixels": int((alone[..., :3].max(axis=-1) > 0).sum()), "vs": "the same frame rendered by a single-GPU context"}
     if world > 1:
         march(); barrier()
         if rank == 0:
@@ -443,11 +463,11 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
     line = None
     if rank == 0:
         line = {
-            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": config_for(workload, world, args.layout, bool(vol_bytes)),
-            "e2e": e2e, "gpu_launches": K * (1 if rows[1] > rows[0] else 0),
+            "config": config_for(workload, n_gpus, args.layout, bool(vol_bytes), group),
+            "e2e": e2e, "gpu_launches": launches,
             "clocks": clocks, "wall_ms_per_step_incl_flush": wall / K * 1e3,
             "covered_rays": covered, "steps_per_frame": steps, "light_samples_per_frame": light_samples,
             "msamples_per_s": (steps + light_samples) / (ms_per_step * 1e-3) / 1e6,
@@ -455,7 +475,7 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
         line["covered_mrays_per_s"] = covered / (ms_per_step * 1e-3) / 1e6      # rays that actually march (the rest are cleared)
         if gather_check is not None:
             line["gather_check"] = gather_check
-        line["roofline"] = roofline(r, args, workload, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, world)
+        line["roofline"] = roofline(r, args, workload, kw, steps, light_samples, ms_per_step, W, H, vol_bytes, n_gpus)
         line["ray_split"] = os.environ.get("VOLRT_RAY_SPLIT_COMPOSITE", "auto")
         if full and not args.no_cpu_baseline and world == 1:
             try:

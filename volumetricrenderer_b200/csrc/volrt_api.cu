@@ -1605,6 +1605,10 @@ extern "C" vr_status vr_gather_collect(vr_context* c, uint32_t slot, uint32_t ar
 // ------------------------------------------------------------------ measurement helpers
 extern "C" vr_status vr_flush_l2(vr_context* c) {
     if (!c) return VR_ERR_INVALID_ARGUMENT;
+    for (vr_context* pc : c->peers) {                    // a group context: every device's L2
+        const vr_status st = vr_flush_l2(pc);
+        if (st != VR_OK) return fail(c, st, ("vr_flush_l2 on a device of the group: " + pc->err).c_str());
+    }
     const size_t bytes = (size_t)256 << 20;             // 2x the 126 MB L2
     VR_CUDA(c, cudaSetDevice(c->device));
     if (!c->flush_buf) VR_CUDA(c, cudaMalloc(&c->flush_buf, bytes));
