@@ -130,3 +130,36 @@ def test_error_paths():
             r.set_params(u0, u1)
             r.render()                                           # RGBA product needs an RGBA8 volume
         assert e.value.status == capi.VR_ERR_BAD_STATE
+
+
+def test_a_rejected_bake_leaves_the_resident_volume_alone(oracle):
+    """vr_generate_volume checks every argument before it touches the volume storage: after a bad recipe the context still
+    renders the volume it held"""
+    from volumetricrenderer_b200 import scene
+    W, H = 160, 90
+    rng = np.random.default_rng(21)
+    vol = rng.integers(0, 256, size=(16, 16, 16, 4), dtype=np.uint8)
+    u0, u1 = scene.default_scene(10.0, 5.0)
+    with vr.Renderer(W, H, capi.OUT_RGBA8_UNORM) as r:
+        r.upload_volume(vol, capi.VOL_RGBA8_UNORM, capi.LAYOUT_TEXTURE)
+        r.set_params(u0, u1)
+        before = r.render()[0].copy()
+        for bad in ("power", "generator", "norm"):
+            d = r.default_noise_desc()
+            d.size = 16                                          # same shape as the resident volume: its storage would be reused
+            if bad == "power":
+                d.channel[2].power = 99
+            elif bad == "generator":
+                d.channel[1].generator = 77
+            else:
+                d.channel[3].norm_generator = capi.NOISE_ZERO
+            with pytest.raises(vr.VolrtError) as e:
+                r.generate_volume(d)
+            assert e.value.status == capi.VR_ERR_INVALID_ARGUMENT
+            assert np.array_equal(r.render()[0], before)
+            assert np.array_equal(r.download_volume(), vol)
+        p = r.default_params()
+        p.fbm_octaves = 77
+        with pytest.raises(vr.VolrtError):
+            r.generate_volume(size=16, format=capi.VOL_R16F, fbm_params=p)
+        assert np.array_equal(r.render()[0], before)

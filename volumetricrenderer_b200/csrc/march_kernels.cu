@@ -1096,11 +1096,14 @@ cudaError_t launch_march_brick(const MarchParams& p_in, const void* tensor_map, 
     if (rows <= 0 || n_views <= 0) return cudaSuccess;
     MarchParams p = p_in;
     p.n_views = n_views;
-    static bool attr_set = false;
-    if (!attr_set) {
+    // function attributes are per device: a process may hold contexts on several (vr_create_info.device_count)
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         cudaError_t e = cudaFuncSetAttribute(march_brick_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BRICK_BYTES);
         if (e != cudaSuccess) return e;
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     CUtensorMap tm;
     memcpy(&tm, tensor_map, sizeof tm);
@@ -1135,14 +1138,12 @@ static cudaError_t launch_one(const MarchParams& p, dim3 grid, bool persistent, 
     if constexpr (VARIANT != MARCH_TREE) {      // a tree sample is hundreds of instructions: no queue variant is built for it
         if (persistent) {
             // resident CTAs per SM x SM count, from the occupancy calculator (registers decide)
-            static int resident = 0;       // per instantiation
-            if (resident == 0) {
-                int dev = 0, sms = 0, per_sm = 0;
-                cudaGetDevice(&dev);
-                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            static int per_sm = 0;         // per instantiation; the same on every device of one architecture
+            if (per_sm == 0) {
                 cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, march_kernel_persistent<VARIANT, COMPOSITE, STATS>, 128, 0);
-                resident = sms * (per_sm > 0 ? per_sm : 1);
+                if (per_sm <= 0) per_sm = 1;
             }
+            const int resident = (p.sm_count > 0 ? p.sm_count : 148) * per_sm;
             const long long tiles = (long long)((p.width + 7) / 8) * ((p.row_end - p.row_begin + 3) / 4) * p.n_views;
             const long long want = (tiles + 3) / 4;
             march_kernel_persistent<VARIANT, COMPOSITE, STATS><<<(unsigned)(want < resident ? want : resident), 128, 0, s>>>(p);

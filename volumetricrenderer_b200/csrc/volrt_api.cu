@@ -461,6 +461,10 @@ static vr_status prepare_volume(vr_context* c, const vr_volume_desc& d) {
     const bool same = c->has_volume && o.width == d.width && o.height == d.height && o.depth == d.depth && o.format == d.format &&
                       o.address_mode == d.address_mode && o.layout == layout;
     VR_CUDA(c, cudaStreamSynchronize(c->stream));
+    // a march enqueued on a caller's stream, or a frame copy on the copy stream, may still be reading the storage about
+    // to be rewritten
+    if (c->foreign_stream_pending) { VR_CUDA(c, cudaEventSynchronize(c->ev1)); c->foreign_stream_pending = false; }
+    VR_CUDA(c, cudaStreamSynchronize(c->copy_stream));
     if (same) c->has_volume = false;                         // storage stays; has_volume returns with finish_volume
     else {
         release_volume(c);
@@ -750,6 +754,21 @@ extern "C" vr_status vr_generate_volume(vr_context* c, const vr_noise_desc* d, c
     vr_status st = check_volume_desc(c, &vd);
     if (st != VR_OK) return st;
     if (d->format == VR_VOL_R8_UNORM) return fail(c, VR_ERR_UNSUPPORTED, "vr_generate_volume: RGBA8 (channel recipes) or R16F (fBm smoke) only");
+    // every argument is checked BEFORE the resident volume's storage is touched: a bad call leaves the context as it was
+    if (d->format == VR_VOL_R16F) {
+        if (fbm && (fbm->fbm_octaves < 1 || fbm->fbm_octaves > 16)) return fail(c, VR_ERR_INVALID_ARGUMENT, "fbm_octaves must be in 1..16");
+    } else {
+        const bool trees = d->struct_size >= offsetof(vr_noise_desc, tree) + sizeof(d->tree);
+        for (int k = 0; k < 4; ++k) {
+            const vr_noise_channel& ch = d->channel[k];
+            const vr_noise_tree* tr = (ch.generator == VR_NOISE_TREE && trees) ? d->tree[k] : nullptr;
+            if (ch.generator > VR_NOISE_TREE || (ch.generator == VR_NOISE_TREE && (!tr || tr->prog.empty())) ||
+                (ch.norm_generator > VR_NOISE_ZERO && ch.norm_generator != VR_NOISE_SAME) || ch.power < 1 || ch.power > 8)
+                return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: bad channel recipe (a VR_NOISE_TREE channel needs desc.tree[k] and normalises with VR_NOISE_SAME or a built-in field)");
+            if (ch.norm_generator == VR_NOISE_ZERO || (ch.norm_generator == VR_NOISE_SAME && ch.generator == VR_NOISE_ZERO))
+                return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_generate_volume: a channel needs a non-zero field to normalise with");
+        }
+    }
     VR_CUDA(c, cudaSetDevice(c->device));
     st = prepare_volume(c, vd);
     if (st != VR_OK) return st;
@@ -1359,6 +1378,9 @@ extern "C" vr_status vr_render(vr_context* c, const vr_target* t) {
         if (slot == 1) frame = (char*)c->frame2;
         if (c->copy_pending[slot]) VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_copy_done[slot], 0));   // frame slot is free again
         m.out = frame;
+    } else if (!no_march && !direct && c->copy_pending[0]) {
+        // a pipelined frame may still be leaving slot 0 on the copy stream: this render writes the same memory
+        VR_CUDA(c, cudaStreamWaitEvent(s, c->ev_copy_done[0], 0));
     }
     c->group_timed = false;
     // several GPUs behind this context: whole-frame renders into the context's own frame are cut over the devices
