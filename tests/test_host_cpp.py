@@ -47,8 +47,9 @@ def test_host_fails_loudly_without_a_device():
 
 
 @pytest.mark.gpu
-def test_headless_loop_matches_the_python_host(tmp_path):
-    """same key trace through the C++ host and through the Python host -> same frames (sum of R)"""
+def test_headless_loop_matches_the_python_host(tmp_path, oracle):
+    """same key trace through the C++ host and through the Python host -> same frames (sum of R); and the frame the C++ host
+    wrote to disk is the ORACLE's frame of that scene (and the compiled reference shaders' where oracle/_ref is present)"""
     import volumetricrenderer_b200 as vr
     from volumetricrenderer_b200 import capi, scene
     _build()
@@ -70,11 +71,24 @@ def test_headless_loop_matches_the_python_host(tmp_path):
             img = rr.render()[0]
             s = int(img[..., 0].astype(np.int64).sum())
             assert abs(s - sums[f]) <= 2e-4 * max(s, 1), (f, s, sums[f])     # libm vs numpy sin/cos: a few ulp in Model
+        baked = rr.download_volume()                                         # the bake is deterministic: the C++ host marched these texels
     # the PPM of the last frame is the frame
     ppm = open(os.path.join(str(tmp_path), "frame_0011.ppm"), "rb").read()
     assert ppm.startswith(b"P6\n1280 720\n255\n")
     px = np.frombuffer(ppm[len(b"P6\n1280 720\n255\n"):], np.uint8).reshape(720, 1280, 3)
     assert int(px[..., 0].astype(np.int64).sum()) == sums[11]
+    # ... and it is the right frame: the oracle (and the reference's own shaders compiled as C++) on the scene of frame 11
+    from util import oracle_params, psnr8, max_abs8
+    p = oracle_params(oracle, u0, u1)
+    ov, _keep = oracle.make_volume(baked, oracle.VOL_RGBA8)
+    ref, st = oracle.render(ov, p, 1280, 720)
+    ref8 = oracle.encode(ref, oracle.OUT_RGBA8_UNORM)[..., :3]
+    assert st["covered"] > 150000 and ref8.max() > 40
+    assert max_abs8(px, ref8) <= 2 and psnr8(px, ref8) >= 50.0
+    if oracle.have_ref_glsl():
+        drawn, _cov, _fp = oracle.ref_draw(u0, u1, baked, 1280, 720)
+        d8 = oracle.encode(drawn, oracle.OUT_RGBA8_UNORM)[..., :3]
+        assert max_abs8(px, d8) <= 2 and psnr8(px, d8) >= 50.0
 
 
 @pytest.mark.gpu

@@ -686,20 +686,35 @@ __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
 #endif                              // would take 223 registers (2 CTAs/SM, C2 1.96 ms); measured 3 / 4 / 5 / 6 CTAs: 1.797 / 1.72 / 1.76 / 1.76 ms
 
 constexpr int kCtaWx = VOLRT_CTA_WX, kCtaWy = VOLRT_CTA_WY, kCtaThreads = 32 * kCtaWx * kCtaWy;
+// Register caps (resident CTAs per SM asked of ptxas).  fBm: 128 registers (VOLRT_DIRECT_MIN_CTAS).  Texture marches, measured
+// on B200: the compositing march over a grid far larger than L2 (C5) is latency-bound and wants warps — 8 / 10 / 12 CTAs
+// (64 / 48 / 40 registers): 7.63 / 6.66 / 6.49 ms per 64 views; the reference integrator (C4) wants registers for its four-step
+// fetch batches — 7 / 8 / 10 / 12 CTAs: 0.0925 / 0.0936 / 0.0975 / 0.0991 ms.  Left to itself ptxas took 103 registers for the
+// compositing march once the depth-piece hand-over was added (46 before) and C5 doubled to 13.4 ms: hence explicit caps.
+// FP32-filtered parity variants: 80 registers; the node-tree interpreter: 168 (its V[]/P[] live in local memory anyway).
+__host__ __device__ constexpr int direct_min_ctas(int variant, bool composite) {
+    return is_fbm(variant) ? VOLRT_DIRECT_MIN_CTAS
+         : (variant == MARCH_RGBA_TEX || variant == MARCH_SINGLE_TEX) ? (composite ? 12 : 7)
+         : variant == MARCH_TREE ? 3 : 6;
+}
 template <int VARIANT, bool COMPOSITE, bool STATS>
-__global__ void __launch_bounds__(kCtaThreads, is_fbm(VARIANT) ? VOLRT_DIRECT_MIN_CTAS : 1) march_kernel(const __grid_constant__ MarchParams P) {
+__global__ void __launch_bounds__(kCtaThreads, direct_min_ctas(VARIANT, COMPOSITE)) march_kernel(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
     __shared__ MarchSmem<LINEAR> smem;
     float* const unorm = smem.unorm;
     GradLut& lut = smem.lut;
     stage_tables<VARIANT>(unorm, &lut);
-    int tx, ty, seg = 0;
+    int tx, ty, seg = 0, vin = 0;
+    int view = P.view_begin + blockIdx.z;
     if (COMPOSITE && !STATS && P.segments > 1) tile_of_cta(P, 4 * kCtaWy, tx, ty, P.segments, &seg);     // grid x = tiles x depth segments
-    else tile_of_cta(P, 4 * kCtaWy, tx, ty);
+    else if (P.view_group > 1) {                                                                            // grid x = tiles x views of a group
+        tile_of_cta(P, 4 * kCtaWy, tx, ty, P.view_group, &vin);
+        view = P.view_begin + (int)blockIdx.z * P.view_group + vin;
+        if (view >= P.view_begin + P.n_views) return;
+    } else tile_of_cta(P, 4 * kCtaWy, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = tx * (8 * kCtaWx) + (warp % kCtaWx) * 8 + (lane & 7);
     const int py = P.row_begin + ty * (4 * kCtaWy) + (warp / kCtaWx) * 4 + (lane >> 3);
-    const int view = P.view_begin + blockIdx.z;
     if (px >= P.width || py >= P.row_end) return;
     march_pixel<VARIANT, COMPOSITE, STATS>(P, unorm, lut, px, py, view, seg);
 }
@@ -1150,6 +1165,10 @@ static cudaError_t launch_one(const MarchParams& p, dim3 grid, bool persistent, 
             return cudaGetLastError();
         }
     }
+    if (p.view_group > 1 && p.segments <= 1) {      // grid x = tiles x views of a group, grid z = groups (march_kernel)
+        grid.x *= p.view_group;
+        grid.z = (grid.z + p.view_group - 1) / p.view_group;
+    }
     march_kernel<VARIANT, COMPOSITE, STATS><<<grid, kCtaThreads, 0, s>>>(p);
     return cudaGetLastError();
 }
@@ -1209,6 +1228,19 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
         return cudaErrorInvalidValue;
     }
     p.segments = 1;
+    // view batches over a volume that does not fit L2: interleave the views' tiles (MarchParams::view_group)
+    int vg = 1;
+    if (n_views > 1 && !stats) {
+        static const int env_vg = [] { const char* e = getenv("VOLRT_VIEW_GROUP"); return e ? atoi(e) : -1; }();
+        // auto: four views' tiles interleaved when the volume cannot stay in the 126 MB L2 (C5: 64 views over a 2 GiB grid,
+        // 6.49 -> 6.01 ms; 2 / 8 / 16 views per group: 6.2 / 6.3 / 6.4), otherwise whole views one after the other
+        const double vol_bytes = (double)p.vw * p.vh * p.vd * (p.vol_format == VR_VOL_RGBA8_UNORM ? 4 : p.vol_format == VR_VOL_R16F ? 2 : 1);
+        const bool grid_density = variant == MARCH_RGBA_TEX || variant == MARCH_SINGLE_TEX || variant == MARCH_RGBA_LINEAR || variant == MARCH_SINGLE_LINEAR;
+        vg = env_vg >= 1 ? env_vg : (grid_density && vol_bytes > 96e6 && n_views >= 4) ? 4 : 1;
+        if (vg > n_views) vg = n_views;
+        if (vg > 16) vg = 16;
+    }
+    p.view_group = vg;
     // schedule: 0 = direct tiles, 1 = persistent warps, -1 = auto
     bool persistent = p.schedule > 0;    // auto = direct: the queue did not pay off on B200 (measurements)
     if (!p.queue) persistent = false;

@@ -111,6 +111,9 @@ struct MarchParams {
     float4* seg_partials;       // [view][segment][row - row_begin][x], context scratch
     unsigned int* seg_arrived;  // [view][row - row_begin][x], zero between launches (the composing thread resets it)
     size_t seg_capacity;        // pixel-segments the scratch holds
+    // view batches: the same screen tile of `view_group` consecutive views is dispatched back to back (grid x = tiles x
+    // view_group, grid z = groups), so that CTAs resident together look at the same region of a volume larger than L2
+    int view_group;             // 0 / 1 = views are whole z slices
 };
 constexpr int kMaxRaySegments = 8;
 
