@@ -752,6 +752,18 @@ def roofline(r, args, workload, kw, steps, light_samples, ms_per_step, W, H, vol
                     "constant_channels_elided": const_ch if kw.get("density_mode", 0) == 0 else 0,
                     "note": "the volume is cache-resident or streamed once; compulsory HBM traffic is under 'hbm'; achieved counts "
                             "the fetches actually issued (a constant channel of the volume is not fetched)"})
+    if workload.startswith("c4") and args.layout == "texture":
+        # what the texture path can stream out of DRAM at all (every texel of the resident grid fetched exactly once): the
+        # ceiling of the 128-step march, whose fetches are nearly all first touches
+        try:
+            g = r.measure_tex_stream()
+            out["hbm"]["tex_stream_gbs"] = g
+            out["hbm"]["frac_of_tex_stream"] = out["hbm"]["achieved"] / (g * world) if g else None
+            out["hbm"]["tex_stream_note"] = ("vr_measure_tex_stream in this process: the grid read once through tex3D (trilinear fetches "
+                                             "on a 2-texel lattice, L2 flushed)")
+        except Exception as e:
+            out["hbm"]["tex_stream_gbs"] = None
+            out["hbm"]["tex_stream_note"] = "failed: %r" % (e,)
     out["frac"] = out["achieved"] / out["peak"] if out["peak"] else None
     return out
 

@@ -311,6 +311,10 @@ VR_API vr_status vr_flush_l2(vr_context* ctx);
 /* roofline denominators measured on this device: peaks4 = { FP32-FMA TFLOP/s, trilinear RGBA8 texture
  * fetches G/s (0 without a TEXTURE-layout RGBA8 volume), SM count, max SM clock MHz } */
 VR_API vr_status vr_measure_peaks(vr_context* ctx, float* peaks4);
+/* GB/s at which the texture unit streams the resident one-channel TEXTURE-layout volume out of DRAM when every texel is fetched
+ * exactly once (trilinear fetches on a 2-texel lattice, L2 flushed): the ceiling of a grid march whose fetches are all first
+ * touches — what the "fraction of HBM bandwidth" of the 512^3 smoke workload is bounded by.  No counterpart in the reference. */
+VR_API vr_status vr_measure_tex_stream(vr_context* ctx, float* gbs);
 VR_API void* vr_host_alloc(size_t bytes);
 VR_API void vr_host_free(void* p);
 

@@ -116,6 +116,7 @@ EXPORTS = {
     "vr_gather_collect": (C.c_int32, [_VP, C.c_uint32, C.c_uint32, _VP, C.c_size_t]),
     "vr_flush_l2": (C.c_int32, [_VP]),
     "vr_measure_peaks": (C.c_int32, [_VP, C.POINTER(C.c_float)]),
+    "vr_measure_tex_stream": (C.c_int32, [_VP, C.POINTER(C.c_float)]),
     "vr_host_alloc": (_VP, [C.c_size_t]),
     "vr_host_free": (None, [_VP]),
     "vr_sha256": (C.c_int32, [_VP, C.c_size_t, C.POINTER(C.c_uint8)]),

@@ -38,6 +38,50 @@ __global__ void __launch_bounds__(128) tex_peak_kernel(cudaTextureObject_t tex, 
     if (s == 12345.678f) sink[0] = s;
 }
 
+// What the texture path can stream out of DRAM: every texel of a one-channel 3-D texture read exactly once, by trilinear
+// fetches placed between texels 2i and 2i+1 on every axis (one fetch filters a 2x2x2 block: 1/8 fetch per texel, so the
+// fetch rate — 16.8 M fetches for 512^3 — is not the limit; at the unit's peak they take ~30 us, the 268 MB take 41 us at
+// the measured HBM rate).  SHAPE = how a warp's 32 fetches are laid out, PER_THREAD = independent fetches per thread along z.
+// This is the ceiling of the C4 march at 128 steps, where nearly every fetch is a first touch: DESIGN.md §7.
+template <int PER_THREAD, int SHAPE>
+__global__ void __launch_bounds__(256) tex_stream_kernel(cudaTextureObject_t tex, int nx, int ny, int nz, float* __restrict__ sink) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int bx, by, bz;                                                            // fetch coordinates (units of 2 texels)
+    if (SHAPE == 0) {            // warp = 8x2x2 fetches, CTA = 16x8x2
+        bx = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+        by = blockIdx.y * 8 + ((warp >> 1) & 3) * 2 + ((lane >> 3) & 1);
+        bz = (blockIdx.z * 2 + (lane >> 4)) * PER_THREAD;
+    } else if (SHAPE == 1) {     // warp = 32x1x1 fetches, CTA = 32x8x1
+        bx = blockIdx.x * 32 + lane;
+        by = blockIdx.y * 8 + warp;
+        bz = blockIdx.z * PER_THREAD;
+    } else {                     // warp = 4x4x2 fetches, CTA = 8x8x4
+        bx = blockIdx.x * 8 + (warp & 1) * 4 + (lane & 3);
+        by = blockIdx.y * 8 + ((warp >> 1) & 1) * 4 + ((lane >> 2) & 3);
+        bz = (blockIdx.z * 4 + (warp >> 2) * 2 + (lane >> 4)) * PER_THREAD;
+    }
+    float s = 0.0f;
+    if (2 * bx < nx && 2 * by < ny) {
+        float v[PER_THREAD];
+#pragma unroll
+        for (int k = 0; k < PER_THREAD; ++k) {
+            const int z = bz + k;
+            v[k] = 2 * z < nz ? tex3D<float>(tex, (float)(2 * bx + 1) / (float)nx, (float)(2 * by + 1) / (float)ny, (float)(2 * z + 1) / (float)nz) : 0.0f;
+        }
+#pragma unroll
+        for (int k = 0; k < PER_THREAD; ++k) s += v[k];
+    }
+    if (s == 12345.678f) sink[0] = s;
+}
+// Measured on B200 over the 512^3 fp16 grid (268 MB, L2 flushed), GB/s: warp = 8x2x2 fetches with 1 / 4 / 8 per thread along z
+// 3449 / 3547 / 3542; warp = 32x1x1 with 1 / 4: 3451 / 3591; warp = 4x4x2 with 1 / 4: 3544 / 3644.  Whatever the walk, the
+// texture path streams first-touch texels out of DRAM at 3.45-3.65 TB/s = 53-56 % of the 6551 GB/s a copy reaches.
+cudaError_t launch_tex_stream(cudaTextureObject_t tex, int nx, int ny, int nz, float* sink, cudaStream_t s) {
+    const int fx = nx / 2, fy = ny / 2, fz = nz / 2;
+    tex_stream_kernel<4, 2><<<dim3((fx + 7) / 8, (fy + 7) / 8, (fz + 15) / 16), 256, 0, s>>>(tex, nx, ny, nz, sink);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s) {
     fma_peak_kernel<<<blocks, 256, 0, s>>>(sink, iters, 0.999f, 0.001f);
     return cudaGetLastError();

@@ -1644,6 +1644,37 @@ extern "C" void* vr_host_alloc(size_t bytes) {
 }
 extern "C" void vr_host_free(void* p) { if (p) cudaFreeHost(p); }
 
+// GB/s at which the texture path streams the resident one-channel TEXTURE-layout volume out of DRAM when every texel is read
+// exactly once (tex_stream_kernel; L2 flushed before every repetition): the ceiling of a march whose fetches are all first
+// touches (C4 at 128 steps)
+extern "C" vr_status vr_measure_tex_stream(vr_context* c, float* gbs) {
+    if (!c) return VR_ERR_INVALID_ARGUMENT;
+    if (!gbs) return fail(c, VR_ERR_INVALID_ARGUMENT, "vr_measure_tex_stream: null output");
+    if (!c->has_volume || !c->tex || c->vdesc.format == VR_VOL_RGBA8_UNORM || c->vdesc.layout != VR_LAYOUT_TEXTURE)
+        return fail(c, VR_ERR_BAD_STATE, "vr_measure_tex_stream: needs a resident one-channel volume in the TEXTURE layout");
+    VR_CUDA(c, cudaSetDevice(c->device));
+    cudaEvent_t e0, e1;
+    VR_CUDA(c, cudaEventCreate(&e0));
+    VR_CUDA(c, cudaEventCreate(&e1));
+    float best = 0.0f;
+    const double bytes = (double)c->lin_bytes;
+    for (int rep = 0; rep < 6; ++rep) {
+        vr_status st = vr_flush_l2(c);
+        cudaError_t e = st == VR_OK ? cudaEventRecord(e0, c->stream) : cudaErrorUnknown;
+        if (e == cudaSuccess) e = launch_tex_stream(c->tex, (int)c->vdesc.width, (int)c->vdesc.height, (int)c->vdesc.depth, (float*)c->d_counters, c->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(e1, c->stream);
+        if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+        if (e != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return fail(c, VR_ERR_CUDA, "tex_stream", e); }
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const float g = (float)(bytes / (ms * 1e-3) / 1e9);
+        if (rep >= 1 && g > best) best = g;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *gbs = best;
+    return VR_OK;
+}
+
 // peaks[0] = FP32 FMA TFLOP/s (FMA = 2 flop); peaks[1] = trilinear RGBA8 texture fetches, G/s
 // (needs a TEXTURE-layout volume, else 0); peaks[2] = SM count; peaks[3] = SM clock MHz (max).
 extern "C" vr_status vr_measure_peaks(vr_context* c, float* peaks4) {

@@ -160,6 +160,7 @@ cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_
 // ---- peak_kernels.cu: measured roofline denominators
 cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_tex_peak(cudaTextureObject_t tex, float* sink, int blocks, int iters, cudaStream_t s);
+cudaError_t launch_tex_stream(cudaTextureObject_t tex, int nx, int ny, int nz, float* sink, cudaStream_t s);
 // ---- min-max pyramid (noise_kernels.cu; layout in include/volrt.h)
 // level 0 from the texels: out[brick][channel][{min,max}]
 cudaError_t launch_pyramid_base(const void* lin, int vol_format, int w, int h, int d, float* out, int bx, int by, int bz, cudaStream_t s);

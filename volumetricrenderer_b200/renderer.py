@@ -270,6 +270,12 @@ class Renderer:
         self._check(self._lib.vr_measure_peaks(self._ctx, out))
         return {"fp32_tflops": out[0], "tex_gfetch": out[1], "sms": int(out[2]), "sm_max_mhz": out[3]}
 
+    def measure_tex_stream(self):
+        """GB/s of the texture path streaming the resident one-channel volume out of DRAM once (vr_measure_tex_stream)"""
+        g = C.c_float()
+        self._check(self._lib.vr_measure_tex_stream(self._ctx, C.byref(g)))
+        return g.value
+
     def stats(self):
         s = capi.vr_stats()
         s.struct_size = C.sizeof(capi.vr_stats)
