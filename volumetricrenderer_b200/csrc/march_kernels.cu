@@ -971,6 +971,135 @@ static cudaError_t launch_split(const MarchParams& p, int split, int rows, int n
     return cudaGetLastError();
 }
 
+// (d') compositing march over a texture-filtered one-channel grid with RAY COMPACTION (north_star: "early-ray termination with
+// warp-vote (__ballot_sync) compaction").  With early termination and empty-space leaping the rays of a warp end at very
+// different times (C5: 25 of 32 lanes busy per issued instruction, profiles/r02_march_c5_viewgroup4.txt), and the kernel is
+// issue-bound.  The refill scheme of round 1 (idle lanes take NEW pixels) put rays of unrelated depth into one warp and lost
+// 2.5x to scattered fetches.  Here the unit is the CTA's own 16x8-pixel tile: every COMPACT_ROUND loop iterations the CTA
+// counts its live rays; when a whole warp's worth of lanes has fallen idle, the live rays are ranked with __ballot_sync,
+// written to shared memory and re-dealt to the lowest warps.  The rays of a warp still come from one screen tile and sit at
+// neighbouring depths, so their fetches stay coherent; emptied warps only attend the CTA's barriers.  The loop body is the
+// batched body of march_pixel (same leaps, same two fetches in flight, same early-termination test): the frame is identical.
+#ifndef VOLRT_COMPACT_DEFAULT
+#define VOLRT_COMPACT_DEFAULT 0
+#endif
+#ifndef VOLRT_COMPACT_ROUND
+#define VOLRT_COMPACT_ROUND 8
+#endif
+struct CompactRay {                 // what a ray carries from lane to lane: 15 words
+    f3 p, step;
+    float T, cr, cg, cb, leap_k, leap_e;
+    int i, n;
+    unsigned int pix;               // py << 16 | px
+};
+template <int VARIANT>
+__global__ void __launch_bounds__(128, 10) march_compact_kernel(const __grid_constant__ MarchParams P) {
+    __shared__ CompactRay pool[128];
+    __shared__ int warp_live[4];
+    int tx, ty, vin = 0;
+    int view = P.view_begin + blockIdx.z;
+    if (P.view_group > 1) {
+        tile_of_cta(P, 8, tx, ty, P.view_group, &vin);
+        view = P.view_begin + (int)blockIdx.z * P.view_group + vin;
+        if (view >= P.view_begin + P.n_views) return;           // CTA-uniform
+    } else tile_of_cta(P, 8, tx, ty);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
+    const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
+    const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
+    const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);
+    const bool skip = P.skip_empty != 0;
+    const bool et = P.early_term_eps > 0.0f;
+    const RayConst rc = {};                                      // one-channel grids take no scroll offsets
+    CompactRay r;
+    r.T = 1.0f; r.cr = r.cg = r.cb = 0.0f; r.i = 0; r.n = 0; r.leap_k = r.leap_e = 0.0f;
+    r.pix = ((unsigned)py << 16) | (unsigned)px;
+    bool live = false;
+    if (px < P.width && py < P.row_end) {
+        Ray ray;
+        if (setup_ray(P, V, px, py, step_size, ray)) {
+            r.p = ray.pin; r.step = ray.step; r.n = ray.n;
+            if (skip) { const Leap L = leap_setup(P, ray.step); r.leap_k = L.k; r.leap_e = L.e; }
+            live = ray.n > 0;
+            if (!live) store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);
+        } else {
+            store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);                      // VulkanRenderPass.cpp:17-19
+        }
+    }
+    int slots = 128;                                             // lanes of the warps that still hold rays
+    for (;;) {
+        for (int round = 0; round < VOLRT_COMPACT_ROUND && live; ++round) {
+            bool finished = false;
+            int bd = 0;
+            if (skip) bd = brick_distance_fast(P, r.p);
+            if (bd) {
+                const Leap L = {r.leap_k, r.leap_e};
+                const float fm = (float)(leap_steps(L, bd, r.n - 1 - r.i) + 1);
+                r.p = {fmaf(fm, r.step.x, r.p.x), fmaf(fm, r.step.y, r.p.y), fmaf(fm, r.step.z, r.p.z)};
+                r.i += (int)fm;
+            } else {
+                constexpr int CB = VOLRT_COMPOSITE_BATCH;
+                const int nb = min(CB, r.n - r.i);
+                float d[CB];
+                f3 q = r.p;
+#pragma unroll
+                for (int k = 0; k < CB; ++k) {
+                    d[k] = 0.0f;
+                    if (k < nb) { d[k] = density_at<VARIANT>(P, rc, nullptr, nullptr, q); q = add3(q, r.step); }
+                }
+#pragma unroll
+                for (int k = 0; k < CB; ++k) {
+                    if (k < nb && !finished) {
+                        const float rho = d[k];
+                        if (rho > 0.0f) {
+                            const float a = 1.0f - expf(-P.sigma_t * rho * step_size);
+                            const float w = r.T * a;
+                            r.cr = fmaf(w, P.sun_color[0] + P.ambient, r.cr);
+                            r.cg = fmaf(w, P.sun_color[1] + P.ambient, r.cg);
+                            r.cb = fmaf(w, P.sun_color[2] + P.ambient, r.cb);
+                            r.T *= 1.0f - a;
+                        }
+                        r.p = add3(r.p, r.step);
+                        if (et && r.T < P.early_term_eps) finished = true;
+                    }
+                }
+                r.i += nb;
+            }
+            if (finished || r.i >= r.n) {
+                store_pixel(P, view, (int)(r.pix & 0xffffu), (int)(r.pix >> 16), r.cr, r.cg, r.cb, 1.0f);
+                live = false;
+            }
+        }
+        const int total = __syncthreads_count(live);
+        if (total == 0) return;
+        if (total <= slots - 32) {
+            // a warp's worth of lanes is idle: rank the live rays (ballot within the warp, counts across warps) and re-deal them
+            const unsigned int ballot = __ballot_sync(0xffffffffu, live);
+            if (lane == 0) warp_live[warp] = __popc(ballot);
+            __syncthreads();
+            int base = 0;
+            for (int w = 0; w < warp; ++w) base += warp_live[w];
+            if (live) pool[base + __popc(ballot & ((1u << lane) - 1u))] = r;
+            __syncthreads();
+            live = tid < total;
+            if (live) r = pool[tid];
+            slots = (total + 31) & ~31;
+            __syncthreads();                                     // pool and warp_live are rewritten by the next compaction
+        }
+    }
+}
+template <int VARIANT>
+static cudaError_t launch_compact(const MarchParams& p_in, int rows, int n_views, cudaStream_t s) {
+    MarchParams p = p_in;
+    dim3 grid((p.width + 15) / 16, (rows + 7) / 8, n_views);
+    if (p.view_group > 1) {
+        grid.x *= p.view_group;
+        grid.z = (grid.z + p.view_group - 1) / p.view_group;
+    }
+    march_compact_kernel<VARIANT><<<grid, 128, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
 // (e) TMA-staged brick march (VR_LAYOUT_BRICK, one-channel fp16 grids, reference integrator).
 // A CTA owns a 16x8-pixel tile and walks it through the volume in slabs of K steps.  For each slab it
 // takes the bounding box (in voxels) of every tap its rays will touch, has ONE thread fetch that box with
@@ -1244,6 +1373,12 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     // schedule: 0 = direct tiles, 1 = persistent warps, -1 = auto
     bool persistent = p.schedule > 0;    // auto = direct: the queue did not pay off on B200 (measurements)
     if (!p.queue) persistent = false;
+    // ray compaction (march_compact_kernel): early-terminating compositing march over a one-channel texture grid, no light-march
+    if (composite && !stats && !persistent && variant == MARCH_SINGLE_TEX && p.early_term_eps > 0.0f && p.light_steps == 0) {
+        static const int env_compact = [] { const char* e = getenv("VOLRT_COMPACT"); return e ? atoi(e) : -1; }();
+        const bool use = env_compact >= 0 ? env_compact != 0 : VOLRT_COMPACT_DEFAULT != 0;
+        if (use && launch_waves(p, rows, n_views) >= 3.0) return launch_compact<MARCH_SINGLE_TEX>(p, rows, n_views, stream);
+    }
     // ray split of the compositing integrator (any density source; not with device counters)
     if (composite && !stats && !persistent) {
         int split = p.ray_split_composite;
