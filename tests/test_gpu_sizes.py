@@ -300,3 +300,23 @@ def test_c5_at_its_stated_size_against_the_oracle(oracle):
         worst = max(worst, max_abs8(got, ref8))
         psnrs.append(psnr8(got, ref8))
     assert worst <= 2 and min(psnrs) >= 50.0, (worst, psnrs)
+
+
+def test_ray_compaction_kernel_gives_the_same_frame(monkeypatch):
+    """VOLRT_COMPACT=1: the early-terminating grid march with ballot-ranked re-dealing of live rays inside a CTA's tile
+    (march_compact_kernel; measured slower than the plain mapping, so not the default).  Same loop body, same positions:
+    the frames are identical."""
+    W, H, NV = 480, 270, 4
+    views = scene.orbit_views(64)[::16][:NV]
+    kw = dict(density_mode=1, max_steps=256, sample_scale=1.0, sigma_t=400.0, ambient=1.0, sun_color=[0.0, 0.0, 0.0], skip_empty=1,
+              early_term_eps=1.0 / 512)
+    frames = {}
+    monkeypatch.setenv("VOLRT_RAY_SPLIT_COMPOSITE", "1")      # one thread per ray in the plain mapping too (a frame this small would get two lanes)
+    with vr.Renderer(W, H, capi.OUT_RGBA32F, max_views=NV) as r:
+        r.generate_volume(size=256, format=capi.VOL_R16F, layout=capi.LAYOUT_TEXTURE, threshold=0.07)
+        r.set_params(view_ubos=views, **kw)
+        for knob in ("0", "1"):
+            monkeypatch.setenv("VOLRT_COMPACT", knob)
+            frames[knob] = r.render().copy()
+    assert frames["0"][..., :3].max() > 0.5
+    assert np.array_equal(frames["0"].view(np.uint32), frames["1"].view(np.uint32))

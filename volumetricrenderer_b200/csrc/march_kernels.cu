@@ -980,11 +980,17 @@ static cudaError_t launch_split(const MarchParams& p, int split, int rows, int n
 // written to shared memory and re-dealt to the lowest warps.  The rays of a warp still come from one screen tile and sit at
 // neighbouring depths, so their fetches stay coherent; emptied warps only attend the CTA's barriers.  The loop body is the
 // batched body of march_pixel (same leaps, same two fetches in flight, same early-termination test): the frame is identical.
+// MEASURED, and NOT the default (VOLRT_COMPACT=1 selects it): C5 7.23 ms against 6.02 ms for the plain mapping, and the lanes
+// busy per instruction do not move (25.0 of 32 either way, profiles/r02_c5_compaction.txt vs r02_march_c5_viewgroup4.txt).
+// The idle lanes of this march are not finished rays: they are lanes that LEAP over empty bricks while their neighbours
+// fetch (and lanes whose sample is exactly zero while the neighbours composite) — divergence inside an iteration, which
+// re-dealing rays between warps cannot remove.  What the re-dealing costs is real: 2.4 barrier stalls per issue, the four
+// warps of a CTA forced into step every 32 iterations, issue-active 73 -> 59 %.
 #ifndef VOLRT_COMPACT_DEFAULT
 #define VOLRT_COMPACT_DEFAULT 0
 #endif
 #ifndef VOLRT_COMPACT_ROUND
-#define VOLRT_COMPACT_ROUND 8
+#define VOLRT_COMPACT_ROUND 32
 #endif
 struct CompactRay {                 // what a ray carries from lane to lane: 15 words
     f3 p, step;
@@ -1375,9 +1381,10 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     if (!p.queue) persistent = false;
     // ray compaction (march_compact_kernel): early-terminating compositing march over a one-channel texture grid, no light-march
     if (composite && !stats && !persistent && variant == MARCH_SINGLE_TEX && p.early_term_eps > 0.0f && p.light_steps == 0) {
-        static const int env_compact = [] { const char* e = getenv("VOLRT_COMPACT"); return e ? atoi(e) : -1; }();
+        const char* env = getenv("VOLRT_COMPACT");               // 1 = use it whatever the size, 0 = never; unset = the default below
+        const int env_compact = env ? atoi(env) : -1;
         const bool use = env_compact >= 0 ? env_compact != 0 : VOLRT_COMPACT_DEFAULT != 0;
-        if (use && launch_waves(p, rows, n_views) >= 3.0) return launch_compact<MARCH_SINGLE_TEX>(p, rows, n_views, stream);
+        if (use && (env_compact > 0 || launch_waves(p, rows, n_views) >= 3.0)) return launch_compact<MARCH_SINGLE_TEX>(p, rows, n_views, stream);
     }
     // ray split of the compositing integrator (any density source; not with device counters)
     if (composite && !stats && !persistent) {
