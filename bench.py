@@ -266,8 +266,10 @@ def run_volrt(args, rank, world, local):
         # BASELINE.json configs[2] (4K, 256 + 8) on the same record, at every N: the configuration north_star wants
         # "near-linear" on.  Fewer frames (a 4K frame is ~10x the work), same timing rules.
         extra = measure_workload(args, "c3", rank, world, local, dist, max(5, args.steps // 3), full=False)
+        # BASELINE.json configs[4] (64 views over a 1024^3 fp16 grid, skipping + early termination, views sharded over the GPUs)
+        extra5 = measure_views(args, rank, world, local, dist, max(3, args.steps // 6))
         if rank == 0:
-            line["extra"] = {"c3": extra}
+            line["extra"] = {"c3": extra, "c5": extra5}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -490,22 +492,32 @@ def measure_workload(args, workload, rank, world, local, dist, K, full):
 
 
 def run_views(args, rank, world, local):
-    """C5: a batch of independent views, sharded contiguously over the ranks (no exchange: every rank delivers its own
-    views).  value = W*H*views / max-over-ranks device time."""
-    import volumetricrenderer_b200 as vr
-    from volumetricrenderer_b200 import capi, scene, multigpu
     dist = None
     if world > 1:
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    W, H, desc, kw = WORKLOADS[args.workload]
-    K, Wm = args.steps, max(args.warmup, 3)
+    line = measure_views(args, rank, world, local, dist, args.steps)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def measure_views(args, rank, world, local, dist, K):
+    """C5: a batch of independent views, sharded contiguously over the ranks — or, with --single-process, over the devices of
+    one group context (no exchange: every GPU stores its own views).  value = W*H*views / max-over-GPUs device time."""
+    import volumetricrenderer_b200 as vr
+    from volumetricrenderer_b200 import capi, scene, multigpu
+    group = args.single_process and args.gpus > 1 and world == 1
+    n_gpus = args.gpus if group else world
+    W, H, desc, kw = WORKLOADS["c5"]
+    Wm = max(args.warmup, 3)
     v0, v1 = multigpu.shard_views(C5_VIEWS, world)[rank]
     nv = v1 - v0
     views = scene.orbit_views(C5_VIEWS)[v0:v1]
-    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local, max_views=max(nv, 1))
+    r = vr.Renderer(W, H, capi.OUT_RGBA8_UNORM, device=local, max_views=max(nv, 1), devices=list(range(args.gpus)) if group else None)
     grid = int(os.environ.get("VOLRT_C5_GRID", C5_GRID))
     r.generate_volume(size=grid, format=capi.VOL_R16F, layout=capi.LAYOUT_TEXTURE, threshold=C5_THRESHOLD)
     vol_bytes = grid ** 3 * 2
@@ -559,30 +571,30 @@ def run_views(args, rank, world, local):
         e2e_step(i)
     barrier()
     e2e_s = (time.perf_counter() - t0) / K
+    line = None
     if rank == 0:
         covered, steps, early, skipped = (int(x) for x in counts)
         peaks = r.measure_peaks()
         t = ms_per_step * 1e-3
         fetches = steps - skipped
-        line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+        line = {"metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": K, "warmup": Wm,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
-                "config": {"workload": "%s: %s" % (args.workload, desc), "width": W, "height": H, "views": C5_VIEWS, "grid": grid,
+                "config": {"workload": "c5: %s" % desc, "width": W, "height": H, "views": C5_VIEWS, "grid": grid,
                            "l2": "flushed between batches; the %d MiB grid exceeds L2" % (vol_bytes >> 20),
-                           "partition": "contiguous view shards, no exchange"},
+                           "partition": ("contiguous view shards over the devices of one context, peer stores into GPU0's frames" if group
+                                         else "contiguous view shards, no exchange")},
                 "e2e": {"value": W * H * C5_VIEWS / e2e_s / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_s * 1e3, "frames_in_flight": 2,
                         "h2d_bytes_per_step": 336 * C5_VIEWS, "d2h_bytes_per_step": W * H * 4 * C5_VIEWS},
                 "gpu_launches": K, "clocks": clocks, "covered_rays": covered, "steps_per_frame": steps,
                 "early_terminated_frac": early / max(covered, 1), "skipped_step_frac": skipped / max(steps, 1),
-                "roofline": {"bound": "tex", "achieved": fetches / t / 1e9, "peak": peaks["tex_gfetch"] * world, "unit": "Gfetch/s",
-                             "frac": fetches / t / 1e9 / (peaks["tex_gfetch"] * world) if peaks["tex_gfetch"] else None,
+                "roofline": {"bound": "tex", "achieved": fetches / t / 1e9, "peak": peaks["tex_gfetch"] * n_gpus, "unit": "Gfetch/s",
+                             "frac": fetches / t / 1e9 / (peaks["tex_gfetch"] * n_gpus) if peaks["tex_gfetch"] else None,
                              "note": "fetches = steps not skipped by the brick grid, before early termination (upper bound of the executed ones)",
                              "traffic": None, "peaks_measured_here": peaks}}
-        print(json.dumps(line), flush=True)
     barrier()
     r.close()
-    if dist is not None:
-        dist.destroy_process_group()
+    return line
 
 
 def time_cpu_bake(repeats):
