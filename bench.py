@@ -190,6 +190,25 @@ def time_oracle(workload, target_seconds, threads=0):
     """Oracle on a bounded strided row sample -> dict(value Mrays/s, cores, sample, seconds)."""
     from oracle import oracle
     W, H, _, _ = WORKLOADS[workload]
+    if workload == "c1" and oracle.have_ref_glsl():
+        # config 1 has reference semantics, and the reference's own shaders compile here (oracle/glsl_shim.h): time THEM —
+        # vert.glsl -> fixed-function rasteriser (oracle/ref_raster.cpp) -> frag.glsl on the reference's own FastNoise2 bake
+        from volumetricrenderer_b200 import scene
+        u0, u1 = scene.default_scene()
+        vol = oracle.ref_bake_default(128)[0]
+        cores = threads or oracle.lib().vo_hw_threads()
+        oracle.ref_draw(u0, u1, vol, W, H, threads)          # warm the pages
+        reps, t0 = 0, time.perf_counter()
+        while True:
+            _img, cov, _fp = oracle.ref_draw(u0, u1, vol, W, H, threads)
+            reps += 1
+            dt = time.perf_counter() - t0
+            if dt >= min(target_seconds, 20.0) or reps >= 200:
+                break
+        return {"value": reps * W * H / dt / 1e6, "unit": "Mrays/s", "cores": int(cores), "kind": "reference",
+                "sample": "%d whole %dx%d frames of the reference's vert.glsl + frag.glsl compiled as C++ (oracle/_ref), %.2f s, %d covered px per frame"
+                          % (reps, W, H, dt, int(cov.sum())),
+                "seconds": dt, "msamples_per_s": None}
     p = oracle_params_for(workload)
     vol, keep = oracle_volume_for(workload)
     cores = threads or oracle.lib().vo_hw_threads()
@@ -233,7 +252,7 @@ def run_reference(args, rank, world):
         "config": config_for(args.workload, max(1, args.gpus), args.layout, args.workload == "c1" or args.workload.startswith("c4"),
                              args.single_process),
         "note": "ms_per_step = full-frame time extrapolated from the timed row sample; the CPU arm runs on rank 0's host cores whatever --gpus says",
-        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": last["cores"], "kind": "port", "sample": last["sample"]},
+        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": last["cores"], "kind": last["kind"], "sample": last["sample"]},
         "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "sample_seconds": secs,
     }
