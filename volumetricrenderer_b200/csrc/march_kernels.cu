@@ -662,6 +662,21 @@ struct __align__(256) MarchSmem {
     float unorm[LINEAR ? 256 : 1];     // LINEAR variants: i / 255
 };
 
+// The fBm kernels fetch gradients at an IMMEDIATE shared address (noise_device.cuh: GradLutFixed): the first static __shared__
+// object of a kernel sits at window address VOLRT_LUT_FIXED_ADDR on this toolchain and driver.  That is an observation, not
+// a guarantee, so it is checked where a failure is an error code instead of a trap (a trap is sticky and takes the host
+// application's CUDA context with it): this probe has the march kernels' shared layout and reports where the table landed.
+__global__ void lut_address_probe_kernel(unsigned int* out) {
+    __shared__ MarchSmem<false> smem;
+    smem.lut.g[threadIdx.x & 15].x = 0.0f;             // keep the object
+    if (threadIdx.x == 0) out[0] = (unsigned int)__cvta_generic_to_shared(&smem.lut);
+}
+cudaError_t march_probe_lut_address(unsigned int* d_out, cudaStream_t s) {
+    lut_address_probe_kernel<<<1, 32, 0, s>>>(d_out);
+    return cudaGetLastError();
+}
+unsigned int march_lut_fixed_address() { return (unsigned int)VOLRT_LUT_FIXED_ADDR; }
+
 template <int VARIANT>
 __device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);

@@ -97,6 +97,7 @@ struct vr_context {
     int queue_chunk = 1;
     int ray_split = -1;                // lanes per ray (texture march): -1 auto
     int ray_split_composite = -1;      // lanes per ray (compositing march): -1 auto
+    int lut_addr_ok = -1;              // -1 not probed yet; fBm kernels fetch their gradient table at an immediate shared address
     int ray_segments = -1;             // depth segments per ray (compositing march): -1 auto
     int sm_count = 0;
     float4* d_seg_partials = nullptr;  // depth-segment scratch (MarchParams::seg_partials), grow-only
@@ -1168,6 +1169,17 @@ static vr_status fill_march_params(vr_context* c, MarchParams& m, int& variant) 
     m.ray_segments = c->ray_segments;
     m.sm_count = c->sm_count;
     if (p.density_mode == VR_DENSITY_FBM) {
+        if (c->lut_addr_ok < 0) {            // once per context: is the gradient table where the fBm kernels fetch it?
+            unsigned int got = 0;
+            cudaError_t e = march_probe_lut_address((unsigned int*)c->d_counters + 14, c->stream);
+            if (e == cudaSuccess) e = cudaMemcpyAsync(&got, (unsigned int*)c->d_counters + 14, sizeof got, cudaMemcpyDeviceToHost, c->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+            if (e != cudaSuccess) return fail(c, VR_ERR_CUDA, "vr_render: gradient-table address probe", e);
+            c->lut_addr_ok = got == march_lut_fixed_address() ? 1 : 0;
+        }
+        if (!c->lut_addr_ok)
+            return fail(c, VR_ERR_UNSUPPORTED, "vr_render: this toolchain / driver places static shared memory elsewhere than the fBm kernels "
+                                                "assume (rebuild libvolrt with -DVOLRT_LUT_FIXED_ADDR=<address>); VR_DENSITY_TREE renders the same field");
         variant = MARCH_FBM;
         if (c->fbm_cells_ok) { m.cells = c->fbm_cells; variant = MARCH_FBM_CELLS; }
         return VR_OK;

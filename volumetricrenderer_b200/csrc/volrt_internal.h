@@ -132,6 +132,10 @@ constexpr size_t kGatherMailboxBytes = 256;    // behind the context's frames: c
 
 // launches one march over rows [row_begin,row_end) x views; returns cudaGetLastError()
 cudaError_t launch_march(const MarchParams& p, int variant, int n_views, bool stats, cudaStream_t stream);
+// where the march kernels' gradient table lands in the shared window (one word written to d_out), and where the fBm kernels
+// expect it: the host checks the two agree before the first procedural render (an error code instead of a device trap)
+cudaError_t march_probe_lut_address(unsigned int* d_out, cudaStream_t s);
+unsigned int march_lut_fixed_address();
 // how many depth segments (MarchParams::segments) this launch should use: 1 = none.  The caller sizes seg_partials / seg_arrived
 // for rows x width x views x segments before it launches.
 int march_pick_segments(const MarchParams& p, int variant, int n_views, bool stats);
