@@ -287,8 +287,17 @@ def run_volrt(args, rank, world, local):
         extra = measure_workload(args, "c3", rank, world, local, dist, max(5, args.steps // 3), full=False)
         # BASELINE.json configs[4] (64 views over a 1024^3 fp16 grid, skipping + early termination, views sharded over the GPUs)
         extra5 = measure_views(args, rank, world, local, dist, max(3, args.steps // 6))
+        # BASELINE.json configs[0]: the reference's own scene and shader semantics (1280x720, baked 128^3 RGBA8 volume); its CPU
+        # baseline is the reference's shaders compiled as C++ (kind "reference")
+        extra1 = measure_workload(args, "c1", rank, world, local, dist, args.steps, full=False)
         if rank == 0:
-            line["extra"] = {"c3": extra, "c5": extra5}
+            if world == 1 and not args.no_cpu_baseline:
+                try:
+                    cb = time_oracle("c1", min(args.cpu_seconds, 5.0))
+                    extra1["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+                except Exception as e:
+                    extra1["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "reference", "sample": "failed: %r" % (e,)}
+            line["extra"] = {"c1": extra1, "c3": extra, "c5": extra5}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if dist is not None:
