@@ -97,21 +97,11 @@ __device__ __forceinline__ unsigned int grad_lut_offset8(int t);
 #endif
 struct GradLutFixed {};     // tag type: "the table is at VOLRT_LUT_FIXED_ADDR"
 
-#ifndef VOLRT_HASH_SHIFT_ON_FMA
-#define VOLRT_HASH_SHIFT_ON_FMA 0
-#endif
 __device__ __forceinline__ unsigned int grad_lut_offset(int t) {
     const unsigned int h16 = (unsigned int)t * (0x27d4eb2du << 4);     // = h << 4 (mod 2^32)
-#if VOLRT_HASH_SHIFT_ON_FMA
-    // h16 >> 15 as the high word of h16 * 2^17: an IMAD.HI on the FMA pipe instead of a SHF on the (half-rate) ALU pipe.
-    // Measured on B200: slower (C2 1.769 -> 1.936 ms, C3 17.17 -> 18.95) — IMAD.HI costs more than the shift it replaces.
-    unsigned int k, sh;
-    asm("mov.u32 %0, 0x20000;" : "=r"(k));
-    asm("mul.hi.u32 %0, %1, %2;" : "=r"(sh) : "r"(h16), "r"(k));
-    return (h16 ^ sh) & 0xF0u;
-#else
+    // (h16 >> 15 as the high word of h16 * 2^17 — an IMAD.HI on the FMA pipe instead of a shift on the half-rate ALU pipe — was
+    // measured in round 1: C2 1.769 -> 1.936 ms; not kept)
     return (h16 ^ (h16 >> 15)) & 0xF0u;
-#endif
 }
 __device__ __forceinline__ unsigned int grad_lut_offset8(int t) { return grad_lut_offset(t) >> 1; }
 // what a cell-table byte holds (grad_lut_at)
@@ -237,11 +227,8 @@ __device__ __forceinline__ float cellular3(int seed, float x, float y, float z) 
     return best;
 }
 
-// Unrolling the one-point routine as well (it serves the primary sample) was measured slower: C2 1.733 -> 1.80 ms, C3 16.87 -> 17.19 ms
-// (three unrolled copies of the octave body in one kernel, spills under the 128-register cap).  Off.
-#ifndef VOLRT_FBM_UNROLL_SCALAR
-#define VOLRT_FBM_UNROLL_SCALAR 0
-#endif
+// (Unrolling this one-point routine of the HASH variant at five octaves was measured slower in round 1 — C2 1.733 -> 1.80 ms,
+// spills under the 128-register cap; the cell-table variant below does unroll its one-point routine.)
 template <int OCT, class LUT>
 __device__ __forceinline__ float fbm_perlin_n(LUT lut, const FbmField& F, float x, float y, float z) {
     const int n = OCT > 0 ? OCT : F.octaves;
@@ -259,7 +246,6 @@ __device__ __forceinline__ float fbm_perlin_n(LUT lut, const FbmField& F, float 
 }
 template <class LUT>
 __device__ __forceinline__ float fbm_perlin(LUT lut, const FbmField& F, float x, float y, float z) {
-    if (VOLRT_FBM_UNROLL_SCALAR > 0 && F.octaves == VOLRT_FBM_UNROLL_SCALAR) return fbm_perlin_n<VOLRT_FBM_UNROLL_SCALAR>(lut, F, x, y, z);
     return fbm_perlin_n<0>(lut, F, x, y, z);
 }
 
@@ -322,37 +308,21 @@ __device__ __forceinline__ f2 grad_edge_lut2(LUT lut, int tA0, int tA1, int tB0,
     return fma2(s, e, d0);
 }
 
-#ifndef VOLRT_FBM_FLOOR_MODE
-#define VOLRT_FBM_FLOOR_MODE 1
-#endif
 template <class LUT>
 __device__ __forceinline__ f2 perlin3_lut2(LUT lut, int seed, f2 x, f2 y, f2 z) {
-#if VOLRT_FBM_FLOOR_MODE == 0
-    const float xsA = floorf(f2_a(x)), xsB = floorf(f2_b(x)), ysA = floorf(f2_a(y)), ysB = floorf(f2_b(y)), zsA = floorf(f2_a(z)), zsB = floorf(f2_b(z));
-    f2 xs = make_f2(xsA, xsB), ys = make_f2(ysA, ysB), zs = make_f2(zsA, zsB);
-    const int ax0 = __float2int_rn(xsA) * kPrimeX, ay0 = __float2int_rn(ysA) * kPrimeY, az0 = __float2int_rn(zsA) * kPrimeZ;
-    const int bx0 = __float2int_rn(xsB) * kPrimeX, by0 = __float2int_rn(ysB) * kPrimeY, bz0 = __float2int_rn(zsB) * kPrimeZ;
-#else
     // The lattice coordinate as an integer without F2I (an XU-pipe instruction, 4 lanes/clk per scheduler): for an integral
     // |v| <= 2^22 the binary32 sum v + 1.5*2^23 is exact and its bit pattern is 0x4B400000 + v, so v * prime is one IMAD
     // on those bits with the constant -0x4B400000 * prime as addend.  Coordinates beyond 2^22 have no fraction bits
     // left for a noise lattice anyway.
+    // (floor itself on the FMA pipe as rint(v - 1/2) was measured equal within noise in round 1 and slower on the cell-table
+    // variant in round 2: profiles/r02_fbm_cells_experiments.txt)
     const f2 magic = splat2(12582912.0f);
-#if VOLRT_FBM_FLOOR_MODE == 1
     f2 xs = make_f2(floorf(f2_a(x)), floorf(f2_b(x))), ys = make_f2(floorf(f2_a(y)), floorf(f2_b(y))), zs = make_f2(floorf(f2_a(z)), floorf(f2_b(z)));
     const f2 xt = add2(xs, magic), yt = add2(ys, magic), zt = add2(zs, magic);
-#else
-    // floor itself on the FMA pipe too: rint(v - 1/2) is floor(v) except that an integral v may land one cell lower with
-    // fraction exactly 1, where Perlin noise has the same value (the fade is 1 and the far corner's offset is 0)
-    const f2 mh = splat2(-0.5f);
-    const f2 xt = add2(add2(x, mh), magic), yt = add2(add2(y, mh), magic), zt = add2(add2(z, mh), magic);
-    f2 xs = sub2(xt, magic), ys = sub2(yt, magic), zs = sub2(zt, magic);
-#endif
     constexpr unsigned int kBias = 0x4B400000u;
     constexpr int kx = (int)(0u - kBias * (unsigned int)kPrimeX), ky = (int)(0u - kBias * (unsigned int)kPrimeY), kz = (int)(0u - kBias * (unsigned int)kPrimeZ);
     const int ax0 = __float_as_int(f2_a(xt)) * kPrimeX + kx, ay0 = __float_as_int(f2_a(yt)) * kPrimeY + ky, az0 = __float_as_int(f2_a(zt)) * kPrimeZ + kz;
     const int bx0 = __float_as_int(f2_b(xt)) * kPrimeX + kx, by0 = __float_as_int(f2_b(yt)) * kPrimeY + ky, bz0 = __float_as_int(f2_b(zt)) * kPrimeZ + kz;
-#endif
     const int ax1 = ax0 + kPrimeX, ay1 = ay0 + kPrimeY, az1 = az0 + kPrimeZ;
     const int bx1 = bx0 + kPrimeX, by1 = by0 + kPrimeY, bz1 = bz0 + kPrimeZ;
     const f2 xf0 = sub2(x, xs), yf0 = sub2(y, ys), zf0 = sub2(z, zs);
@@ -410,28 +380,10 @@ __device__ __forceinline__ uint2 fbm_cell_fetch(const FbmCellOctave& C, float xs
     const float t = fmaf(zs, C.n2f, fmaf(ys, C.nf, xs + C.kf));
     return __ldg(reinterpret_cast<const uint2*>(C.base_adj + (unsigned long long)__float_as_uint(t) * 8ull));
 }
-// floor() of a lattice coordinate on the FMA pipe instead of FRND (an XU-pipe instruction: 8 issue cycles per warp, three per
-// octave and point).  Coordinates are in [0, 2^22) here (inside the unit box, times frequency * lacunarity^o), so
-// x + (2^23 - 1/2) rounds — once, to nearest — to 2^23 + rint(x - 1/2), which is 2^23 + floor(x) except that an integral x
-// may land one cell lower with fraction exactly 1, where Perlin noise has the same value (fade 1, far corner's offset 0;
-// the tables keep a guard cell at -1).
-#ifndef VOLRT_CELLS_FLOOR_MAGIC
-#define VOLRT_CELLS_FLOOR_MAGIC 0
-#endif
-__device__ __forceinline__ float cell_floor(float x) {
-#if VOLRT_CELLS_FLOOR_MAGIC
-    return (x + 8388607.5f) - 8388608.0f;
-#else
-    return floorf(x);
-#endif
-}
-__device__ __forceinline__ f2 cell_floor2(f2 x) {
-#if VOLRT_CELLS_FLOOR_MAGIC
-    return sub2(add2(x, splat2(8388607.5f)), splat2(8388608.0f));
-#else
-    return make_f2(floorf(f2_a(x)), floorf(f2_b(x)));
-#endif
-}
+// (floor() on the FMA pipe instead of FRND — x + (2^23 - 1/2) rounds once to 2^23 + rint(x - 1/2) — was measured: 1.457 vs
+// 1.441 ms at C2, profiles/r02_fbm_cells_experiments.txt; the XU pipe at 20 % is not what binds.)
+__device__ __forceinline__ float cell_floor(float x) { return floorf(x); }
+__device__ __forceinline__ f2 cell_floor2(f2 x) { return make_f2(floorf(f2_a(x)), floorf(f2_b(x))); }
 __device__ __forceinline__ unsigned int cell_corner(unsigned int w, int k) { return __byte_perm(w, 0u, 0x4440u + (unsigned)k); }
 // off = the byte a cell-table entry holds for the corner: n * 16 into g[], or (VOLRT_CELLS_LDS64) n * 8 into h[].
 // Measured on B200, C2: the 8-byte entries halve the shared-memory wavefronts (306 M -> 146 M per frame) but their two
