@@ -382,10 +382,15 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
     constexpr bool TEXTURED = (VARIANT == MARCH_RGBA_TEX || VARIANT == MARCH_SINGLE_TEX);
     const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
 
+    // three quarters of a frame's pixels lie outside the cube's screen rectangle: they leave before anything is computed
+    if (px < V->rect[0] || py < V->rect[1] || px >= V->rect[2] || py >= V->rect[3]) {
+        if (seg == 0) store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);            // VulkanRenderPass.cpp:17-19
+        return;
+    }
     const float step_size = mul(dvd(1.0f, (float)P.max_steps), P.step_scale);          // frag.glsl:42
     Ray ray;
     if (!setup_ray(P, V, px, py, step_size, ray)) {
-        if (seg == 0) store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);            // VulkanRenderPass.cpp:17-19
+        if (seg == 0) store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);
         return;
     }
     RayConst rc;
@@ -649,24 +654,36 @@ __device__ __forceinline__ int outward_from(int k, int n, int c) {
 // middle first, a third of the SM time of a 1/8 band was idle (profiles/r01_band8_before.txt).
 // segs > 1 (depth segments, march_pixel): the grid's x extent is tiles x segs and the pieces of one tile are NEIGHBOURS in dispatch
 // order (piece index fastest) — as separate z slices the pieces of a frame would be dispatched one whole frame after the other
-__device__ __forceinline__ void tile_of_cta(const MarchParams& P, int tile_h, int& tx, int& ty, int segs = 1, int* seg = nullptr) {
-    const int gx = (int)gridDim.x / segs, gy = (int)gridDim.y;
+// The map's numbers come from the host (set_tile_map): as runtime divisions this prologue was ~175 instructions per warp, 15 % of
+// all the instructions of a 64-view batch, most of them in CTAs over empty tiles (ncu source page, round 2).
+__device__ __forceinline__ unsigned int fast_div(unsigned int n, unsigned int m) { return m ? __umulhi(n, m) : n; }
+__device__ __forceinline__ void tile_of_cta(const MarchParams& P, int& tx, int& ty, int* inner = nullptr) {
+    const TileMap& M = P.map;
     int kx = (int)blockIdx.x, ky = (int)blockIdx.y;
-    if (segs > 1) {
-        int lin = kx + (int)gridDim.x * ky;
-        *seg = lin % segs;
-        lin /= segs;
-        ky = lin / gx;
-        kx = lin - ky * gx;
+    if (M.inner > 1) {
+        const int q = (int)fast_div((unsigned)kx, M.div_inner);
+        if (inner) *inner = kx - q * M.inner;
+        kx = q;
     }
-    if (gy < gx) {
-        const int lin = kx + gx * ky;
-        kx = lin / gy;
-        ky = lin - kx * gy;
+    if (M.swap) {
+        const int lin = kx + M.gx * ky;
+        kx = (int)fast_div((unsigned)lin, M.div_gy);
+        ky = lin - kx * M.gy;
     }
-    const int cy = min(max((P.height / 2 - P.row_begin) / tile_h, 0), gy - 1);
-    tx = centre_out(kx, gx);
-    ty = outward_from(ky, gy, cy);
+    tx = centre_out(kx, M.gx);
+    ty = outward_from(ky, M.gy, M.cy);
+}
+static unsigned int fast_div_magic(unsigned int d) { return d <= 1 ? 0u : (unsigned int)((0x100000000ull + d - 1) / d); }
+// grid: tiles along x and y (before the inner index is folded into x); tile_h: rows of a tile
+static void set_tile_map(MarchParams& p, dim3 grid, int inner, int tile_h) {
+    TileMap& M = p.map;
+    M.gx = (int)grid.x; M.gy = (int)grid.y;
+    M.inner = inner > 1 ? inner : 1;
+    M.div_inner = fast_div_magic((unsigned)M.inner);
+    M.div_gy = fast_div_magic((unsigned)M.gy);
+    M.swap = M.gy < M.gx;
+    const int cy = (p.height / 2 - p.row_begin) / tile_h;
+    M.cy = cy < 0 ? 0 : cy > M.gy - 1 ? M.gy - 1 : cy;
 }
 
 // static shared memory of the march kernels: the gradient table first, so that it starts the CTA's shared window
@@ -737,14 +754,14 @@ __global__ void __launch_bounds__(kCtaThreads, direct_min_ctas(VARIANT, COMPOSIT
     float* const unorm = smem.unorm;
     GradLut& lut = smem.lut;
     stage_tables<VARIANT>(unorm, &lut);
-    int tx, ty, seg = 0, vin = 0;
+    int tx, ty, seg = 0, inner = 0;
     int view = P.view_begin + blockIdx.z;
-    if (COMPOSITE && !STATS && P.segments > 1) tile_of_cta(P, 4 * kCtaWy, tx, ty, P.segments, &seg);     // grid x = tiles x depth segments
-    else if (P.view_group > 1) {                                                                            // grid x = tiles x views of a group
-        tile_of_cta(P, 4 * kCtaWy, tx, ty, P.view_group, &vin);
-        view = P.view_begin + (int)blockIdx.z * P.view_group + vin;
+    tile_of_cta(P, tx, ty, &inner);
+    if (COMPOSITE && !STATS && P.segments > 1) seg = inner;      // grid x = tiles x depth segments
+    else if (P.view_group > 1) {                                 // grid x = tiles x views of a group
+        view = P.view_begin + (int)blockIdx.z * P.view_group + inner;
         if (view >= P.view_begin + P.n_views) return;
-    } else tile_of_cta(P, 4 * kCtaWy, tx, ty);
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = tx * (8 * kCtaWx) + (warp % kCtaWx) * 8 + (lane & 7);
     const int py = P.row_begin + ty * (4 * kCtaWy) + (warp / kCtaWx) * 4 + (lane >> 3);
@@ -810,7 +827,7 @@ __global__ void __launch_bounds__(128) march_tex_split_kernel(const __grid_const
     constexpr int RAYS = 32 / S;            // rays per warp
     constexpr int RW = RAYS / 2;            // warp tile = RW x 2 pixels
     int tx, ty;
-    tile_of_cta(P, 4, tx, ty);
+    tile_of_cta(P, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = lane / S, sub = lane % S;
     // CTA tile = (2*RW) x 4 pixels: warps 0,1 side by side on rows 0-1, warps 2,3 on rows 2-3
@@ -888,7 +905,7 @@ march_composite_split_kernel(const __grid_constant__ MarchParams P) {
     GradLut& lut = smem.lut;
     stage_tables<VARIANT>(unorm, &lut);
     int tx, ty;
-    tile_of_cta(P, 4, tx, ty);
+    tile_of_cta(P, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int r = lane / S, sub = lane % S;
     const int px = tx * (2 * RW) + (warp & 1) * RW + (r % RW);
@@ -979,9 +996,11 @@ march_composite_split_kernel(const __grid_constant__ MarchParams P) {
 }
 
 template <int VARIANT>
-static cudaError_t launch_composite_split(const MarchParams& p, int split, int rows, int n_views, cudaStream_t s) {
+static cudaError_t launch_composite_split(const MarchParams& p_in, int split, int rows, int n_views, cudaStream_t s) {
     const int rw = 32 / split / 2;
-    dim3 grid((p.width + 2 * rw - 1) / (2 * rw), (rows + 3) / 4, n_views);
+    dim3 grid((p_in.width + 2 * rw - 1) / (2 * rw), (rows + 3) / 4, n_views);
+    MarchParams p = p_in;
+    set_tile_map(p, grid, 1, 4);
     switch (split) {
         case 2: march_composite_split_kernel<VARIANT, 2><<<grid, 128, 0, s>>>(p); break;
         case 4: march_composite_split_kernel<VARIANT, 4><<<grid, 128, 0, s>>>(p); break;
@@ -992,9 +1011,11 @@ static cudaError_t launch_composite_split(const MarchParams& p, int split, int r
 }
 
 template <int VARIANT>
-static cudaError_t launch_split(const MarchParams& p, int split, int rows, int n_views, cudaStream_t s) {
+static cudaError_t launch_split(const MarchParams& p_in, int split, int rows, int n_views, cudaStream_t s) {
     const int rw = 32 / split / 2;
-    dim3 grid((p.width + 2 * rw - 1) / (2 * rw), (rows + 3) / 4, n_views);
+    dim3 grid((p_in.width + 2 * rw - 1) / (2 * rw), (rows + 3) / 4, n_views);
+    MarchParams p = p_in;
+    set_tile_map(p, grid, 1, 4);
     switch (split) {
         case 2: march_tex_split_kernel<VARIANT, 2><<<grid, 128, 0, s>>>(p); break;
         case 4: march_tex_split_kernel<VARIANT, 4><<<grid, 128, 0, s>>>(p); break;
@@ -1037,11 +1058,11 @@ __global__ void __launch_bounds__(128, 10) march_compact_kernel(const __grid_con
     __shared__ int warp_live[4];
     int tx, ty, vin = 0;
     int view = P.view_begin + blockIdx.z;
+    tile_of_cta(P, tx, ty, &vin);
     if (P.view_group > 1) {
-        tile_of_cta(P, 8, tx, ty, P.view_group, &vin);
         view = P.view_begin + (int)blockIdx.z * P.view_group + vin;
         if (view >= P.view_begin + P.n_views) return;           // CTA-uniform
-    } else tile_of_cta(P, 8, tx, ty);
+    }
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -1131,6 +1152,7 @@ template <int VARIANT>
 static cudaError_t launch_compact(const MarchParams& p_in, int rows, int n_views, cudaStream_t s) {
     MarchParams p = p_in;
     dim3 grid((p.width + 15) / 16, (rows + 7) / 8, n_views);
+    set_tile_map(p, grid, p.view_group, 8);
     if (p.view_group > 1) {
         grid.x *= p.view_group;
         grid.z = (grid.z + p.view_group - 1) / p.view_group;
@@ -1170,7 +1192,7 @@ __global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant_
     }
     __syncthreads();
     int tx, ty;
-    tile_of_cta(P, 8, tx, ty);
+    tile_of_cta(P, tx, ty);
     const int warp = tid >> 5, lane = tid & 31;
     const int px = tx * 16 + (warp & 1) * 8 + (lane & 7);
     const int py = P.row_begin + ty * 8 + (warp >> 1) * 4 + (lane >> 3);
@@ -1291,6 +1313,7 @@ cudaError_t launch_march_brick(const MarchParams& p_in, const void* tensor_map, 
     CUtensorMap tm;
     memcpy(&tm, tensor_map, sizeof tm);
     dim3 grid((p.width + 8 * kCtaWx - 1) / (8 * kCtaWx), (rows + 4 * kCtaWy - 1) / (4 * kCtaWy), n_views);
+    set_tile_map(p, grid, 1, 4 * kCtaWy);
     march_brick_kernel<<<grid, 128, BRICK_BYTES, stream>>>(p, tm);
     return cudaGetLastError();
 }
@@ -1317,7 +1340,8 @@ __global__ void __launch_bounds__(256) row_cost_kernel(const __grid_constant__ M
 }
 
 template <int VARIANT, bool COMPOSITE, bool STATS>
-static cudaError_t launch_one(const MarchParams& p, dim3 grid, bool persistent, cudaStream_t s) {
+static cudaError_t launch_one(const MarchParams& p_in, dim3 grid, bool persistent, cudaStream_t s) {      // grid: tiles x tiles x views
+    MarchParams p = p_in;
     if constexpr (VARIANT != MARCH_TREE) {      // a tree sample is hundreds of instructions: no queue variant is built for it
         if (persistent) {
             // resident CTAs per SM x SM count, from the occupancy calculator (registers decide)
@@ -1333,7 +1357,11 @@ static cudaError_t launch_one(const MarchParams& p, dim3 grid, bool persistent, 
             return cudaGetLastError();
         }
     }
-    if (p.view_group > 1 && p.segments <= 1) {      // grid x = tiles x views of a group, grid z = groups (march_kernel)
+    const bool segmented = COMPOSITE && !STATS && p.segments > 1;
+    if (segmented) p.view_group = 1;
+    set_tile_map(p, grid, segmented ? p.segments : p.view_group, 4 * kCtaWy);
+    if (segmented) grid.x *= p.segments;             // grid x = tiles x depth segments
+    else if (p.view_group > 1) {                     // grid x = tiles x views of a group, grid z = groups (march_kernel)
         grid.x *= p.view_group;
         grid.z = (grid.z + p.view_group - 1) / p.view_group;
     }
@@ -1383,7 +1411,6 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     if (p.segments > 1) {
         if (!composite || stats || !p.seg_partials || !p.seg_arrived ||
             (size_t)rows * p.width * n_views * p.segments > p.seg_capacity) return cudaErrorInvalidValue;
-        grid.x *= p.segments;
         switch (variant) {
             case MARCH_RGBA_TEX: return launch_one<MARCH_RGBA_TEX, true, false>(p, grid, false, stream);
             case MARCH_RGBA_LINEAR: return launch_one<MARCH_RGBA_LINEAR, true, false>(p, grid, false, stream);

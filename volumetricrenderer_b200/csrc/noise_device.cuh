@@ -105,7 +105,7 @@ __device__ __forceinline__ unsigned int grad_lut_offset(int t) {
 }
 __device__ __forceinline__ unsigned int grad_lut_offset8(int t) { return grad_lut_offset(t) >> 1; }
 // what a cell-table byte holds (grad_lut_at)
-__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t);
+__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t, int corner);
 __device__ __forceinline__ float4 grad_lut_fetch(const GradLut* lut, int t) {
     return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + grad_lut_offset(t));
 }
@@ -392,29 +392,38 @@ __device__ __forceinline__ unsigned int cell_corner(unsigned int w, int k) { ret
 #ifndef VOLRT_CELLS_LDS64
 #define VOLRT_CELLS_LDS64 0
 #endif
+// bit c set: corner c of a cell (x0y0z0, x1y0z0, x0y1z0, x1y1z0, then z1) takes the 8-byte form.  A mix relieves the
+// shared-memory pipe a little at a time: each such corner costs it 2 wavefronts instead of 4 and the issue ports 2 more slots.
+#ifndef VOLRT_CELLS_LDS64_MASK
+#define VOLRT_CELLS_LDS64_MASK (VOLRT_CELLS_LDS64 ? 0xFF : 0)
+#endif
+__host__ __device__ constexpr bool cell_corner_is64(int c) { return ((VOLRT_CELLS_LDS64_MASK) >> c) & 1; }
+template <bool W64>
 __device__ __forceinline__ float4 grad_lut_at(GradLutFixed, unsigned int off) {
-#if VOLRT_CELLS_LDS64
-    unsigned int a, b;
-    asm("ld.shared.v2.u32 {%0, %1}, [%2 + %3];" : "=r"(a), "=r"(b) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR + 256));
-    return make_float4(__uint_as_float(a), __uint_as_float(b & 0xffff0000u), __uint_as_float(b << 16), 0.0f);
-#else
-    float4 g;
-    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4 + %5];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR));
-    return g;
-#endif
+    if constexpr (W64) {
+        unsigned int a, b;
+        asm("ld.shared.v2.u32 {%0, %1}, [%2 + %3];" : "=r"(a), "=r"(b) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR + 256));
+        return make_float4(__uint_as_float(a), __uint_as_float(b & 0xffff0000u), __uint_as_float(b << 16), 0.0f);
+    } else {
+        float4 g;
+        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4 + %5];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR));
+        return g;
+    }
 }
-__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t) { return VOLRT_CELLS_LDS64 ? grad_lut_offset8(t) : grad_lut_offset(t); }
+__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t, int corner) { return cell_corner_is64(corner) ? grad_lut_offset8(t) : grad_lut_offset(t); }
+template <bool W64>
 __device__ __forceinline__ float4 grad_lut_at(const GradLut* lut, unsigned int off) {
-#if VOLRT_CELLS_LDS64
-    const uint2 v = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(lut->h) + off);
-    return make_float4(__uint_as_float(v.x), __uint_as_float(v.y & 0xffff0000u), __uint_as_float(v.y << 16), 0.0f);
-#else
-    return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
-#endif
+    if constexpr (W64) {
+        const uint2 v = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(lut->h) + off);
+        return make_float4(__uint_as_float(v.x), __uint_as_float(v.y & 0xffff0000u), __uint_as_float(v.y << 16), 0.0f);
+    } else {
+        return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
+    }
 }
-template <int I = -1, class LUT>
+// C0: the cell corner o0 belongs to (o1: C0 + 1)
+template <int C0, class LUT>
 __device__ __forceinline__ float grad_edge_at(LUT lut, unsigned int o0, unsigned int o1, float fx0, float fx1, float fy, float fz, float s) {
-    const float4 g0 = grad_lut_at(lut, o0), g1 = grad_lut_at(lut, o1);
+    const float4 g0 = grad_lut_at<cell_corner_is64(C0)>(lut, o0), g1 = grad_lut_at<cell_corner_is64(C0 + 1)>(lut, o1);
     const float d0 = fmaf(fz, g0.z, fmaf(fy, g0.y, fx0 * g0.x));
     const float e = fmaf(fz, g1.z, fmaf(fy, g1.y, fmaf(fx1, g1.x, -d0)));
     return fmaf(s, e, d0);
@@ -426,17 +435,17 @@ __device__ __forceinline__ float perlin3_cells(LUT lut, const FbmCellOctave& C, 
     float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
     float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
     xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
-    float a = lerpf(grad_edge_at<I>(lut, cell_corner(w.x, 0), cell_corner(w.x, 1), xf0, xf1, yf0, zf0, xs),
-                    grad_edge_at<I>(lut, cell_corner(w.x, 2), cell_corner(w.x, 3), xf0, xf1, yf1, zf0, xs), ys);
-    float b = lerpf(grad_edge_at<I>(lut, cell_corner(w.y, 0), cell_corner(w.y, 1), xf0, xf1, yf0, zf1, xs),
-                    grad_edge_at<I>(lut, cell_corner(w.y, 2), cell_corner(w.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    float a = lerpf(grad_edge_at<0>(lut, cell_corner(w.x, 0), cell_corner(w.x, 1), xf0, xf1, yf0, zf0, xs),
+                    grad_edge_at<2>(lut, cell_corner(w.x, 2), cell_corner(w.x, 3), xf0, xf1, yf1, zf0, xs), ys);
+    float b = lerpf(grad_edge_at<4>(lut, cell_corner(w.y, 0), cell_corner(w.y, 1), xf0, xf1, yf0, zf1, xs),
+                    grad_edge_at<6>(lut, cell_corner(w.y, 2), cell_corner(w.y, 3), xf0, xf1, yf1, zf1, xs), ys);
     return lerpf(a, b, zs);
 }
-template <int I = -1, class LUT>
+template <int C0, class LUT>
 __device__ __forceinline__ f2 grad_edge_at2(LUT lut, unsigned int oA0, unsigned int oA1, unsigned int oB0, unsigned int oB1,
                                             f2 fx0, f2 fx1, f2 fy, f2 fz, f2 s) {
-    const float4 a0 = grad_lut_at(lut, oA0), a1 = grad_lut_at(lut, oA1);
-    const float4 b0 = grad_lut_at(lut, oB0), b1 = grad_lut_at(lut, oB1);
+    const float4 a0 = grad_lut_at<cell_corner_is64(C0)>(lut, oA0), a1 = grad_lut_at<cell_corner_is64(C0 + 1)>(lut, oA1);
+    const float4 b0 = grad_lut_at<cell_corner_is64(C0)>(lut, oB0), b1 = grad_lut_at<cell_corner_is64(C0 + 1)>(lut, oB1);
     const float fyA = f2_a(fy), fyB = f2_b(fy), fzA = f2_a(fz), fzB = f2_b(fz);
     const float d0A = fmaf(fzA, a0.z, fmaf(fyA, a0.y, f2_a(fx0) * a0.x));
     const float d0B = fmaf(fzB, b0.z, fmaf(fyB, b0.y, f2_b(fx0) * b0.x));
@@ -453,10 +462,10 @@ __device__ __forceinline__ f2 perlin3_cells2(LUT lut, const FbmCellOctave& C, f2
     const f2 m1 = splat2(-1.0f);
     const f2 xf1 = add2(xf0, m1), yf1 = add2(yf0, m1), zf1 = add2(zf0, m1);
     xs = quintic2(xf0); ys = quintic2(yf0); zs = quintic2(zf0);
-    const f2 a = lerp2(grad_edge_at2<I>(lut, cell_corner(wA.x, 0), cell_corner(wA.x, 1), cell_corner(wB.x, 0), cell_corner(wB.x, 1), xf0, xf1, yf0, zf0, xs),
-                       grad_edge_at2<I>(lut, cell_corner(wA.x, 2), cell_corner(wA.x, 3), cell_corner(wB.x, 2), cell_corner(wB.x, 3), xf0, xf1, yf1, zf0, xs), ys);
-    const f2 b = lerp2(grad_edge_at2<I>(lut, cell_corner(wA.y, 0), cell_corner(wA.y, 1), cell_corner(wB.y, 0), cell_corner(wB.y, 1), xf0, xf1, yf0, zf1, xs),
-                       grad_edge_at2<I>(lut, cell_corner(wA.y, 2), cell_corner(wA.y, 3), cell_corner(wB.y, 2), cell_corner(wB.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    const f2 a = lerp2(grad_edge_at2<0>(lut, cell_corner(wA.x, 0), cell_corner(wA.x, 1), cell_corner(wB.x, 0), cell_corner(wB.x, 1), xf0, xf1, yf0, zf0, xs),
+                       grad_edge_at2<2>(lut, cell_corner(wA.x, 2), cell_corner(wA.x, 3), cell_corner(wB.x, 2), cell_corner(wB.x, 3), xf0, xf1, yf1, zf0, xs), ys);
+    const f2 b = lerp2(grad_edge_at2<4>(lut, cell_corner(wA.y, 0), cell_corner(wA.y, 1), cell_corner(wB.y, 0), cell_corner(wB.y, 1), xf0, xf1, yf0, zf1, xs),
+                       grad_edge_at2<6>(lut, cell_corner(wA.y, 2), cell_corner(wA.y, 3), cell_corner(wB.y, 2), cell_corner(wB.y, 3), xf0, xf1, yf1, zf1, xs), ys);
     return lerp2(a, b, zs);
 }
 // the compile-time octave count (C2 / C3: 5), octave by octave

@@ -153,8 +153,8 @@ __global__ void __launch_bounds__(256) fbm_cell_table_kernel(int seed, int n, ui
     const int x1 = x0 + kPrimeX, y1 = y0 + kPrimeY, z1 = z0 + kPrimeZ;
     const int sz0 = seed ^ z0, sz1 = seed ^ z1;
     uint2 e;
-    e.x = grad_lut_cell_byte(sz0 ^ x0 ^ y0) | grad_lut_cell_byte(sz0 ^ x1 ^ y0) << 8 | grad_lut_cell_byte(sz0 ^ x0 ^ y1) << 16 | grad_lut_cell_byte(sz0 ^ x1 ^ y1) << 24;
-    e.y = grad_lut_cell_byte(sz1 ^ x0 ^ y0) | grad_lut_cell_byte(sz1 ^ x1 ^ y0) << 8 | grad_lut_cell_byte(sz1 ^ x0 ^ y1) << 16 | grad_lut_cell_byte(sz1 ^ x1 ^ y1) << 24;
+    e.x = grad_lut_cell_byte(sz0 ^ x0 ^ y0, 0) | grad_lut_cell_byte(sz0 ^ x1 ^ y0, 1) << 8 | grad_lut_cell_byte(sz0 ^ x0 ^ y1, 2) << 16 | grad_lut_cell_byte(sz0 ^ x1 ^ y1, 3) << 24;
+    e.y = grad_lut_cell_byte(sz1 ^ x0 ^ y0, 4) | grad_lut_cell_byte(sz1 ^ x1 ^ y0, 5) << 8 | grad_lut_cell_byte(sz1 ^ x0 ^ y1, 6) << 16 | grad_lut_cell_byte(sz1 ^ x1 ^ y1, 7) << 24;
     entries[idx] = e;
 }
 cudaError_t launch_fbm_cell_table(int seed, int n, uint2* entries, cudaStream_t s) {

@@ -59,6 +59,15 @@ struct FbmCells {
     FbmCellOctave oct[kFbmCellMaxOctaves];
 };
 
+// blockIdx -> tile, with the divisions as multiplications by host-made reciprocals (q = umulhi(n, m), exact while n * d < 2^32;
+// m = 0 stands for d = 1)
+struct TileMap {
+    int gx, gy;                 // tiles of the launch along x and y (grid x = gx * inner)
+    int inner;                  // depth segments or views of a group folded into grid x (fastest in dispatch order); 1 = none
+    unsigned int div_inner, div_gy;
+    int swap;                   // gy < gx: the linear index runs down the columns
+    int cy;                     // tile row nearest the frame's centre row
+};
 struct MarchParams {
     // target
     int width, height;
@@ -114,6 +123,9 @@ struct MarchParams {
     // view batches: the same screen tile of `view_group` consecutive views is dispatched back to back (grid x = tiles x
     // view_group, grid z = groups), so that CTAs resident together look at the same region of a volume larger than L2
     int view_group;             // 0 / 1 = views are whole z slices
+    // how a CTA finds its tile (march_kernels.cu: tile_of_cta), filled by the launch functions (set_tile_map): every warp of
+    // every CTA runs this, and three quarters of a frame's CTAs are empty tiles that do nothing else
+    TileMap map;
 };
 constexpr int kMaxRaySegments = 8;
 
