@@ -285,11 +285,13 @@ __device__ __forceinline__ int brick_distance(const MarchParams& P, f3 p) {
 __device__ __forceinline__ int brick_distance_fast(const MarchParams& P, f3 p) {
     const BrickInfo& B = P.bricks;
     constexpr float kM = 8388607.5f;
-    constexpr int kLo = 0x4B000000;
-    const int bx = min(max(__float_as_int(fmaf(p.x, B.inv_brick[0], kM)), kLo), kLo + B.bx - 1) - kLo;
-    const int by = min(max(__float_as_int(fmaf(p.y, B.inv_brick[1], kM)), kLo), kLo + B.by - 1) - kLo;
-    const int bz = min(max(__float_as_int(fmaf(p.z, B.inv_brick[2], kM)), kLo), kLo + B.bz - 1) - kLo;
-    return (int)__ldg(B.dist + (unsigned int)((bz * B.by + by) * B.bx + bx));
+    // raw bit patterns 0x4B000000 + brick index, combined over the padded map (BrickInfo::dist_pad) and corrected once; the one
+    // clamp of the linear index keeps a NaN position inside the map (it reads some brick's byte instead of faulting)
+    const unsigned int rx = __float_as_uint(fmaf(p.x, B.inv_brick[0], kM));
+    const unsigned int ry = __float_as_uint(fmaf(p.y, B.inv_brick[1], kM));
+    const unsigned int rz = __float_as_uint(fmaf(p.z, B.inv_brick[2], kM));
+    const unsigned int idx = (rz * (unsigned)(B.by + 2) + ry) * (unsigned)(B.bx + 2) + rx - B.pad_bias;
+    return (int)__ldg(B.dist_pad + min(idx, B.pad_last));
 }
 // Empty-space leaping.  From a sample in a brick of distance d >= 2, every sample whose coordinates have moved by less
 // than (d-1) bricks on every axis still lies in an empty brick, so m = floor(min_c((d-1)*brick_c - eps) / |step_c|)
@@ -488,12 +490,39 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
         constexpr bool BATCHED = TEXTURED && !STATS && CB > 1;
         int i0 = 0;
         if constexpr (BATCHED) {
-            const bool et = P.early_term_eps > 0.0f;
-            const float kexp = -P.sigma_t * step_size * 1.4426950408889634f;         // exp(-sigma rho delta) = 2^(rho * kexp)
+            // T < eps_t ends the ray; without early termination eps_t = 0 and T, never negative, never is
+            const float eps_t = P.early_term_eps > 0.0f ? P.early_term_eps : 0.0f;
+            // exp(-sigma rho delta) = 2^(rho * kexp); the one-channel grid's sample scale is folded in (x = texel * kd), and
+            // since kexp < 0 "rho > 0" reads "x < 0" whatever the sign of the scale
+            const float kexp = -P.sigma_t * step_size * 1.4426950408889634f;
+            const float kd = VARIANT == MARCH_SINGLE_TEX ? kexp * P.sample_scale : kexp;
             const bool lit = P.light_steps > 0;
-            const float k_unlit[3] = {P.sun_color[0] + P.ambient, P.sun_color[1] + P.ambient, P.sun_color[2] + P.ambient};   // S = 1
+            auto fetch = [&](f3 at) -> float {
+                if constexpr (VARIANT == MARCH_SINGLE_TEX) return tex3D<float>(P.tex, at.x, at.y, at.z);
+                else return density_at<VARIANT>(P, rc, unorm, &lut, at);
+            };
+            // one sample: T' = T * exp(-sigma rho delta) and its weight is what the ray lost, T - T' — the same numbers as
+            // a = 1 - exp(..), w = T a, T *= 1 - a in five instructions instead of eleven (the march over a grid is issue-bound:
+            // profiles/r02_final_c5.txt)
+            auto composite = [&](float raw, f3 at) {
+                const float x = raw * kd;
+                if (x < 0.0f) {
+                    const float Tn = T * ex2_approx(x);
+                    const float w = T - Tn;
+                    if (lit) {
+                        const float S = expf(-P.sigma_t * light_sum<VARIANT>(P, rc, unorm, &lut, at, lv, skip) * P.light_step_len);
+                        cr = fmaf(w, fmaf(P.sun_color[0], S, P.ambient), cr);
+                        cg = fmaf(w, fmaf(P.sun_color[1], S, P.ambient), cg);
+                        cb = fmaf(w, fmaf(P.sun_color[2], S, P.ambient), cb);
+                    } else {
+                        cr = fmaf(w, P.unlit[0], cr); cg = fmaf(w, P.unlit[1], cg); cb = fmaf(w, P.unlit[2], cb);
+                    }
+                    T = Tn;
+                }
+            };
+            // whole batches only: no per-member bounds in the loop; the last n mod CB steps of a ray go through the loop below
             int i = 0;
-            while (i < n && !early) {
+            while (i + CB <= n) {
                 if (skip) {
                     // (A leap loop of its own in front of the fetches — so that lanes with empty bricks ahead catch up in cheap
                     // iterations and the warp meets at the fetch batch — was measured: C5 6.02 -> 7.42 ms.  The march is bound by
@@ -501,47 +530,31 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
                     // is better hidden behind its neighbours' fetches than run on its own.)
                     const int bd = VOLRT_FAST_BRICK ? brick_distance_fast(P, p) : brick_distance(P, p);
                     if (bd) {
-                        const float fm = (float)(leap_steps(leap, bd, n - 1 - i) + 1);
+                        const int m1 = leap_steps(leap, bd, n - 1 - i) + 1;
+                        const float fm = (float)m1;
                         p = {fmaf(fm, ray.step.x, p.x), fmaf(fm, ray.step.y, p.y), fmaf(fm, ray.step.z, p.z)};
-                        i += (int)fm;
+                        i += m1;
                         continue;
                     }
                 }
-                const int nb = min(CB, n - i);
                 float d[CB];
-                f3 q = p;
+                f3 q[CB + 1];
+                q[0] = p;
+#pragma unroll
+                for (int k = 0; k < CB; ++k) { d[k] = fetch(q[k]); q[k + 1] = add3(q[k], ray.step); }
+                bool stop = false;
 #pragma unroll
                 for (int k = 0; k < CB; ++k) {
-                    d[k] = 0.0f;
-                    if (k < nb) { d[k] = density_at<VARIANT>(P, rc, unorm, &lut, q); q = add3(q, ray.step); }
-                }
-#pragma unroll
-                for (int k = 0; k < CB; ++k) {
-                    if (k < nb && !early) {
-                        const float rho = d[k];
-                        if (rho > 0.0f) {
-                            // T' = T * exp(-sigma rho delta) and the sample's weight is what the ray lost, T - T': the same
-                            // numbers as a = 1 - exp(..), w = T a, T *= 1 - a in five instructions instead of eleven (the
-                            // march over a grid is issue-bound: profiles/r02_final_c5.txt)
-                            const float Tn = T * ex2_approx(rho * kexp);
-                            const float w = T - Tn;
-                            if (lit) {
-                                const float S = expf(-P.sigma_t * light_sum<VARIANT>(P, rc, unorm, &lut, p, lv, skip) * P.light_step_len);
-                                cr = fmaf(w, fmaf(P.sun_color[0], S, P.ambient), cr);
-                                cg = fmaf(w, fmaf(P.sun_color[1], S, P.ambient), cg);
-                                cb = fmaf(w, fmaf(P.sun_color[2], S, P.ambient), cb);
-                            } else {
-                                cr = fmaf(w, k_unlit[0], cr); cg = fmaf(w, k_unlit[1], cg); cb = fmaf(w, k_unlit[2], cb);
-                            }
-                            T = Tn;
-                        }
-                        p = add3(p, ray.step);
-                        if (et && T < P.early_term_eps) early = true;
+                    if (!stop) {
+                        composite(d[k], q[k]);
+                        stop = T < eps_t;
                     }
                 }
-                i += nb;
+                p = q[CB];
+                i += CB;
+                if (stop) { early = true; i = n; }
             }
-            i0 = n;
+            i0 = i;
         }
         for (int i = i0; i < n; ++i) {
             float rho = 0.0f;
@@ -1071,8 +1084,8 @@ __global__ void __launch_bounds__(128, 10) march_compact_kernel(const __grid_con
     const bool skip = P.skip_empty != 0;
     const bool et = P.early_term_eps > 0.0f;
     const RayConst rc = {};                                      // one-channel grids take no scroll offsets
-    const float kexp = -P.sigma_t * step_size * 1.4426950408889634f;
-    const float k_unlit[3] = {P.sun_color[0] + P.ambient, P.sun_color[1] + P.ambient, P.sun_color[2] + P.ambient};
+    const float kd = -P.sigma_t * step_size * 1.4426950408889634f * P.sample_scale;
+    const float eps_t = et ? P.early_term_eps : 0.0f;
     CompactRay r;
     r.T = 1.0f; r.cr = r.cg = r.cb = 0.0f; r.i = 0; r.n = 0; r.leap_k = r.leap_e = 0.0f;
     r.pix = ((unsigned)py << 16) | (unsigned)px;
@@ -1096,34 +1109,49 @@ __global__ void __launch_bounds__(128, 10) march_compact_kernel(const __grid_con
             if (skip) bd = brick_distance_fast(P, r.p);
             if (bd) {
                 const Leap L = {r.leap_k, r.leap_e};
-                const float fm = (float)(leap_steps(L, bd, r.n - 1 - r.i) + 1);
+                const int m1 = leap_steps(L, bd, r.n - 1 - r.i) + 1;
+                const float fm = (float)m1;
                 r.p = {fmaf(fm, r.step.x, r.p.x), fmaf(fm, r.step.y, r.p.y), fmaf(fm, r.step.z, r.p.z)};
-                r.i += (int)fm;
+                r.i += m1;
             } else {
+                // the arithmetic of march_pixel's compositing loops, member for member (the frames are compared bit for bit):
+                // whole batches on the 2^x form with the sample scale folded in, the last n mod CB steps on the exp form
                 constexpr int CB = VOLRT_COMPOSITE_BATCH;
-                const int nb = min(CB, r.n - r.i);
-                float d[CB];
-                f3 q = r.p;
+                if (r.i + CB <= r.n) {
+                    float d[CB];
+                    f3 q[CB + 1];
+                    q[0] = r.p;
 #pragma unroll
-                for (int k = 0; k < CB; ++k) {
-                    d[k] = 0.0f;
-                    if (k < nb) { d[k] = density_at<VARIANT>(P, rc, nullptr, nullptr, q); q = add3(q, r.step); }
-                }
+                    for (int k = 0; k < CB; ++k) { d[k] = tex3D<float>(P.tex, q[k].x, q[k].y, q[k].z); q[k + 1] = add3(q[k], r.step); }
 #pragma unroll
-                for (int k = 0; k < CB; ++k) {
-                    if (k < nb && !finished) {
-                        const float rho = d[k];
-                        if (rho > 0.0f) {
-                            const float Tn = r.T * ex2_approx(rho * kexp);
-                            const float w = r.T - Tn;
-                            r.cr = fmaf(w, k_unlit[0], r.cr); r.cg = fmaf(w, k_unlit[1], r.cg); r.cb = fmaf(w, k_unlit[2], r.cb);
-                            r.T = Tn;
+                    for (int k = 0; k < CB; ++k) {
+                        if (!finished) {
+                            const float x = d[k] * kd;
+                            if (x < 0.0f) {
+                                const float Tn = r.T * ex2_approx(x);
+                                const float w = r.T - Tn;
+                                r.cr = fmaf(w, P.unlit[0], r.cr); r.cg = fmaf(w, P.unlit[1], r.cg); r.cb = fmaf(w, P.unlit[2], r.cb);
+                                r.T = Tn;
+                            }
+                            finished = r.T < eps_t;
                         }
-                        r.p = add3(r.p, r.step);
-                        if (et && r.T < P.early_term_eps) finished = true;
                     }
+                    r.p = q[CB];
+                    r.i += CB;
+                } else {
+                    const float rho = density_at<VARIANT>(P, rc, nullptr, nullptr, r.p);
+                    if (rho > 0.0f) {
+                        const float a = 1.0f - expf(-P.sigma_t * rho * step_size);
+                        const float w = r.T * a;
+                        r.cr = fmaf(w, fmaf(P.sun_color[0], 1.0f, P.ambient), r.cr);
+                        r.cg = fmaf(w, fmaf(P.sun_color[1], 1.0f, P.ambient), r.cg);
+                        r.cb = fmaf(w, fmaf(P.sun_color[2], 1.0f, P.ambient), r.cb);
+                        r.T *= 1.0f - a;
+                    }
+                    r.p = add3(r.p, r.step);
+                    r.i += 1;
+                    if (et && r.T < P.early_term_eps) finished = true;
                 }
-                r.i += nb;
             }
             if (finished || r.i >= r.n) {
                 store_pixel(P, view, (int)(r.pix & 0xffffu), (int)(r.pix >> 16), r.cr, r.cg, r.cb, 1.0f);
@@ -1405,6 +1433,7 @@ cudaError_t launch_march(const MarchParams& p_in, int variant, int n_views, bool
     if (rows <= 0 || n_views <= 0) return cudaSuccess;
     MarchParams p = p_in;
     p.n_views = n_views;
+    for (int c = 0; c < 3; ++c) p.unlit[c] = p.sun_color[c] + p.ambient;
     dim3 grid((p.width + 8 * kCtaWx - 1) / (8 * kCtaWx), (rows + 4 * kCtaWy - 1) / (4 * kCtaWy), n_views);
     bool composite = p.sigma_t > 0.0f;
     // depth segments (march_pixel): one thread per ray and piece, grid x = tiles x pieces

@@ -269,6 +269,18 @@ cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_
     return cudaGetLastError();
 }
 
+__global__ void __launch_bounds__(256) brick_pad_kernel(const unsigned char* __restrict__ dist, unsigned char* __restrict__ pad, int bx, int by, int bz) {
+    const int px = bx + 2, py = by + 2, total = px * py * (bz + 2), idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    const int ix = min(max(idx % px - 1, 0), bx - 1), iy = min(max((idx / px) % py - 1, 0), by - 1), iz = min(max(idx / (px * py) - 1, 0), bz - 1);
+    pad[idx] = dist[((size_t)iz * by + iy) * bx + ix];
+}
+cudaError_t launch_brick_pad(const uint8_t* dist, uint8_t* pad, int bx, int by, int bz, cudaStream_t s) {
+    const int total = (bx + 2) * (by + 2) * (bz + 2);
+    brick_pad_kernel<<<(total + 255) / 256, 256, 0, s>>>(dist, pad, bx, by, bz);
+    return cudaGetLastError();
+}
+
 // ---- min-max pyramid (include/volrt.h): level 0 = per 8^3 brick incl. the one-texel apron, then 2x2x2 reductions.
 // Same traversal as the occupancy kernel: one CTA per brick row, whole texel rows read coalesced; the 8 lanes that
 // share a brick fold their values with REDUX on order-preserving bits, and three lanes per group (the leader, and

@@ -429,16 +429,24 @@ static vr_status finish_volume(vr_context* c, const vr_volume_desc& d) {
     if (!c->occupied) VR_CUDA(c, cudaMalloc(&c->occupied, (size_t)B.bx * B.by * B.bz));
     B.occupied = c->occupied;
     const size_t nbricks = (size_t)B.bx * B.by * B.bz;
-    if (!c->brick_dist) VR_CUDA(c, cudaMalloc(&c->brick_dist, 2 * nbricks));
+    const size_t npad = (size_t)(B.bx + 2) * (B.by + 2) * (B.bz + 2);
+    if (!c->brick_dist) VR_CUDA(c, cudaMalloc(&c->brick_dist, 2 * nbricks + npad));      // distance map, pass scratch, padded copy
     B.dist = c->brick_dist;
+    B.dist_pad = c->brick_dist + 2 * nbricks;
+    {
+        const unsigned long long cell = (unsigned long long)(B.by + 2) * (B.bx + 2) + (B.bx + 2) + 1;
+        B.pad_bias = (unsigned int)((0x4B000000ull - 1ull) * cell);       // mod 2^32, like the index arithmetic it corrects
+        B.pad_last = (unsigned int)(npad - 1);
+    }
     if (c->trusted_level0) VR_CUDA(c, launch_occupancy_from_pyramid(c->trusted_level0, d.format == VR_VOL_RGBA8_UNORM ? 4 : 1, c->occupied, (int)nbricks, c->stream));
     else VR_CUDA(c, launch_occupancy(c->lin, d.format, d.width, d.height, d.depth, d.address_mode, c->occupied, B.bx, B.by, B.bz, c->stream));
     VR_CUDA(c, launch_brick_distance(c->occupied, c->brick_dist, c->brick_dist + nbricks, B.bx, B.by, B.bz, c->stream));
+    VR_CUDA(c, launch_brick_pad(c->brick_dist, c->brick_dist + 2 * nbricks, B.bx, B.by, B.bz, c->stream));
     VR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
     c->foreign_stream_pending = false;
     c->stats.rays = 0;
-    c->stats.kernel_launches = c->fill_launches + 4;       // + the occupancy kernel and the 3 distance passes
+    c->stats.kernel_launches = c->fill_launches + 5;       // + the occupancy kernel, the 3 distance passes and the padded copy
     c->fill_launches = 0;
     std::memset(c->h_counters, 0, 8 * sizeof(unsigned long long));
     unsigned int mm[8];

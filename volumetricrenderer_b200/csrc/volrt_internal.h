@@ -35,6 +35,11 @@ struct BrickInfo {          // min-max grid for empty-space skipping (8^3 voxel 
     const uint8_t* dist;       // 1 byte per brick: 0 = occupied, else Chebyshev distance (bricks, <= 255) to the nearest occupied brick
     int bx, by, bz;            // bricks per axis
     float inv_brick[3];        // bricks per unit of texture coordinate
+    // the distance map again with one brick of border on every side (the border repeats the nearest brick, which is what clamping
+    // the index did), for the march's lookup: brick_distance_fast forms the index from the raw bit patterns of three float
+    // additions, takes pad_bias off once and clamps the LINEAR index once instead of three coordinates twice
+    const uint8_t* dist_pad;   // (bx+2) x (by+2) x (bz+2)
+    unsigned int pad_bias, pad_last;
 };
 
 // procedural density: FastNoise2 FractalFBm over Perlin, remapped
@@ -102,6 +107,7 @@ struct MarchParams {
     int light_steps;
     float light_step_len, sun_dir[3], sun_color[3], ambient, sigma_t, early_term_eps;
     int skip_empty;
+    float unlit[3];             // sun_color + ambient: what a sample scatters when there is no light-march (filled by launch_march)
     BrickInfo bricks;
     FbmField fbm;
     FbmCells cells;             // MARCH_FBM_CELLS only
@@ -173,6 +179,8 @@ cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int 
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
 cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, unsigned int* mm8, cudaStream_t s);   // mm8 may be null
 cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_t* tmp, int bx, int by, int bz, cudaStream_t s);
+// pad[(bz+2)(by+2)(bx+2)] = dist with a border that repeats the nearest brick
+cudaError_t launch_brick_pad(const uint8_t* dist, uint8_t* pad, int bx, int by, int bz, cudaStream_t s);
 // ---- peak_kernels.cu: measured roofline denominators
 cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_tex_peak(cudaTextureObject_t tex, float* sink, int blocks, int iters, cudaStream_t s);
