@@ -520,28 +520,30 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
                     T = Tn;
                 }
             };
-            // whole batches only: no per-member bounds in the loop; the last n mod CB steps of a ray go through the loop below
+            // whole batches only: no per-member bounds in the loop; the last n mod CB steps of a ray go through the loop below.
+            // The brick byte of the position AFTER a batch is requested together with the batch's fetches, so the chain of an
+            // iteration is one memory round trip, not lookup -> fetch (ncu, round 2: 16 % of the stall samples sat on that byte).
+            // (A leap loop of its own in front of the fetches — so that lanes with empty bricks ahead catch up in cheap
+            // iterations and the warp meets at the fetch batch — was measured: C5 6.02 -> 7.42 ms; the chain lookup -> leap ->
+            // lookup of a lane running through empty space is better hidden behind its neighbours' fetches than run on its own.)
+            auto lookup = [&](f3 at) -> int { return VOLRT_FAST_BRICK ? brick_distance_fast(P, at) : brick_distance(P, at); };
             int i = 0;
+            int bd = (skip && CB <= n) ? lookup(p) : 0;
             while (i + CB <= n) {
-                if (skip) {
-                    // (A leap loop of its own in front of the fetches — so that lanes with empty bricks ahead catch up in cheap
-                    // iterations and the warp meets at the fetch batch — was measured: C5 6.02 -> 7.42 ms.  The march is bound by
-                    // latency as much as by issue, and the chain lookup -> leap -> lookup of a lane running through empty space
-                    // is better hidden behind its neighbours' fetches than run on its own.)
-                    const int bd = VOLRT_FAST_BRICK ? brick_distance_fast(P, p) : brick_distance(P, p);
-                    if (bd) {
-                        const int m1 = leap_steps(leap, bd, n - 1 - i) + 1;
-                        const float fm = (float)m1;
-                        p = {fmaf(fm, ray.step.x, p.x), fmaf(fm, ray.step.y, p.y), fmaf(fm, ray.step.z, p.z)};
-                        i += m1;
-                        continue;
-                    }
+                if (bd) {
+                    const int m1 = leap_steps(leap, bd, n - 1 - i) + 1;
+                    const float fm = (float)m1;
+                    p = {fmaf(fm, ray.step.x, p.x), fmaf(fm, ray.step.y, p.y), fmaf(fm, ray.step.z, p.z)};
+                    i += m1;
+                    bd = lookup(p);
+                    continue;
                 }
                 float d[CB];
                 f3 q[CB + 1];
                 q[0] = p;
 #pragma unroll
                 for (int k = 0; k < CB; ++k) { d[k] = fetch(q[k]); q[k + 1] = add3(q[k], ray.step); }
+                if (skip) bd = lookup(q[CB]);
                 bool stop = false;
 #pragma unroll
                 for (int k = 0; k < CB; ++k) {
@@ -755,9 +757,12 @@ constexpr int kCtaWx = VOLRT_CTA_WX, kCtaWy = VOLRT_CTA_WY, kCtaThreads = 32 * k
 // fetch batches — 7 / 8 / 10 / 12 CTAs: 0.0925 / 0.0936 / 0.0975 / 0.0991 ms.  Left to itself ptxas took 103 registers for the
 // compositing march once the depth-piece hand-over was added (46 before) and C5 doubled to 13.4 ms: hence explicit caps.
 // FP32-filtered parity variants: 80 registers; the node-tree interpreter: 168 (its V[]/P[] live in local memory anyway).
+#ifndef VOLRT_TEX_COMPOSITE_MIN_CTAS
+#define VOLRT_TEX_COMPOSITE_MIN_CTAS 12
+#endif
 __host__ __device__ constexpr int direct_min_ctas(int variant, bool composite) {
     return is_fbm(variant) ? VOLRT_DIRECT_MIN_CTAS
-         : (variant == MARCH_RGBA_TEX || variant == MARCH_SINGLE_TEX) ? (composite ? 12 : 7)
+         : (variant == MARCH_RGBA_TEX || variant == MARCH_SINGLE_TEX) ? (composite ? VOLRT_TEX_COMPOSITE_MIN_CTAS : 7)
          : variant == MARCH_TREE ? 3 : 6;
 }
 template <int VARIANT, bool COMPOSITE, bool STATS>
