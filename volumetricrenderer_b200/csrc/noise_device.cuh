@@ -67,18 +67,24 @@ __device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
 // zero, so one AND and one shift give the floats back exactly.  An LDS.64 costs the shared-memory pipe 2 wavefronts per
 // warp where the LDS.128 costs 4, and that pipe — not issue — bounds the march once the hashes are gone
 // (profiles/r02_march_fbm_cells_lds128.txt: 75 % of its peak at 68 % issue).
+// the components (cx, cy, cz) of gradient n of the 16 (Utils.inl:229-247: what GetGradientDot multiplies by)
+__host__ __device__ inline void grad_components(int n, float& cx, float& cy, float& cz) {
+    const int h13 = n & 13;
+    const int iu = h13 < 8 ? 0 : 1;
+    int iv = h13 == 12 ? 0 : 2;
+    iv = h13 < 2 ? 1 : iv;
+    const float su = (n & 1) ? -1.0f : 1.0f, sv = (n & 2) ? -1.0f : 1.0f;
+    cx = (iu == 0 ? su : 0.0f) + (iv == 0 ? sv : 0.0f);
+    cy = (iu == 1 ? su : 0.0f) + (iv == 1 ? sv : 0.0f);
+    cz = iv == 2 ? sv : 0.0f;
+}
 struct __align__(16) GradLut { float4 g[16]; uint2 h[16]; };
 
 __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
     if (tid < 16) {
-        const int n = tid, h13 = n & 13;
-        const int iu = h13 < 8 ? 0 : 1;
-        int iv = h13 == 12 ? 0 : 2;
-        iv = h13 < 2 ? 1 : iv;
-        const float su = (n & 1) ? -1.0f : 1.0f, sv = (n & 2) ? -1.0f : 1.0f;
-        const float cx = (iu == 0 ? su : 0.0f) + (iv == 0 ? sv : 0.0f);
-        const float cy = (iu == 1 ? su : 0.0f) + (iv == 1 ? sv : 0.0f);
-        const float cz = iv == 2 ? sv : 0.0f;
+        const int n = tid;
+        float cx, cy, cz;
+        grad_components(n, cx, cy, cz);
         lut->g[n] = make_float4(cx, cy, cz, 0.0f);
         lut->h[n] = make_uint2(__float_as_uint(cx), (__float_as_uint(cy) & 0xffff0000u) | (__float_as_uint(cz) >> 16));
     }
@@ -376,24 +382,59 @@ __device__ __forceinline__ f2 fbm_perlin2(LUT lut, const FbmField& F, f2 x, f2 y
 // cell (0,0,0)), whose bit pattern is 0x4B400000 + index, so the address is one IMAD.WIDE with an adjusted base.
 // Everything after the hash — fractions, fades, gradient dot products, lerps, in the same order — is unchanged, and the
 // table holds exactly what the hash would have produced: the value is bit-identical to perlin3_lut / perlin3_lut2.
-__device__ __forceinline__ uint2 fbm_cell_fetch(const FbmCellOctave& C, float xs, float ys, float zs) {
+// Two entry formats (VOLRT_CELL_GRADIENT_BYTES, volrt_internal.h: kFbmCellBytes):
+//   0  8 bytes per cell: the eight corners' byte offsets into the shared-memory gradient table; a corner costs one PRMT, one
+//      LDS.128 and three FFMAs.  The LDS results are what binds then: 4 write-back cycles per corner and warp, the LSU
+//      write-back port 77 % busy at 68 % issue (profiles/r02_final_c2.txt).
+//   1  32 bytes per cell: the gradients THEMSELVES, one byte per component — 0x40, 0xC0 or 0x00, the top byte of +2.0f, -2.0f
+//      or 0.0f — so a component is one PRMT (byte -> top of a zero word) and nothing goes through shared memory.  The factor 2
+//      is taken out of the octave amplitude (amp / 2): every product, sum and lerp is scaled by an exact power of two, so the
+//      value is bit-identical.  Corner c's components are bytes 3c, 3c+1, 3c+2 of the entry (24 of the 32 bytes used).
+struct CellWords { unsigned int w[VOLRT_CELL_GRADIENT_BYTES ? 6 : 2]; };
+__device__ __forceinline__ CellWords fbm_cell_fetch(const FbmCellOctave& C, float xs, float ys, float zs) {
     const float t = fmaf(zs, C.n2f, fmaf(ys, C.nf, xs + C.kf));
-    return __ldg(reinterpret_cast<const uint2*>(C.base_adj + (unsigned long long)__float_as_uint(t) * 8ull));
+    CellWords W;
+#if VOLRT_CELL_GRADIENT_BYTES
+    const char* e = reinterpret_cast<const char*>(C.base_adj + (unsigned long long)__float_as_uint(t) * 32ull);
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(e));
+    const uint2 b = __ldg(reinterpret_cast<const uint2*>(e + 16));
+    W.w[0] = a.x; W.w[1] = a.y; W.w[2] = a.z; W.w[3] = a.w; W.w[4] = b.x; W.w[5] = b.y;
+#else
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(C.base_adj + (unsigned long long)__float_as_uint(t) * 8ull));
+    W.w[0] = v.x; W.w[1] = v.y;
+#endif
+    return W;
 }
 // (floor() on the FMA pipe instead of FRND — x + (2^23 - 1/2) rounds once to 2^23 + rint(x - 1/2) — was measured: 1.457 vs
 // 1.441 ms at C2, profiles/r02_fbm_cells_experiments.txt; the XU pipe at 20 % is not what binds.)
 __device__ __forceinline__ float cell_floor(float x) { return floorf(x); }
 __device__ __forceinline__ f2 cell_floor2(f2 x) { return make_f2(floorf(f2_a(x)), floorf(f2_b(x))); }
 __device__ __forceinline__ unsigned int cell_corner(unsigned int w, int k) { return __byte_perm(w, 0u, 0x4440u + (unsigned)k); }
-// off = the byte a cell-table entry holds for the corner: n * 16 into g[], or (VOLRT_CELLS_LDS64) n * 8 into h[].
+// byte b of w as the top byte of an otherwise zero word
+__device__ __forceinline__ float cell_top_byte(unsigned int w, int b) { return __uint_as_float(__byte_perm(w, 0u, 0x0444u | ((unsigned)b << 12))); }
+// the 24 gradient bytes of a cell from its eight corner hashes t[c], as six words
+__device__ __forceinline__ void cell_gradient_words(const int t[8], unsigned int w[6]) {
+    unsigned char b[24];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        float g[3];
+        grad_components((int)(grad_lut_offset(t[c]) >> 4), g[0], g[1], g[2]);
+#pragma unroll
+        for (int j = 0; j < 3; ++j) b[3 * c + j] = g[j] > 0.0f ? 0x40 : g[j] < 0.0f ? 0xC0 : 0x00;
+    }
+#pragma unroll
+    for (int k = 0; k < 6; ++k) w[k] = (unsigned)b[4 * k] | (unsigned)b[4 * k + 1] << 8 | (unsigned)b[4 * k + 2] << 16 | (unsigned)b[4 * k + 3] << 24;
+}
+constexpr float kCellAmpScale = VOLRT_CELL_GRADIENT_BYTES ? 0.5f : 1.0f;      // the gradients above are twice FastNoise2's
+// off = the byte an 8-byte cell-table entry holds for the corner: n * 16 into g[], or (VOLRT_CELLS_LDS64) n * 8 into h[].
 // Measured on B200, C2: the 8-byte entries halve the shared-memory wavefronts (306 M -> 146 M per frame) but their two
 // decode instructions per corner cost more than that buys — 1.104 G -> 1.296 G warp instructions, 1.478 -> 1.553 ms
-// (profiles/r02_march_fbm_cells_lds128.txt / _lds64.txt).  The march is issue-bound before it is LDS-bound.
+// (profiles/r02_march_fbm_cells_lds128.txt / _lds64.txt); with some corners of a cell on either form the time does not move
+// (mask 0x01 / 0x11 / 0x21 / 0x55: 1.435 / 1.427 / 1.421 / 1.462 against 1.430 ms).
 #ifndef VOLRT_CELLS_LDS64
 #define VOLRT_CELLS_LDS64 0
 #endif
-// bit c set: corner c of a cell (x0y0z0, x1y0z0, x0y1z0, x1y1z0, then z1) takes the 8-byte form.  A mix relieves the
-// shared-memory pipe a little at a time: each such corner costs it 2 wavefronts instead of 4 and the issue ports 2 more slots.
+// bit c set: corner c of a cell (x0y0z0, x1y0z0, x0y1z0, x1y1z0, then z1) takes the 8-byte form
 #ifndef VOLRT_CELLS_LDS64_MASK
 #define VOLRT_CELLS_LDS64_MASK (VOLRT_CELLS_LDS64 ? 0xFF : 0)
 #endif
@@ -420,10 +461,20 @@ __device__ __forceinline__ float4 grad_lut_at(const GradLut* lut, unsigned int o
         return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
     }
 }
-// C0: the cell corner o0 belongs to (o1: C0 + 1)
+// gradient of corner C of the fetched cell
+template <int C, class LUT>
+__device__ __forceinline__ float4 cell_gradient(LUT lut, const CellWords& W) {
+#if VOLRT_CELL_GRADIENT_BYTES
+    return make_float4(cell_top_byte(W.w[(3 * C) >> 2], (3 * C) & 3), cell_top_byte(W.w[(3 * C + 1) >> 2], (3 * C + 1) & 3),
+                       cell_top_byte(W.w[(3 * C + 2) >> 2], (3 * C + 2) & 3), 0.0f);
+#else
+    return grad_lut_at<cell_corner_is64(C)>(lut, cell_corner(W.w[C >> 2], C & 3));
+#endif
+}
+// the x edge between corners C0 and C0 + 1
 template <int C0, class LUT>
-__device__ __forceinline__ float grad_edge_at(LUT lut, unsigned int o0, unsigned int o1, float fx0, float fx1, float fy, float fz, float s) {
-    const float4 g0 = grad_lut_at<cell_corner_is64(C0)>(lut, o0), g1 = grad_lut_at<cell_corner_is64(C0 + 1)>(lut, o1);
+__device__ __forceinline__ float grad_edge_at(LUT lut, const CellWords& W, float fx0, float fx1, float fy, float fz, float s) {
+    const float4 g0 = cell_gradient<C0>(lut, W), g1 = cell_gradient<C0 + 1>(lut, W);
     const float d0 = fmaf(fz, g0.z, fmaf(fy, g0.y, fx0 * g0.x));
     const float e = fmaf(fz, g1.z, fmaf(fy, g1.y, fmaf(fx1, g1.x, -d0)));
     return fmaf(s, e, d0);
@@ -431,21 +482,18 @@ __device__ __forceinline__ float grad_edge_at(LUT lut, unsigned int o0, unsigned
 template <int I = -1, class LUT>
 __device__ __forceinline__ float perlin3_cells(LUT lut, const FbmCellOctave& C, float x, float y, float z) {
     float xs = cell_floor(x), ys = cell_floor(y), zs = cell_floor(z);
-    const uint2 w = fbm_cell_fetch(C, xs, ys, zs);
+    const CellWords W = fbm_cell_fetch(C, xs, ys, zs);
     float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
     float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
     xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
-    float a = lerpf(grad_edge_at<0>(lut, cell_corner(w.x, 0), cell_corner(w.x, 1), xf0, xf1, yf0, zf0, xs),
-                    grad_edge_at<2>(lut, cell_corner(w.x, 2), cell_corner(w.x, 3), xf0, xf1, yf1, zf0, xs), ys);
-    float b = lerpf(grad_edge_at<4>(lut, cell_corner(w.y, 0), cell_corner(w.y, 1), xf0, xf1, yf0, zf1, xs),
-                    grad_edge_at<6>(lut, cell_corner(w.y, 2), cell_corner(w.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    float a = lerpf(grad_edge_at<0>(lut, W, xf0, xf1, yf0, zf0, xs), grad_edge_at<2>(lut, W, xf0, xf1, yf1, zf0, xs), ys);
+    float b = lerpf(grad_edge_at<4>(lut, W, xf0, xf1, yf0, zf1, xs), grad_edge_at<6>(lut, W, xf0, xf1, yf1, zf1, xs), ys);
     return lerpf(a, b, zs);
 }
 template <int C0, class LUT>
-__device__ __forceinline__ f2 grad_edge_at2(LUT lut, unsigned int oA0, unsigned int oA1, unsigned int oB0, unsigned int oB1,
-                                            f2 fx0, f2 fx1, f2 fy, f2 fz, f2 s) {
-    const float4 a0 = grad_lut_at<cell_corner_is64(C0)>(lut, oA0), a1 = grad_lut_at<cell_corner_is64(C0 + 1)>(lut, oA1);
-    const float4 b0 = grad_lut_at<cell_corner_is64(C0)>(lut, oB0), b1 = grad_lut_at<cell_corner_is64(C0 + 1)>(lut, oB1);
+__device__ __forceinline__ f2 grad_edge_at2(LUT lut, const CellWords& WA, const CellWords& WB, f2 fx0, f2 fx1, f2 fy, f2 fz, f2 s) {
+    const float4 a0 = cell_gradient<C0>(lut, WA), a1 = cell_gradient<C0 + 1>(lut, WA);
+    const float4 b0 = cell_gradient<C0>(lut, WB), b1 = cell_gradient<C0 + 1>(lut, WB);
     const float fyA = f2_a(fy), fyB = f2_b(fy), fzA = f2_a(fz), fzB = f2_b(fz);
     const float d0A = fmaf(fzA, a0.z, fmaf(fyA, a0.y, f2_a(fx0) * a0.x));
     const float d0B = fmaf(fzB, b0.z, fmaf(fyB, b0.y, f2_b(fx0) * b0.x));
@@ -456,16 +504,14 @@ __device__ __forceinline__ f2 grad_edge_at2(LUT lut, unsigned int oA0, unsigned 
 template <int I = -1, class LUT>
 __device__ __forceinline__ f2 perlin3_cells2(LUT lut, const FbmCellOctave& C, f2 x, f2 y, f2 z) {
     f2 xs = cell_floor2(x), ys = cell_floor2(y), zs = cell_floor2(z);
-    const uint2 wA = fbm_cell_fetch(C, f2_a(xs), f2_a(ys), f2_a(zs));
-    const uint2 wB = fbm_cell_fetch(C, f2_b(xs), f2_b(ys), f2_b(zs));
+    const CellWords WA = fbm_cell_fetch(C, f2_a(xs), f2_a(ys), f2_a(zs));
+    const CellWords WB = fbm_cell_fetch(C, f2_b(xs), f2_b(ys), f2_b(zs));
     const f2 xf0 = sub2(x, xs), yf0 = sub2(y, ys), zf0 = sub2(z, zs);
     const f2 m1 = splat2(-1.0f);
     const f2 xf1 = add2(xf0, m1), yf1 = add2(yf0, m1), zf1 = add2(zf0, m1);
     xs = quintic2(xf0); ys = quintic2(yf0); zs = quintic2(zf0);
-    const f2 a = lerp2(grad_edge_at2<0>(lut, cell_corner(wA.x, 0), cell_corner(wA.x, 1), cell_corner(wB.x, 0), cell_corner(wB.x, 1), xf0, xf1, yf0, zf0, xs),
-                       grad_edge_at2<2>(lut, cell_corner(wA.x, 2), cell_corner(wA.x, 3), cell_corner(wB.x, 2), cell_corner(wB.x, 3), xf0, xf1, yf1, zf0, xs), ys);
-    const f2 b = lerp2(grad_edge_at2<4>(lut, cell_corner(wA.y, 0), cell_corner(wA.y, 1), cell_corner(wB.y, 0), cell_corner(wB.y, 1), xf0, xf1, yf0, zf1, xs),
-                       grad_edge_at2<6>(lut, cell_corner(wA.y, 2), cell_corner(wA.y, 3), cell_corner(wB.y, 2), cell_corner(wB.y, 3), xf0, xf1, yf1, zf1, xs), ys);
+    const f2 a = lerp2(grad_edge_at2<0>(lut, WA, WB, xf0, xf1, yf0, zf0, xs), grad_edge_at2<2>(lut, WA, WB, xf0, xf1, yf1, zf0, xs), ys);
+    const f2 b = lerp2(grad_edge_at2<4>(lut, WA, WB, xf0, xf1, yf0, zf1, xs), grad_edge_at2<6>(lut, WA, WB, xf0, xf1, yf1, zf1, xs), ys);
     return lerp2(a, b, zs);
 }
 // the compile-time octave count (C2 / C3: 5), octave by octave
@@ -491,7 +537,7 @@ __device__ __forceinline__ f2 fbm_cells_unrolled2(LUT lut, const FbmField& F, co
 template <int OCT, class LUT>
 __device__ __forceinline__ float fbm_perlin_cells_n(LUT lut, const FbmField& F, const FbmCells& T, float x, float y, float z) {
     const int n = OCT > 0 ? OCT : F.octaves;
-    float amp = F.bounding * kPerlinScale;
+    float amp = F.bounding * kPerlinScale * kCellAmpScale;
     if constexpr (OCT > 0) return fbm_cells_unrolled<0, OCT>(lut, F, T, x, y, z, amp, 0.0f);
     float sum = perlin3_cells(lut, T.oct[0], x, y, z) * amp;
 #pragma unroll
@@ -505,7 +551,7 @@ __device__ __forceinline__ float fbm_perlin_cells_n(LUT lut, const FbmField& F, 
 template <int OCT, class LUT>
 __device__ __forceinline__ f2 fbm_perlin_cells2_n(LUT lut, const FbmField& F, const FbmCells& T, f2 x, f2 y, f2 z) {
     const int n = OCT > 0 ? OCT : F.octaves;
-    float amp = F.bounding * kPerlinScale;
+    float amp = F.bounding * kPerlinScale * kCellAmpScale;
     const f2 lac = splat2(F.lacunarity);
     if constexpr (OCT > 0) return fbm_cells_unrolled2<0, OCT>(lut, F, T, x, y, z, lac, amp, make_f2(0.0f, 0.0f));
     f2 sum = mul2(perlin3_cells2(lut, T.oct[0], x, y, z), splat2(amp));

@@ -75,7 +75,7 @@ struct vr_context {
     float* d_tree_out = nullptr;
     size_t tree_out_bytes = 0;
     // fBm lattice-cell tables (volrt_internal.h: FbmCells), rebuilt by vr_set_params when the field's lattice changes
-    uint2* d_fbm_cells = nullptr;          // the tables of every octave, back to back
+    unsigned char* d_fbm_cells = nullptr;  // the tables of every octave, back to back (kFbmCellBytes per cell)
     size_t fbm_cells_bytes = 0;
     FbmCells fbm_cells{};
     bool fbm_cells_ok = false;
@@ -1019,8 +1019,8 @@ static vr_status prepare_fbm_cells(vr_context* c, const vr_params* p) {
         total += (size_t)n[o] * n[o] * n[o];
         top *= (double)p->fbm_lacunarity * (1.0 + 1e-5);
     }
-    if (total * sizeof(uint2) > ((size_t)64 << 20)) return VR_OK;
-    const size_t need = total * sizeof(uint2);
+    if (total * (size_t)kFbmCellBytes > ((size_t)256 << 20)) return VR_OK;
+    const size_t need = total * (size_t)kFbmCellBytes;
     const bool same = c->d_fbm_cells && c->fbm_cells_key_oct == p->fbm_octaves && c->fbm_cells_key_seed == p->fbm_seed &&
                       c->fbm_cells_key_freq == p->fbm_frequency && c->fbm_cells_key_lac == p->fbm_lacunarity;
     if (!same) {
@@ -1031,16 +1031,16 @@ static vr_status prepare_fbm_cells(vr_context* c, const vr_params* p) {
             VR_CUDA(c, cudaMalloc(&c->d_fbm_cells, need));
             c->fbm_cells_bytes = need;
         }
-        uint2* at = c->d_fbm_cells;
+        unsigned char* at = c->d_fbm_cells;
         for (int o = 0; o < p->fbm_octaves; ++o) {
             VR_CUDA(c, launch_fbm_cell_table(p->fbm_seed + o, n[o], at, c->stream));     // Fractal.inl: seed + octave index
             FbmCellOctave& C = c->fbm_cells.oct[o];
-            C.base_adj = (unsigned long long)(uintptr_t)at - 8ull * 0x4B400000ull;
+            C.base_adj = (unsigned long long)(uintptr_t)at - (unsigned long long)kFbmCellBytes * 0x4B400000ull;
             C.nf = (float)n[o];
             C.n2f = (float)(n[o] * n[o]);
             C.kf = 12582912.0f + (float)(n[o] * n[o] + n[o] + 1);
             C.pad = 0.0f;
-            at += (size_t)n[o] * n[o] * n[o];
+            at += (size_t)n[o] * n[o] * n[o] * (size_t)kFbmCellBytes;
         }
         VR_CUDA(c, cudaEventRecord(c->ev_params, c->stream));      // a render on a caller's stream waits for the tables
         c->fbm_cells_key_oct = p->fbm_octaves; c->fbm_cells_key_seed = p->fbm_seed;

@@ -55,8 +55,16 @@ struct FbmField {
 // FastNoise2's HashPrimes + the low nibble GetGradientDot looks at (Utils.inl:229-247,295-302), evaluated once per cell
 // at vr_set_params instead of eight times per sample per octave.  Cells cover lattice coordinates -1 .. n-2 per axis.
 constexpr int kFbmCellMaxOctaves = 8;
+// 0: an entry holds eight offsets into the shared-memory gradient table (8-byte entry); 1: the eight gradients themselves (24 bytes
+// of a 32-byte entry, no shared memory on the path; noise_device.cuh: fbm_cell_fetch).  Measured on B200, bit-identical frames:
+// C2 1.433 (0) against 1.448 ms (1), C3 13.56 against 14.01 — the 16 extra PRMTs per octave and point cost what the LDS
+// write-back port gives back (profiles/r02_fbm_cells_experiments.txt).
+#ifndef VOLRT_CELL_GRADIENT_BYTES
+#define VOLRT_CELL_GRADIENT_BYTES 0
+#endif
+constexpr int kFbmCellBytes = VOLRT_CELL_GRADIENT_BYTES ? 32 : 8;
 struct FbmCellOctave {
-    unsigned long long base_adj;   // device address of cell (-1,-1,-1)'s entry, minus 8 * 0x4B400000 (the index arrives as float bits)
+    unsigned long long base_adj;   // device address of cell (-1,-1,-1)'s entry, minus kFbmCellBytes * 0x4B400000 (the index arrives as float bits)
     float nf, n2f, kf;             // n, n*n, and 1.5*2^23 + n*n + n + 1 (magic + the offset of lattice coordinate (0,0,0))
     float pad;
 };
@@ -174,7 +182,7 @@ struct PackChannel { const float* field; float mn, mx; uint32_t power; };
 cudaError_t launch_noise_pack(const PackChannel ch[4], int64_t n, uint8_t* out_rgba8, cudaStream_t s);
 cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_t s);
 // fBm lattice-cell tables: entries[n^3] for one octave (seed already offset by the octave index), cells -1 .. n-2 per axis
-cudaError_t launch_fbm_cell_table(int seed, int n, uint2* entries, cudaStream_t s);
+cudaError_t launch_fbm_cell_table(int seed, int n, void* entries, cudaStream_t s);      // n^3 entries of kFbmCellBytes
 cudaError_t launch_occupancy(const void* lin, int vol_format, int w, int h, int d, int address_mode,
                              uint8_t* occupied, int bx, int by, int bz, cudaStream_t s);
 cudaError_t launch_deinterleave_rgba8(const uint8_t* rgba, uint8_t* planes4, size_t voxels, unsigned int* mm8, cudaStream_t s);   // mm8 may be null
