@@ -320,3 +320,30 @@ def test_ray_compaction_kernel_gives_the_same_frame(monkeypatch):
             frames[knob] = r.render().copy()
     assert frames["0"][..., :3].max() > 0.5
     assert np.array_equal(frames["0"].view(np.uint32), frames["1"].view(np.uint32))
+
+
+@pytest.mark.parametrize("fmt", ["OUT_RGBA8_UNORM", "OUT_RGBA16F", "OUT_RGBA32F"])
+def test_view_batch_over_its_screen_rectangle_only_gives_the_same_frames(monkeypatch, fmt):
+    """A batch of views launches tiles over the union of the views' screen rectangles and clears the rest of the frames with
+    clear_outside_kernel (launch_one; by default only where that saves >= 100 000 CTAs — forced here).  Every pixel of every
+    view, in all three target formats and for an odd frame width, equals the full-grid launch bit for bit; so does a row band."""
+    W, H, NV = 482, 270, 4
+    views = scene.orbit_views(64)[::16][:NV]
+    kw = dict(density_mode=1, max_steps=256, sample_scale=1.0, sigma_t=400.0, ambient=1.0, sun_color=[0.0, 0.0, 0.0], skip_empty=1,
+              early_term_eps=1.0 / 512)
+    monkeypatch.setenv("VOLRT_RAY_SPLIT_COMPOSITE", "1")
+    frames = {}
+    with vr.Renderer(W, H, getattr(capi, fmt), max_views=NV) as r:
+        r.generate_volume(size=128, format=capi.VOL_R16F, layout=capi.LAYOUT_TEXTURE, threshold=0.07)
+        r.set_params(view_ubos=views, **kw)
+        for knob in ("1000000000", "0"):
+            monkeypatch.setenv("VOLRT_RECT_GRID_MIN_SAVED", knob)
+            frames[knob] = r.render().copy()
+            launches = r.stats()["kernel_launches"]
+            assert launches == (2 if knob == "0" else 1)
+            r.render(rows=(40, 201))                       # a band that cuts the rectangle: only its rows may change
+            frames[knob + "band"] = r.render(flags=capi.RENDER_NO_MARCH).copy()
+    full, rect = frames["1000000000"], frames["0"]
+    assert (full[..., :3].reshape(NV, -1).max(axis=1) > 0).all()
+    assert np.array_equal(full.view(np.uint8), rect.view(np.uint8))
+    assert np.array_equal(frames["1000000000band"].view(np.uint8), frames["0band"].view(np.uint8))

@@ -685,19 +685,20 @@ __device__ __forceinline__ void tile_of_cta(const MarchParams& P, int& tx, int& 
         kx = (int)fast_div((unsigned)lin, M.div_gy);
         ky = lin - kx * M.gy;
     }
-    tx = centre_out(kx, M.gx);
-    ty = outward_from(ky, M.gy, M.cy);
+    tx = centre_out(kx, M.gx) + M.tx0;
+    ty = outward_from(ky, M.gy, M.cy) + M.ty0;
 }
 static unsigned int fast_div_magic(unsigned int d) { return d <= 1 ? 0u : (unsigned int)((0x100000000ull + d - 1) / d); }
 // grid: tiles along x and y (before the inner index is folded into x); tile_h: rows of a tile
-static void set_tile_map(MarchParams& p, dim3 grid, int inner, int tile_h) {
+static void set_tile_map(MarchParams& p, dim3 grid, int inner, int tile_h, int tx0 = 0, int ty0 = 0) {
     TileMap& M = p.map;
     M.gx = (int)grid.x; M.gy = (int)grid.y;
+    M.tx0 = tx0; M.ty0 = ty0;
     M.inner = inner > 1 ? inner : 1;
     M.div_inner = fast_div_magic((unsigned)M.inner);
     M.div_gy = fast_div_magic((unsigned)M.gy);
     M.swap = M.gy < M.gx;
-    const int cy = (p.height / 2 - p.row_begin) / tile_h;
+    const int cy = (p.height / 2 - p.row_begin) / tile_h - ty0;
     M.cy = cy < 0 ? 0 : cy > M.gy - 1 ? M.gy - 1 : cy;
 }
 
@@ -1372,6 +1373,29 @@ __global__ void __launch_bounds__(256) row_cost_kernel(const __grid_constant__ M
     }
 }
 
+// The clear colour (VulkanRenderPass.cpp:17-19) for every pixel of rows [row_begin, row_end) x n_views OUTSIDE the pixel block
+// [x0, x1) x [y0, y1) that a restricted march launch covers.  x0 and x1 are multiples of 16, so a quad of four pixels is inside
+// or outside as a whole; quads go out as 16-byte stores where the target allows.
+__global__ void __launch_bounds__(256) clear_outside_kernel(const __grid_constant__ MarchParams P, int x0, int y0, int x1, int y1) {
+    const int px = 4 * (int)(blockIdx.x * blockDim.x + threadIdx.x), py = P.row_begin + (int)blockIdx.y, view = P.view_begin + (int)blockIdx.z;
+    if (px >= P.width) return;
+    if (py >= y0 && py < y1 && px >= x0 && px < x1) return;
+    const int bpp = (P.out_format == VR_OUT_RGBA8_UNORM || P.out_format == VR_OUT_RGBA8_SRGB) ? 4 : P.out_format == VR_OUT_RGBA16F ? 8 : 16;
+    char* row = (char*)P.out + (size_t)view * P.view_stride + (size_t)py * P.row_pitch;
+    char* at = row + (size_t)px * bpp;
+    if (px + 4 <= P.width && ((size_t)at & 15) == 0) {
+        uint4* q = (uint4*)at;
+        if (bpp == 4) q[0] = make_uint4(0xFF000000u, 0xFF000000u, 0xFF000000u, 0xFF000000u);
+        else if (bpp == 8) { q[0] = make_uint4(0u, 0x3C000000u, 0u, 0x3C000000u); q[1] = q[0]; }
+        else { const uint4 one = make_uint4(0u, 0u, 0u, 0x3F800000u); q[0] = one; q[1] = one; q[2] = one; q[3] = one; }
+        return;
+    }
+    for (int k = 0; k < 4 && px + k < P.width; ++k) store_pixel(P, view, px + k, py, 0.0f, 0.0f, 0.0f, 1.0f);
+}
+#ifndef VOLRT_RECT_GRID_MIN_SAVED
+#define VOLRT_RECT_GRID_MIN_SAVED 100000       // CTAs a restricted launch must save before the extra clear launch is worth it
+#endif
+
 template <int VARIANT, bool COMPOSITE, bool STATS>
 static cudaError_t launch_one(const MarchParams& p_in, dim3 grid, bool persistent, cudaStream_t s) {      // grid: tiles x tiles x views
     MarchParams p = p_in;
@@ -1392,7 +1416,27 @@ static cudaError_t launch_one(const MarchParams& p_in, dim3 grid, bool persisten
     }
     const bool segmented = COMPOSITE && !STATS && p.segments > 1;
     if (segmented) p.view_group = 1;
-    set_tile_map(p, grid, segmented ? p.segments : p.view_group, 4 * kCtaWy);
+    // A batch of views: tiles over the union of the views' screen rectangles only (the cube fills a quarter of a frame; the CTAs
+    // of the other three quarters did nothing but find that out and clear their pixels — 70 % of the 1 M CTAs of a 64-view
+    // batch), the rest of the frames cleared by clear_outside_kernel.  One more launch: only where it saves many CTAs.
+    int tx0 = 0, ty0 = 0;
+    if (!STATS && !segmented && p.batch_rect[2] > p.batch_rect[0] && p.batch_rect[3] > p.batch_rect[1]) {
+        constexpr int TW = 8 * kCtaWx, TH = 4 * kCtaWy;
+        const int bx0 = p.batch_rect[0] / TW, bx1 = (p.batch_rect[2] + TW - 1) / TW;
+        const int ry0 = p.batch_rect[1] - p.row_begin, ry1 = p.batch_rect[3] - p.row_begin;
+        const int by0 = (ry0 > 0 ? ry0 : 0) / TH, by1 = ((ry1 < 0 ? 0 : ry1) + TH - 1) / TH;
+        const int nx = (bx1 < (int)grid.x ? bx1 : (int)grid.x) - bx0, ny = (by1 < (int)grid.y ? by1 : (int)grid.y) - by0;
+        const char* env = getenv("VOLRT_RECT_GRID_MIN_SAVED");         // tests: 0 = always, a huge number = never
+        const long long min_saved = env ? atoll(env) : (long long)VOLRT_RECT_GRID_MIN_SAVED;
+        if (nx > 0 && ny > 0 && ((long long)grid.x * grid.y - (long long)nx * ny) * grid.z >= min_saved) {
+            tx0 = bx0; ty0 = by0;
+            const dim3 cgrid((unsigned)((p.width + 1023) / 1024), (unsigned)(p.row_end - p.row_begin), grid.z);
+            clear_outside_kernel<<<cgrid, 256, 0, s>>>(p, bx0 * TW, p.row_begin + by0 * TH, (bx0 + nx) * TW, p.row_begin + (by0 + ny) * TH);
+            grid.x = (unsigned)nx; grid.y = (unsigned)ny;
+            if (p.extra_launches) ++*p.extra_launches;
+        }
+    }
+    set_tile_map(p, grid, segmented ? p.segments : p.view_group, 4 * kCtaWy, tx0, ty0);
     if (segmented) grid.x *= p.segments;             // grid x = tiles x depth segments
     else if (p.view_group > 1) {                     // grid x = tiles x views of a group, grid z = groups (march_kernel)
         grid.x *= p.view_group;

@@ -1252,10 +1252,21 @@ static vr_status enqueue_march(vr_context* c, MarchParams& m, int variant, uint3
             m.seg_partials = c->d_seg_partials; m.seg_arrived = c->d_seg_arrived; m.seg_capacity = c->seg_capacity;
         }
     }
+    // a batch of views: the union of their screen rectangles (launch_one restricts the grid to it when that saves enough CTAs)
+    if (v1 - v0 > 1 && c->views_on_device && c->h_views) {
+        int u[4] = {(int)c->width, (int)c->height, 0, 0};
+        for (uint32_t v = v0; v < v1; ++v) {
+            const int* r = c->h_views[v].rect;
+            if (r[2] <= r[0] || r[3] <= r[1]) continue;
+            u[0] = r[0] < u[0] ? r[0] : u[0]; u[1] = r[1] < u[1] ? r[1] : u[1];
+            u[2] = r[2] > u[2] ? r[2] : u[2]; u[3] = r[3] > u[3] ? r[3] : u[3];
+        }
+        if (u[2] > u[0] && u[3] > u[1]) for (int k = 0; k < 4; ++k) m.batch_rect[k] = u[k];
+    }
     VR_CUDA(c, cudaEventRecord(c->ev0, s));
     if (!no_march) {
         if (variant == MARCH_SINGLE_BRICK) VR_CUDA(c, launch_march_brick(m, c->tensor_map, (int)(v1 - v0), s));
-        else VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s));
+        else { m.extra_launches = n_launches; VR_CUDA(c, launch_march(m, variant, (int)(v1 - v0), stats, s)); m.extra_launches = nullptr; }
         if (r1 > r0 && v1 > v0) ++*n_launches;
     }
     VR_CUDA(c, cudaEventRecord(c->ev1, s));

@@ -80,6 +80,7 @@ struct TileMap {
     unsigned int div_inner, div_gy;
     int swap;                   // gy < gx: the linear index runs down the columns
     int cy;                     // tile row nearest the frame's centre row
+    int tx0, ty0;               // first tile of the launch (a launch restricted to the views' screen rectangle: batch_rect)
 };
 struct MarchParams {
     // target
@@ -137,6 +138,10 @@ struct MarchParams {
     // view batches: the same screen tile of `view_group` consecutive views is dispatched back to back (grid x = tiles x
     // view_group, grid z = groups), so that CTAs resident together look at the same region of a volume larger than L2
     int view_group;             // 0 / 1 = views are whole z slices
+    // union of the screen rectangles (ViewConst::rect) of the views of this launch, from the caller (x1 <= x0: not known).  A
+    // batch of many views launches tiles over this rectangle only and clears the rest of the frames with a copy-like kernel
+    int batch_rect[4];
+    int* extra_launches;        // HOST pointer or null: launch_march adds the kernels it launched besides the march itself
     // how a CTA finds its tile (march_kernels.cu: tile_of_cta), filled by the launch functions (set_tile_map): every warp of
     // every CTA runs this, and three quarters of a frame's CTAs are empty tiles that do nothing else
     TileMap map;
