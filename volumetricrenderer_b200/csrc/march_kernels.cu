@@ -1203,24 +1203,31 @@ static cudaError_t launch_compact(const MarchParams& p_in, int rows, int n_views
 // filters from there in FP32 with the oracle's operation order (bit-exact, like the LINEAR layout).
 // Slabs shrink (K/2) while the box does not fit; taps that would need mirrored addressing (index -1 or N,
 // i.e. the first/last sample of a ray on a volume face) and anything else outside the staged box take the
-// global-memory path of the LINEAR variant.  Latency is hidden by occupancy (one 27 KB box per CTA,
-// up to 8 CTAs per SM) rather than by a second stage.
-constexpr int BRICK_X = 32, BRICK_Y = 24, BRICK_Z = 24;            // voxels.  TMA wants the box's first byte 16-byte aligned, so
-                                                                   // the x origin is rounded down to a multiple of 8 halves: usable x extent >= 25
-constexpr int BRICK_BYTES = BRICK_X * BRICK_Y * BRICK_Z * 2;
+// global-memory path of the LINEAR variant.
+constexpr int BRICK_X = kBrickBox[0], BRICK_Y = kBrickBox[1], BRICK_Z = kBrickBox[2];   // voxels.  TMA wants the box's first byte 16-byte
+                                                                   // aligned, so the x origin is rounded down to a multiple of 8 halves: usable x extent >= BRICK_X - 7
+constexpr int BRICK_BOX_BYTES = BRICK_X * BRICK_Y * BRICK_Z * 2;
+constexpr int BRICK_STAGES = VOLRT_BRICK_STAGES;
+constexpr int BRICK_BOX_STRIDE = (BRICK_BOX_BYTES + 127) & ~127;   // a TMA destination is 128-byte aligned
+constexpr int BRICK_BYTES = BRICK_BOX_STRIDE * BRICK_STAGES;
 constexpr int BRICK_KMAX = 8;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// Round 2's second attempt: the box shape is a build constant (volrt_internal.h: kBrickBox — rows padded against bank conflicts:
+// -DVOLRT_BRICK_X=40 -DVOLRT_BRICK_Y=21 -DVOLRT_BRICK_Z=21) and so is the number of boxes in flight (VOLRT_BRICK_STAGES=2: the box
+// of slab s+1 is requested — its AABB needs only the analytic tap positions — before slab s is filtered out of the other
+// buffer, each buffer completing on its own mbarrier).  Both measured, neither faster: see kBrickBox.
+struct BrickSlab { int i0, K, lo[3]; bool fits; };
 __global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant__ MarchParams P,
                                                           const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(128) unsigned char dyn_smem[];
-    __half* box = reinterpret_cast<__half*>(dyn_smem);
-    __shared__ __align__(8) unsigned long long bar;
+    __shared__ __align__(8) unsigned long long bar[BRICK_STAGES];
     __shared__ int red[8];            // lo xyz, hi xyz, n_max, (unused)
     const int tid = threadIdx.x;
     if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
+#pragma unroll
+        for (int b = 0; b < BRICK_STAGES; ++b) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar[b])));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         red[6] = 0;
     }
@@ -1247,11 +1254,11 @@ __global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant_
     f3 p = ray.pin;
     float acc = 0.0f;
     int K = BRICK_KMAX;
-    unsigned int phase = 0;
-    for (int i0 = 0; i0 < n_max;) {
-        // ---- bounding box of the slab's taps (analytic positions; 0.02-voxel slack against the running add)
-        int lo[3], hi[3];
-        bool fits;
+    // ---- the slab that starts at step i0: bounding box of its taps (analytic positions; 0.02-voxel slack against the running
+    // add), halved until the box fits; CTA-uniform result.  Uses red[0..5] between two barriers of its own.
+    auto plan = [&](int i0) -> BrickSlab {
+        BrickSlab S;
+        S.i0 = i0;
         for (;;) {
             if (tid < 6) red[tid] = tid < 3 ? 0x7fffffff : (int)0x80000000;
             __syncthreads();
@@ -1272,35 +1279,53 @@ __global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant_
                 atomicMax(&red[3], h0); atomicMax(&red[4], h1); atomicMax(&red[5], h2);
             }
             __syncthreads();
+            int hi[3];
 #pragma unroll
-            for (int a = 0; a < 3; ++a) { lo[a] = red[a]; hi[a] = red[3 + a]; }
-            lo[0] &= ~7;                               // floor to a multiple of 8 (two's complement: also for negatives)
-            fits = hi[0] - lo[0] < BRICK_X && hi[1] - lo[1] < BRICK_Y && hi[2] - lo[2] < BRICK_Z;
+            for (int a = 0; a < 3; ++a) { S.lo[a] = red[a]; hi[a] = red[3 + a]; }
+            S.lo[0] &= ~7;                             // floor to a multiple of 8 (two's complement: also for negatives)
+            S.fits = hi[0] - S.lo[0] < BRICK_X && hi[1] - S.lo[1] < BRICK_Y && hi[2] - S.lo[2] < BRICK_Z;
             __syncthreads();                       // red[] is rewritten by the next attempt / slab
-            if (fits || K == 1) break;
+            if (S.fits || K == 1) break;
             K >>= 1;
         }
-        // ---- one TMA copy of the box (zero-filled outside the volume), everyone waits on the mbarrier
-        if (fits) {
-            if (tid == 0) {
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar)), "r"(BRICK_BYTES) : "memory");
-                asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-                             ::"r"(smem_u32(box)), "l"(&tmap), "r"(lo[0]), "r"(lo[1]), "r"(lo[2]), "r"(smem_u32(&bar)) : "memory");
-            }
+        S.K = K;
+        return S;
+    };
+    // ---- one TMA copy of the slab's box (zero-filled outside the volume) into buffer b, completing on bar[b]
+    auto request = [&](const BrickSlab& S, int b) {
+        if (S.fits && tid == 0) {
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bar[b])), "r"(BRICK_BOX_BYTES) : "memory");
+            asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                         ::"r"(smem_u32(dyn_smem + b * BRICK_BOX_STRIDE)), "l"(&tmap), "r"(S.lo[0]), "r"(S.lo[1]), "r"(S.lo[2]), "r"(smem_u32(&bar[b])) : "memory");
+        }
+    };
+    unsigned int phase_bits = 0;          // bit b: the parity bar[b] completes next
+    int buf = 0;
+    BrickSlab cur{};
+    if (n_max > 0) { cur = plan(0); request(cur, 0); }
+    for (int i0 = 0; i0 < n_max;) {
+        // the next slab's box goes out before this one is consumed (its buffer was last read one iteration ago, behind a barrier)
+        BrickSlab nxt{};
+        const int i_next = i0 + cur.K;
+        const bool more = i_next < n_max;
+        if (BRICK_STAGES > 1 && more) { nxt = plan(i_next); request(nxt, buf ^ 1); }
+        if (cur.fits) {
             unsigned int ok = 0;
+            const unsigned int ph = (phase_bits >> buf) & 1u;
             while (!ok)
                 asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                             : "=r"(ok) : "r"(smem_u32(&bar)), "r"(phase) : "memory");
-            phase ^= 1u;
+                             : "=r"(ok) : "r"(smem_u32(&bar[buf])), "r"(ph) : "memory");
+            phase_bits ^= 1u << buf;
         }
         // ---- K steps out of shared memory
-        const int i1 = min(i0 + K, n);
+        const __half* box = reinterpret_cast<const __half*>(dyn_smem + buf * BRICK_BOX_STRIDE);
+        const int i1 = min(i0 + cur.K, n);
         for (int i = i0; i < i1; ++i) {
             const float x = sub(mul(p.x, fw), 0.5f), y = sub(mul(p.y, fh), 0.5f), z = sub(mul(p.z, fd), 0.5f);
             const float x0 = floorf(x), y0 = floorf(y), z0 = floorf(z);
             const int gi = (int)x0, gj = (int)y0, gk = (int)z0;
-            const int li = gi - lo[0], lj = gj - lo[1], lk = gk - lo[2];
-            const bool staged = fits && gi >= 0 && gi + 1 < P.vw && gj >= 0 && gj + 1 < P.vh && gk >= 0 && gk + 1 < P.vd &&
+            const int li = gi - cur.lo[0], lj = gj - cur.lo[1], lk = gk - cur.lo[2];
+            const bool staged = cur.fits && gi >= 0 && gi + 1 < P.vw && gj >= 0 && gj + 1 < P.vh && gk >= 0 && gk + 1 < P.vd &&
                                 (unsigned)li < (unsigned)(BRICK_X - 1) && (unsigned)lj < (unsigned)(BRICK_Y - 1) && (unsigned)lk < (unsigned)(BRICK_Z - 1);
             float s;
             if (staged) {
@@ -1319,8 +1344,10 @@ __global__ void __launch_bounds__(128) march_brick_kernel(const __grid_constant_
             acc = add(acc, mul(s, P.sample_scale));
             p = add3(p, ray.step);                                  // running add, frag.glsl:74
         }
-        i0 += K;
-        __syncthreads();                           // everyone is done with the box before the next copy lands
+        i0 = i_next;
+        __syncthreads();                           // everyone is done with this box before a copy lands in it again
+        if (BRICK_STAGES > 1) { cur = nxt; buf ^= 1; }
+        else if (more) { cur = plan(i0); request(cur, 0); }
     }
     if (!in_frame) return;
     if (!covered) { store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f); return; }

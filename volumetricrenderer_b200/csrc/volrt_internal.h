@@ -173,7 +173,22 @@ int march_pick_segments(const MarchParams& p, int variant, int n_views, bool sta
 
 // TMA-staged brick march (VR_LAYOUT_BRICK): tensor_map = 128-byte CUtensorMap over the x-fastest fp16 volume
 cudaError_t launch_march_brick(const MarchParams& p, const void* tensor_map, int n_views, cudaStream_t stream);
-constexpr int kBrickBox[3] = {32, 24, 24};
+// The box a CTA of the TMA-staged march pulls per slab.  Round 1's 32 x 24 x 24 halves (16-word rows, 384-word planes) puts every
+// other row and every plane on the same banks: 70 % of the shared-memory wavefronts were conflicts.  Rows of 40 halves = 20 words
+// (consecutive rows start 20 banks apart: 20 m mod 32 runs through 8 windows of 4 banks) with 21 rows per plane (window 5 lk + lj
+// mod 8) cut the wavefronts 109 M -> 41 M and the conflicts 77 M -> 10.5 M per C4 frame — and the frame takes 1.55 ms instead of
+// 1.50: the kernel is bound by its 0.62 G warp instructions (software trilinear, ~75 per step against one TEX), not by the
+// shared-memory pipe.  Two boxes in flight (VOLRT_BRICK_STAGES=2, 3 CTAs per SM instead of 6): 1.81 ms.  Texture unit: 0.252 ms.
+// profiles/r02_march_brick_c4.txt.  Default = the fastest measured.
+#ifndef VOLRT_BRICK_X
+#define VOLRT_BRICK_X 32
+#define VOLRT_BRICK_Y 24
+#define VOLRT_BRICK_Z 24
+#endif
+#ifndef VOLRT_BRICK_STAGES
+#define VOLRT_BRICK_STAGES 1        // boxes in flight per CTA (each on its own mbarrier)
+#endif
+constexpr int kBrickBox[3] = {VOLRT_BRICK_X, VOLRT_BRICK_Y, VOLRT_BRICK_Z};
 
 // analytic per-row cost (sum of chord steps) for band balancing; cost[height] on device
 cudaError_t launch_row_cost(const MarchParams& p, int view, float* row_cost, cudaStream_t stream);
