@@ -11,7 +11,7 @@ for w in c2 c1 c3 c4s128 c4 c4s1024 c5 bake; do
 done
 python bench.py --impl reference --steps 2 --warmup 1 2>>$O/${R}_bench_final.err | tail -1 >> $O/${R}_bench_final.jsonl
 python bench.py --impl reference --workload c1 --steps 2 --warmup 1 2>>$O/${R}_bench_final.err | tail -1 >> $O/${R}_bench_final.jsonl
-python bench.py --steps 30 --warmup 5 > $O/${R}_bench_default.json 2>>$O/${R}_bench_final.err
+python bench.py --steps 30 --warmup 5 > $O/${R}_bench_default_pre.json 2>>$O/${R}_bench_final.err
 # launch list of the default command (after it has exited 0 without ncu, above)
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${R}_launches_default.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline > $O/ncu_launches.log 2>&1
 cap() {  # workload, kernel regex, skip: capture, summarise and record the DRAM traffic here (the reports are too large to travel)
@@ -26,4 +26,6 @@ cap c1 march_tex_split 4
 cap c4s128 march_kernel 4
 cap c5 march_kernel 4
 cp profiles/traffic.json $O/traffic.json
+# the default bench line again, now that traffic.json belongs to this kernel source (roofline.traffic filled in)
+python bench.py --steps 30 --warmup 5 > $O/${R}_bench_default.json 2>>$O/${R}_bench_final.err
 ls -la $O | tail -20
