@@ -363,6 +363,9 @@ __device__ __forceinline__ float light_sum(const MarchParams& P, const RayConst&
     return sumL;
 }
 
+// q = n / d with m = ceil(2^32 / d) from the host (0 stands for d = 1): exact while n * d < 2^32
+__device__ __forceinline__ unsigned int fast_div(unsigned int n, unsigned int m) { return m ? __umulhi(n, m) : n; }
+
 // ------------------------------------------------------------------ the march
 // one pixel: ray set-up, step loop, resolve, store  (frag.glsl:34-81 + A.6 extensions)
 // seg: this thread's depth segment of the ray (0 when the launch has none).  A thick ray of the procedural cloud is a
@@ -406,8 +409,10 @@ __device__ __forceinline__ void march_pixel(const MarchParams& P, const float* _
     if (segmented) {
         // this piece: steps [n*seg/K, n*(seg+1)/K), first position Pin + i*stepVec (like the lanes-per-ray kernels).  The loops
         // below count from 0 to the piece's length, so the lanes of a warp start together whatever their rays' lengths
-        const int seg_begin = (int)(((long long)n * seg) / P.segments);
-        n = (int)(((long long)n * (seg + 1)) / P.segments) - seg_begin;
+        // (n * seg / segments by the tile map's reciprocal of the inner count, which is the piece count here: two 64-bit
+        // divisions were ~200 instructions per piece and warp)
+        const int seg_begin = (int)fast_div((unsigned)(n * seg), P.map.div_inner);
+        n = (int)fast_div((unsigned)(n * (seg + 1)), P.map.div_inner) - seg_begin;
         const float fi = (float)seg_begin;
         p = {fmaf(ray.step.x, fi, p.x), fmaf(ray.step.y, fi, p.y), fmaf(ray.step.z, fi, p.z)};
     }
@@ -671,7 +676,6 @@ __device__ __forceinline__ int outward_from(int k, int n, int c) {
 // order (piece index fastest) — as separate z slices the pieces of a frame would be dispatched one whole frame after the other
 // The map's numbers come from the host (set_tile_map): as runtime divisions this prologue was ~175 instructions per warp, 15 % of
 // all the instructions of a 64-view batch, most of them in CTAs over empty tiles (ncu source page, round 2).
-__device__ __forceinline__ unsigned int fast_div(unsigned int n, unsigned int m) { return m ? __umulhi(n, m) : n; }
 __device__ __forceinline__ void tile_of_cta(const MarchParams& P, int& tx, int& ty, int* inner = nullptr) {
     const TileMap& M = P.map;
     int kx = (int)blockIdx.x, ky = (int)blockIdx.y;
