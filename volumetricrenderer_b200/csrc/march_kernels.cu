@@ -706,12 +706,21 @@ static void set_tile_map(MarchParams& p, dim3 grid, int inner, int tile_h, int t
     M.cy = cy < 0 ? 0 : cy > M.gy - 1 ? M.gy - 1 : cy;
 }
 
-// static shared memory of the march kernels: the gradient table first, so that it starts the CTA's shared window
-template <bool LINEAR>
-struct __align__(256) MarchSmem {
+// static shared memory of the march kernels: the gradient table first, so that it starts the CTA's shared window; the pair
+// table of the cell-table march (noise_device.cuh: PairLut) at a fixed offset behind it
+template <bool LINEAR, bool PAIR = false>
+struct __align__(512) MarchSmem {
     GradLut lut;                       // FBM / TREE variants
+    alignas(512) PairLut pair[1];      // MARCH_FBM_CELLS (PAIR; the other variants take the specialisation below)
     float unorm[LINEAR ? 256 : 1];     // LINEAR variants: i / 255
 };
+template <bool LINEAR>
+struct __align__(256) MarchSmem<LINEAR, false> {
+    GradLut lut;
+    float unorm[LINEAR ? 256 : 1];
+};
+using MarchSmemPair = MarchSmem<false, true>;
+static_assert(offsetof(MarchSmemPair, pair) == VOLRT_PAIR_LUT_OFFSET, "the cell-table march fetches its pair table at an immediate address");
 
 // The fBm kernels fetch gradients at an IMMEDIATE shared address (noise_device.cuh: GradLutFixed): the first static __shared__
 // object of a kernel sits at window address VOLRT_LUT_FIXED_ADDR on this toolchain and driver.  That is an observation, not
@@ -728,15 +737,16 @@ cudaError_t march_probe_lut_address(unsigned int* d_out, cudaStream_t s) {
 }
 unsigned int march_lut_fixed_address() { return (unsigned int)VOLRT_LUT_FIXED_ADDR; }
 
-template <int VARIANT>
-__device__ __forceinline__ void stage_tables(float* unorm, GradLut* lut) {
+template <int VARIANT, class SMEM>
+__device__ __forceinline__ void stage_tables(SMEM& smem) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
-    if (LINEAR) for (int i = threadIdx.x; i < 256; i += blockDim.x) unorm[i] = dvd((float)i, 255.0f);
+    if (LINEAR) for (int i = threadIdx.x; i < 256; i += blockDim.x) smem.unorm[i] = dvd((float)i, 255.0f);
     if (is_fbm(VARIANT)) {
         // the fBm march fetches gradients at an immediate shared address (noise_device.cuh: GradLutFixed)
-        if ((unsigned)__cvta_generic_to_shared(lut) != (unsigned)VOLRT_LUT_FIXED_ADDR) __trap();
+        if ((unsigned)__cvta_generic_to_shared(&smem.lut) != (unsigned)VOLRT_LUT_FIXED_ADDR) __trap();
     }
-    if (is_fbm(VARIANT) || VARIANT == MARCH_TREE) grad_lut_init(lut, threadIdx.x);
+    if (is_fbm(VARIANT) || VARIANT == MARCH_TREE) grad_lut_init(&smem.lut, threadIdx.x);
+    if constexpr (VARIANT == MARCH_FBM_CELLS) pair_lut_init(&smem.pair[0], threadIdx.x, blockDim.x);
     if (LINEAR || is_fbm(VARIANT) || VARIANT == MARCH_TREE) __syncthreads();
 }
 
@@ -773,10 +783,9 @@ __host__ __device__ constexpr int direct_min_ctas(int variant, bool composite) {
 template <int VARIANT, bool COMPOSITE, bool STATS>
 __global__ void __launch_bounds__(kCtaThreads, direct_min_ctas(VARIANT, COMPOSITE)) march_kernel(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
-    __shared__ MarchSmem<LINEAR> smem;
+    __shared__ MarchSmem<LINEAR, VARIANT == MARCH_FBM_CELLS> smem;
     float* const unorm = smem.unorm;
     GradLut& lut = smem.lut;
-    stage_tables<VARIANT>(unorm, &lut);
     int tx, ty, seg = 0, inner = 0;
     int view = P.view_begin + blockIdx.z;
     tile_of_cta(P, tx, ty, &inner);
@@ -788,6 +797,17 @@ __global__ void __launch_bounds__(kCtaThreads, direct_min_ctas(VARIANT, COMPOSIT
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int px = tx * (8 * kCtaWx) + (warp % kCtaWx) * 8 + (lane & 7);
     const int py = P.row_begin + ty * (4 * kCtaWy) + (warp / kCtaWx) * 4 + (lane >> 3);
+    {
+        // a tile that misses the cube's screen rectangle altogether (three quarters of a frame's tiles) clears its pixels and
+        // leaves before the tables are staged: CTA-uniform, ahead of the barrier in stage_tables
+        const ViewConst* __restrict__ V = P.views ? P.views + view : &P.view0;
+        const int x0 = tx * (8 * kCtaWx), y0 = P.row_begin + ty * (4 * kCtaWy);
+        if (x0 >= V->rect[2] || x0 + 8 * kCtaWx <= V->rect[0] || y0 >= V->rect[3] || y0 + 4 * kCtaWy <= V->rect[1]) {
+            if (seg == 0 && px < P.width && py < P.row_end) store_pixel(P, view, px, py, 0.0f, 0.0f, 0.0f, 1.0f);
+            return;
+        }
+    }
+    stage_tables<VARIANT>(smem);
     if (px >= P.width || py >= P.row_end) return;
     march_pixel<VARIANT, COMPOSITE, STATS>(P, unorm, lut, px, py, view, seg);
 }
@@ -804,10 +824,10 @@ __global__ void __launch_bounds__(kCtaThreads, direct_min_ctas(VARIANT, COMPOSIT
 template <int VARIANT, bool COMPOSITE, bool STATS>
 __global__ void __launch_bounds__(128, VOLRT_PERSISTENT_MIN_CTAS) march_kernel_persistent(const __grid_constant__ MarchParams P) {
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
-    __shared__ MarchSmem<LINEAR> smem;
+    __shared__ MarchSmem<LINEAR, VARIANT == MARCH_FBM_CELLS> smem;
     float* const unorm = smem.unorm;
     GradLut& lut = smem.lut;
-    stage_tables<VARIANT>(unorm, &lut);
+    stage_tables<VARIANT>(smem);
     const int lane = threadIdx.x & 31;
     const int tiles_x = (P.width + 7) >> 3, tiles_y = (P.row_end - P.row_begin + 3) >> 2;
     const int per_view = tiles_x * tiles_y, total = per_view * P.n_views;
@@ -923,10 +943,10 @@ march_composite_split_kernel(const __grid_constant__ MarchParams P) {
     constexpr int RAYS = 32 / S, RW = RAYS / 2;
     constexpr bool CAN_SKIP = (VARIANT == MARCH_SINGLE_TEX || VARIANT == MARCH_SINGLE_LINEAR);
     constexpr bool LINEAR = (VARIANT == MARCH_RGBA_LINEAR || VARIANT == MARCH_SINGLE_LINEAR);
-    __shared__ MarchSmem<LINEAR> smem;
+    __shared__ MarchSmem<LINEAR, VARIANT == MARCH_FBM_CELLS> smem;
     float* const unorm = smem.unorm;
     GradLut& lut = smem.lut;
-    stage_tables<VARIANT>(unorm, &lut);
+    stage_tables<VARIANT>(smem);
     int tx, ty;
     tile_of_cta(P, tx, ty);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -382,138 +382,97 @@ __device__ __forceinline__ f2 fbm_perlin2(LUT lut, const FbmField& F, f2 x, f2 y
 // cell (0,0,0)), whose bit pattern is 0x4B400000 + index, so the address is one IMAD.WIDE with an adjusted base.
 // Everything after the hash — fractions, fades, gradient dot products, lerps, in the same order — is unchanged, and the
 // table holds exactly what the hash would have produced: the value is bit-identical to perlin3_lut / perlin3_lut2.
-// Two entry formats (VOLRT_CELL_GRADIENT_BYTES, volrt_internal.h: kFbmCellBytes):
-//   0  8 bytes per cell: the eight corners' byte offsets into the shared-memory gradient table; a corner costs one PRMT, one
-//      LDS.128 and three FFMAs.  The LDS results are what binds then: 4 write-back cycles per corner and warp, the LSU
-//      write-back port 77 % busy at 68 % issue (profiles/r02_final_c2.txt).
-//   1  32 bytes per cell: the gradients THEMSELVES, one byte per component — 0x40, 0xC0 or 0x00, the top byte of +2.0f, -2.0f
-//      or 0.0f — so a component is one PRMT (byte -> top of a zero word) and nothing goes through shared memory.  The factor 2
-//      is taken out of the octave amplitude (amp / 2): every product, sum and lerp is scaled by an exact power of two, so the
-//      value is bit-identical.  Corner c's components are bytes 3c, 3c+1, 3c+2 of the entry (24 of the 32 bytes used).
-struct CellWords { unsigned int w[VOLRT_CELL_GRADIENT_BYTES ? 6 : 2]; };
+// What a cell entry holds and how a sample uses it (round 2, third form — the first two are in the experiments log):
+// the eight corners of a cell are taken as four PAIRS, (x0y0, x0y1) and (x1y0, x1y1) at z0 and at z1, and a pair fetches both
+// its gradients with one index from a 256-entry shared-memory table (PairLut: pair (n_a, n_b) of the 16 gradients -> their
+// components interleaved, (ax, bx, ay, by | az, bz)).  The dot products of the two x edges of a z plane then run side by side in
+// the halves of the packed FP32 instructions: d0 = g.(fx0, fy, fz) for corners x0y0 | x0y1 is FMUL2 + 2 FFMA2 (fy differs between
+// the halves: (fy0, fy1) is a register pair; fx0 and fz are broadcast operands), e' = d0 - g.(fx1, fy, fz) for x1y0 | x1y1 three
+// more FFMA2 with negated operands, and the x lerp d0 - s e' one — seven packed instructions for four corners where the
+// one-corner-at-a-time form took 28 scalar ones, four index extractions instead of eight, 24 LDS write-back cycles instead of
+// 32.  Each half performs the operations of grad_edge_lut in the same order with the same roundings (negating both factors'
+// sign and the accumulated value is exact), so the value is bit-identical to perlin3_lut.
+// ncu source page of the C2 kernel before this (profiles/r02_c2_source_hot.txt): 70.6 instructions per octave and point in the
+// light-march pairs, 26.7 of them the scalar corner FFMAs / FMULs, 8 PRMT, 8 LDS.
+struct __align__(16) PairLut { float4 a[256]; float4 b[256]; };      // a[i] = (ax, bx, ay, by), b[i] = (az, bz, -, -); i = n_a * 16 + n_b
+#ifndef VOLRT_PAIR_LUT_OFFSET
+#define VOLRT_PAIR_LUT_OFFSET 512            // of MarchSmem::pair from the start of the CTA's static shared memory (march_kernels.cu asserts it)
+#endif
+__device__ __forceinline__ void pair_lut_init(PairLut* t, int tid, int nthreads) {
+    for (int i = tid; i < 256; i += nthreads) {
+        float ax, ay, az, bx, by, bz;
+        grad_components(i >> 4, ax, ay, az);
+        grad_components(i & 15, bx, by, bz);
+        t->a[i] = make_float4(ax, bx, ay, by);
+        t->b[i] = make_float4(az, bz, 0.0f, 0.0f);
+    }
+}
+// byte offset of pair (ta, tb) in PairLut::a / ::b from the corners' lattice hashes (what a cell entry stores, 16 bits per pair)
+__device__ __forceinline__ unsigned int pair_lut_offset(int ta, int tb) { return (grad_lut_offset(ta) << 4) | grad_lut_offset(tb); }
+
+struct CellWords { unsigned int w[2]; };     // .w[0]: pairs of the z0 plane (x0 pair | x1 pair << 16), .w[1]: of the z1 plane
 __device__ __forceinline__ CellWords fbm_cell_fetch(const FbmCellOctave& C, float xs, float ys, float zs) {
     const float t = fmaf(zs, C.n2f, fmaf(ys, C.nf, xs + C.kf));
-    CellWords W;
-#if VOLRT_CELL_GRADIENT_BYTES
-    const char* e = reinterpret_cast<const char*>(C.base_adj + (unsigned long long)__float_as_uint(t) * 32ull);
-    const uint4 a = __ldg(reinterpret_cast<const uint4*>(e));
-    const uint2 b = __ldg(reinterpret_cast<const uint2*>(e + 16));
-    W.w[0] = a.x; W.w[1] = a.y; W.w[2] = a.z; W.w[3] = a.w; W.w[4] = b.x; W.w[5] = b.y;
-#else
     const uint2 v = __ldg(reinterpret_cast<const uint2*>(C.base_adj + (unsigned long long)__float_as_uint(t) * 8ull));
+    CellWords W;
     W.w[0] = v.x; W.w[1] = v.y;
-#endif
     return W;
 }
 // (floor() on the FMA pipe instead of FRND — x + (2^23 - 1/2) rounds once to 2^23 + rint(x - 1/2) — was measured: 1.457 vs
 // 1.441 ms at C2, profiles/r02_fbm_cells_experiments.txt; the XU pipe at 20 % is not what binds.)
 __device__ __forceinline__ float cell_floor(float x) { return floorf(x); }
 __device__ __forceinline__ f2 cell_floor2(f2 x) { return make_f2(floorf(f2_a(x)), floorf(f2_b(x))); }
-__device__ __forceinline__ unsigned int cell_corner(unsigned int w, int k) { return __byte_perm(w, 0u, 0x4440u + (unsigned)k); }
-// byte b of w as the top byte of an otherwise zero word
-__device__ __forceinline__ float cell_top_byte(unsigned int w, int b) { return __uint_as_float(__byte_perm(w, 0u, 0x0444u | ((unsigned)b << 12))); }
-// the 24 gradient bytes of a cell from its eight corner hashes t[c], as six words
-__device__ __forceinline__ void cell_gradient_words(const int t[8], unsigned int w[6]) {
-    unsigned char b[24];
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        float g[3];
-        grad_components((int)(grad_lut_offset(t[c]) >> 4), g[0], g[1], g[2]);
-#pragma unroll
-        for (int j = 0; j < 3; ++j) b[3 * c + j] = g[j] > 0.0f ? 0x40 : g[j] < 0.0f ? 0xC0 : 0x00;
-    }
-#pragma unroll
-    for (int k = 0; k < 6; ++k) w[k] = (unsigned)b[4 * k] | (unsigned)b[4 * k + 1] << 8 | (unsigned)b[4 * k + 2] << 16 | (unsigned)b[4 * k + 3] << 24;
+
+struct PairGrad { f2 x, y, z; };             // components of the pair's two gradients, side by side
+__device__ __forceinline__ PairGrad pair_lut_at(GradLutFixed, unsigned int off) {
+    PairGrad g;
+    asm("ld.shared.v2.b64 {%0, %1}, [%2 + %3];" : "=l"(g.x.v), "=l"(g.y.v) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR + VOLRT_PAIR_LUT_OFFSET));
+    asm("ld.shared.b64 %0, [%1 + %2];" : "=l"(g.z.v) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR + VOLRT_PAIR_LUT_OFFSET + 4096));
+    return g;
 }
-constexpr float kCellAmpScale = VOLRT_CELL_GRADIENT_BYTES ? 0.5f : 1.0f;      // the gradients above are twice FastNoise2's
-// off = the byte an 8-byte cell-table entry holds for the corner: n * 16 into g[], or (VOLRT_CELLS_LDS64) n * 8 into h[].
-// Measured on B200, C2: the 8-byte entries halve the shared-memory wavefronts (306 M -> 146 M per frame) but their two
-// decode instructions per corner cost more than that buys — 1.104 G -> 1.296 G warp instructions, 1.478 -> 1.553 ms
-// (profiles/r02_march_fbm_cells_lds128.txt / _lds64.txt); with some corners of a cell on either form the time does not move
-// (mask 0x01 / 0x11 / 0x21 / 0x55: 1.435 / 1.427 / 1.421 / 1.462 against 1.430 ms).
-#ifndef VOLRT_CELLS_LDS64
-#define VOLRT_CELLS_LDS64 0
-#endif
-// bit c set: corner c of a cell (x0y0z0, x1y0z0, x0y1z0, x1y1z0, then z1) takes the 8-byte form
-#ifndef VOLRT_CELLS_LDS64_MASK
-#define VOLRT_CELLS_LDS64_MASK (VOLRT_CELLS_LDS64 ? 0xFF : 0)
-#endif
-__host__ __device__ constexpr bool cell_corner_is64(int c) { return ((VOLRT_CELLS_LDS64_MASK) >> c) & 1; }
-template <bool W64>
-__device__ __forceinline__ float4 grad_lut_at(GradLutFixed, unsigned int off) {
-    if constexpr (W64) {
-        unsigned int a, b;
-        asm("ld.shared.v2.u32 {%0, %1}, [%2 + %3];" : "=r"(a), "=r"(b) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR + 256));
-        return make_float4(__uint_as_float(a), __uint_as_float(b & 0xffff0000u), __uint_as_float(b << 16), 0.0f);
-    } else {
-        float4 g;
-        asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4 + %5];" : "=f"(g.x), "=f"(g.y), "=f"(g.z), "=f"(g.w) : "r"(off), "n"(VOLRT_LUT_FIXED_ADDR));
-        return g;
-    }
+// one z plane of a cell: the x edges at y0 | y1 lerped along x, then along y
+__device__ __forceinline__ float cell_plane(GradLutFixed lut, unsigned int w, float fx0, float fx1, f2 fy, float fz, float sx, float sy) {
+    const PairGrad g0 = pair_lut_at(lut, w & 0xffffu), g1 = pair_lut_at(lut, w >> 16);
+    f2 d0 = mul2(splat2(fx0), g0.x);
+    d0 = fma2(fy, g0.y, d0);
+    d0 = fma2(splat2(fz), g0.z, d0);
+    const f2 nfy = make_f2(-f2_a(fy), -f2_b(fy));
+    f2 e = fma2(splat2(-fx1), g1.x, d0);          // d0 - g1.(fx1, fy, fz): the negative of grad_edge_lut's e, to the bit
+    e = fma2(nfy, g1.y, e);
+    e = fma2(splat2(-fz), g1.z, e);
+    const f2 r = fma2(splat2(-sx), e, d0);        // = fma(sx, e_of_grad_edge_lut, d0)
+    return lerpf(f2_a(r), f2_b(r), sy);
 }
-__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t, int corner) { return cell_corner_is64(corner) ? grad_lut_offset8(t) : grad_lut_offset(t); }
-template <bool W64>
-__device__ __forceinline__ float4 grad_lut_at(const GradLut* lut, unsigned int off) {
-    if constexpr (W64) {
-        const uint2 v = *reinterpret_cast<const uint2*>(reinterpret_cast<const char*>(lut->h) + off);
-        return make_float4(__uint_as_float(v.x), __uint_as_float(v.y & 0xffff0000u), __uint_as_float(v.y << 16), 0.0f);
-    } else {
-        return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + off);
-    }
-}
-// gradient of corner C of the fetched cell
-template <int C, class LUT>
-__device__ __forceinline__ float4 cell_gradient(LUT lut, const CellWords& W) {
-#if VOLRT_CELL_GRADIENT_BYTES
-    return make_float4(cell_top_byte(W.w[(3 * C) >> 2], (3 * C) & 3), cell_top_byte(W.w[(3 * C + 1) >> 2], (3 * C + 1) & 3),
-                       cell_top_byte(W.w[(3 * C + 2) >> 2], (3 * C + 2) & 3), 0.0f);
-#else
-    return grad_lut_at<cell_corner_is64(C)>(lut, cell_corner(W.w[C >> 2], C & 3));
-#endif
-}
-// the x edge between corners C0 and C0 + 1
-template <int C0, class LUT>
-__device__ __forceinline__ float grad_edge_at(LUT lut, const CellWords& W, float fx0, float fx1, float fy, float fz, float s) {
-    const float4 g0 = cell_gradient<C0>(lut, W), g1 = cell_gradient<C0 + 1>(lut, W);
-    const float d0 = fmaf(fz, g0.z, fmaf(fy, g0.y, fx0 * g0.x));
-    const float e = fmaf(fz, g1.z, fmaf(fy, g1.y, fmaf(fx1, g1.x, -d0)));
-    return fmaf(s, e, d0);
-}
-template <int I = -1, class LUT>
-__device__ __forceinline__ float perlin3_cells(LUT lut, const FbmCellOctave& C, float x, float y, float z) {
+template <int I = -1>
+__device__ __forceinline__ float perlin3_cells(GradLutFixed lut, const FbmCellOctave& C, float x, float y, float z) {
     float xs = cell_floor(x), ys = cell_floor(y), zs = cell_floor(z);
     const CellWords W = fbm_cell_fetch(C, xs, ys, zs);
-    float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
-    float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
+    const float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
+    const float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
     xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
-    float a = lerpf(grad_edge_at<0>(lut, W, xf0, xf1, yf0, zf0, xs), grad_edge_at<2>(lut, W, xf0, xf1, yf1, zf0, xs), ys);
-    float b = lerpf(grad_edge_at<4>(lut, W, xf0, xf1, yf0, zf1, xs), grad_edge_at<6>(lut, W, xf0, xf1, yf1, zf1, xs), ys);
+    const f2 fy = make_f2(yf0, yf1);
+    const float a = cell_plane(lut, W.w[0], xf0, xf1, fy, zf0, xs, ys);
+    const float b = cell_plane(lut, W.w[1], xf0, xf1, fy, zf1, xs, ys);
     return lerpf(a, b, zs);
 }
-template <int C0, class LUT>
-__device__ __forceinline__ f2 grad_edge_at2(LUT lut, const CellWords& WA, const CellWords& WB, f2 fx0, f2 fx1, f2 fy, f2 fz, f2 s) {
-    const float4 a0 = cell_gradient<C0>(lut, WA), a1 = cell_gradient<C0 + 1>(lut, WA);
-    const float4 b0 = cell_gradient<C0>(lut, WB), b1 = cell_gradient<C0 + 1>(lut, WB);
-    const float fyA = f2_a(fy), fyB = f2_b(fy), fzA = f2_a(fz), fzB = f2_b(fz);
-    const float d0A = fmaf(fzA, a0.z, fmaf(fyA, a0.y, f2_a(fx0) * a0.x));
-    const float d0B = fmaf(fzB, b0.z, fmaf(fyB, b0.y, f2_b(fx0) * b0.x));
-    const float eA = fmaf(fzA, a1.z, fmaf(fyA, a1.y, fmaf(f2_a(fx1), a1.x, -d0A)));
-    const float eB = fmaf(fzB, b1.z, fmaf(fyB, b1.y, fmaf(f2_b(fx1), b1.x, -d0B)));
-    return fma2(s, make_f2(eA, eB), make_f2(d0A, d0B));
-}
-template <int I = -1, class LUT>
-__device__ __forceinline__ f2 perlin3_cells2(LUT lut, const FbmCellOctave& C, f2 x, f2 y, f2 z) {
+// two points: what does not go through the table (floor, fractions, fades, the z lerp) stays packed ACROSS the points
+template <int I = -1>
+__device__ __forceinline__ f2 perlin3_cells2(GradLutFixed lut, const FbmCellOctave& C, f2 x, f2 y, f2 z) {
     f2 xs = cell_floor2(x), ys = cell_floor2(y), zs = cell_floor2(z);
     const CellWords WA = fbm_cell_fetch(C, f2_a(xs), f2_a(ys), f2_a(zs));
     const CellWords WB = fbm_cell_fetch(C, f2_b(xs), f2_b(ys), f2_b(zs));
     const f2 xf0 = sub2(x, xs), yf0 = sub2(y, ys), zf0 = sub2(z, zs);
     const f2 m1 = splat2(-1.0f);
-    const f2 xf1 = add2(xf0, m1), yf1 = add2(yf0, m1), zf1 = add2(zf0, m1);
+    const f2 xf1 = add2(xf0, m1), zf1 = add2(zf0, m1);
     xs = quintic2(xf0); ys = quintic2(yf0); zs = quintic2(zf0);
-    const f2 a = lerp2(grad_edge_at2<0>(lut, WA, WB, xf0, xf1, yf0, zf0, xs), grad_edge_at2<2>(lut, WA, WB, xf0, xf1, yf1, zf0, xs), ys);
-    const f2 b = lerp2(grad_edge_at2<4>(lut, WA, WB, xf0, xf1, yf0, zf1, xs), grad_edge_at2<6>(lut, WA, WB, xf0, xf1, yf1, zf1, xs), ys);
-    return lerp2(a, b, zs);
+    const f2 fyA = make_f2(f2_a(yf0), f2_a(yf0) - 1.0f), fyB = make_f2(f2_b(yf0), f2_b(yf0) - 1.0f);
+    const float a0 = cell_plane(lut, WA.w[0], f2_a(xf0), f2_a(xf1), fyA, f2_a(zf0), f2_a(xs), f2_a(ys));
+    const float a1 = cell_plane(lut, WA.w[1], f2_a(xf0), f2_a(xf1), fyA, f2_a(zf1), f2_a(xs), f2_a(ys));
+    const float b0 = cell_plane(lut, WB.w[0], f2_b(xf0), f2_b(xf1), fyB, f2_b(zf0), f2_b(xs), f2_b(ys));
+    const float b1 = cell_plane(lut, WB.w[1], f2_b(xf0), f2_b(xf1), fyB, f2_b(zf1), f2_b(xs), f2_b(ys));
+    return lerp2(make_f2(a0, b0), make_f2(a1, b1), zs);
 }
+constexpr float kCellAmpScale = 1.0f;
 // the compile-time octave count (C2 / C3: 5), octave by octave
 template <int I, int OCT, class LUT>
 __device__ __forceinline__ float fbm_cells_unrolled(LUT lut, const FbmField& F, const FbmCells& T, float x, float y, float z, float amp, float sum) {

@@ -144,8 +144,8 @@ cudaError_t launch_smoke_fill(const FbmField& f, int n, __half* out, cudaStream_
 
 // fBm lattice-cell table of one octave (volrt_internal.h: FbmCells; noise_device.cuh: perlin3_cells): entry (ix,iy,iz), stored at
 // ((iz+1)*n + iy+1)*n + ix+1 for lattice coordinates -1 .. n-2, holds the gradient-table offsets of the cell's eight corners —
-// what perlin3_lut derives per sample from HashPrimes (Utils.inl:295-302) — as bytes x0y0, x1y0, x0y1, x1y1 at z0 (.x) and z1 (.y) —
-// or, in the 32-byte format, the eight gradients themselves (noise_device.cuh: fbm_cell_fetch).
+// what perlin3_lut derives per sample from HashPrimes (Utils.inl:295-302) — as four 16-bit offsets into the pair table
+// (noise_device.cuh: PairLut), the z0 plane's two corner pairs in .x and the z1 plane's in .y.
 __global__ void __launch_bounds__(256) fbm_cell_table_kernel(int seed, int n, void* __restrict__ entries) {
     const int total = n * n * n, idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
@@ -154,18 +154,10 @@ __global__ void __launch_bounds__(256) fbm_cell_table_kernel(int seed, int n, vo
     const int x1 = x0 + kPrimeX, y1 = y0 + kPrimeY, z1 = z0 + kPrimeZ;
     const int sz0 = seed ^ z0, sz1 = seed ^ z1;
     const int t[8] = {sz0 ^ x0 ^ y0, sz0 ^ x1 ^ y0, sz0 ^ x0 ^ y1, sz0 ^ x1 ^ y1, sz1 ^ x0 ^ y0, sz1 ^ x1 ^ y0, sz1 ^ x0 ^ y1, sz1 ^ x1 ^ y1};
-#if VOLRT_CELL_GRADIENT_BYTES
-    unsigned int w[6];
-    cell_gradient_words(t, w);                     // the gradients themselves, a byte per component
-    uint4* e = reinterpret_cast<uint4*>(entries) + 2 * (size_t)idx;
-    e[0] = make_uint4(w[0], w[1], w[2], w[3]);
-    e[1] = make_uint4(w[4], w[5], 0u, 0u);
-#else
     uint2 e;
-    e.x = grad_lut_cell_byte(t[0], 0) | grad_lut_cell_byte(t[1], 1) << 8 | grad_lut_cell_byte(t[2], 2) << 16 | grad_lut_cell_byte(t[3], 3) << 24;
-    e.y = grad_lut_cell_byte(t[4], 4) | grad_lut_cell_byte(t[5], 5) << 8 | grad_lut_cell_byte(t[6], 6) << 16 | grad_lut_cell_byte(t[7], 7) << 24;
+    e.x = pair_lut_offset(t[0], t[2]) | pair_lut_offset(t[1], t[3]) << 16;      // z0: corners x0y0 | x0y1, then x1y0 | x1y1
+    e.y = pair_lut_offset(t[4], t[6]) | pair_lut_offset(t[5], t[7]) << 16;      // z1
     reinterpret_cast<uint2*>(entries)[idx] = e;
-#endif
 }
 cudaError_t launch_fbm_cell_table(int seed, int n, void* entries, cudaStream_t s) {
     const int total = n * n * n;

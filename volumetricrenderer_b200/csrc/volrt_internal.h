@@ -51,18 +51,11 @@ struct FbmField {
 };
 
 // Lattice-cell tables of the fBm field (noise_device.cuh: perlin3_cells).  Per octave, one uint2 per lattice CELL of the
-// box: the eight corners' offsets into the gradient table (bytes: x0y0, x1y0, x0y1, x1y1 at z0 in .x, at z1 in .y), i.e.
-// FastNoise2's HashPrimes + the low nibble GetGradientDot looks at (Utils.inl:229-247,295-302), evaluated once per cell
+// box: its eight corners as four pairs, each a 16-bit offset into the shared-memory pair table (x0y0 | x0y1 and x1y0 | x1y1 at z0
+// in .x, at z1 in .y), i.e. FastNoise2's HashPrimes + the low nibble GetGradientDot looks at (Utils.inl:229-247,295-302), evaluated once per cell
 // at vr_set_params instead of eight times per sample per octave.  Cells cover lattice coordinates -1 .. n-2 per axis.
 constexpr int kFbmCellMaxOctaves = 8;
-// 0: an entry holds eight offsets into the shared-memory gradient table (8-byte entry); 1: the eight gradients themselves (24 bytes
-// of a 32-byte entry, no shared memory on the path; noise_device.cuh: fbm_cell_fetch).  Measured on B200, bit-identical frames:
-// C2 1.433 (0) against 1.448 ms (1), C3 13.56 against 14.01 — the 16 extra PRMTs per octave and point cost what the LDS
-// write-back port gives back (profiles/r02_fbm_cells_experiments.txt).
-#ifndef VOLRT_CELL_GRADIENT_BYTES
-#define VOLRT_CELL_GRADIENT_BYTES 0
-#endif
-constexpr int kFbmCellBytes = VOLRT_CELL_GRADIENT_BYTES ? 32 : 8;
+constexpr int kFbmCellBytes = 8;     // four 16-bit offsets into the shared-memory pair table (noise_device.cuh: PairLut)
 struct FbmCellOctave {
     unsigned long long base_adj;   // device address of cell (-1,-1,-1)'s entry, minus kFbmCellBytes * 0x4B400000 (the index arrives as float bits)
     float nf, n2f, kf;             // n, n*n, and 1.5*2^23 + n*n + n + 1 (magic + the offset of lattice coordinate (0,0,0))
