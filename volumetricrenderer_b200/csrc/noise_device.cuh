@@ -448,9 +448,9 @@ __device__ __forceinline__ float perlin3_cells(GradLutFixed lut, const FbmCellOc
     float xs = cell_floor(x), ys = cell_floor(y), zs = cell_floor(z);
     const CellWords W = fbm_cell_fetch(C, xs, ys, zs);
     const float xf0 = x - xs, yf0 = y - ys, zf0 = z - zs;
-    const float xf1 = xf0 - 1.0f, yf1 = yf0 - 1.0f, zf1 = zf0 - 1.0f;
+    const float xf1 = xf0 - 1.0f, zf1 = zf0 - 1.0f;
     xs = quintic(xf0); ys = quintic(yf0); zs = quintic(zf0);
-    const f2 fy = make_f2(yf0, yf1);
+    const f2 fy = add2(splat2(yf0), make_f2(0.0f, -1.0f));
     const float a = cell_plane(lut, W.w[0], xf0, xf1, fy, zf0, xs, ys);
     const float b = cell_plane(lut, W.w[1], xf0, xf1, fy, zf1, xs, ys);
     return lerpf(a, b, zs);
@@ -465,7 +465,9 @@ __device__ __forceinline__ f2 perlin3_cells2(GradLutFixed lut, const FbmCellOcta
     const f2 m1 = splat2(-1.0f);
     const f2 xf1 = add2(xf0, m1), zf1 = add2(zf0, m1);
     xs = quintic2(xf0); ys = quintic2(yf0); zs = quintic2(zf0);
-    const f2 fyA = make_f2(f2_a(yf0), f2_a(yf0) - 1.0f), fyB = make_f2(f2_b(yf0), f2_b(yf0) - 1.0f);
+    // (fy0, fy0 - 1) per point as ONE packed add of the broadcast fraction and the pair (0, -1): t + 0 is t (fractions are never -0)
+    const f2 c01 = make_f2(0.0f, -1.0f);
+    const f2 fyA = add2(splat2(f2_a(yf0)), c01), fyB = add2(splat2(f2_b(yf0)), c01);
     const float a0 = cell_plane(lut, WA.w[0], f2_a(xf0), f2_a(xf1), fyA, f2_a(zf0), f2_a(xs), f2_a(ys));
     const float a1 = cell_plane(lut, WA.w[1], f2_a(xf0), f2_a(xf1), fyA, f2_a(zf1), f2_a(xs), f2_a(ys));
     const float b0 = cell_plane(lut, WB.w[0], f2_b(xf0), f2_b(xf1), fyB, f2_b(zf0), f2_b(xs), f2_b(ys));
