@@ -25,7 +25,7 @@ for line in out.splitlines():
         kernels[cur][m.group(1)] += 1
 print("# static SASS instruction counts per kernel, cuobjdump -sass %s (sm_100a)" % os.path.relpath(lib, ROOT))
 print("# FFMA2/FMUL2/FADD2 = packed FP32 (two binary32 operations per instruction, sm_100+), UTMALDG = TMA tensor load, SYNCS = mbarrier,")
-print("# TEX/TLD = texture unit, PRMT = byte extraction of the fBm cell tables' corner offsets, REDUX = warp reduce")
+print("# TEX/TLD = texture unit, PRMT = byte permute, REDUX = warp reduce")
 hdr = ["total"] + WATCH
 print("%-78s %s" % ("kernel", " ".join("%7s" % h for h in hdr)))
 for k, c in kernels.items():

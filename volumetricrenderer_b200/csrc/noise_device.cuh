@@ -62,11 +62,6 @@ __device__ __forceinline__ float perlin3(int seed, float x, float y, float z) {
 // The table offset n*16 comes straight from the integer pipe of the FMA unit:
 //   h = t*C;  h16 = t*(C<<4) = h<<4;  off = (h16 ^ (h16 >> 15)) & 0xF0  ==  (((h >> 15) ^ h) & 15) * 16
 // (bits 4..7 of h16>>15 are bits 15..18 of h: the four bits the left shift drops are never looked at)
-// h[n] = the same gradient in 8 bytes for the cell-table march (perlin3_cells): .x = cx as float, .y = the upper halves of cy
-// and cz side by side (cy_bits & 0xffff0000 | cz_bits >> 16) — components are -1, 0 or +1, whose lower 16 mantissa bits are
-// zero, so one AND and one shift give the floats back exactly.  An LDS.64 costs the shared-memory pipe 2 wavefronts per
-// warp where the LDS.128 costs 4, and that pipe — not issue — bounds the march once the hashes are gone
-// (profiles/r02_march_fbm_cells_lds128.txt: 75 % of its peak at 68 % issue).
 // the components (cx, cy, cz) of gradient n of the 16 (Utils.inl:229-247: what GetGradientDot multiplies by)
 __host__ __device__ inline void grad_components(int n, float& cx, float& cy, float& cz) {
     const int h13 = n & 13;
@@ -78,7 +73,7 @@ __host__ __device__ inline void grad_components(int n, float& cx, float& cy, flo
     cy = (iu == 1 ? su : 0.0f) + (iv == 1 ? sv : 0.0f);
     cz = iv == 2 ? sv : 0.0f;
 }
-struct __align__(16) GradLut { float4 g[16]; uint2 h[16]; };
+struct __align__(16) GradLut { float4 g[16]; };
 
 __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
     if (tid < 16) {
@@ -86,11 +81,8 @@ __device__ __forceinline__ void grad_lut_init(GradLut* lut, int tid) {
         float cx, cy, cz;
         grad_components(n, cx, cy, cz);
         lut->g[n] = make_float4(cx, cy, cz, 0.0f);
-        lut->h[n] = make_uint2(__float_as_uint(cx), (__float_as_uint(cy) & 0xffff0000u) | (__float_as_uint(cz) >> 16));
     }
 }
-// byte offset of h[n] from the start of the table for a lattice hash t (the cell tables store this, one byte per corner)
-__device__ __forceinline__ unsigned int grad_lut_offset8(int t);
 
 // A table the kernel guarantees to sit at shared-window address kLutFixedAddr (the first static __shared__ object of a
 // non-cluster launch on sm_100a: the window starts with 1 KiB the system keeps).  The table base then is an immediate
@@ -109,9 +101,6 @@ __device__ __forceinline__ unsigned int grad_lut_offset(int t) {
     // measured in round 1: C2 1.769 -> 1.936 ms; not kept)
     return (h16 ^ (h16 >> 15)) & 0xF0u;
 }
-__device__ __forceinline__ unsigned int grad_lut_offset8(int t) { return grad_lut_offset(t) >> 1; }
-// what a cell-table byte holds (grad_lut_at)
-__device__ __forceinline__ unsigned int grad_lut_cell_byte(int t, int corner);
 __device__ __forceinline__ float4 grad_lut_fetch(const GradLut* lut, int t) {
     return *reinterpret_cast<const float4*>(reinterpret_cast<const char*>(lut->g) + grad_lut_offset(t));
 }

@@ -74,6 +74,7 @@ struct TileMap {
     int swap;                   // gy < gx: the linear index runs down the columns
     int cy;                     // tile row nearest the frame's centre row
     int tx0, ty0;               // first tile of the launch (a launch restricted to the views' screen rectangle: batch_rect)
+    int linear;                 // tiles in plain row-major order instead of centre-out (view batches over a volume larger than L2)
 };
 struct MarchParams {
     // target
