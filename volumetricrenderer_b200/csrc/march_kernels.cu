@@ -706,7 +706,9 @@ static void set_tile_map(MarchParams& p, dim3 grid, int inner, int tile_h, int t
     M.inner = inner > 1 ? inner : 1;
     M.div_inner = fast_div_magic((unsigned)M.inner);
     M.div_gy = fast_div_magic((unsigned)M.gy);
-    M.swap = M.gy < M.gx;
+    // the reciprocal division is exact while n * d < 2^32: n < gx * gy, d = gy (frames up to 32768^2 are accepted; the ones
+    // too large for that keep x as the fast axis)
+    M.swap = M.gy < M.gx && (unsigned long long)M.gx * M.gy * M.gy < 0x100000000ull;
     const int cy = (p.height / 2 - p.row_begin) / tile_h - ty0;
     M.cy = cy < 0 ? 0 : cy > M.gy - 1 ? M.gy - 1 : cy;
 }
