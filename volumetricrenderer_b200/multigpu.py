@@ -77,6 +77,7 @@ class BandGather:
             raise ValueError(mode)
         self.dist, self.rank, self.world, self.height, self.mode = dist, rank, world, height, mode
         self.bounds = [0, height] if world == 1 else None
+        self.last_times = self.last_bounds = None
         self.mapped = None
 
     # ---- partition (rank 0 decides, everyone learns)
@@ -101,6 +102,7 @@ class BandGather:
             return self.bounds
         times = [None] * self.world
         self.dist.all_gather_object(times, float(my_ms))
+        self.last_times, self.last_bounds = times, list(self.bounds)      # what was measured, and for which cut
         self.bounds = rescale_and_split(row_cost, self.bounds, times)
         return self.bounds
 
