@@ -72,7 +72,7 @@ def config_for(workload, world, layout, has_volume, single_process=False):
         part = ("cost-balanced row bands, peer stores into GPU0's frame over NVLink; one process, one context over all devices"
                 if single_process else "cost-balanced row bands, peer stores into GPU0's frame over NVLink (CUDA IPC)")
     return {"workload": "%s: %s" % (workload, desc), "width": W, "height": H,
-            "l2": "flushed between frames (256 MiB write); the procedural workloads read no input",
+            "l2": "flushed between frames (256 MiB written, then read back so that L2 is left clean); the procedural workloads read no input",
             "partition": part, "volume_layout": layout if has_volume else None}
 
 
@@ -718,7 +718,7 @@ def run_bake(args, rank, world, local):
         line = {
             "metric": "Mpoints/s", "value": world * pts / (ms * 1e-3) / 1e6, "unit": "Mpoints/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "bake: " + desc, "size": n, "l2": "flushed between bakes (256 MiB write)",
+            "config": {"workload": "bake: " + desc, "size": n, "l2": "flushed between bakes (256 MiB written, then read back)",
                        "partition": "replicas (every GPU bakes its own copy of the volume)" if world > 1 else "single GPU"},
             "e2e": {"value": world * pts / e2e_s / 1e6, "unit": "Mpoints/s", "ms_per_bake": e2e_s * 1e3,
                     "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 4 * n ** 3},

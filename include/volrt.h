@@ -304,7 +304,7 @@ VR_API vr_status vr_gather_acquire(vr_context* ctx, void* frame0, uint32_t frame
 VR_API vr_status vr_gather_signal(vr_context* ctx, void* frame0, uint32_t frames, uint32_t slot);
 VR_API vr_status vr_gather_collect(vr_context* ctx, uint32_t slot, uint32_t arrivals, void* dst_host, size_t row_pitch);
 /* measurement helpers: evict the 126 MB L2 between timed frames (writes a 256 MiB scratch buffer on
- * the context's stream); page-locked host memory so that vr_render's D2H copy and
+ * the context's stream and reads it back, so that L2 is left without dirty lines); page-locked host memory so that vr_render's D2H copy and
  * vr_upload_volume's H2D copy run at full PCIe rate (the reference maps its UBOs and stages
  * its texture through host-visible Vulkan memory: VulkanUniformBuffer.h:30-45, VulkanTexture.cpp:121-128) */
 VR_API vr_status vr_flush_l2(vr_context* ctx);

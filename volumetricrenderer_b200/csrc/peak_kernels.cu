@@ -75,10 +75,27 @@ __global__ void __launch_bounds__(256) tex_stream_kernel(cudaTextureObject_t tex
 }
 // Measured on B200 over the 512^3 fp16 grid (268 MB, L2 flushed), GB/s: warp = 8x2x2 fetches with 1 / 4 / 8 per thread along z
 // 3449 / 3547 / 3542; warp = 32x1x1 with 1 / 4: 3451 / 3591; warp = 4x4x2 with 1 / 4: 3544 / 3644.  Whatever the walk, the
-// texture path streams first-touch texels out of DRAM at 3.45-3.65 TB/s = 53-56 % of the 6551 GB/s a copy reaches.
+// texture path streams first-touch texels out of DRAM at 3.45-3.65 TB/s behind a write-only L2 flush and at 4.30-4.37 TB/s = 66 % of the
+// 6551 GB/s a copy reaches behind a flush that leaves L2 clean (l2_sweep_kernel below).
 cudaError_t launch_tex_stream(cudaTextureObject_t tex, int nx, int ny, int nz, float* sink, cudaStream_t s) {
     const int fx = nx / 2, fy = ny / 2, fz = nz / 2;
     tex_stream_kernel<4, 2><<<dim3((fx + 7) / 8, (fy + 7) / 8, (fz + 15) / 16), 256, 0, s>>>(tex, nx, ny, nz, sink);
+    return cudaGetLastError();
+}
+
+// Second half of vr_flush_l2: read the buffer the memset has just written.  The write alone leaves L2 full of DIRTY lines, and
+// the kernel that is then timed pays for their write-back while it streams its own data in (a 512^3 fp16 march: 92 us against the
+// 80 us ncu measures for it behind a clean flush).  After this sweep L2 holds clean lines of an unrelated buffer: cold and quiet.
+__global__ void __launch_bounds__(256) l2_sweep_kernel(const uint4* __restrict__ buf, size_t n16, unsigned int* __restrict__ sink) {
+    unsigned int acc = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) {
+        const uint4 v = __ldcg(buf + i);
+        acc ^= v.x ^ v.y ^ v.z ^ v.w;
+    }
+    if (acc == 0x12345679u) *sink = acc;          // never (the buffer holds 0xA5 bytes): keeps the loads
+}
+cudaError_t launch_l2_sweep(const void* buf, size_t bytes, unsigned int* sink, int sms, cudaStream_t s) {
+    l2_sweep_kernel<<<(sms > 0 ? sms : 148) * 8, 256, 0, s>>>((const uint4*)buf, bytes / 16, sink);
     return cudaGetLastError();
 }
 

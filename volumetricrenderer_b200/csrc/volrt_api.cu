@@ -1666,6 +1666,9 @@ extern "C" vr_status vr_flush_l2(vr_context* c) {
     VR_CUDA(c, cudaSetDevice(c->device));
     if (!c->flush_buf) VR_CUDA(c, cudaMalloc(&c->flush_buf, bytes));
     VR_CUDA(c, cudaMemsetAsync(c->flush_buf, 0xA5, bytes, c->stream));
+    // ... and read it back, so that what the write leaves in L2 is clean (peak_kernels.cu: l2_sweep_kernel)
+    const char* env = std::getenv("VOLRT_FLUSH_READ");
+    if (!env || std::atoi(env) != 0) VR_CUDA(c, launch_l2_sweep(c->flush_buf, bytes, (unsigned int*)c->d_counters + 15, c->sm_count, c->stream));
     return VR_OK;
 }
 extern "C" void* vr_host_alloc(size_t bytes) {

@@ -205,6 +205,7 @@ cudaError_t launch_brick_distance(const uint8_t* occupied, uint8_t* dist, uint8_
 cudaError_t launch_brick_pad(const uint8_t* dist, uint8_t* pad, int bx, int by, int bz, cudaStream_t s);
 // ---- peak_kernels.cu: measured roofline denominators
 cudaError_t launch_fma_peak(float* sink, int blocks, int iters, cudaStream_t s);
+cudaError_t launch_l2_sweep(const void* buf, size_t bytes, unsigned int* sink, int sms, cudaStream_t s);
 cudaError_t launch_tex_peak(cudaTextureObject_t tex, float* sink, int blocks, int iters, cudaStream_t s);
 cudaError_t launch_tex_stream(cudaTextureObject_t tex, int nx, int ny, int nz, float* sink, cudaStream_t s);
 // ---- min-max pyramid (noise_kernels.cu; layout in include/volrt.h)
