@@ -463,7 +463,6 @@ __device__ __forceinline__ f2 perlin3_cells2(GradLutFixed lut, const FbmCellOcta
     const float b1 = cell_plane(lut, WB.w[1], f2_b(xf0), f2_b(xf1), fyB, f2_b(zf1), f2_b(xs), f2_b(ys));
     return lerp2(make_f2(a0, b0), make_f2(a1, b1), zs);
 }
-constexpr float kCellAmpScale = 1.0f;
 // the compile-time octave count (C2 / C3: 5), octave by octave
 template <int I, int OCT, class LUT>
 __device__ __forceinline__ float fbm_cells_unrolled(LUT lut, const FbmField& F, const FbmCells& T, float x, float y, float z, float amp, float sum) {
@@ -487,7 +486,7 @@ __device__ __forceinline__ f2 fbm_cells_unrolled2(LUT lut, const FbmField& F, co
 template <int OCT, class LUT>
 __device__ __forceinline__ float fbm_perlin_cells_n(LUT lut, const FbmField& F, const FbmCells& T, float x, float y, float z) {
     const int n = OCT > 0 ? OCT : F.octaves;
-    float amp = F.bounding * kPerlinScale * kCellAmpScale;
+    float amp = F.bounding * kPerlinScale;
     if constexpr (OCT > 0) return fbm_cells_unrolled<0, OCT>(lut, F, T, x, y, z, amp, 0.0f);
     float sum = perlin3_cells(lut, T.oct[0], x, y, z) * amp;
 #pragma unroll
@@ -501,7 +500,7 @@ __device__ __forceinline__ float fbm_perlin_cells_n(LUT lut, const FbmField& F, 
 template <int OCT, class LUT>
 __device__ __forceinline__ f2 fbm_perlin_cells2_n(LUT lut, const FbmField& F, const FbmCells& T, f2 x, f2 y, f2 z) {
     const int n = OCT > 0 ? OCT : F.octaves;
-    float amp = F.bounding * kPerlinScale * kCellAmpScale;
+    float amp = F.bounding * kPerlinScale;
     const f2 lac = splat2(F.lacunarity);
     if constexpr (OCT > 0) return fbm_cells_unrolled2<0, OCT>(lut, F, T, x, y, z, lac, amp, make_f2(0.0f, 0.0f));
     f2 sum = mul2(perlin3_cells2(lut, T.oct[0], x, y, z), splat2(amp));
